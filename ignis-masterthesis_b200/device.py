@@ -1,0 +1,70 @@
+"""Host-side mirror of the reference's `IG::Device` (src/runtime/device/Device.h:14-74) over the C ABI.
+
+Same lifetime rules as the reference: one scene per device, `assign_scene` before `trace`
+(Runtime.cpp:478-487), ray directions are normalised on upload (Device.cpp:585-607), outputs are the
+five hit columns of the primary stream (src/artic/driver/streams.art:80-100).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .tables import RAY_DTYPE, SceneTables
+
+
+class Device:
+    def __init__(self, device=0, acquire_stats=False):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        setup = _lib.Setup(device=device, acquire_stats=1 if acquire_stats else 0)
+        _lib.check(self._lib.igb200_create(C.byref(setup), C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.igb200_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # Device::assignScene
+    def assign_scene(self, tables: SceneTables):
+        sc = tables.c_scene()
+        _lib.check(self._lib.igb200_assign_scene(self._h, C.byref(sc)))
+
+    # Runtime::trace(rays, out) for hit records; host numpy buffers in, host numpy buffers out.
+    def trace(self, rays, ray_flags=0, any_hit=False):
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        n = rays.size
+        ent = np.empty(n, np.int32)
+        prim = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        u = np.empty(n, np.float32)
+        v = np.empty(n, np.float32)
+        _lib.check(self._lib.igb200_trace_rays(self._h, rays.ctypes.data, n, ray_flags, 1 if any_hit else 0,
+                                               ent.ctypes.data, prim.ctypes.data, t.ctypes.data, u.ctypes.data,
+                                               v.ctypes.data))
+        return ent, prim, t, u, v
+
+    # Same call on device-resident buffers (raw device pointers, e.g. torch tensors' data_ptr()).
+    def trace_device(self, d_rays, n, d_ent, d_prim, d_t, d_u, d_v, ray_flags=0, any_hit=False, stream=0):
+        _lib.check(self._lib.igb200_trace_rays_device(self._h, d_rays, n, ray_flags, 1 if any_hit else 0,
+                                                      d_ent, d_prim, d_t, d_u, d_v, stream))
+
+    # Device::getStatistics
+    def trace_stats(self):
+        st = _lib.TraceStats()
+        _lib.check(self._lib.igb200_get_trace_stats(self._h, C.byref(st)))
+        return {"rays": st.rays, "nodes_visited": st.nodes_visited, "tris_tested": st.tris_tested,
+                "entities_entered": st.entities_entered, "kernel_ms": st.kernel_ms}
+
+    def bvh_info(self):
+        nb, tb, lb, d = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_uint32()
+        _lib.check(self._lib.igb200_get_bvh_info(self._h, C.byref(nb), C.byref(tb), C.byref(lb), C.byref(d)))
+        return {"node_bytes": nb.value, "tri_bytes": tb.value, "leaf_bytes": lb.value, "max_depth": d.value}

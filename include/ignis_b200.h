@@ -1,0 +1,164 @@
+/* ignis_b200.h -- C ABI of the B200-native ray-traversal / wavefront backend for Ignis.
+ *
+ * This is the drop-in boundary.  Every entry point replaces one member of the
+ * reference's `IG::Device` class (src/runtime/device/Device.h:14-74), which is the only seam the
+ * reference's `IG::Runtime` talks to.  All arguments are plain pointers and sizes; inputs are
+ * borrowed for the duration of the call only (the reference borrows them for the Device lifetime,
+ * Device.h:25-30 -- we copy to HBM in `igb200_assign_scene`, so the caller may free afterwards).
+ *
+ * Error behaviour: the reference aborts on OOM and logs on bad input (Device.cpp:271-274,1303-1305).
+ * Here every call returns 0 on success or a negative IGB200_E_* code; `igb200_last_error()` gives
+ * the message.  There is NO CPU fallback: without a CUDA device `igb200_create` fails.
+ */
+#ifndef IGNIS_B200_H
+#define IGNIS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IGB200_ABI_VERSION 1
+
+enum {
+    IGB200_OK            = 0,
+    IGB200_E_NODEVICE    = -1, /* no CUDA device / wrong architecture */
+    IGB200_E_INVALID     = -2, /* malformed argument or table */
+    IGB200_E_OOM         = -3, /* cudaMalloc failed (reference: std::abort, Device.cpp:271-274) */
+    IGB200_E_CUDA        = -4, /* a CUDA call or kernel failed */
+    IGB200_E_STATE       = -5, /* call order violated (e.g. trace before assign_scene) */
+    IGB200_E_UNSUPPORTED = -6
+};
+
+/* Ray visibility bits; identical to src/artic/traversal/ray.art:21-25 and the entity flags
+ * written by src/runtime/loader/LoaderEntity.cpp:122-131. */
+#define IGB200_RAY_CAMERA 0x1u
+#define IGB200_RAY_LIGHT  0x2u
+#define IGB200_RAY_BOUNCE 0x4u
+#define IGB200_RAY_SHADOW 0x8u
+
+/* One igtrace input ray; byte-identical to `StreamRay` (src/artic/traversal/ray.art:2-7) and to
+ * `IG::Ray` (src/runtime/RuntimeStructs.h:71-75).  32 bytes. */
+typedef struct igb200_ray {
+    float org[3];
+    float dir[3];
+    float tmin;
+    float tmax;
+} igb200_ray;
+
+/* `LookupEntry` of a DynTable (src/runtime/table/DynTable.h:6-10). 16 bytes. */
+typedef struct igb200_lookup_entry {
+    uint32_t type_id;
+    uint32_t flags;
+    uint64_t offset; /* byte offset into the table data */
+} igb200_lookup_entry;
+
+/* Top-level BVH leaf; byte-identical to `EntityLeaf1` (src/artic/traversal/bvh.art:52-61, written by
+ * src/runtime/bvh/SceneBVHAdapter.h:73-105).  96 bytes.  The sign bit of entity_id is the reference's
+ * "last in leaf" sentinel and is ignored on input. */
+typedef struct igb200_entity_leaf {
+    float    bbox_min[3];
+    int32_t  entity_id;
+    float    bbox_max[3];
+    int32_t  shape_id;
+    float    local[12]; /* world->object 3x4, column major: col0 xyz, col1 xyz, col2 xyz, col3 xyz */
+    uint32_t flags;     /* visibility bits IGB200_RAY_* */
+    int32_t  mat_id;
+    int32_t  user1;     /* reference: low/high words of the prim-BVH offset; unused by this backend */
+    int32_t  user2;
+} igb200_entity_leaf;
+
+/* Primitive type of a shape table entry (`type_id` in the `shapes` DynTable lookups): the index of the
+ * shape provider, src/runtime/loader/LoaderShape.cpp:20-60 ("trimesh" = 0, "sphere" = 1). */
+#define IGB200_PRIM_TRIMESH 0u
+#define IGB200_PRIM_SPHERE  1u
+
+/* Scene description = the slices of `IG::SceneDatabase` (src/runtime/table/SceneDatabase.h:8-20) that the
+ * hot path consumes.  Replaces `Device::SceneSettings` (Device.h:25-30).
+ *  - shapes: DynTable "shapes" (TriMeshProvider.cpp:574-602): per trimesh
+ *      [nf,nv,nn,nt : u32x4][bbox min xyz,0, max xyz,0][verts vec4-aligned][normals vec4-aligned]
+ *      [indices 4 x u32 per face][texcoords 2 x f32]; per sphere (SphereProvider.cpp:33-45)
+ *      [origin xyz, radius].
+ *  - entities: FixTable "entities" (LoaderEntity.cpp:150-176): 36 floats per entity.
+ *  - leaves[k]: `SceneBVHs[provider k].Leaves` -- the EntityLeaf1 array of primitive type k.
+ *    The reference's own Node2/4/8 arrays are NOT consumed: the backend builds its compressed BVH8. */
+typedef struct igb200_scene {
+    const igb200_lookup_entry* shape_lookups;
+    uint64_t                   shape_count;
+    const uint8_t*             shape_data;
+    uint64_t                   shape_bytes;
+    const float*               entities;     /* entity_count * 36 floats, may be NULL for trace-only use */
+    uint64_t                   entity_count;
+    const igb200_entity_leaf*  leaves[2];    /* [IGB200_PRIM_TRIMESH], [IGB200_PRIM_SPHERE] */
+    uint64_t                   leaf_count[2];
+    float                      scene_bbox[6]; /* min xyz, max xyz */
+    uint32_t                   material_count;
+    uint32_t                   _pad;
+} igb200_scene;
+
+/* Replaces `Device::SetupSettings` (Device.h:18-23). */
+typedef struct igb200_setup {
+    int32_t device;        /* CUDA ordinal (Target::device) */
+    int32_t acquire_stats; /* count nodes/triangles visited per trace call (slower kernels) */
+    int32_t debug_trace;
+    int32_t _pad;
+} igb200_setup;
+
+/* Per-call statistics (the algorithmic-byte terms of SURVEY.md 8(d)). */
+typedef struct igb200_trace_stats {
+    uint64_t rays;
+    uint64_t nodes_visited;    /* BVH8 inner nodes fetched (80 B each) */
+    uint64_t tris_tested;      /* triangle records fetched (48 B each) */
+    uint64_t entities_entered; /* entity leaves entered (96 B each) */
+    float    kernel_ms;        /* device time of the traversal kernel(s), CUDA events */
+    float    _pad;
+} igb200_trace_stats;
+
+typedef struct igb200_device igb200_device;
+
+/* ---- lifetime (Device::Device / ~Device, Device.cpp:1562-1573) ---- */
+int         igb200_abi_version(void);
+const char* igb200_last_error(void);
+int         igb200_create(const igb200_setup* setup, igb200_device** out);
+void        igb200_destroy(igb200_device* dev);
+
+/* ---- scene (Device::assignScene, Device.h:52; BVH upload Device.cpp:663-706) ---- */
+int igb200_assign_scene(igb200_device* dev, const igb200_scene* scene);
+
+/* ---- igtrace ray list -> hit records.
+ * Host-buffer form: the reference path is Runtime::trace (Runtime.cpp:375-407) ->
+ * Interface::loadRayList (Device.cpp:573-611; directions are normalised here the same way) ->
+ * K2 primary traversal (src/artic/driver/mapping_gpu.art:45-68).  Outputs are the five hit columns of
+ * the primary stream (src/artic/driver/streams.art:80-100): ent_id, prim_id (-1 on miss), t (= tmax on
+ * miss), u, v.  `any_hit` != 0 runs the shadow-ray variant (mapping_gpu.art:70-112): ent_id/prim_id are
+ * then only meaningful as hit (>=0) / miss (-1).  Any output pointer may be NULL.
+ * `ray_flags` is the ray-type visibility mask (0 = igtrace behaviour: visible to everything). */
+int igb200_trace_rays(igb200_device* dev, const igb200_ray* rays, uint64_t n, uint32_t ray_flags, int any_hit,
+                      int32_t* ent_id, int32_t* prim_id, float* t, float* u, float* v);
+
+/* Device-resident form of the same call: `d_rays` and the outputs are device pointers (e.g. torch
+ * tensors' data_ptr) on this device; enqueued on `stream` (a cudaStream_t, 0 = default), not synchronised.
+ * Directions must already be normalised. */
+int igb200_trace_rays_device(igb200_device* dev, const igb200_ray* d_rays, uint64_t n, uint32_t ray_flags,
+                             int any_hit, int32_t* d_ent_id, int32_t* d_prim_id, float* d_t, float* d_u,
+                             float* d_v, void* stream);
+
+/* Statistics of the most recent trace call (Device::getStatistics, Device.h:68). */
+int igb200_get_trace_stats(igb200_device* dev, igb200_trace_stats* out);
+
+/* Sizes of the device-side acceleration structure (for the roofline's working-set statement). */
+int igb200_get_bvh_info(igb200_device* dev, uint64_t* node_bytes, uint64_t* tri_bytes, uint64_t* leaf_bytes,
+                        uint32_t* max_depth);
+
+/* Host-only test hook (no GPU needed): builds the compressed BVH8 over `n` boxes (min xyz, max xyz) and
+ * checks its invariants -- every primitive referenced exactly once, every dequantised child box contains
+ * the exact bounds of its subtree, meta/imask encoding consistent.
+ * out5 = {node_count, max_depth, violations, primitives_not_seen_exactly_once, leaf_count}. */
+int igb200_debug_check_bvh8(const float* boxes, uint32_t n, uint32_t max_leaf, uint64_t* out5);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IGNIS_B200_H */

@@ -1,0 +1,109 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes binding of oracle/libignis_oracle.so (see oracle/oracle.h).
+
+May be imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs only.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libignis_oracle.so")
+
+
+class Counters(C.Structure):
+    _fields_ = [("scene_nodes", C.c_uint64), ("prim_nodes", C.c_uint64), ("tri_packets", C.c_uint64),
+                ("tri_tests", C.c_uint64), ("entities", C.c_uint64)]
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE])
+
+
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        lib = C.CDLL(LIB_PATH)
+        vp = C.c_void_p
+        lib.igo_scene_create.restype = vp
+        lib.igo_scene_create.argtypes = [vp]
+        lib.igo_scene_destroy.argtypes = [vp]
+        lib.igo_trace.argtypes = [vp, vp, C.c_uint64, C.c_uint32, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]
+        lib.igo_brute.argtypes = [vp, vp, C.c_uint64, C.c_uint32, C.c_int, vp, vp, vp, vp, vp, vp, vp]
+        lib.igo_normalize_rays.argtypes = [vp, C.c_uint64]
+        lib.igo_kat_ray_triangle.argtypes = [vp, vp, vp, C.c_float, C.c_float, vp]
+        lib.igo_kat_ray_box.argtypes = [vp, vp, vp, C.c_float, C.c_float, vp]
+        lib.igo_scene_info.argtypes = [vp, vp, vp, vp]
+        _lib = lib
+    return _lib
+
+
+class OracleScene:
+    def __init__(self, tables):
+        self._lib = load()
+        self._tables = tables  # keep the blobs alive
+        sc = tables.c_scene()
+        self._h = self._lib.igo_scene_create(C.addressof(sc))
+        if not self._h:
+            raise ValueError("oracle rejected the scene tables")
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.igo_scene_destroy(self._h)
+            self._h = None
+
+    @staticmethod
+    def normalized(rays):
+        r = np.array(rays, copy=True)
+        load().igo_normalize_rays(r.ctypes.data, r.size)
+        return r
+
+    def trace(self, rays, ray_flags=0, any_hit=False, threads=0, normalize=True):
+        r = self.normalized(rays) if normalize else np.ascontiguousarray(rays)
+        n = r.size
+        ent, prim = np.empty(n, np.int32), np.empty(n, np.int32)
+        t, u, v = np.empty(n, np.float32), np.empty(n, np.float32), np.empty(n, np.float32)
+        cnt = Counters()
+        self._lib.igo_trace(self._h, r.ctypes.data, n, ray_flags, int(any_hit), threads, ent.ctypes.data,
+                            prim.ctypes.data, t.ctypes.data, u.ctypes.data, v.ctypes.data, C.addressof(cnt))
+        self.counters = {k: getattr(cnt, k) for k, _ in Counters._fields_}
+        return ent, prim, t, u, v
+
+    def brute(self, rays, ray_flags=0, threads=0, normalize=True):
+        r = self.normalized(rays) if normalize else np.ascontiguousarray(rays)
+        n = r.size
+        ent, prim = np.empty(n, np.int32), np.empty(n, np.int32)
+        t, u, v = np.empty(n, np.float32), np.empty(n, np.float32), np.empty(n, np.float32)
+        tie, second = np.empty(n, np.uint8), np.empty(n, np.float32)
+        self._lib.igo_brute(self._h, r.ctypes.data, n, ray_flags, threads, ent.ctypes.data, prim.ctypes.data,
+                            t.ctypes.data, u.ctypes.data, v.ctypes.data, tie.ctypes.data, second.ctypes.data)
+        return ent, prim, t, u, v, tie.astype(bool), second
+
+    def info(self):
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._lib.igo_scene_info(self._h, C.addressof(a), C.addressof(b), C.addressof(c))
+        return {"node4": a.value, "tri4": b.value, "tris": c.value}
+
+
+def kat_ray_triangle(tri, org, direction, tmin=0.0, tmax=3.4028234e38):
+    tri = np.ascontiguousarray(tri, np.float32).reshape(9)
+    org = np.ascontiguousarray(org, np.float32)
+    d = np.ascontiguousarray(direction, np.float32)
+    out = np.zeros(3, np.float32)
+    hit = load().igo_kat_ray_triangle(tri.ctypes.data, org.ctypes.data, d.ctypes.data, tmin, tmax, out.ctypes.data)
+    return (bool(hit), out)
+
+
+def kat_ray_box(box, org, direction, tmin=0.0, tmax=3.4028234e38):
+    box = np.ascontiguousarray(box, np.float32).reshape(6)
+    org = np.ascontiguousarray(org, np.float32)
+    d = np.ascontiguousarray(direction, np.float32)
+    out = np.zeros(1, np.float32)
+    hit = load().igo_kat_ray_box(box.ctypes.data, org.ctypes.data, d.ctypes.data, tmin, tmax, out.ctypes.data)
+    return (bool(hit), float(out[0]))

@@ -1,0 +1,78 @@
+"""C-ABI library: loads, exports every declared symbol, host-only hooks work, fails loudly without a GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol(ig):
+    lib = ig._lib.load()
+    header = open(os.path.join(ROOT, "include", "ignis_b200.h")).read()
+    declared = set(re.findall(r"\b(igb200_[a-z0-9_]+)\s*\(", header))
+    assert declared == set(ig._lib.ABI_SYMBOLS)
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.igb200_abi_version() == 1
+
+
+def test_struct_sizes_match_reference_layouts(ig):
+    # StreamRay 32 B (ray.art:2-7), LookupEntry 16 B (DynTable.h:6-10), EntityLeaf1 96 B (bvh.art:52-61)
+    assert C.sizeof(ig._lib.Ray) == 32
+    assert C.sizeof(ig._lib.LookupEntry) == 16
+    assert C.sizeof(ig._lib.EntityLeaf) == 96
+    assert ig.tables.RAY_DTYPE.itemsize == 32 and ig.tables.LEAF_DTYPE.itemsize == 96
+
+
+def test_create_fails_loudly_without_gpu(ig):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(ig._lib.BackendError) as e:
+        ig.Device(0)
+    assert e.value.code == -1 and "no CPU fallback" in str(e.value)
+
+
+def test_null_arguments_are_rejected(ig):
+    lib = ig._lib.load()
+    assert lib.igb200_assign_scene(None, None) == -2
+    assert lib.igb200_trace_rays(None, None, 0, 0, 0, None, None, None, None, None) == -2
+    assert b"NULL" in lib.igb200_last_error()
+
+
+def _check(ig, boxes, max_leaf=3):
+    boxes = np.ascontiguousarray(boxes, np.float32)
+    out = np.zeros(5, np.uint64)
+    rc = ig._lib.load().igb200_debug_check_bvh8(boxes.ctypes.data, boxes.shape[0], max_leaf, out.ctypes.data)
+    return rc, dict(zip(["nodes", "depth", "violations", "missing", "leaves"], out.tolist()))
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 3, 4, 9, 100, 5000])
+def test_bvh8_conservative_bounds_random(ig, n):
+    rng = np.random.default_rng(n)
+    c = rng.uniform(-100, 100, (n, 3))
+    h = rng.uniform(0, 3, (n, 3)) * rng.integers(0, 2, (n, 3))  # some flat boxes
+    rc, st = _check(ig, np.concatenate([c - h, c + h], axis=1))
+    assert rc == 0 and st["violations"] == 0 and st["missing"] == 0, st
+
+
+def test_bvh8_degenerate_inputs(ig):
+    # all primitives identical (centres coincide -> median split path), and a huge dynamic range
+    same = np.tile(np.array([[1, 2, 3, 1, 2, 3]], np.float32), (50, 1))
+    rc, st = _check(ig, same)
+    assert rc == 0, st
+    wide = np.array([[0, 0, 0, 1e-6, 1e-6, 1e-6], [1e6, 1e6, 1e6, 1e6 + 1, 1e6 + 1, 1e6 + 1],
+                     [-1e6, 5, 5, -1e6 + 1e-3, 5, 5]], np.float32)
+    rc, st = _check(ig, wide, max_leaf=1)
+    assert rc == 0, st
+
+
+def test_bvh8_c3_mesh(ig):
+    v, f, _ = ig.workloads.uv_sphere(64, 128)
+    assert f.shape[0] == 16128
+    tri = v[f]
+    rc, st = _check(ig, np.concatenate([tri.min(axis=1), tri.max(axis=1)], axis=1))
+    assert rc == 0 and st["depth"] <= 16, st
