@@ -1,0 +1,272 @@
+#!/usr/bin/env python
+"""bench.py -- closest-hit ray throughput on the BASELINE.json config-3 workload.
+
+Workload (config.workload "c3-instanced"): 64 instances of a 16 128-triangle sphere mesh = 1 032 192 triangles,
+16 777 216 incoherent rays per step per GPU (uniform directions, generation order), closest-hit.
+A step = one pass of the traversal hot path over one ray batch.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--rays R] [--impl ours|reference]
+
+Prints ONE JSON line (rank 0).  `value` = whole-job Mrays/s with rays resident in HBM; `e2e` = the same
+metric through the host-buffer C-ABI call igb200_trace_rays (H2D of the rays + D2H of the five hit columns
+inside the timed region); `roofline` relates the kernel to measured HBM bandwidth via the algorithmic bytes
+per ray of SURVEY.md 8(d); `cpu_baseline` = the oracle (restated reference CPU traversal) on the host cores.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s closest-hit (incoherent)"
+UNIT = "Mrays/s"
+FULL_RAYS = 16_777_216
+
+
+def load_pkg():
+    return importlib.import_module("ignis-masterthesis_b200")
+
+
+def load_oracle():
+    # bench.py's cpu_baseline / --impl reference legs are the only product-side users of oracle/
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle
+    pyoracle.load()
+    return pyoracle
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self._halt = index, [], threading.Event()
+
+    def run(self):
+        while not self._halt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            self._halt.wait(0.2)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=6)
+        sm = [float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit()]
+        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def oracle_throughput(pkg, tables, rays, budget_rays):
+    """Times the oracle on a bounded sample of the workload; returns (Mrays/s, cores, sample text)."""
+    oracle = load_oracle()
+    osc = oracle.OracleScene(tables)
+    sample = oracle.OracleScene.normalized(rays[:budget_rays])
+    cores = os.cpu_count() or 1
+    osc.trace(sample[: min(65536, sample.size)], threads=cores, normalize=False)  # warm-up
+    t0 = time.perf_counter()
+    osc.trace(sample, threads=cores, normalize=False)
+    dt = time.perf_counter() - t0
+    return sample.size / dt / 1e6, cores, f"first {sample.size} rays of the c3-instanced batch, closest-hit"
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU traversal (oracle restatement: the reference itself needs
+    AnyDSL/Artic and cannot be built here) on all host cores, bounded sample per step."""
+    if rank != 0:
+        return
+    pkg = load_pkg()
+    tables = pkg.workloads.c3_scene()
+    n = min(args.rays, 2_000_000)
+    rays = pkg.workloads.c3_rays(tables, n=n)
+    oracle = load_oracle()
+    osc = oracle.OracleScene(tables)
+    sample = oracle.OracleScene.normalized(rays)
+    cores = os.cpu_count() or 1
+    for _ in range(args.warmup):
+        osc.trace(sample, threads=cores, normalize=False)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        osc.trace(sample, threads=cores, normalize=False)
+    dt = time.perf_counter() - t0
+    val = n * args.steps / dt / 1e6
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "c3-instanced", "triangles": 1032192, "entities": 64, "rays_per_step": n,
+                   "ray_order": "generation order (incoherent)"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{n} rays per step of the c3-instanced batch (bounded sample of 16 777 216)"},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    pkg = load_pkg()
+    W = pkg.workloads
+    tables = W.c3_scene()
+    n = args.rays
+    # weak scaling: every rank traces its own batch (distinct seed), scene replicated, no data-path collective
+    rays = W.c3_rays(tables, n=n, seed=0xB200 + rank)
+
+    dev = pkg.Device(local_rank)
+    dev.assign_scene(tables)
+    info = dev.bvh_info()
+
+    d_rays = torch.from_numpy(rays.view(np.float32).reshape(-1, 8)).cuda()
+    d_ent = torch.empty(n, dtype=torch.int32, device="cuda")
+    d_prim = torch.empty(n, dtype=torch.int32, device="cuda")
+    d_t, d_u, d_v = (torch.empty(n, dtype=torch.float32, device="cuda") for _ in range(3))
+    stream = torch.cuda.current_stream()
+
+    def step():
+        dev.trace_device(d_rays.data_ptr(), n, d_ent.data_ptr(), d_prim.data_ptr(), d_t.data_ptr(), d_u.data_ptr(),
+                         d_v.data_ptr(), stream=stream.cuda_stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_begin.record(stream)
+    for a, b in evs:
+        a.record(stream)
+        step()
+        b.record(stream)
+    t_end.record(stream)
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    total_ms = t_begin.elapsed_time(t_end)
+    kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
+    if world > 1:
+        tm = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        total_ms = float(tm.item())
+    value = world * n * args.steps / (total_ms * 1e-3) / 1e6
+    hits = int((d_prim >= 0).sum().item())
+
+    # ---- end to end through the host-buffer C-ABI call (pinned host memory in, pinned host memory out) ----
+    h_rays = torch.from_numpy(rays.view(np.float32).reshape(-1, 8)).pin_memory()
+    h_i = [torch.empty(n, dtype=torch.int32).pin_memory() for _ in range(2)]
+    h_f = [torch.empty(n, dtype=torch.float32).pin_memory() for _ in range(3)]
+    outs = [x.numpy() for x in h_i + h_f]
+    h_rays_np = h_rays.numpy().view(pkg.tables.RAY_DTYPE).reshape(-1)
+    e2e_steps = max(1, min(args.steps, 5))
+    for _ in range(2):
+        dev.trace_into(h_rays_np, *outs)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        dev.trace_into(h_rays_np, *outs)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        tm = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        e2e_s = float(tm.item())
+    e2e_val = world * n * e2e_steps / e2e_s / 1e6
+    assert int((outs[1] >= 0).sum()) > 0
+
+    if rank == 0:
+        # ---- algorithmic bytes per ray: visit counts from a counting pass over a 2 Mi-ray sample (untimed) ----
+        sdev = pkg.Device(local_rank, acquire_stats=True)
+        sdev.assign_scene(tables)
+        m = min(n, 1 << 21)
+        sdev.trace(rays[:m])
+        st = sdev.trace_stats()
+        sdev.close()
+        n_node, n_tri, n_ent = st["nodes_visited"] / m, st["tris_tested"] / m, st["entities_entered"] / m
+        bytes_per_ray = 32 + 20 + 80 * n_node + 48 * n_tri + 96 * n_ent
+        peak, peak_kind = measured_peak()
+        achieved = bytes_per_ray * n / (kernel_ms * 1e-3) / 1e9
+        # ---- CPU baseline: oracle on a bounded sample ----
+        cpu_val, cores, sample = oracle_throughput(pkg, tables, rays, min(n, args.cpu_rays))
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "c3-instanced", "triangles": 1032192, "entities": 64, "rays_per_step": n,
+                       "ray_order": "generation order (incoherent)", "hit_rate": hits / n,
+                       "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (n * 52 / 1e6),
+                       "bvh": info},
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 20,
+                    "steps": e2e_steps},
+            "gpu_launches": args.steps,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_kind": peak_kind, "kernel": "trace_kernel<closest>",
+                         "kernel_ms": kernel_ms, "bytes_per_ray": bytes_per_ray,
+                         "per_ray": {"nodes": n_node, "tris": n_tri, "entities": n_ent}},
+            "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        }
+        print(json.dumps(line), flush=True)
+    dev.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--rays", type=int, default=FULL_RAYS)
+    ap.add_argument("--cpu-rays", type=int, default=4_000_000)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()
