@@ -70,6 +70,8 @@ struct igb200_device {
     bool         stats   = false;
     cudaStream_t stream  = nullptr;
     cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
+    int          sm_count = 0;
+    DeviceBuffer<uint32_t> d_work; // persistent-kernel work counters (self-resetting)
 
     // scene
     bool                          has_scene = false;
@@ -116,10 +118,15 @@ int igb200_create(const igb200_setup* setup, igb200_device** out)
     igb200_device* dev = new igb200_device();
     dev->ordinal       = ordinal;
     dev->stats         = setup && setup->acquire_stats;
+    dev->sm_count      = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&dev->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&dev->ev0) != cudaSuccess || cudaEventCreate(&dev->ev1) != cudaSuccess) {
         delete dev;
         return fail(IGB200_E_CUDA, "igb200_create: stream/event creation failed");
+    }
+    if (dev->d_work.ensure(2) != cudaSuccess || cudaMemset(dev->d_work.ptr, 0, 2 * sizeof(uint32_t)) != cudaSuccess) {
+        delete dev;
+        return fail(IGB200_E_OOM, "igb200_create: work counter allocation failed");
     }
     *out = dev;
     return IGB200_OK;
@@ -245,7 +252,7 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
         }
         shape_refs[s] = ref;
     }
-    if (tlas.max_depth + blas_depth + 4 > (uint32_t)kStackSize)
+    if (tlas.max_depth + blas_depth + 7 > (uint32_t)kStackSize)
         return fail(IGB200_E_UNSUPPORTED, "BVH too deep for the traversal stack (%u + %u levels)", tlas.max_depth, blas_depth);
 
     // ---- upload ----
@@ -283,7 +290,7 @@ static int trace_on_stream(igb200_device* dev, const igb200_ray* d_rays, uint64_
     }
     if (timed) IGB_CUDA(cudaEventRecord(dev->ev0, stream));
     IGB_CUDA(igb::launch_trace(dev->view, reinterpret_cast<const float4*>(d_rays), n, ray_flags, any_hit, out, counters,
-                               stream));
+                               dev->d_work.ptr, dev->sm_count, stream));
     if (timed) IGB_CUDA(cudaEventRecord(dev->ev1, stream));
     return IGB200_OK;
 }

@@ -15,6 +15,8 @@
 // Box tests are conservative (quantised boxes + ulp slack) and carry no parity requirement.
 #include "trace.cuh"
 
+#include <algorithm>
+
 #include "../../include/ignis_b200.h"
 
 namespace igb {
@@ -23,7 +25,9 @@ namespace {
 constexpr float    kFltEps   = 1.1920928955078125e-7f;
 constexpr float    kFltMax   = 3.402823466e+38f;
 constexpr uint32_t kSentinel = 0xFFFFFFFFu;
-constexpr int      kBlock    = 128;
+constexpr int      kBlock       = 128;
+constexpr int      kBlocksPerSM = 8;
+constexpr int      kChunk       = 64; // rays a warp claims per atomic on the global work counter
 
 struct Vec3 { float x, y, z; };
 
@@ -188,35 +192,73 @@ __device__ __forceinline__ void intersect_sphere(const float4 sph, const TravRay
     }
 }
 
+// Persistent kernel: every lane owns one ray at a time and pulls the next ray from a warp-local pool
+// (refilled in chunks from one global counter) the moment its ray finishes, so lanes never idle while the
+// longest ray of the warp completes.  Each trip of the outer loop performs at most one node step, one
+// primitive batch and one pop per lane, which keeps lanes in different phases converged on the same code.
 template <bool ANY_HIT, bool STATS>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, kBlocksPerSM)
 trace_kernel(const DeviceScene sc, const float4* __restrict__ rays, const uint32_t n, const uint32_t ray_flags,
-             const TraceOutputs out, TraceCounters* __restrict__ counters)
+             const TraceOutputs out, TraceCounters* __restrict__ counters, uint32_t* __restrict__ work)
 {
-    const uint32_t ray_id = blockIdx.x * kBlock + threadIdx.x;
+    const uint32_t lane    = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
     uint32_t       c_nodes = 0, c_tris = 0, c_ents = 0;
 
-    if (ray_id < n) {
-        const float4 r0 = __ldg(rays + 2 * (size_t)ray_id);
-        const float4 r1 = __ldg(rays + 2 * (size_t)ray_id + 1);
-        const Vec3   world_org{ r0.x, r0.y, r0.z }, world_dir{ r0.w, r1.x, r1.y };
-        const float  tmin = r1.z;
+    uint32_t pool_next = 0, pool_end = 0; // warp-uniform
+    bool     exhausted = false;           // warp-uniform
+    bool     active    = false;
 
-        TravRay ray;
-        ray.org = world_org;
-        ray.dir = world_dir;
-        setup_trav_ray(ray);
+    uint32_t ray_id = 0;
+    float    tmin   = 0.0f;
+    TravRay  ray;
+    HitRec   hit;
+    uint2    stack[kStackSize];
+    int      sp      = 0;
+    uint2    ngroup  = make_uint2(0u, 0u);
+    uint2    tgroup  = make_uint2(0u, 0u);
+    bool     in_blas = false;
+    int32_t  cur_ent = -1;
 
-        HitRec hit{ r1.w, 0.0f, 0.0f, -1, -1 };
+    for (;;) {
+        const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !active);
+        if (idle != 0u) {
+            if (!exhausted) {
+                if (pool_next == pool_end) {
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(work, (uint32_t)kChunk);
+                    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                    if (base >= n) {
+                        exhausted = true;
+                    } else {
+                        pool_next = base;
+                        pool_end  = min(base + (uint32_t)kChunk, n);
+                    }
+                }
+                const uint32_t avail = pool_end - pool_next;
+                const uint32_t rank  = __popc(idle & lt_mask);
+                if (!active && rank < avail) {
+                    ray_id          = pool_next + rank;
+                    const float4 r0 = __ldg(rays + 2 * (size_t)ray_id);
+                    const float4 r1 = __ldg(rays + 2 * (size_t)ray_id + 1);
+                    ray.org         = Vec3{ r0.x, r0.y, r0.z };
+                    ray.dir         = Vec3{ r0.w, r1.x, r1.y };
+                    tmin            = r1.z;
+                    setup_trav_ray(ray);
+                    hit     = HitRec{ r1.w, 0.0f, 0.0f, -1, -1 };
+                    sp      = 0;
+                    ngroup  = make_uint2(0u, 0x80000000u);
+                    tgroup  = make_uint2(0u, 0u);
+                    in_blas = false;
+                    active  = true;
+                }
+                pool_next += min(avail, (uint32_t)__popc(idle));
+            } else if (idle == 0xFFFFFFFFu) {
+                break;
+            }
+        }
 
-        uint2    stack[kStackSize];
-        int      sp       = 0;
-        uint2    ngroup   = make_uint2(0u, 0x80000000u);
-        uint2    tgroup   = make_uint2(0u, 0u);
-        bool     in_blas  = false;
-        int32_t  cur_ent  = -1;
-
-        while (true) {
+        if (active) {
             if (ngroup.y > 0x00FFFFFFu) {
                 const uint32_t hits            = ngroup.y;
                 const uint32_t imask           = ngroup.y & 0xFFu;
@@ -249,8 +291,8 @@ trace_kernel(const DeviceScene sc, const float4* __restrict__ rays, const uint32
                     if (ANY_HIT && hit.prim >= 0) break;
                 } else {
                     // Entity leaf step: gpu_traverse_scene::scene_handle (traversal/mapping_gpu.art:196-222)
-                    const float4* lp = sc.leaves + 6 * (size_t)(tgroup.x + idx);
-                    const float4  l0 = __ldg(lp + 0), l1 = __ldg(lp + 1), l5 = __ldg(lp + 5);
+                    const float4*  lp = sc.leaves + 6 * (size_t)(tgroup.x + idx);
+                    const float4   l0 = __ldg(lp + 0), l1 = __ldg(lp + 1), l5 = __ldg(lp + 5);
                     const uint32_t leaf_flags = __float_as_uint(l5.x);
                     // check_ray_visibility (traversal/ray.art:51)
                     if ((ray_flags & 0xFu) != ((ray_flags & leaf_flags) & 0xFu)) continue;
@@ -264,7 +306,7 @@ trace_kernel(const DeviceScene sc, const float4* __restrict__ rays, const uint32
 
                     const float4 l2 = __ldg(lp + 2), l3 = __ldg(lp + 3), l4 = __ldg(lp + 4);
                     if (STATS) c_ents++;
-                    cur_ent = __float_as_int(l0.w) & 0x7FFFFFFF;
+                    cur_ent              = __float_as_int(l0.w) & 0x7FFFFFFF;
                     const ShapeRef shape = sc.shapes[__float_as_int(l1.w)];
                     // transform_ray (traversal/ray.art:56-59): matrix columns l2.xyz | l2.w l3.xy | l3.zw l4.x | l4.yzw
                     TravRay local;
@@ -279,9 +321,12 @@ trace_kernel(const DeviceScene sc, const float4* __restrict__ rays, const uint32
                         if (ANY_HIT && hit.prim >= 0) break;
                         continue;
                     }
-                    // Enter the shape's BVH: park the entity-level state under a sentinel.
+                    // Enter the shape's BVH: park the entity-level state and the world ray under a sentinel.
                     if (ngroup.y > 0x00FFFFFFu) stack[sp++] = ngroup;
                     if (tgroup.y != 0u) stack[sp++] = tgroup;
+                    stack[sp++] = make_uint2(__float_as_uint(ray.org.x), __float_as_uint(ray.org.y));
+                    stack[sp++] = make_uint2(__float_as_uint(ray.org.z), __float_as_uint(ray.dir.x));
+                    stack[sp++] = make_uint2(__float_as_uint(ray.dir.y), __float_as_uint(ray.dir.z));
                     stack[sp++] = make_uint2(kSentinel, 0u);
                     ray         = local;
                     setup_trav_ray(ray);
@@ -291,28 +336,36 @@ trace_kernel(const DeviceScene sc, const float4* __restrict__ rays, const uint32
                     break;
                 }
             }
-            if (ANY_HIT && hit.prim >= 0) break;
 
-            if (ngroup.y <= 0x00FFFFFFu) {
-                if (sp == 0) break;
-                ngroup = stack[--sp];
-                if (ngroup.x == kSentinel) {
-                    // Leave the shape: back to world space.
-                    ray.org = world_org;
-                    ray.dir = world_dir;
-                    setup_trav_ray(ray);
-                    in_blas = false;
-                    if (sp == 0) break;
+            bool finished = ANY_HIT && hit.prim >= 0;
+            if (!finished && ngroup.y <= 0x00FFFFFFu) {
+                if (sp == 0) {
+                    finished = true;
+                } else {
                     ngroup = stack[--sp];
+                    if (ngroup.x == kSentinel) {
+                        // Leave the shape: back to world space.
+                        const uint2 c = stack[--sp], b = stack[--sp], a = stack[--sp];
+                        ray.org = Vec3{ __uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(b.x) };
+                        ray.dir = Vec3{ __uint_as_float(b.y), __uint_as_float(c.x), __uint_as_float(c.y) };
+                        setup_trav_ray(ray);
+                        in_blas = false;
+                        if (sp == 0)
+                            finished = true;
+                        else
+                            ngroup = stack[--sp];
+                    }
                 }
             }
+            if (finished) {
+                if (out.ent_id) out.ent_id[ray_id] = hit.ent;
+                if (out.prim_id) out.prim_id[ray_id] = hit.prim;
+                if (out.t) out.t[ray_id] = hit.t;
+                if (out.u) out.u[ray_id] = hit.u;
+                if (out.v) out.v[ray_id] = hit.v;
+                active = false;
+            }
         }
-
-        if (out.ent_id) out.ent_id[ray_id] = hit.ent;
-        if (out.prim_id) out.prim_id[ray_id] = hit.prim;
-        if (out.t) out.t[ray_id] = hit.t;
-        if (out.u) out.u[ray_id] = hit.u;
-        if (out.v) out.v[ray_id] = hit.v;
     }
 
     if (STATS) {
@@ -322,10 +375,22 @@ trace_kernel(const DeviceScene sc, const float4* __restrict__ rays, const uint32
             c_tris += __shfl_xor_sync(0xFFFFFFFFu, c_tris, o);
             c_ents += __shfl_xor_sync(0xFFFFFFFFu, c_ents, o);
         }
-        if ((threadIdx.x & 31) == 0) {
+        if (lane == 0) {
             atomicAdd(&counters->nodes, (unsigned long long)c_nodes);
             atomicAdd(&counters->tris, (unsigned long long)c_tris);
             atomicAdd(&counters->ents, (unsigned long long)c_ents);
+        }
+    }
+
+    // Self-resetting work counter: the last block to retire rewinds it for the next launch.
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const uint32_t done = atomicAdd(work + 1, 1u);
+        if (done == gridDim.x - 1) {
+            work[0] = 0u;
+            work[1] = 0u;
+            __threadfence();
         }
     }
 }
@@ -349,21 +414,24 @@ __global__ void normalize_rays_kernel(float4* rays, uint64_t n)
 } // namespace
 
 cudaError_t launch_trace(const DeviceScene& scene, const float4* d_rays, uint64_t n, uint32_t ray_flags, int any_hit,
-                         const TraceOutputs& out, TraceCounters* d_counters, cudaStream_t stream)
+                         const TraceOutputs& out, TraceCounters* d_counters, uint32_t* d_work, int sm_count,
+                         cudaStream_t stream)
 {
     if (n == 0) return cudaSuccess;
-    if (n > 0xFFFFFF00ull) return cudaErrorInvalidValue;
-    const uint32_t grid = (uint32_t)((n + kBlock - 1) / kBlock);
+    if (n > 0xFFFF0000ull) return cudaErrorInvalidValue;
+    // persistent grid: one wave of resident CTAs (a multiple of the SM count), fewer for tiny batches
+    const uint64_t want = (n + kChunk - 1) / kChunk; // warps that can get at least one chunk
+    const uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)sm_count * kBlocksPerSM, (want + 3) / 4));
     if (d_counters) {
         if (any_hit)
-            trace_kernel<true, true><<<grid, kBlock, 0, stream>>>(scene, d_rays, (uint32_t)n, ray_flags, out, d_counters);
+            trace_kernel<true, true><<<grid, kBlock, 0, stream>>>(scene, d_rays, (uint32_t)n, ray_flags, out, d_counters, d_work);
         else
-            trace_kernel<false, true><<<grid, kBlock, 0, stream>>>(scene, d_rays, (uint32_t)n, ray_flags, out, d_counters);
+            trace_kernel<false, true><<<grid, kBlock, 0, stream>>>(scene, d_rays, (uint32_t)n, ray_flags, out, d_counters, d_work);
     } else {
         if (any_hit)
-            trace_kernel<true, false><<<grid, kBlock, 0, stream>>>(scene, d_rays, (uint32_t)n, ray_flags, out, nullptr);
+            trace_kernel<true, false><<<grid, kBlock, 0, stream>>>(scene, d_rays, (uint32_t)n, ray_flags, out, nullptr, d_work);
         else
-            trace_kernel<false, false><<<grid, kBlock, 0, stream>>>(scene, d_rays, (uint32_t)n, ray_flags, out, nullptr);
+            trace_kernel<false, false><<<grid, kBlock, 0, stream>>>(scene, d_rays, (uint32_t)n, ray_flags, out, nullptr, d_work);
     }
     return cudaGetLastError();
 }

@@ -36,12 +36,15 @@ struct TraceCounters { // device-side, 3 x u64
     unsigned long long nodes, tris, ents;
 };
 
-constexpr int kStackSize = 40; // traversal stack entries per ray (uint2 each)
+constexpr int kStackSize = 44; // traversal stack entries per ray (uint2 each)
 
 // Launches the closest-hit (any_hit = 0) or any-hit traversal of `n` rays on `stream`.
-// counters may be nullptr (then the non-counting kernel variant is used).
+// counters may be nullptr (then the non-counting kernel variant is used).  d_work: two zero-initialised
+// uint32 (work counter, retired-block counter) owned by the device handle; the kernel rewinds them itself,
+// so only one trace launch per handle may be in flight at a time.
 cudaError_t launch_trace(const DeviceScene& scene, const float4* d_rays, uint64_t n, uint32_t ray_flags, int any_hit,
-                         const TraceOutputs& out, TraceCounters* d_counters, cudaStream_t stream);
+                         const TraceOutputs& out, TraceCounters* d_counters, uint32_t* d_work, int sm_count,
+                         cudaStream_t stream);
 
 // In-place normalisation of ray directions (Interface::loadRayList, src/runtime/device/Device.cpp:585-607).
 cudaError_t launch_normalize_rays(float4* d_rays, uint64_t n, cudaStream_t stream);
