@@ -71,7 +71,11 @@ struct igb200_device {
     cudaStream_t stream  = nullptr;
     cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
     int          sm_count = 0;
-    DeviceBuffer<uint32_t> d_work; // persistent-kernel work counters (self-resetting)
+    static constexpr int      kPipe      = 3;         // streams of the host-buffer pipeline
+    static constexpr uint64_t kChunkRays = 1u << 20;  // rays per pipeline chunk (32 MiB up, 20 MiB down)
+    cudaStream_t             pipe[kPipe] = {};
+    std::vector<cudaEvent_t> chunk_events;
+    DeviceBuffer<uint32_t>   d_work; // persistent-kernel work counters (self-resetting): pair k for pipe[k], last pair for `stream`
 
     // scene
     bool                          has_scene = false;
@@ -120,11 +124,15 @@ int igb200_create(const igb200_setup* setup, igb200_device** out)
     dev->stats         = setup && setup->acquire_stats;
     dev->sm_count      = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&dev->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreate(&dev->ev0) != cudaSuccess || cudaEventCreate(&dev->ev1) != cudaSuccess) {
+        cudaEventCreate(&dev->ev0) != cudaSuccess || cudaEventCreate(&dev->ev1) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&dev->pipe[0], cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&dev->pipe[1], cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&dev->pipe[2], cudaStreamNonBlocking) != cudaSuccess) {
         delete dev;
         return fail(IGB200_E_CUDA, "igb200_create: stream/event creation failed");
     }
-    if (dev->d_work.ensure(2) != cudaSuccess || cudaMemset(dev->d_work.ptr, 0, 2 * sizeof(uint32_t)) != cudaSuccess) {
+    if (dev->d_work.ensure(2 * (igb200_device::kPipe + 1)) != cudaSuccess ||
+        cudaMemset(dev->d_work.ptr, 0, 2 * (igb200_device::kPipe + 1) * sizeof(uint32_t)) != cudaSuccess) {
         delete dev;
         return fail(IGB200_E_OOM, "igb200_create: work counter allocation failed");
     }
@@ -140,6 +148,10 @@ void igb200_destroy(igb200_device* dev)
     if (dev->ev0) cudaEventDestroy(dev->ev0);
     if (dev->ev1) cudaEventDestroy(dev->ev1);
     if (dev->stream) cudaStreamDestroy(dev->stream);
+    for (cudaStream_t p : dev->pipe)
+        if (p) cudaStreamDestroy(p);
+    for (cudaEvent_t e : dev->chunk_events)
+        if (e) cudaEventDestroy(e);
     delete dev; // DeviceBuffer destructors free the allocations (Device::releaseAll, Device.cpp:948-952)
 }
 
@@ -290,7 +302,7 @@ static int trace_on_stream(igb200_device* dev, const igb200_ray* d_rays, uint64_
     }
     if (timed) IGB_CUDA(cudaEventRecord(dev->ev0, stream));
     IGB_CUDA(igb::launch_trace(dev->view, reinterpret_cast<const float4*>(d_rays), n, ray_flags, any_hit, out, counters,
-                               dev->d_work.ptr, dev->sm_count, stream));
+                               dev->d_work.ptr + 2 * igb200_device::kPipe, dev->sm_count, stream));
     if (timed) IGB_CUDA(cudaEventRecord(dev->ev1, stream));
     return IGB200_OK;
 }
@@ -313,33 +325,60 @@ int igb200_trace_rays(igb200_device* dev, const igb200_ray* rays, uint64_t n, ui
     if (!dev->has_scene) return fail(IGB200_E_STATE, "igb200_trace_rays: no scene assigned");
     if (n && !rays) return fail(IGB200_E_INVALID, "igb200_trace_rays: rays is NULL");
     IGB_CUDA(cudaSetDevice(dev->ordinal));
-    cudaStream_t s = dev->stream;
     IGB_CUDA(dev->d_rays.ensure(2 * n));
     if (ent_id) IGB_CUDA(dev->d_ent.ensure(n));
     if (prim_id) IGB_CUDA(dev->d_prim.ensure(n));
     if (t) IGB_CUDA(dev->d_t.ensure(n));
     if (u) IGB_CUDA(dev->d_u.ensure(n));
     if (v) IGB_CUDA(dev->d_v.ensure(n));
-    if (n) {
-        IGB_CUDA(cudaMemcpyAsync(dev->d_rays.ptr, rays, n * sizeof(igb200_ray), cudaMemcpyHostToDevice, s));
-        IGB_CUDA(igb::launch_normalize_rays(dev->d_rays.ptr, n, s));
+
+    igb::TraceCounters* counters = nullptr;
+    if (dev->stats) {
+        IGB_CUDA(dev->d_counters.ensure(1));
+        IGB_CUDA(cudaMemsetAsync(dev->d_counters.ptr, 0, sizeof(igb::TraceCounters), dev->stream));
+        IGB_CUDA(cudaStreamSynchronize(dev->stream));
+        counters = dev->d_counters.ptr;
     }
-    const igb::TraceOutputs out{ ent_id ? dev->d_ent.ptr : nullptr, prim_id ? dev->d_prim.ptr : nullptr,
-                                 t ? dev->d_t.ptr : nullptr, u ? dev->d_u.ptr : nullptr, v ? dev->d_v.ptr : nullptr };
-    int rc = trace_on_stream(dev, reinterpret_cast<const igb200_ray*>(dev->d_rays.ptr), n, ray_flags, any_hit, out, s, true);
-    if (rc != IGB200_OK) return rc;
-    if (n) {
-        if (ent_id) IGB_CUDA(cudaMemcpyAsync(ent_id, dev->d_ent.ptr, n * 4, cudaMemcpyDeviceToHost, s));
-        if (prim_id) IGB_CUDA(cudaMemcpyAsync(prim_id, dev->d_prim.ptr, n * 4, cudaMemcpyDeviceToHost, s));
-        if (t) IGB_CUDA(cudaMemcpyAsync(t, dev->d_t.ptr, n * 4, cudaMemcpyDeviceToHost, s));
-        if (u) IGB_CUDA(cudaMemcpyAsync(u, dev->d_u.ptr, n * 4, cudaMemcpyDeviceToHost, s));
-        if (v) IGB_CUDA(cudaMemcpyAsync(v, dev->d_v.ptr, n * 4, cudaMemcpyDeviceToHost, s));
+
+    // Chunked software pipeline over kPipe streams: upload of chunk k+1, traversal of chunk k and download of
+    // chunk k-1 overlap (PCIe is full duplex), instead of the reference's upload-all / trace / download-all
+    // (Device.cpp:573-611, 1330-1363).  Chunks use disjoint slices of the staging buffers.
+    const uint64_t chunk   = igb200_device::kChunkRays;
+    const uint64_t nchunks = (n + chunk - 1) / chunk;
+    if (dev->chunk_events.size() < 2 * nchunks) {
+        const size_t old = dev->chunk_events.size();
+        dev->chunk_events.resize(2 * nchunks, nullptr);
+        for (size_t i = old; i < dev->chunk_events.size(); ++i) IGB_CUDA(cudaEventCreate(&dev->chunk_events[i]));
     }
-    IGB_CUDA(cudaStreamSynchronize(s));
+    for (uint64_t c = 0; c < nchunks; ++c) {
+        const int      slot = (int)(c % igb200_device::kPipe);
+        cudaStream_t   s    = dev->pipe[slot];
+        const uint64_t off = c * chunk, m = std::min(chunk, n - off);
+        float4*        dr = dev->d_rays.ptr + 2 * off;
+        IGB_CUDA(cudaMemcpyAsync(dr, rays + off, m * sizeof(igb200_ray), cudaMemcpyHostToDevice, s));
+        IGB_CUDA(igb::launch_normalize_rays(dr, m, s));
+        const igb::TraceOutputs out{ ent_id ? dev->d_ent.ptr + off : nullptr, prim_id ? dev->d_prim.ptr + off : nullptr,
+                                     t ? dev->d_t.ptr + off : nullptr, u ? dev->d_u.ptr + off : nullptr,
+                                     v ? dev->d_v.ptr + off : nullptr };
+        IGB_CUDA(cudaEventRecord(dev->chunk_events[2 * c], s));
+        IGB_CUDA(igb::launch_trace(dev->view, dr, m, ray_flags, any_hit, out, counters, dev->d_work.ptr + 2 * slot,
+                                   dev->sm_count, s));
+        IGB_CUDA(cudaEventRecord(dev->chunk_events[2 * c + 1], s));
+        if (ent_id) IGB_CUDA(cudaMemcpyAsync(ent_id + off, out.ent_id, m * 4, cudaMemcpyDeviceToHost, s));
+        if (prim_id) IGB_CUDA(cudaMemcpyAsync(prim_id + off, out.prim_id, m * 4, cudaMemcpyDeviceToHost, s));
+        if (t) IGB_CUDA(cudaMemcpyAsync(t + off, out.t, m * 4, cudaMemcpyDeviceToHost, s));
+        if (u) IGB_CUDA(cudaMemcpyAsync(u + off, out.u, m * 4, cudaMemcpyDeviceToHost, s));
+        if (v) IGB_CUDA(cudaMemcpyAsync(v + off, out.v, m * 4, cudaMemcpyDeviceToHost, s));
+    }
+    for (int k = 0; k < igb200_device::kPipe; ++k) IGB_CUDA(cudaStreamSynchronize(dev->pipe[k]));
+
     dev->last_stats      = igb200_trace_stats{};
     dev->last_stats.rays = n;
-    float ms             = 0.0f;
-    if (cudaEventElapsedTime(&ms, dev->ev0, dev->ev1) == cudaSuccess) dev->last_stats.kernel_ms = ms;
+    for (uint64_t c = 0; c < nchunks; ++c) {
+        float ms = 0.0f;
+        if (cudaEventElapsedTime(&ms, dev->chunk_events[2 * c], dev->chunk_events[2 * c + 1]) == cudaSuccess)
+            dev->last_stats.kernel_ms += ms;
+    }
     if (dev->stats) {
         igb::TraceCounters c{};
         IGB_CUDA(cudaMemcpy(&c, dev->d_counters.ptr, sizeof(c), cudaMemcpyDeviceToHost));
