@@ -1,0 +1,423 @@
+"""Minimal scene ingest for the reference's JSON scene format -- harness level, not the product.
+
+Covers what the BASELINE configs and the evaluation scenes used as golden images need: perspective camera,
+path / debug technique, diffuse / dielectric / mirror / conductor BSDFs, rectangle / triangle / cube / sphere /
+obj / ply shapes, entities with transforms, point / spot / directional / env (constant) / area lights.
+It follows the reference loader where ordering matters for parity:
+  * transforms: src/runtime/loader/Parser.cpp:124-243 (row-major 3x4 / 4x4 arrays; op lists multiply left to right)
+  * procedural meshes: src/runtime/mesh/TriMesh.cpp:700-745,967-1003; flip_normals :34-43
+  * OBJ: fan triangulation + first-appearance vertex numbering (src/runtime/mesh/ObjFile.cpp:113-180)
+  * entity / material numbering: src/runtime/loader/LoaderEntity.cpp:42-103 (material groups, area-light
+    entities get a material of their own)
+  * lights: infinite / finite tables in scene order (src/runtime/loader/LoaderLight.cpp)
+"""
+import json
+import math
+import os
+import struct
+
+import numpy as np
+
+from .shading import Shading, as_plane
+from .tables import SceneBuilder
+
+
+# ---------------------------------------------------------------------------------------- transforms
+def _look_at(eye, center, up):
+    eye, center, up = [np.asarray(a, np.float64) for a in (eye, center, up)]
+    f = center - eye
+    f = f / np.linalg.norm(f) if np.linalg.norm(f) > 0 else np.array([0, 0, 1.0])
+    u = up / np.linalg.norm(up)
+    s = np.cross(f, u)
+    s = s / np.linalg.norm(s)
+    u = np.cross(s, f)
+    m = np.eye(4)
+    m[:3, 0], m[:3, 1], m[:3, 2], m[:3, 3] = s, u, f, eye
+    return m
+
+
+def _rot(axis, deg):
+    a = math.radians(deg)
+    c, s = math.cos(a), math.sin(a)
+    m = np.eye(4)
+    i, j = [(1, 2), (2, 0), (0, 1)][axis]
+    m[i, i], m[i, j], m[j, i], m[j, j] = c, -s, s, c
+    return m
+
+
+def parse_transform(t):
+    if t is None:
+        return np.eye(4)
+    if isinstance(t, list) and t and isinstance(t[0], dict):
+        m = np.eye(4)
+        for op in t:
+            for k, v in op.items():
+                if k == "translate":
+                    o = np.eye(4); o[:3, 3] = v
+                elif k == "scale":
+                    o = np.eye(4)
+                    o[0, 0], o[1, 1], o[2, 2] = (v, v, v) if np.isscalar(v) else v
+                elif k == "rotate":
+                    o = _rot(0, v[0]) @ _rot(1, v[1]) @ _rot(2, v[2])
+                elif k == "lookat":
+                    origin = v.get("origin", [0, 0, 0])
+                    target = np.asarray(v["direction"], float) + np.asarray(origin, float) if "direction" in v \
+                        else v.get("target", [0, 1, 0])
+                    o = _look_at(origin, target, v.get("up", [0, 0, 1]))
+                elif k == "matrix":
+                    o = parse_transform(v)
+                else:
+                    raise ValueError(f"unsupported transform op {k}")
+                m = m @ o
+        return m
+    a = np.asarray(t, np.float64).reshape(-1)
+    m = np.eye(4)
+    if a.size == 16:
+        m = a.reshape(4, 4)
+    elif a.size == 12:
+        m[:3, :] = a.reshape(3, 4)
+    elif a.size == 9:
+        m[:3, :3] = a.reshape(3, 3)
+    else:
+        raise ValueError("transform must have 9, 12 or 16 numbers")
+    return m
+
+
+# ---------------------------------------------------------------------------------------- meshes
+class Mesh:
+    def __init__(self, v, f, n=None, t=None):
+        self.v = np.asarray(v, np.float32).reshape(-1, 3)
+        self.f = np.asarray(f, np.uint32).reshape(-1, 3)
+        self.n = None if n is None else np.asarray(n, np.float32).reshape(-1, 3)
+        self.t = np.zeros((self.v.shape[0], 2), np.float32) if t is None else np.asarray(t, np.float32).reshape(-1, 2)
+        if self.n is None:
+            self.compute_vertex_normals()
+
+    def compute_vertex_normals(self):
+        n = np.zeros_like(self.v, dtype=np.float64)
+        v = self.v.astype(np.float64)
+        fn = np.cross(v[self.f[:, 1]] - v[self.f[:, 0]], v[self.f[:, 2]] - v[self.f[:, 0]])
+        for k in range(3):
+            np.add.at(n, self.f[:, k], fn)
+        ln = np.linalg.norm(n, axis=1, keepdims=True)
+        self.n = (n / np.maximum(ln, 1e-30)).astype(np.float32)
+
+    def flip_normals(self):
+        self.f = self.f[:, [0, 2, 1]].copy()
+        self.n = (-self.n).astype(np.float32)
+
+    def transform(self, m):
+        m = np.asarray(m, np.float64)
+        self.v = (self.v.astype(np.float64) @ m[:3, :3].T + m[:3, 3]).astype(np.float32)
+        nm = np.linalg.inv(m[:3, :3]).T
+        n = self.n.astype(np.float64) @ nm.T
+        self.n = (n / np.maximum(np.linalg.norm(n, axis=1, keepdims=True), 1e-30)).astype(np.float32)
+
+
+def _grid(origin, x_axis, y_axis):  # addGrid(..., 1, 1) == addPlane
+    o, x, y = [np.asarray(a, np.float64) for a in (origin, x_axis, y_axis)]
+    v = [o, o + x, o + y, o + x + y]
+    nrm = np.cross(x, y)
+    nrm = nrm / np.linalg.norm(nrm)
+    return v, [nrm] * 4, [(0, 0), (1, 0), (0, 1), (1, 1)], [(0, 1, 3), (0, 3, 2)]
+
+
+def make_plane(origin, x_axis, y_axis):
+    v, n, t, f = _grid(origin, x_axis, y_axis)
+    return Mesh(v, f, n, t)
+
+
+def make_box(origin, x, y, z):
+    o, x, y, z = [np.asarray(a, np.float64) for a in (origin, x, y, z)]
+    hhh = o + x + y + z
+    vs, ns, ts, fs = [], [], [], []
+    for org, a, b in ((o, y, x), (o, x, z), (o, z, y), (hhh, -x, -y), (hhh, -z, -x), (hhh, -y, -z)):
+        v, n, t, f = _grid(org, a, b)
+        off = len(vs)
+        vs += v; ns += n; ts += t
+        fs += [(i + off, j + off, k + off) for i, j, k in f]
+    return Mesh(vs, fs, ns, ts)
+
+
+def load_obj(path):
+    """OBJ subset: v / vn / vt / f, fan triangulation, vertices numbered by first appearance of the
+    (v, vn, vt) triple (ObjFile.cpp:113-173); missing normals -> computeVertexNormals (ObjFile.cpp:193-196)."""
+    pos, nrm, tex, faces = [], [], [], []
+    with open(path) as fh:
+        for line in fh:
+            p = line.split()
+            if not p:
+                continue
+            if p[0] == "v":
+                pos.append([float(x) for x in p[1:4]])
+            elif p[0] == "vn":
+                nrm.append([float(x) for x in p[1:4]])
+            elif p[0] == "vt":
+                tex.append([float(x) for x in p[1:3]])
+            elif p[0] == "f":
+                idx = []
+                for tok in p[1:]:
+                    q = (tok.split("/") + ["", ""])[:3]
+                    fix = lambda s, n: -1 if s == "" else (int(s) - 1 if int(s) > 0 else n + int(s))
+                    idx.append((fix(q[0], len(pos)), fix(q[2], len(nrm)), fix(q[1], len(tex))))
+                for k in range(1, len(idx) - 1):
+                    faces.append((idx[0], idx[k], idx[k + 1]))
+    has_n = any(i[1] >= 0 for f in faces for i in f)
+    has_t = any(i[2] >= 0 for f in faces for i in f)
+    remap, verts, norms, texs, out = {}, [], [], [], []
+    for tri in faces:
+        o = []
+        for key in tri:
+            if key not in remap:
+                remap[key] = len(verts)
+                verts.append(pos[key[0]])
+                if has_n:
+                    norms.append(nrm[key[1]] if key[1] >= 0 else [0.0, 0.0, 1.0])
+                if has_t:
+                    texs.append(tex[key[2]] if key[2] >= 0 else [0.0, 0.0])
+            o.append(remap[key])
+        out.append(o)
+    return Mesh(verts, out, norms if has_n else None, texs if has_t else None)
+
+
+def load_ply(path):
+    with open(path, "rb") as fh:
+        data = fh.read()
+    end = data.index(b"end_header\n") + len(b"end_header\n")
+    header = data[:end].decode("ascii", "replace").splitlines()
+    fmt, elems, cur = None, [], None
+    for line in header:
+        p = line.split()
+        if not p:
+            continue
+        if p[0] == "format":
+            fmt = p[1]
+        elif p[0] == "element":
+            cur = {"name": p[1], "count": int(p[2]), "props": []}
+            elems.append(cur)
+        elif p[0] == "property":
+            cur["props"].append(p[1:])
+    tmap = {"float": "f", "float32": "f", "double": "d", "uchar": "B", "uint8": "B", "char": "b", "int": "i", "int32": "i",
+            "uint": "I", "uint32": "I", "short": "h", "ushort": "H"}
+    body = data[end:]
+    verts, faces = None, []
+    if fmt == "ascii":
+        toks = body.split()
+        pos = 0
+        for e in elems:
+            if e["name"] == "vertex":
+                k = len(e["props"])
+                arr = np.array(toks[pos:pos + k * e["count"]], dtype=np.float64).reshape(e["count"], k)
+                pos += k * e["count"]
+                verts = {p[-1]: arr[:, i] for i, p in enumerate(e["props"])}
+            elif e["name"] == "face":
+                for _ in range(e["count"]):
+                    n = int(toks[pos]); idx = [int(x) for x in toks[pos + 1:pos + 1 + n]]; pos += 1 + n
+                    for k in range(1, n - 1):
+                        faces.append((idx[0], idx[k], idx[k + 1]))
+    else:
+        en = "<" if fmt == "binary_little_endian" else ">"
+        off = 0
+        for e in elems:
+            if e["name"] == "vertex":
+                dt = np.dtype([(p[-1], en + tmap[p[0]].replace("f", "f4").replace("d", "f8").replace("B", "u1")
+                                .replace("i", "i4").replace("I", "u4")) for p in e["props"]])
+                arr = np.frombuffer(body, dt, e["count"], off)
+                off += dt.itemsize * e["count"]
+                verts = {name: arr[name].astype(np.float64) for name in dt.names}
+            elif e["name"] == "face":
+                lp = e["props"][0]  # list <count type> <index type> name
+                ct, it = tmap[lp[1]], tmap[lp[2]]
+                for _ in range(e["count"]):
+                    n = struct.unpack_from(en + ct, body, off)[0]; off += struct.calcsize(ct)
+                    idx = struct.unpack_from(en + it * n, body, off); off += struct.calcsize(it) * n
+                    for k in range(1, n - 1):
+                        faces.append((idx[0], idx[k], idx[k + 1]))
+    v = np.stack([verts["x"], verts["y"], verts["z"]], axis=1)
+    n = np.stack([verts["nx"], verts["ny"], verts["nz"]], axis=1) if "nx" in verts else None
+    tn = "u" if "u" in verts else ("s" if "s" in verts else None)
+    t = np.stack([verts[tn], verts["v" if tn == "u" else "t"]], axis=1) if tn else None
+    return Mesh(v, faces, n, t)
+
+
+# ---------------------------------------------------------------------------------------- scene
+def _merge_externals(scene, base):
+    for ext in scene.get("externals", []):
+        path = os.path.join(base, ext["filename"])
+        with open(path) as fh:
+            sub = json.load(fh)
+        sub = _merge_externals(sub, os.path.dirname(path))
+        for k, v in sub.items():
+            if isinstance(v, list):
+                scene.setdefault(k, [])
+                scene[k] = scene[k] + v
+            elif k not in scene:
+                scene[k] = v
+    return scene
+
+
+def _color(v, default):
+    if v is None:
+        v = default
+    a = np.asarray(v, np.float32).reshape(-1)
+    return np.repeat(a, 3) if a.size == 1 else a[:3]
+
+
+def build_shape(elem, base):
+    ty = elem["type"]
+    if ty == "rectangle":
+        if "p0" in elem:
+            p0, p1, p2, p3 = [np.asarray(elem.get(k, d), np.float64) for k, d in
+                              (("p0", (-1, -1, 0)), ("p1", (1, -1, 0)), ("p2", (1, 1, 0)), ("p3", (-1, 1, 0)))]
+            vs, ns, ts, fs = [], [], [], []
+            for o, a, b in ((p0, p1 - p0, p3 - p0), (p1, p2 - p1, p3 - p1)):  # MakeRectangle: two addTriangle
+                n = np.cross(a, b); n = n / np.linalg.norm(n)
+                off = len(vs)
+                vs += [o, o + a, o + b]; ns += [n] * 3; ts += [(0, 0), (1, 0), (0, 1)]
+                fs.append((off, off + 1, off + 2))
+            mesh = Mesh(vs, fs, ns, ts)
+        else:
+            w, h = elem.get("width", 2.0), elem.get("height", 2.0)
+            mesh = make_plane(elem.get("origin", (-w / 2, -h / 2, 0)), (w, 0, 0), (0, h, 0))
+    elif ty == "triangle":
+        p0, p1, p2 = [np.asarray(elem.get(k, d), np.float64) for k, d in
+                      (("p0", (0, 0, 0)), ("p1", (1, 0, 0)), ("p2", (0, 1, 0)))]
+        n = np.cross(p1 - p0, p2 - p0); n = n / np.linalg.norm(n)
+        mesh = Mesh([p0, p1, p2], [(0, 1, 2)], [n] * 3, [(0, 0), (1, 0), (0, 1)])
+    elif ty in ("cube", "box"):
+        w, h, d = elem.get("width", 2.0), elem.get("height", 2.0), elem.get("depth", 2.0)
+        mesh = make_box(elem.get("origin", (-w / 2, -h / 2, -d / 2)), (w, 0, 0), (0, h, 0), (0, 0, d))
+    elif ty in ("obj", "ply", "external"):
+        path = os.path.join(base, elem["filename"])
+        mesh = load_obj(path) if path.lower().endswith(".obj") else load_ply(path)
+    elif ty == "sphere":
+        return ("sphere", np.asarray(elem.get("center", (0, 0, 0)), np.float32), float(elem.get("radius", 1.0)))
+    else:
+        raise ValueError(f"shape type '{ty}' is outside the supported subset")
+    if elem.get("flip_normals", False):
+        mesh.flip_normals()
+    if "transform" in elem:
+        m = parse_transform(elem["transform"])
+        if not np.allclose(m, np.eye(4)):
+            mesh.transform(m)
+    return ("trimesh", mesh)
+
+
+def load_scene(scene, base=".", width=None, height=None):
+    """scene: dict or path. Returns (SceneTables, Shading, width, height, info)."""
+    if isinstance(scene, str):
+        base = os.path.dirname(os.path.abspath(scene))
+        with open(scene) as fh:
+            scene = json.load(fh)
+    scene = _merge_externals(dict(scene), base)
+    film = scene.get("film", {}).get("size", [1000, 1000])
+    width, height = width or int(film[0]), height or int(film[1])
+
+    b = SceneBuilder()
+    sh = Shading()
+
+    shapes, shape_mesh = {}, {}
+    for e in scene.get("shapes", []):
+        built = build_shape(e, base)
+        if built[0] == "sphere":
+            shapes[e["name"]] = b.add_sphere(built[1], built[2])
+        else:
+            m = built[1]
+            shapes[e["name"]] = b.add_trimesh(m.v, m.f, m.n, m.t)
+            shape_mesh[e["name"]] = m
+
+    bsdf_ids = {}
+    for e in scene.get("bsdfs", []):
+        ty = e["type"]
+        if ty == "diffuse":
+            bsdf_ids[e["name"]] = sh.add_diffuse(_color(e.get("reflectance"), 0.8))
+        elif ty in ("dielectric", "glass"):
+            bsdf_ids[e["name"]] = sh.add_dielectric(e.get("int_ior", 1.5046), e.get("ext_ior", 1.0),
+                                                    _color(e.get("specular_reflectance"), 1.0),
+                                                    _color(e.get("specular_transmittance"), 1.0))
+        elif ty == "mirror":
+            bsdf_ids[e["name"]] = sh.add_mirror(_color(e.get("specular_reflectance"), 1.0))
+        elif ty == "conductor":
+            bsdf_ids[e["name"]] = sh.add_conductor(_color(e.get("eta"), 0.63660), _color(e.get("k"), 2.7834),
+                                                   _color(e.get("specular_reflectance"), 1.0))
+        else:
+            raise ValueError(f"bsdf type '{ty}' is outside the supported subset")
+
+    lights = scene.get("lights", [])
+    area_entities = {l["entity"] for l in lights if l["type"] == "area"}
+
+    # material groups in first-appearance order; area-light entities get their own (LoaderEntity.cpp:87-103)
+    groups, keys = [], []
+    for e in scene.get("entities", []):
+        key = ("area", e["name"]) if e["name"] in area_entities else ("bsdf", e["bsdf"])
+        if key in keys and key[0] == "bsdf":
+            groups[keys.index(key)].append(e)
+        else:
+            keys.append(key)
+            groups.append([e])
+    entity_ids, entity_xform, mat_of_entity = {}, {}, {}
+    for mat_id, group in enumerate(groups):
+        for e in group:
+            m = parse_transform(e.get("transform"))
+            flags = (1 if e.get("camera_visible", True) else 0) | (2 if e.get("light_visible", True) else 0) | \
+                    (4 if e.get("bounce_visible", True) else 0) | (8 if e.get("shadow_visible", True) else 0)
+            entity_ids[e["name"]] = b.add_entity(shapes[e["shape"]], m, material=mat_id, flags=flags)
+            entity_xform[e["name"]] = m
+            mat_of_entity[e["name"]] = mat_id
+    tables = b.finish()
+
+    # lights: finite ids are needed by the emissive materials
+    area_light_of_entity = {}
+    for l in lights:
+        ty = l["type"]
+        if ty == "point":
+            c = _color(l.get("power"), 4 * math.pi) / np.float32(4 * math.pi) if "power" in l else _color(l.get("intensity"), 1.0)
+            sh.add_point_light(l.get("position", (0, 0, 0)), c)
+        elif ty == "spot":
+            cutoff, falloff = l.get("cutoff", 30.0), l.get("falloff", 20.0)
+            c = _color(l.get("intensity"), 1.0)
+            if "power" in l:  # spot_from_power, light/spot.art:1-6
+                f = 2 * math.pi * (1 - 0.5 * math.cos(math.radians(falloff)) - 0.5 * math.cos(math.radians(cutoff)))
+                c = _color(l.get("power"), 1.0) / np.float32(f)
+            sh.add_spot_light(l.get("position", (0, 0, 0)), l.get("direction", (0, 0, 1)), cutoff, falloff, c)
+        elif ty in ("directional", "direction", "distant"):
+            sh.add_directional_light(l.get("direction", (0, 0, 1)), _color(l.get("irradiance"), 1.0))
+        elif ty in ("env", "envmap", "uniform", "constant"):
+            if isinstance(l.get("radiance"), str):
+                raise ValueError("textured environment lights are outside the supported subset")
+            sh.add_env_light(_color(l.get("radiance"), 1.0), _color(l.get("scale"), 1.0))
+        elif ty == "area":
+            name = l["entity"]
+            ent = next(e for e in scene["entities"] if e["name"] == name)
+            mesh = shape_mesh.get(ent["shape"])
+            plane = None
+            if mesh is not None and l.get("optimize", True):
+                pl = as_plane(mesh.v, mesh.f)
+                if pl is not None:
+                    m = entity_xform[name]
+                    o = (m[:3, :3] @ pl[0].astype(np.float64) + m[:3, 3])
+                    plane = (o, m[:3, :3] @ pl[1].astype(np.float64), m[:3, :3] @ pl[2].astype(np.float64))
+            area_light_of_entity[name] = sh.add_area_light(entity_ids[name], _color(l.get("radiance"), 1.0), plane)
+        else:
+            raise ValueError(f"light type '{ty}' is outside the supported subset")
+
+    for key in keys:
+        if key[0] == "area":
+            ent = next(e for e in scene["entities"] if e["name"] == key[1])
+            sh.add_material(bsdf_ids[ent["bsdf"]], area_light_of_entity[key[1]])
+        else:
+            sh.add_material(bsdf_ids[key[1]])
+
+    cam = scene.get("camera", {})
+    vertical = "vfov" in cam
+    fov = cam.get("vfov", cam.get("hfov", cam.get("fov", 60.0)))
+    sh.set_perspective_from_transform(parse_transform(cam.get("transform")), fov, width, height,
+                                      cam.get("near_clip", 0.0), cam.get("far_clip", float(np.finfo(np.float32).max)), vertical)
+    tech = scene.get("technique", {"type": "path"})
+    if tech.get("type", "path") == "path":
+        sh.set_path(tech.get("max_depth", 64), tech.get("min_depth", 2), tech.get("clamp", 0.0), tech.get("nee", True))
+    elif tech["type"] == "debug":
+        sh.set_debug(tech.get("mode", 0))
+    else:
+        raise ValueError(f"technique '{tech['type']}' is outside the supported subset")
+    return tables, sh, width, height, {"entities": entity_ids, "materials": keys}

@@ -1,0 +1,228 @@
+"""POD shading tables of include/ignis_b200.h (camera, BSDFs, materials, lights, technique).
+
+In the reference these parameters are baked into per-scene Artic source by the loader
+(src/runtime/shader/ShaderUtils.cpp:95-122, src/runtime/loader/LoaderLight.cpp:106-250,
+src/runtime/technique/PathTechnique.cpp:36-79, src/runtime/camera/PerspectiveCamera.cpp:27-67); here they
+travel as plain tables.  The helpers reproduce the loader-side arithmetic (fov -> scale, plane detection for
+area lights, light table split into infinite / finite).
+"""
+import ctypes as C
+import math
+
+import numpy as np
+
+BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_MIRROR, BSDF_CONDUCTOR = 0, 1, 2, 3
+LIGHT_POINT, LIGHT_ENV, LIGHT_AREA_SHAPE, LIGHT_AREA_PLANE, LIGHT_SPOT, LIGHT_DIRECTIONAL = 0, 1, 2, 3, 4, 5
+TECH_PATH, TECH_DEBUG = 0, 1
+TECHFLAG_ONE_SIDED_DIFFUSE = 1
+
+
+class Camera(C.Structure):
+    _fields_ = [("eye", C.c_float * 3), ("dir", C.c_float * 3), ("up", C.c_float * 3), ("scale", C.c_float * 2),
+                ("tmin", C.c_float), ("tmax", C.c_float)]
+
+
+class Bsdf(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("color", C.c_float * 3), ("color2", C.c_float * 3), ("p", C.c_float * 5)]
+
+
+class Material(C.Structure):
+    _fields_ = [("bsdf", C.c_int32), ("light", C.c_int32)]
+
+
+class Light(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("entity", C.c_int32), ("color", C.c_float * 3), ("v", C.c_float * 16),
+                ("_pad", C.c_uint32 * 3)]
+
+
+class Technique(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("max_depth", C.c_int32), ("min_depth", C.c_int32), ("clamp", C.c_float),
+                ("enable_nee", C.c_int32), ("debug_mode", C.c_int32), ("flags", C.c_uint32), ("_pad", C.c_int32)]
+
+
+class ShadingC(C.Structure):
+    _fields_ = [("camera", Camera), ("technique", Technique),
+                ("bsdfs", C.c_void_p), ("bsdf_count", C.c_uint64),
+                ("materials", C.c_void_p), ("material_count", C.c_uint64),
+                ("infinite_lights", C.c_void_p), ("infinite_light_count", C.c_uint64),
+                ("finite_lights", C.c_void_p), ("finite_light_count", C.c_uint64)]
+
+
+class RenderSettings(C.Structure):
+    _fields_ = [("rays", C.c_void_p), ("ray_count", C.c_uint64), ("spi", C.c_uint32), ("width", C.c_uint32),
+                ("height", C.c_uint32), ("iteration", C.c_uint32), ("frame", C.c_uint32), ("user_seed", C.c_uint32)]
+
+
+class RenderStats(C.Structure):
+    _fields_ = [("camera_rays", C.c_uint64), ("bounce_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
+                ("rounds", C.c_uint64), ("kernel_launches", C.c_uint64), ("device_ms", C.c_float), ("_pad", C.c_float)]
+
+
+assert C.sizeof(Bsdf) == 48 and C.sizeof(Light) == 96 and C.sizeof(Camera) == 52 and C.sizeof(Technique) == 32
+
+
+def _f3(dst, src):
+    s = np.asarray(src, np.float32).reshape(-1)
+    if s.size == 1:
+        s = np.repeat(s, 3)
+    for k in range(3):
+        dst[k] = float(s[k])
+
+
+def as_plane(vertices, faces):
+    """TriMesh::getAsPlane (src/runtime/mesh/TriMesh.cpp:520-628) for the 4-vertex / 2-face case.
+    Returns (origin, x_axis, y_axis) in object space or None."""
+    v = np.asarray(vertices, np.float32).reshape(-1, 3)
+    f = np.asarray(faces).reshape(-1, 3)
+    if f.shape[0] != 2 or v.shape[0] != 4:
+        return None
+    fn = lambda t: np.cross(v[t[1]] - v[t[0]], v[t[2]] - v[t[0]])
+    n0, n1 = fn(f[0]), fn(f[1])
+    n0, n1 = n0 / np.linalg.norm(n0), n1 / np.linalg.norm(n1)
+    if not np.allclose(n0, n1, atol=1e-5):
+        return None
+    origin = v[0]
+
+    def angle(start):
+        a = v[(start + 0) % 3 + 1] - origin
+        b = v[(start + 1) % 3 + 1] - origin
+        return abs(math.acos(float(np.clip(np.dot(a / np.linalg.norm(a), b / np.linalg.norm(b)), -1, 1))))
+
+    a12, a23, a31 = angle(0), angle(1), angle(2)
+    if a12 >= a23 and a12 >= a31:
+        sel = 0
+    elif a23 >= a31 and a23 >= a12:
+        sel = 1
+    else:
+        sel = 2
+    x_axis = v[(sel + 0) % 3 + 1] - origin
+    y_axis = v[(sel + 1) % 3 + 1] - origin
+    if float(np.dot(n0, np.cross(x_axis, y_axis))) < 0:
+        x_axis, y_axis = y_axis, x_axis
+    return origin.astype(np.float32), x_axis.astype(np.float32), y_axis.astype(np.float32)
+
+
+class Shading:
+    """Builder + owner of the POD shading tables; `c_shading()` gives the igb200_shading view."""
+
+    def __init__(self):
+        self.camera = Camera()
+        self.technique = Technique(type=TECH_PATH, max_depth=64, min_depth=2, clamp=0.0, enable_nee=1, debug_mode=0)
+        self.bsdfs, self.materials, self.infinite, self.finite = [], [], [], []
+        self._keep = None
+
+    # ---- camera: PerspectiveCamera.cpp:27-67 + compute_scale_from_hfov/vfov (camera/perspective.art:1-11) ----
+    def set_perspective(self, eye, direction, up, fov_deg, width, height, near=0.01, far=100.0, vertical=False):
+        _f3(self.camera.eye, eye)
+        _f3(self.camera.dir, direction)
+        _f3(self.camera.up, up)
+        aspect = np.float32(width) / np.float32(height)
+        t = np.float32(math.tan(np.float32(np.float32(fov_deg) * np.float32(math.pi / 180.0)) / 2))
+        if vertical:
+            sh = t
+            sw = np.float32(sh * aspect)
+        else:
+            sw = t
+            sh = np.float32(sw / aspect)
+        self.camera.scale[0], self.camera.scale[1] = float(sw), float(sh)
+        if far < near:
+            near, far = far, near
+        self.camera.tmin, self.camera.tmax = float(near), float(far)
+        return self
+
+    def set_perspective_from_transform(self, m, fov_deg, width, height, near=0.01, far=100.0, vertical=False):
+        """Camera orientation from a 4x4 (or 3x4) transform: eye = T*0, dir = col 2, up = col 1
+        (PerspectiveCamera::getOrientation, PerspectiveCamera.cpp:69-78)."""
+        m = np.asarray(m, np.float64).reshape(-1, 4)
+        return self.set_perspective(m[:3, 3], m[:3, 2], m[:3, 1], fov_deg, width, height, near, far, vertical)
+
+    def set_path(self, max_depth=64, min_depth=2, clamp=0.0, nee=True, one_sided_diffuse=False):
+        self.technique = Technique(type=TECH_PATH, max_depth=max_depth, min_depth=min_depth, clamp=clamp,
+                                   enable_nee=1 if nee else 0, debug_mode=0,
+                                   flags=TECHFLAG_ONE_SIDED_DIFFUSE if one_sided_diffuse else 0)
+        return self
+
+    def set_debug(self, mode):
+        self.technique = Technique(type=TECH_DEBUG, max_depth=1, min_depth=1, clamp=0.0, enable_nee=0, debug_mode=mode)
+        return self
+
+    # ---- BSDFs ----
+    def _bsdf(self, type_, color=(0, 0, 0), color2=(0, 0, 0), p=()):
+        b = Bsdf(type=type_)
+        _f3(b.color, color)
+        _f3(b.color2, color2)
+        for i, x in enumerate(p):
+            b.p[i] = float(x)
+        self.bsdfs.append(b)
+        return len(self.bsdfs) - 1
+
+    def add_diffuse(self, reflectance=(0.8, 0.8, 0.8)):
+        return self._bsdf(BSDF_DIFFUSE, reflectance)
+
+    def add_dielectric(self, int_ior=1.5046, ext_ior=1.0, specular_reflectance=(1, 1, 1), specular_transmittance=(1, 1, 1)):
+        # n1 = ext_ior (default vacuum), n2 = int_ior (default bk7): runtime/bsdf/DielectricBSDF.cpp:14-35, BSDF.cpp:8-9
+        return self._bsdf(BSDF_DIELECTRIC, specular_reflectance, specular_transmittance, (ext_ior, int_ior))
+
+    def add_mirror(self, specular_reflectance=(1, 1, 1)):
+        return self._bsdf(BSDF_MIRROR, specular_reflectance)
+
+    def add_conductor(self, eta, k, specular_reflectance=(1, 1, 1)):
+        kk = np.asarray(k, np.float32).reshape(-1)
+        kk = np.repeat(kk, 3) if kk.size == 1 else kk
+        return self._bsdf(BSDF_CONDUCTOR, specular_reflectance, eta, tuple(kk[:3]))
+
+    def add_material(self, bsdf, light=-1):
+        self.materials.append(Material(bsdf=bsdf, light=light))
+        return len(self.materials) - 1
+
+    # ---- lights ----
+    def _light(self, table, type_, color, v=(), entity=-1):
+        l = Light(type=type_, entity=entity)
+        _f3(l.color, color)
+        for i, x in enumerate(v):
+            l.v[i] = float(x)
+        table.append(l)
+        return len(table) - 1
+
+    def add_point_light(self, position, intensity=(1, 1, 1)):
+        return self._light(self.finite, LIGHT_POINT, intensity, tuple(np.asarray(position, np.float32)))
+
+    def add_spot_light(self, position, direction, cutoff_deg=30.0, falloff_deg=20.0, intensity=(1, 1, 1)):
+        d = np.asarray(direction, np.float64)
+        d = (d / np.linalg.norm(d)).astype(np.float32)
+        v = list(np.asarray(position, np.float32)) + list(d) + [np.float32(math.radians(cutoff_deg)),
+                                                                  np.float32(math.radians(falloff_deg))]
+        return self._light(self.finite, LIGHT_SPOT, intensity, v)
+
+    def add_directional_light(self, direction, irradiance=(1, 1, 1)):
+        d = np.asarray(direction, np.float64)
+        d = (d / np.linalg.norm(d)).astype(np.float32)
+        return self._light(self.infinite, LIGHT_DIRECTIONAL, irradiance, tuple(d))
+
+    def add_env_light(self, radiance=(1, 1, 1), scale=(1, 1, 1)):
+        r = np.asarray(radiance, np.float32).reshape(-1)
+        s = np.asarray(scale, np.float32).reshape(-1)
+        c = (np.repeat(r, 3) if r.size == 1 else r) * (np.repeat(s, 3) if s.size == 1 else s)
+        return self._light(self.infinite, LIGHT_ENV, c, (1, 0, 0, 0, 1, 0, 0, 0, 1))
+
+    def add_area_light(self, entity, radiance, plane=None):
+        """plane = (origin, x_axis, y_axis) in WORLD space selects make_plane_area_emitter
+        (AreaLight.cpp:56-70,143-160), otherwise make_shape_area_emitter."""
+        if plane is None:
+            return self._light(self.finite, LIGHT_AREA_SHAPE, radiance, (), entity)
+        o, x, y = [np.asarray(a, np.float32) for a in plane]
+        n = np.cross(x, y).astype(np.float32)
+        area = np.float32(np.linalg.norm(n))
+        n = (n / area).astype(np.float32)
+        return self._light(self.finite, LIGHT_AREA_PLANE, radiance, list(o) + list(x) + list(y) + list(n) + [area], entity)
+
+    def c_shading(self):
+        arr = lambda cls, items: (cls * max(1, len(items)))(*items)
+        b, m, i, f = arr(Bsdf, self.bsdfs), arr(Material, self.materials), arr(Light, self.infinite), arr(Light, self.finite)
+        self._keep = (b, m, i, f)
+        sh = ShadingC(camera=self.camera, technique=self.technique)
+        sh.bsdfs, sh.bsdf_count = C.addressof(b), len(self.bsdfs)
+        sh.materials, sh.material_count = C.addressof(m), len(self.materials)
+        sh.infinite_lights, sh.infinite_light_count = C.addressof(i), len(self.infinite)
+        sh.finite_lights, sh.finite_light_count = C.addressof(f), len(self.finite)
+        return sh

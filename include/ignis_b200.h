@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define IGB200_ABI_VERSION 1
+#define IGB200_ABI_VERSION 2
 
 enum {
     IGB200_OK            = 0,
@@ -151,6 +151,151 @@ int igb200_get_trace_stats(igb200_device* dev, igb200_trace_stats* out);
 /* Sizes of the device-side acceleration structure (for the roofline's working-set statement). */
 int igb200_get_bvh_info(igb200_device* dev, uint64_t* node_bytes, uint64_t* tri_bytes, uint64_t* leaf_bytes,
                         uint32_t* max_depth);
+
+/* =====================================================================================================
+ * Wavefront path tracing.
+ *
+ * In the reference, cameras / BSDFs / lights / the technique reach the device as per-scene Artic SOURCE
+ * that is JIT-compiled (src/runtime/shader/, , ShaderUtils.cpp:95-122, loader/LoaderLight.cpp:106-240,
+ * technique/PathTechnique.cpp:36-79).  This backend has no JIT: the same parameters travel as the POD
+ * tables below ("the one place the seam must be widened").  Every field names the Artic
+ * constructor argument it feeds.
+ * ===================================================================================================== */
+
+/* make_perspective_camera(eye, dir, up, scale, w, h, tmin, tmax) (src/artic/camera/perspective.art:29-41);
+ * scale = compute_scale_from_hfov / _vfov (perspective.art:1-11), chosen by the loader
+ * (src/runtime/camera/PerspectiveCamera.cpp:40-54). */
+typedef struct igb200_camera {
+    float eye[3];
+    float dir[3];
+    float up[3];
+    float scale[2];
+    float tmin; /* near clip */
+    float tmax; /* far clip */
+} igb200_camera;
+
+#define IGB200_BSDF_DIFFUSE    0u /* make_lambertian_bsdf(surf, kd = color)           bsdf/diffuse.art:2-11 */
+#define IGB200_BSDF_DIELECTRIC 1u /* make_pure_dielectric_bsdf(surf, n1 = p[0] (exterior), n2 = p[1] (interior),
+                                     ks = color, kt = color2)                          bsdf/dielectric.art:2-23 */
+#define IGB200_BSDF_MIRROR     2u /* make_mirror_bsdf(surf, ks = color)                bsdf/conductor.art:1-9 */
+#define IGB200_BSDF_CONDUCTOR  3u /* make_pure_conductor_bsdf(surf, ior = color2, k = p[0..2], ks = color)
+                                     bsdf/conductor.art:12-30 */
+typedef struct igb200_bsdf {
+    uint32_t type;
+    float    color[3];
+    float    color2[3];
+    float    p[5];
+} igb200_bsdf; /* 48 bytes */
+
+/* One row per material id (the ids written into the entity table, LoaderEntity.cpp:87-103,171):
+ * make_material / make_emissive_material (src/artic/driver/material.art:10-28, ShaderUtils.cpp:95-122). */
+typedef struct igb200_material {
+    int32_t bsdf;  /* index into igb200_shading::bsdfs */
+    int32_t light; /* index into the FINITE light table of the area light this material emits, or -1 */
+} igb200_material;
+
+#define IGB200_LIGHT_POINT      0u /* make_point_light(pos = v[0..2], intensity = color)   light/point.art:1-18 */
+#define IGB200_LIGHT_ENV        1u /* make_environment_light(scene_bbox, scale*radiance = color, transform = v[0..8]
+                                      column major): constant radiance, spherical sampling   light/env.art:75-101,163-166 */
+#define IGB200_LIGHT_AREA_SHAPE 2u /* make_area_light(make_shape_area_emitter(entity, trimesh), radiance = color)
+                                      light/area.art:10-88 */
+#define IGB200_LIGHT_AREA_PLANE 3u /* make_area_light(make_plane_area_emitter(origin v[0..2], x_axis v[3..5],
+                                      y_axis v[6..8], normal v[9..11], area v[12]), radiance = color)
+                                      light/area.art:107-232, runtime/light/AreaLight.cpp:143-160 */
+#define IGB200_LIGHT_SPOT       4u /* make_spot_light(pos v[0..2], dir v[3..5], cutoff v[6], falloff v[7] (radians),
+                                      intensity = color)                                   light/spot.art */
+#define IGB200_LIGHT_DIRECTIONAL 5u /* make_directional_light(dir v[0..2], scene_bbox, irradiance = color)
+                                      light/directional.art */
+typedef struct igb200_light {
+    uint32_t type;
+    int32_t  entity; /* area lights: the emissive entity id */
+    float    color[3];
+    float    v[16];
+    uint32_t _pad[3];
+} igb200_light; /* 96 bytes */
+
+#define IGB200_TECH_PATH  0u /* make_path_renderer (src/artic/technique/pathtracer.art:40-218) */
+#define IGB200_TECH_DEBUG 1u /* make_debug_renderer (src/artic/technique/debugtracer.art), mode = debug_mode */
+/* The reference's lambertian eval is kd*|cos|/pi for ANY incoming direction (bsdf/diffuse.art:3), so next event
+ * estimation lets light through one-sided geometry from behind (e.g. a full-sphere environment sample below a
+ * ground plane, light/env.art:82-86).  The reference's own golden values that involve this case
+ * (tests/integrator/test_lights.py:37-44 expects 1.0; scenes/evaluation plane-d6 vs Mitsuba) only hold with a
+ * one-sided eval kd*max(cos,0)/pi; this flag selects it.  Default (0) restates the reference's code as written. */
+#define IGB200_TECHFLAG_ONE_SIDED_DIFFUSE 0x1u
+typedef struct igb200_technique {
+    uint32_t type;
+    int32_t  max_depth;  /* __tech_max_depth, default 64 (runtime/technique/Technique.h:8) */
+    int32_t  min_depth;  /* __tech_min_depth, default 2 */
+    float    clamp;      /* __tech_clamp, <= 0 disables */
+    int32_t  enable_nee; /* "nee", default true */
+    int32_t  debug_mode; /* __debug_mode for IGB200_TECH_DEBUG */
+    uint32_t flags;      /* IGB200_TECHFLAG_*; 0 = the reference's behaviour */
+    int32_t  _pad;
+} igb200_technique;
+
+/* The light tables are split exactly like the reference's `infinite_lights` / `finite_lights`
+ * (loader/LoaderLight.cpp:118-250); the light selector is make_uniform_light_selector
+ * (src/artic/light/light_selector.art:26-45). */
+typedef struct igb200_shading {
+    igb200_camera          camera;
+    igb200_technique       technique;
+    const igb200_bsdf*     bsdfs;
+    uint64_t               bsdf_count;
+    const igb200_material* materials; /* material_count of the scene */
+    uint64_t               material_count;
+    const igb200_light*    infinite_lights;
+    uint64_t               infinite_light_count;
+    const igb200_light*    finite_lights;
+    uint64_t               finite_light_count;
+} igb200_shading;
+
+/* Replaces Device::RenderSettings (Device.h:32-42).  One call = one ITERATION = spi samples per pixel
+ * (Device::render, Device.cpp:1588-1612).  rays != NULL selects igtrace mode (list emitter,
+ * src/artic/driver/emitter.art:18-31): width = ray_count, height = 1, ray i lands in pixel i. */
+typedef struct igb200_render_settings {
+    const igb200_ray* rays;
+    uint64_t          ray_count;
+    uint32_t          spi;
+    uint32_t          width;
+    uint32_t          height;
+    uint32_t          iteration;
+    uint32_t          frame;
+    uint32_t          user_seed;
+} igb200_render_settings;
+
+/* Ray counters of src/runtime/Statistics.h:56-63 (the numerators of Msamples/s and Mrays/s). */
+typedef struct igb200_render_stats {
+    uint64_t camera_rays;
+    uint64_t bounce_rays;
+    uint64_t shadow_rays;
+    uint64_t rounds;        /* wavefront rounds (generate/trace/sort/shade/shadow) of the last iteration */
+    uint64_t kernel_launches;
+    float    device_ms;     /* device time of the last iteration */
+    float    _pad;
+} igb200_render_stats;
+
+/* Shading tables (no reference counterpart: replaces shader compilation, Runtime.cpp:542-626). Must follow
+ * igb200_assign_scene; copies everything. */
+int igb200_assign_shading(igb200_device* dev, const igb200_shading* shading);
+
+/* Device::render (Device.h:53): synchronous; accumulates into the film and bumps the iteration count. */
+int igb200_render(igb200_device* dev, const igb200_render_settings* settings);
+
+/* Device::getFramebufferForHost / ForDevice (Device.h:63-64, Device.cpp:1330-1443): RGB f32, w*h*3, SUM over
+ * iterations; *iterations = IterationCount.  name NULL, "" or "Color" = the film.  The pointer is owned by
+ * the device and valid until resize / destroy.  device != 0 returns the device pointer (no copy). */
+int igb200_framebuffer(igb200_device* dev, const char* name, int device, float** data, uint64_t* iterations);
+
+/* Device::clearAllFramebuffer / resize (Device.h:65-66, Device.cpp:306-313,1407-1443). */
+int igb200_clear_framebuffer(igb200_device* dev);
+int igb200_resize(igb200_device* dev, uint32_t width, uint32_t height);
+
+/* Multi-GPU film combine: adds `count` floats from `src` (a device pointer on this device,
+ * e.g. the result of an NCCL reduce) into the film, or overwrites it when overwrite != 0, and sets the
+ * iteration count. */
+int igb200_set_framebuffer(igb200_device* dev, const float* d_src, uint64_t count, uint64_t iterations);
+
+int igb200_get_render_stats(igb200_device* dev, igb200_render_stats* out);
 
 /* Host-only test hook (no GPU needed): builds the compressed BVH8 over `n` boxes (min xyz, max xyz) and
  * checks its invariants -- every primitive referenced exactly once, every dequantised child box contains

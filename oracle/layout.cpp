@@ -166,6 +166,10 @@ extern "C" igo_scene* igo_scene_create(const igb200_scene* sc)
     s->shapes.resize(sc->shape_count);
     s->spheres.resize(sc->shape_count, Sphere{ v3(0, 0, 0), 0.0f });
     s->shape_type.resize(sc->shape_count);
+    s->lookups.assign(sc->shape_lookups, sc->shape_lookups + sc->shape_count);
+    s->shape_data.assign(sc->shape_data, sc->shape_data + sc->shape_bytes);
+    if (sc->entities) s->entities.assign(sc->entities, sc->entities + 36 * sc->entity_count);
+    std::memcpy(s->bbox, sc->scene_bbox, sizeof(s->bbox));
     for (uint64_t i = 0; i < sc->shape_count; ++i) {
         const igb200_lookup_entry& e = sc->shape_lookups[i];
         s->shape_type[i]             = e.type_id;

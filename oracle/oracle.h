@@ -68,6 +68,20 @@ int igo_kat_ray_triangle(const float* tri, const float* org, const float* dir, f
 int igo_kat_ray_box(const float* box, const float* org, const float* dir, float tmin, float tmax,
                     float* out_t);
 
+/* Restated render iteration (Device::render, src/runtime/device/Device.cpp:1588-1612 -> cpu_trace,
+ * src/artic/driver/mapping_cpu.art:694-836) for the path / debug techniques and the shading subset of
+ * include/ignis_b200.h: adds one iteration (spi samples per pixel) into `film` (w*h*3 f32, RGB sums).
+ * stats3 = camera, bounce, shadow ray counts (src/runtime/Statistics.h:56-63).  Returns 0 on success.
+ * Pinned by the reference's closed-form integrator tests (src/tests/integrator/test_lights.py:5-44) and the
+ * evaluation images (scenes/evaluation/references/ EXRs, scripts/RunEvaluations.py:79-113). */
+int igo_render(const igo_scene* scene, const igb200_shading* shading, const igb200_render_settings* settings,
+               float* film, uint64_t* stats3, int threads);
+
+/* Integer RNG known answers (src/artic/core/random.art): seed = create_random_seed(...), then n draws of
+ * sample_tea_u32(seed, counter++) from counter 1, raw and as next_f32. */
+void igo_kat_rng(int32_t sample, int32_t iter, int32_t frame, int32_t x, int32_t y, int32_t user, uint32_t n,
+                 uint32_t* out_seed, uint32_t* out_raw, float* out_f32);
+
 /* Structure statistics for reports. */
 void igo_scene_info(const igo_scene* s, uint64_t* node4_count, uint64_t* tri4_count, uint64_t* tri_count);
 

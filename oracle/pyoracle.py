@@ -40,6 +40,9 @@ def load():
         lib.igo_kat_ray_triangle.argtypes = [vp, vp, vp, C.c_float, C.c_float, vp]
         lib.igo_kat_ray_box.argtypes = [vp, vp, vp, C.c_float, C.c_float, vp]
         lib.igo_scene_info.argtypes = [vp, vp, vp, vp]
+        lib.igo_render.argtypes = [vp, vp, vp, vp, vp, C.c_int]
+        lib.igo_render.restype = C.c_int
+        lib.igo_kat_rng.argtypes = [C.c_int32] * 6 + [C.c_uint32, vp, vp, vp]
         _lib = lib
     return _lib
 
@@ -85,10 +88,41 @@ class OracleScene:
                             t.ctypes.data, u.ctypes.data, v.ctypes.data, tie.ctypes.data, second.ctypes.data)
         return ent, prim, t, u, v, tie.astype(bool), second
 
+    def render(self, shading, width, height, spi, iterations=1, seed=0, frame=0, rays=None, threads=0, film=None,
+               first_iteration=0):
+        """Restated Device::render: adds `iterations` iterations into a (h, w, 3) f32 film of RGB SUMS.
+        `shading` is an ignis-masterthesis_b200.shading.Shading; rays != None selects igtrace (list) mode."""
+        from importlib import import_module
+        S = import_module("ignis-masterthesis_b200").shading
+        if rays is not None:
+            rays = np.ascontiguousarray(rays)
+            width, height = rays.size, 1
+        if film is None:
+            film = np.zeros((height, width, 3), np.float32)
+        sh = shading.c_shading()
+        stats = np.zeros(3, np.uint64)
+        self.ray_stats = np.zeros(3, np.uint64)
+        for it in range(first_iteration, first_iteration + iterations):
+            rs = S.RenderSettings(rays=rays.ctypes.data if rays is not None else None,
+                                  ray_count=rays.size if rays is not None else 0, spi=spi, width=width, height=height,
+                                  iteration=it, frame=frame, user_seed=seed)
+            rc = self._lib.igo_render(self._h, C.addressof(sh), C.addressof(rs), film.ctypes.data, stats.ctypes.data, threads)
+            if rc != 0:
+                raise ValueError("oracle rejected the shading tables / settings")
+            self.ray_stats += stats
+        return film
+
     def info(self):
         a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
         self._lib.igo_scene_info(self._h, C.addressof(a), C.addressof(b), C.addressof(c))
         return {"node4": a.value, "tri4": b.value, "tris": c.value}
+
+
+def kat_rng(sample, it, frame, x, y, user, n=8):
+    seed = C.c_uint32()
+    raw, f32 = np.zeros(n, np.uint32), np.zeros(n, np.float32)
+    load().igo_kat_rng(sample, it, frame, x, y, user, n, C.addressof(seed), raw.ctypes.data, f32.ctypes.data)
+    return seed.value, raw, f32
 
 
 def kat_ray_triangle(tri, org, direction, tmin=0.0, tmax=3.4028234e38):

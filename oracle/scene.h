@@ -129,4 +129,14 @@ struct igo_scene {
     std::vector<uint32_t>           shape_type;
     igo::SceneBvh                   scene[2];
     std::vector<igb200_entity_leaf> flat_leaves[2]; // input order, sentinel stripped
+    // copies of the tables the shading path reads (render.cpp)
+    std::vector<igb200_lookup_entry> lookups;
+    std::vector<uint8_t>             shape_data;
+    std::vector<float>               entities; // 36 floats per entity
+    float                            bbox[6] = { 0, 0, 0, 0, 0, 0 };
 };
+
+namespace igo {
+// One ray through cpu_traverse_primary / cpu_traverse_secondary (traverse.cpp); used by render.cpp.
+Hit trace_one(const igo_scene& s, const Ray& ray, bool any_hit);
+} // namespace igo

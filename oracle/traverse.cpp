@@ -294,6 +294,20 @@ void parallel_chunks(uint64_t n, int threads, F&& f)
 }
 
 } // namespace
+
+// cpu_traverse_primary / cpu_traverse_secondary for one ray: loop over the primitive types carrying the
+// best hit (src/artic/driver/mapping_cpu.art:366-424).
+Hit trace_one(const igo_scene& s, const Ray& ray, bool any_hit)
+{
+    igo_counters cnt{ 0, 0, 0, 0, 0 };
+    Hit          hit = empty_hit(ray.tmax);
+    for (int type = 0; type < 2; ++type) {
+        if (s.scene[type].nodes.empty()) continue;
+        hit = traverse_scene(ray, s, type, any_hit, hit, cnt);
+    }
+    return hit;
+}
+
 } // namespace igo
 
 using namespace igo;
