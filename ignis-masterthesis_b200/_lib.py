@@ -21,6 +21,13 @@ ABI_SYMBOLS = [
     "igb200_get_trace_stats",
     "igb200_get_bvh_info",
     "igb200_debug_check_bvh8",
+    "igb200_assign_shading",
+    "igb200_render",
+    "igb200_framebuffer",
+    "igb200_clear_framebuffer",
+    "igb200_resize",
+    "igb200_set_framebuffer",
+    "igb200_get_render_stats",
 ]
 
 
@@ -104,6 +111,13 @@ def load():
     lib.igb200_get_trace_stats.argtypes = [vp, C.POINTER(TraceStats)]
     lib.igb200_get_bvh_info.argtypes = [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(u32)]
     lib.igb200_debug_check_bvh8.argtypes = [vp, u32, u32, vp]
+    lib.igb200_assign_shading.argtypes = [vp, vp]
+    lib.igb200_render.argtypes = [vp, vp]
+    lib.igb200_framebuffer.argtypes = [vp, C.c_char_p, i32, C.POINTER(vp), C.POINTER(u64)]
+    lib.igb200_clear_framebuffer.argtypes = [vp]
+    lib.igb200_resize.argtypes = [vp, u32, u32]
+    lib.igb200_set_framebuffer.argtypes = [vp, vp, u64, u64]
+    lib.igb200_get_render_stats.argtypes = [vp, vp]
     _lib = lib
     return lib
 

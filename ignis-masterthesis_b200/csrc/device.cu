@@ -3,12 +3,16 @@
 #include "../../include/ignis_b200.h"
 #include "bvh8.h"
 #include "trace.cuh"
+#include "wavefront.cuh"
+#include "shade_scene.h"
 
 #include <cuda_runtime.h>
 
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -94,6 +98,39 @@ struct igb200_device {
     DeviceBuffer<float>              d_t, d_u, d_v;
     DeviceBuffer<igb::TraceCounters> d_counters;
     igb200_trace_stats               last_stats{};
+
+    // ---- shading tables + wavefront state (igb200_assign_shading / igb200_render) ----
+    DeviceBuffer<float>           d_entities;
+    DeviceBuffer<float>           d_shape_data;
+    DeviceBuffer<uint2>           d_shape_info;
+    DeviceBuffer<int32_t>         d_ent_mat;
+    DeviceBuffer<igb200_bsdf>     d_bsdfs;
+    DeviceBuffer<igb200_material> d_materials;
+    DeviceBuffer<igb200_light>    d_inf_lights, d_fin_lights;
+    igb::shade::ShadeScene        shade{};
+    bool                          has_shading = false;
+    uint64_t                      entity_count = 0;
+    uint32_t                      scene_material_count = 0;
+    float                         scene_bbox[6] = {};
+
+    uint32_t                      wave_capacity = 0;
+    bool                          wave_sort     = true;
+    DeviceBuffer<float4>          w_f4[2][3], w_sh_f4[3];
+    DeviceBuffer<uint4>           w_u4[2][2];
+    DeviceBuffer<float>           w_f1[2][2];
+    DeviceBuffer<uint32_t>        w_keys, w_sorted;
+    DeviceBuffer<igb::WaveControl> w_ctl;
+    igb::WaveBuffers              wave{};
+    uint32_t*                     h_done = nullptr; // mapped pinned host flag
+    cudaEvent_t                   round_ev[4] = {};
+    DeviceBuffer<float4>          d_list_rays;
+
+    DeviceBuffer<float>           d_film;
+    float*                        h_film = nullptr; // pinned host copy
+    uint32_t                      film_w = 0, film_h = 0;
+    uint64_t                      iterations = 0;
+    bool                          film_mapped = false; // host copy is current
+    igb200_render_stats           render_stats{};
 };
 
 extern "C" {
@@ -152,6 +189,10 @@ void igb200_destroy(igb200_device* dev)
         if (p) cudaStreamDestroy(p);
     for (cudaEvent_t e : dev->chunk_events)
         if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : dev->round_ev)
+        if (e) cudaEventDestroy(e);
+    if (dev->h_done) cudaFreeHost(dev->h_done);
+    if (dev->h_film) cudaFreeHost(dev->h_film);
     delete dev; // DeviceBuffer destructors free the allocations (Device::releaseAll, Device.cpp:948-952)
 }
 
@@ -274,6 +315,30 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
     IGB_CUDA(dev->leaves.upload(reinterpret_cast<const float4*>(ordered.data()), ordered.size() * 6, dev->stream));
     IGB_CUDA(dev->shapes.upload(shape_refs.data(), shape_refs.size(), dev->stream));
     IGB_CUDA(dev->spheres.upload(all_spheres.data(), all_spheres.size(), dev->stream));
+    // tables the shading kernels read (entities FixTable, shapes DynTable data)
+    dev->has_shading = false;
+    {
+        std::vector<uint2>   info(sc->shape_count);
+        for (uint64_t s = 0; s < sc->shape_count; ++s) {
+            if (sc->shape_lookups[s].offset % 16 != 0) return fail(IGB200_E_INVALID, "shape %llu: offset is not 16-byte aligned", (unsigned long long)s);
+            info[s] = make_uint2((uint32_t)(sc->shape_lookups[s].offset / 4), sc->shape_lookups[s].type_id);
+        }
+        std::vector<int32_t> ent_mat(sc->entities ? sc->entity_count : 0);
+        for (size_t i = 0; i < ent_mat.size(); ++i) {
+            std::memcpy(&ent_mat[i], sc->entities + 36 * i + 34, 4);
+            int32_t shape_id;
+            std::memcpy(&shape_id, sc->entities + 36 * i + 33, 4);
+            if (shape_id < 0 || (uint64_t)shape_id >= sc->shape_count || ent_mat[i] < 0 || (uint32_t)ent_mat[i] >= sc->material_count)
+                return fail(IGB200_E_INVALID, "entity %zu: shape %d / material %d out of range", i, shape_id, ent_mat[i]);
+        }
+        IGB_CUDA(dev->d_shape_info.upload(info.data(), info.size(), dev->stream));
+        IGB_CUDA(dev->d_shape_data.upload(reinterpret_cast<const float*>(sc->shape_data), (sc->shape_bytes + 3) / 4, dev->stream));
+        IGB_CUDA(dev->d_entities.upload(sc->entities, ent_mat.size() * 36, dev->stream));
+        IGB_CUDA(dev->d_ent_mat.upload(ent_mat.data(), ent_mat.size(), dev->stream));
+        dev->entity_count         = ent_mat.size();
+        dev->scene_material_count = sc->material_count;
+        std::memcpy(dev->scene_bbox, sc->scene_bbox, sizeof(dev->scene_bbox));
+    }
     IGB_CUDA(cudaStreamSynchronize(dev->stream));
 
     dev->view.nodes      = dev->nodes.ptr;
@@ -415,6 +480,247 @@ int igb200_get_bvh_info(igb200_device* dev, uint64_t* node_bytes, uint64_t* tri_
     if (tri_bytes) *tri_bytes = dev->tri_bytes;
     if (leaf_bytes) *leaf_bytes = dev->leaf_bytes;
     if (max_depth) *max_depth = dev->max_depth;
+    return IGB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Wavefront path tracing
+// ---------------------------------------------------------------------------------------------------------
+int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
+{
+    if (!dev || !sh) return fail(IGB200_E_INVALID, "igb200_assign_shading: NULL argument");
+    if (!dev->has_scene) return fail(IGB200_E_STATE, "igb200_assign_shading: no scene assigned");
+    if ((sh->bsdf_count && !sh->bsdfs) || (sh->material_count && !sh->materials) || (sh->infinite_light_count && !sh->infinite_lights) ||
+        (sh->finite_light_count && !sh->finite_lights))
+        return fail(IGB200_E_INVALID, "igb200_assign_shading: table pointer is NULL");
+    if (sh->material_count < dev->scene_material_count)
+        return fail(IGB200_E_INVALID, "igb200_assign_shading: %llu material rows for %u scene materials",
+                    (unsigned long long)sh->material_count, dev->scene_material_count);
+    if (sh->material_count + 1 > igb::kWaveMaxBins) return fail(IGB200_E_UNSUPPORTED, "more than %u materials", igb::kWaveMaxBins - 1);
+    if (dev->entity_count == 0 && dev->view.leaf_count != 0)
+        return fail(IGB200_E_STATE, "igb200_assign_shading: the scene was assigned without an entity table");
+    for (uint64_t i = 0; i < sh->material_count; ++i) {
+        const igb200_material& m = sh->materials[i];
+        if (m.bsdf < 0 || (uint64_t)m.bsdf >= sh->bsdf_count) return fail(IGB200_E_INVALID, "material %llu: bsdf %d out of range", (unsigned long long)i, m.bsdf);
+        if (m.light >= (int64_t)sh->finite_light_count) return fail(IGB200_E_INVALID, "material %llu: light %d out of range", (unsigned long long)i, m.light);
+    }
+    for (uint64_t i = 0; i < sh->bsdf_count; ++i)
+        if (sh->bsdfs[i].type > IGB200_BSDF_CONDUCTOR) return fail(IGB200_E_UNSUPPORTED, "bsdf %llu: unknown type %u", (unsigned long long)i, sh->bsdfs[i].type);
+    for (int t = 0; t < 2; ++t) {
+        const igb200_light* ls = t ? sh->finite_lights : sh->infinite_lights;
+        const uint64_t      n  = t ? sh->finite_light_count : sh->infinite_light_count;
+        for (uint64_t i = 0; i < n; ++i) {
+            const bool inf = ls[i].type == IGB200_LIGHT_ENV || ls[i].type == IGB200_LIGHT_DIRECTIONAL;
+            if (ls[i].type > IGB200_LIGHT_DIRECTIONAL || inf != (t == 0))
+                return fail(IGB200_E_INVALID, "%s light %llu has type %u", t ? "finite" : "infinite", (unsigned long long)i, ls[i].type);
+            if ((ls[i].type == IGB200_LIGHT_AREA_SHAPE || ls[i].type == IGB200_LIGHT_AREA_PLANE) &&
+                (ls[i].entity < 0 || (uint64_t)ls[i].entity >= dev->entity_count))
+                return fail(IGB200_E_INVALID, "area light %llu: entity %d out of range", (unsigned long long)i, ls[i].entity);
+        }
+    }
+    if (sh->technique.type > IGB200_TECH_DEBUG) return fail(IGB200_E_UNSUPPORTED, "unknown technique %u", sh->technique.type);
+    IGB_CUDA(cudaSetDevice(dev->ordinal));
+    IGB_CUDA(dev->d_bsdfs.upload(sh->bsdfs, sh->bsdf_count, dev->stream));
+    IGB_CUDA(dev->d_materials.upload(sh->materials, sh->material_count, dev->stream));
+    IGB_CUDA(dev->d_inf_lights.upload(sh->infinite_lights, sh->infinite_light_count, dev->stream));
+    IGB_CUDA(dev->d_fin_lights.upload(sh->finite_lights, sh->finite_light_count, dev->stream));
+    IGB_CUDA(cudaStreamSynchronize(dev->stream));
+    igb::shade::ShadeScene& s = dev->shade;
+    s.entities   = dev->d_entities.ptr;
+    s.shape_data = dev->d_shape_data.ptr;
+    s.shape_info = dev->d_shape_info.ptr;
+    s.bsdfs      = dev->d_bsdfs.ptr;
+    s.materials  = dev->d_materials.ptr;
+    s.inf_lights = dev->d_inf_lights.ptr;
+    s.fin_lights = dev->d_fin_lights.ptr;
+    s.n_inf      = (int32_t)sh->infinite_light_count;
+    s.n_fin      = (int32_t)sh->finite_light_count;
+    s.n_mat      = (int32_t)sh->material_count;
+    s.n_ent      = (int32_t)dev->entity_count;
+    s.cam        = sh->camera;
+    s.tech       = sh->technique;
+    {
+        // bbox_radius(scene_bbox) * 1.01 with vec3_len = sqrt of the fma-chain dot (core/bbox.art:24, vector.art:99)
+        const float* b = dev->scene_bbox;
+        const float  x = b[3] - b[0], y = b[4] - b[1], z = b[5] - b[2];
+        s.scene_radius = std::sqrt(std::fmaf(x, x, std::fmaf(y, y, z * z))) / 2 * 1.01f;
+    }
+    dev->has_shading = true;
+    return IGB200_OK;
+}
+
+static int ensure_film(igb200_device* dev, uint32_t w, uint32_t h)
+{
+    if (dev->film_w == w && dev->film_h == h && dev->d_film.ptr) return IGB200_OK;
+    const size_t n = (size_t)w * h * 3;
+    IGB_CUDA(dev->d_film.ensure(n));
+    if (dev->h_film) { cudaFreeHost(dev->h_film); dev->h_film = nullptr; }
+    IGB_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&dev->h_film), std::max<size_t>(n, 1) * sizeof(float), cudaHostAllocDefault));
+    IGB_CUDA(cudaMemsetAsync(dev->d_film.ptr, 0, n * sizeof(float), dev->stream));
+    dev->film_w = w; dev->film_h = h;
+    dev->iterations  = 0;
+    dev->film_mapped = false;
+    return IGB200_OK;
+}
+
+static int ensure_wave(igb200_device* dev)
+{
+    if (dev->wave_capacity) return IGB200_OK;
+    uint32_t cap = 1u << 20; // the reference's GPU stream capacity (mapping_gpu.art:1125)
+    if (const char* e = std::getenv("IGB200_WAVE_CAPACITY")) cap = (uint32_t)std::max(1024l, std::atol(e));
+    if (const char* e = std::getenv("IGB200_WAVE_SORT")) dev->wave_sort = std::atoi(e) != 0;
+    for (int b = 0; b < 2; ++b) {
+        for (int k = 0; k < 3; ++k) IGB_CUDA(dev->w_f4[b][k].ensure(cap));
+        for (int k = 0; k < 2; ++k) IGB_CUDA(dev->w_u4[b][k].ensure(cap));
+        for (int k = 0; k < 2; ++k) IGB_CUDA(dev->w_f1[b][k].ensure(cap));
+        igb::PathStream& s = dev->wave.stream[b];
+        s.org_tmin = dev->w_f4[b][0].ptr; s.dir_tmax = dev->w_f4[b][1].ptr; s.contrib_invpdf = dev->w_f4[b][2].ptr;
+        s.meta = dev->w_u4[b][0].ptr; s.hit0 = dev->w_u4[b][1].ptr;
+        s.eta = dev->w_f1[b][0].ptr; s.hit_v = dev->w_f1[b][1].ptr;
+    }
+    for (int k = 0; k < 3; ++k) IGB_CUDA(dev->w_sh_f4[k].ensure(cap));
+    dev->wave.shadow = igb::ShadowStream{ dev->w_sh_f4[0].ptr, dev->w_sh_f4[1].ptr, dev->w_sh_f4[2].ptr };
+    IGB_CUDA(dev->w_keys.ensure(cap));
+    IGB_CUDA(dev->w_sorted.ensure(cap));
+    IGB_CUDA(dev->w_ctl.ensure(1));
+    IGB_CUDA(cudaMemset(dev->w_ctl.ptr, 0, sizeof(igb::WaveControl)));
+    IGB_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&dev->h_done), sizeof(uint32_t), cudaHostAllocMapped));
+    *dev->h_done = 0;
+    uint32_t* d_alias = nullptr;
+    IGB_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d_alias), dev->h_done, 0));
+    dev->wave.host_done = d_alias;
+    dev->wave.keys      = dev->w_keys.ptr;
+    dev->wave.sorted    = dev->w_sorted.ptr;
+    dev->wave.ctl       = dev->w_ctl.ptr;
+    for (cudaEvent_t& e : dev->round_ev) IGB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    dev->wave_capacity = cap;
+    return IGB200_OK;
+}
+
+int igb200_render(igb200_device* dev, const igb200_render_settings* rs)
+{
+    if (!dev || !rs) return fail(IGB200_E_INVALID, "igb200_render: NULL argument");
+    if (!dev->has_scene || !dev->has_shading) return fail(IGB200_E_STATE, "igb200_render: scene and shading must be assigned first");
+    const bool     list = rs->rays != nullptr;
+    const uint64_t w = list ? rs->ray_count : rs->width, h = list ? 1 : rs->height;
+    if (w == 0 || h == 0 || rs->spi == 0) return fail(IGB200_E_INVALID, "igb200_render: empty film or spi == 0");
+    if (w * h * rs->spi >= 0xFFFF0000ull) return fail(IGB200_E_UNSUPPORTED, "igb200_render: more than 2^32 samples per iteration");
+    IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (int rc = ensure_wave(dev)) return rc;
+    if (int rc = ensure_film(dev, (uint32_t)w, (uint32_t)h)) return rc;
+    cudaStream_t st = dev->stream;
+
+    igb::WaveSettings set{};
+    set.spi = rs->spi; set.width = (uint32_t)w; set.height = (uint32_t)h;
+    set.iter = rs->iteration; set.frame = rs->frame; set.seed = rs->user_seed;
+    set.inv_spi  = 1.0f / (float)rs->spi;
+    set.capacity = dev->wave_capacity;
+    if (list) {
+        // Interface::loadRayList (Device.cpp:573-611): upload + normalise
+        IGB_CUDA(dev->d_list_rays.ensure(2 * rs->ray_count));
+        IGB_CUDA(cudaMemcpyAsync(dev->d_list_rays.ptr, rs->rays, rs->ray_count * sizeof(igb200_ray), cudaMemcpyHostToDevice, st));
+        IGB_CUDA(igb::launch_normalize_rays(dev->d_list_rays.ptr, rs->ray_count, st));
+        set.list_rays = dev->d_list_rays.ptr;
+    }
+    dev->wave.film    = dev->d_film.ptr;
+    dev->wave.ent_mat = dev->d_ent_mat.ptr;
+
+    IGB_CUDA(cudaEventRecord(dev->ev0, st));
+    IGB_CUDA(igb::launch_wave_reset(dev->wave, (uint32_t)(w * h * rs->spi), st));
+    IGB_CUDA(cudaStreamSynchronize(st)); // the mapped flag is cleared before the host starts polling it
+    // The host runs ahead of the device by up to kAhead round pairs and polls the mapped `done` flag; rounds
+    // enqueued after the queue has drained are no-ops (every kernel reads a zero count).
+    constexpr int kAhead = 3;
+    uint64_t      pairs  = 0;
+    const uint64_t max_pairs = 1ull << 24;
+    for (; pairs < max_pairs; ++pairs) {
+        IGB_CUDA(igb::launch_wave_round(dev->view, dev->shade, dev->wave, set, 0, dev->wave_sort, dev->sm_count, st));
+        IGB_CUDA(igb::launch_wave_round(dev->view, dev->shade, dev->wave, set, 1, dev->wave_sort, dev->sm_count, st));
+        IGB_CUDA(cudaEventRecord(dev->round_ev[pairs % 4], st));
+        if (pairs >= (uint64_t)kAhead) IGB_CUDA(cudaEventSynchronize(dev->round_ev[(pairs - kAhead) % 4]));
+        if (*reinterpret_cast<volatile uint32_t*>(dev->h_done)) { ++pairs; break; }
+    }
+    IGB_CUDA(cudaEventRecord(dev->ev1, st));
+    IGB_CUDA(cudaStreamSynchronize(st));
+    if (!*reinterpret_cast<volatile uint32_t*>(dev->h_done)) return fail(IGB200_E_CUDA, "igb200_render: wavefront did not drain");
+    igb::WaveControl ctl;
+    IGB_CUDA(cudaMemcpy(&ctl, dev->w_ctl.ptr, offsetof(igb::WaveControl, bins), cudaMemcpyDeviceToHost));
+    dev->render_stats.camera_rays     = ctl.camera_rays;
+    dev->render_stats.bounce_rays     = ctl.bounce_rays;
+    dev->render_stats.shadow_rays     = ctl.shadow_rays;
+    dev->render_stats.rounds          = ctl.rounds;
+    dev->render_stats.kernel_launches = 1 + pairs * 2 * (igb::kWaveLaunchesPerRound - (dev->wave_sort ? 0 : 1)) + (list ? 1 : 0);
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, dev->ev0, dev->ev1);
+    dev->render_stats.device_ms = ms;
+    dev->iterations += 1; // Interface::present, Device.cpp:1460-1472
+    dev->film_mapped = false;
+    return IGB200_OK;
+}
+
+int igb200_framebuffer(igb200_device* dev, const char* name, int device, float** data, uint64_t* iterations)
+{
+    if (!dev || !data) return fail(IGB200_E_INVALID, "igb200_framebuffer: NULL argument");
+    *data = nullptr;
+    if (iterations) *iterations = 0;
+    if (name && name[0] != '\0' && std::strcmp(name, "Color") != 0)
+        return fail(IGB200_E_INVALID, "igb200_framebuffer: unknown AOV '%s'", name); // Device.cpp:1303-1305
+    if (!dev->d_film.ptr) return fail(IGB200_E_STATE, "igb200_framebuffer: nothing rendered yet");
+    IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (iterations) *iterations = dev->iterations;
+    if (device) {
+        *data = dev->d_film.ptr;
+        return IGB200_OK;
+    }
+    if (!dev->film_mapped) { // lazy D2H once per iteration (the `Mapped` flag, Device.cpp:1330-1363)
+        IGB_CUDA(cudaMemcpyAsync(dev->h_film, dev->d_film.ptr, (size_t)dev->film_w * dev->film_h * 3 * sizeof(float),
+                                 cudaMemcpyDeviceToHost, dev->stream));
+        IGB_CUDA(cudaStreamSynchronize(dev->stream));
+        dev->film_mapped = true;
+    }
+    *data = dev->h_film;
+    return IGB200_OK;
+}
+
+int igb200_clear_framebuffer(igb200_device* dev)
+{
+    if (!dev) return fail(IGB200_E_INVALID, "igb200_clear_framebuffer: NULL device");
+    IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (dev->d_film.ptr) {
+        IGB_CUDA(cudaMemsetAsync(dev->d_film.ptr, 0, (size_t)dev->film_w * dev->film_h * 3 * sizeof(float), dev->stream));
+        IGB_CUDA(cudaStreamSynchronize(dev->stream));
+    }
+    dev->iterations  = 0;
+    dev->film_mapped = false;
+    return IGB200_OK;
+}
+
+int igb200_resize(igb200_device* dev, uint32_t width, uint32_t height)
+{
+    if (!dev) return fail(IGB200_E_INVALID, "igb200_resize: NULL device");
+    if (width == 0 || height == 0) return fail(IGB200_E_INVALID, "igb200_resize: empty film");
+    IGB_CUDA(cudaSetDevice(dev->ordinal));
+    dev->film_w = dev->film_h = 0; // force re-allocation + zero (Device.cpp:306-313)
+    return ensure_film(dev, width, height);
+}
+
+int igb200_set_framebuffer(igb200_device* dev, const float* d_src, uint64_t count, uint64_t iterations)
+{
+    if (!dev || !d_src) return fail(IGB200_E_INVALID, "igb200_set_framebuffer: NULL argument");
+    if (!dev->d_film.ptr || count != (uint64_t)dev->film_w * dev->film_h * 3)
+        return fail(IGB200_E_INVALID, "igb200_set_framebuffer: size does not match the film");
+    IGB_CUDA(cudaSetDevice(dev->ordinal));
+    IGB_CUDA(igb::launch_film_combine(dev->d_film.ptr, d_src, count, true, dev->stream));
+    IGB_CUDA(cudaStreamSynchronize(dev->stream));
+    dev->iterations  = iterations;
+    dev->film_mapped = false;
+    return IGB200_OK;
+}
+
+int igb200_get_render_stats(igb200_device* dev, igb200_render_stats* out)
+{
+    if (!dev || !out) return fail(IGB200_E_INVALID, "igb200_get_render_stats: NULL argument");
+    *out = dev->render_stats;
     return IGB200_OK;
 }
 

@@ -1,0 +1,421 @@
+// trace_core.cuh -- closest-hit / any-hit ray traversal for sm_100a (kernel template shared by the igtrace
+// ray-list path, trace.cu, and the wavefront path tracer, wavefront.cu).
+//
+// Replaces the reference's K2/K3 kernels: gpu_traverse_primary / gpu_traverse_secondary
+// (src/artic/driver/mapping_gpu.art:45-112) -> gpu_traverse_scene / gpu_traverse_prim / gpu_traverse_helper
+// (src/artic/traversal/mapping_gpu.art:73-226), which walk a binary Node2 tree with a 64-entry local stack.
+// Design here: one ray per lane over a compressed 8-wide BVH (80 B nodes, five 16 B loads), octant-ordered
+// child visiting driven by a bit mask, a small (node-group, hit-mask) stack, and ONE unified loop for the
+// two-level scene (entity level and triangle level share the node step; only the leaf step differs).
+//
+// Arithmetic contract shared with oracle/ (bit-exact t,u,v for the same triangle):
+//   * ray transform: mat3x4_mul = vec4_dot fma chains (src/artic/core/matrix.art:95-98, vector.art:100)
+//   * Moeller-Trumbore: intersect_ray_tri_mt_gen (src/artic/traversal/intersection.art:71-101) with
+//     vec3_dot = fma chain (vector.art:99) and vec3_cross un-fused (vector.art:106-109)
+//   * this file is compiled with -fmad=false; every fused op is an explicit __fmaf_rn.
+// Box tests are conservative (quantised boxes + ulp slack) and carry no parity requirement.
+#pragma once
+#include "trace.cuh"
+
+#include "../../include/ignis_b200.h"
+
+namespace igb {
+namespace core {
+
+constexpr float    kFltEps   = 1.1920928955078125e-7f;
+constexpr float    kFltMax   = 3.402823466e+38f;
+constexpr uint32_t kSentinel = 0xFFFFFFFFu;
+constexpr int      kBlock       = 128;
+constexpr int      kBlocksPerSM = 8;
+constexpr int      kChunk       = 64; // rays a warp claims per atomic on the global work counter
+
+struct Vec3 { float x, y, z; };
+
+__device__ __forceinline__ float dot3(Vec3 a, Vec3 b) { return __fmaf_rn(a.x, b.x, __fmaf_rn(a.y, b.y, a.z * b.z)); }
+__device__ __forceinline__ Vec3  cross3(Vec3 a, Vec3 b)
+{
+    return Vec3{ a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x };
+}
+__device__ __forceinline__ float dot4(float ax, float ay, float az, float aw, float bx, float by, float bz, float bw)
+{
+    return __fmaf_rn(ax, bx, __fmaf_rn(ay, by, __fmaf_rn(az, bz, aw * bw)));
+}
+
+// Box-test reciprocal: |d| clamped away from zero so 0 * idir never produces NaN.
+__device__ __forceinline__ float box_rcp(float d)
+{
+    const float eps = 8.271806125530277e-25f; // 2^-80
+    return 1.0f / (fabsf(d) > eps ? d : copysignf(eps, d));
+}
+
+__device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x)
+{
+    uint32_t r;
+    asm("prmt.b32 %0, %1, 0x0, 0x0000BA98;" : "=r"(r) : "r"(x));
+    return r;
+}
+// byte j of w as a float in [0, 255]
+__device__ __forceinline__ float byte_to_float(uint32_t w, int j)
+{
+    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7540u | (uint32_t)j)) - 8388608.0f;
+}
+__device__ __forceinline__ uint32_t extract_byte(uint32_t w, int j) { return (w >> (8 * j)) & 0xFFu; }
+
+struct TravRay {
+    Vec3     org, dir;    // current space (world or object); dir un-normalised in object space
+    Vec3     idir;        // box-test reciprocals
+    uint32_t octinv4;     // (7 - octant) replicated to four bytes
+};
+
+__device__ __forceinline__ void setup_trav_ray(TravRay& r)
+{
+    r.idir = Vec3{ box_rcp(r.dir.x), box_rcp(r.dir.y), box_rcp(r.dir.z) };
+    const uint32_t oct = (r.dir.x < 0.0f ? 4u : 0u) | (r.dir.y < 0.0f ? 2u : 0u) | (r.dir.z < 0.0f ? 1u : 0u);
+    r.octinv4          = (7u - oct) * 0x01010101u;
+}
+
+// Tests the 8 quantised child boxes of one node; returns the (octant-ordered) hit mask:
+// bits 31..24 inner children, bits 23..0 primitives of leaf children.
+__device__ __forceinline__ uint32_t intersect_children(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
+                                                       const uint4 n4, const TravRay& r, float tmin, float tmax)
+{
+    const uint32_t e  = n0.w;
+    const float    sx = __uint_as_float((e & 0xFFu) << 23) * r.idir.x;
+    const float    sy = __uint_as_float(((e >> 8) & 0xFFu) << 23) * r.idir.y;
+    const float    sz = __uint_as_float(((e >> 16) & 0xFFu) << 23) * r.idir.z;
+    const float    ox = (__uint_as_float(n0.x) - r.org.x) * r.idir.x;
+    const float    oy = (__uint_as_float(n0.y) - r.org.y) * r.idir.y;
+    const float    oz = (__uint_as_float(n0.z) - r.org.z) * r.idir.z;
+    const bool     nx = r.dir.x < 0.0f, ny = r.dir.y < 0.0f, nz = r.dir.z < 0.0f;
+
+    uint32_t hitmask = 0;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const uint32_t meta4       = i ? n1.w : n1.z;
+        const uint32_t is_inner4   = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
+        const uint32_t bit_index4  = (meta4 ^ (r.octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
+        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+
+        const uint32_t qlox = i ? n2.y : n2.x, qloy = i ? n2.w : n2.z, qloz = i ? n3.y : n3.x;
+        const uint32_t qhix = i ? n3.w : n3.z, qhiy = i ? n4.y : n4.x, qhiz = i ? n4.w : n4.z;
+        const uint32_t nearx = nx ? qhix : qlox, farx = nx ? qlox : qhix;
+        const uint32_t neary = ny ? qhiy : qloy, fary = ny ? qloy : qhiy;
+        const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float t0x = __fmaf_rn(byte_to_float(nearx, j), sx, ox);
+            const float t0y = __fmaf_rn(byte_to_float(neary, j), sy, oy);
+            const float t0z = __fmaf_rn(byte_to_float(nearz, j), sz, oz);
+            const float t1x = __fmaf_rn(byte_to_float(farx, j), sx, ox);
+            const float t1y = __fmaf_rn(byte_to_float(fary, j), sy, oy);
+            const float t1z = __fmaf_rn(byte_to_float(farz, j), sz, oz);
+            const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
+            // 2-ulp slack on the exit distance: the box test must never reject what the triangle test accepts
+            const float cmax = fminf(fminf(fminf(t1x, t1y), t1z) * 1.0000004f, tmax);
+            if (cmin <= cmax) hitmask |= extract_byte(child_bits4, j) << extract_byte(bit_index4, j);
+        }
+    }
+    return hitmask;
+}
+
+struct HitRec {
+    float   t, u, v;
+    int32_t prim, ent;
+};
+
+// Deterministic replacement rule.  The reference accepts `t <= tmax` (later equal-t hits replace earlier
+// ones, src/artic/traversal/mapping_cpu.art:469), which makes exact ties depend on tree order; here ties
+// resolve to the smallest (entity, primitive) so the result is independent of traversal order.
+__device__ __forceinline__ bool accepts(const HitRec& h, float t, int32_t ent, int32_t prim)
+{
+    if (t < h.t) return true;
+    if (t > h.t) return false;                 // also rejects NaN
+    if (h.prim < 0) return true;               // t == initial tmax
+    return (ent < h.ent) || (ent == h.ent && prim < h.prim);
+}
+
+// intersect_ray_tri_mt_gen (intersection.art:71-101), no back-face culling, Tri1 record (trimesh.art:146-170).
+__device__ __forceinline__ void intersect_triangle(const float4 a, const float4 b, const float4 c4, const TravRay& r,
+                                                   float tmin, int32_t ent, HitRec& hit)
+{
+    const Vec3  v0{ a.x, a.y, a.z }, e1{ b.x, b.y, b.z }, e2{ c4.x, c4.y, c4.z };
+    const Vec3  n   = cross3(e1, e2);
+    const Vec3  c   = Vec3{ v0.x - r.org.x, v0.y - r.org.y, v0.z - r.org.z };
+    const Vec3  rr  = cross3(r.dir, c);
+    const float det = dot3(n, r.dir);
+    const float inv = __frcp_rn(det); // == IEEE 1.0f / det
+    const float u   = dot3(rr, e2) * inv;
+    const float v   = dot3(rr, e1) * inv;
+    const float w   = 1.0f - u - v;
+    if (u >= -kFltEps && v >= -kFltEps && w >= -kFltEps) {
+        const float   t    = dot3(c, n) * inv;
+        const int32_t prim = __float_as_int(c4.w) & 0x7FFFFFFF;
+        if (t >= tmin && accepts(hit, t, ent, prim)) {
+            hit.t    = t;
+            hit.u    = u > 0.0f ? u : 0.0f;
+            hit.v    = v > 0.0f ? v : 0.0f;
+            hit.prim = prim;
+            hit.ent  = ent;
+        }
+    }
+}
+
+// intersect_sphere (src/artic/shapes/sphere.art:104-132) on the object-space ray.
+__device__ __forceinline__ void intersect_sphere(const float4 sph, const TravRay& r, float tmin, int32_t ent, HitRec& hit)
+{
+    const float pi = 3.14159265359f;
+    const Vec3  L{ r.org.x - sph.x, r.org.y - sph.y, r.org.z - sph.z };
+    const float S  = -dot3(L, r.dir);
+    const float D2 = dot3(r.dir, r.dir);
+    const float L2 = dot3(L, L);
+    const float R2 = sph.w * sph.w * D2;
+    const float M2 = L2 * D2 - S * S;
+    if ((S < 0.0f) || (M2 > R2)) return;
+    const float Q   = __fsqrt_rn(R2 - M2);
+    const float t0_ = __fdiv_rn(S - Q, D2);
+    const float t1_ = __fdiv_rn(S + Q, D2);
+    const float t0  = t0_ > t1_ ? t1_ : t0_;
+    const float t1  = t0_ > t1_ ? t0_ : t1_;
+    const float tm  = t0 < tmin ? t1 : t0;
+    if (tm >= tmin && tm <= hit.t && accepts(hit, tm, ent, 0)) {
+        const float ir    = __frcp_rn(sph.w);
+        const Vec3  d{ (L.x + r.dir.x * tm) * ir, (L.y + r.dir.y * tm) * ir, (L.z + r.dir.z * tm) * ir };
+        const float theta = acosf(d.z);
+        float       phi   = atan2f(-d.x, d.y);
+        if (phi < 0.0f) phi += 2.0f * pi;
+        hit.t    = tm;
+        hit.u    = phi / (2.0f * pi);
+        hit.v    = theta / pi;
+        hit.prim = 0;
+        hit.ent  = ent;
+    }
+}
+
+// Persistent kernel: every lane owns one ray at a time and pulls the next ray from a warp-local pool
+// (refilled in chunks from one global counter) the moment its ray finishes, so lanes never idle while the
+// longest ray of the warp completes.  Each trip of the outer loop performs at most one node step, one
+// primitive batch and one pop per lane, which keeps lanes in different phases converged on the same code.
+//
+// IO policy (how rays come in and results go out):
+//   uint32_t count() const                                         number of rays (may read device memory)
+//   bool     load(i, org, dir, tmin, tmax, flags) const            false = slot holds no ray
+//   void     store(i, hit, s_bins)                                 ray i finished (hit.prim < 0: miss, hit.t = tmax)
+//   static constexpr bool kBins                                    block-level key histogram in shared memory
+//   uint32_t bin_count() const; uint32_t* global_bins() const; void finalize_last_block() const   (only when kBins)
+constexpr int kMaxSmemBins = 512;
+
+template <typename IO, bool ANY_HIT, bool STATS>
+__global__ void __launch_bounds__(kBlock, kBlocksPerSM)
+trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ counters, uint32_t* __restrict__ work)
+{
+    __shared__ uint32_t s_bins[IO::kBins ? kMaxSmemBins : 1];
+    if (IO::kBins) {
+        for (uint32_t b = threadIdx.x; b < min(io.bin_count(), (uint32_t)kMaxSmemBins); b += blockDim.x) s_bins[b] = 0u;
+        __syncthreads();
+    }
+    const uint32_t n = io.count();
+    uint32_t       ray_flags = 0;
+    const uint32_t lane    = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    uint32_t       c_nodes = 0, c_tris = 0, c_ents = 0;
+
+    uint32_t pool_next = 0, pool_end = 0; // warp-uniform
+    bool     exhausted = false;           // warp-uniform
+    bool     active    = false;
+
+    uint32_t ray_id = 0;
+    float    tmin   = 0.0f;
+    TravRay  ray;
+    HitRec   hit;
+    uint2    stack[kStackSize];
+    int      sp      = 0;
+    uint2    ngroup  = make_uint2(0u, 0u);
+    uint2    tgroup  = make_uint2(0u, 0u);
+    bool     in_blas = false;
+    int32_t  cur_ent = -1;
+
+    for (;;) {
+        const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !active);
+        if (idle != 0u) {
+            if (!exhausted) {
+                if (pool_next == pool_end) {
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(work, (uint32_t)kChunk);
+                    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                    if (base >= n) {
+                        exhausted = true;
+                    } else {
+                        pool_next = base;
+                        pool_end  = min(base + (uint32_t)kChunk, n);
+                    }
+                }
+                const uint32_t avail = pool_end - pool_next;
+                const uint32_t rank  = __popc(idle & lt_mask);
+                if (!active && rank < avail) {
+                    ray_id     = pool_next + rank;
+                    float tmax = 0.0f;
+                    if (io.load(ray_id, ray.org, ray.dir, tmin, tmax, ray_flags)) {
+                        setup_trav_ray(ray);
+                        hit     = HitRec{ tmax, 0.0f, 0.0f, -1, -1 };
+                        sp      = 0;
+                        ngroup  = make_uint2(0u, 0x80000000u);
+                        tgroup  = make_uint2(0u, 0u);
+                        in_blas = false;
+                        active  = true;
+                    }
+                }
+                pool_next += min(avail, (uint32_t)__popc(idle));
+            } else if (idle == 0xFFFFFFFFu) {
+                break;
+            }
+        }
+
+        if (active) {
+            if (ngroup.y > 0x00FFFFFFu) {
+                const uint32_t hits            = ngroup.y;
+                const uint32_t imask           = ngroup.y & 0xFFu;
+                const uint32_t child_bit_index = 31u - (uint32_t)__clz(hits);
+                ngroup.y &= ~(1u << child_bit_index);
+                if (ngroup.y > 0x00FFFFFFu) stack[sp++] = ngroup;
+
+                const uint32_t slot_index     = (child_bit_index - 24u) ^ (ray.octinv4 & 0xFFu);
+                const uint32_t relative_index = __popc(imask & ~(0xFFFFFFFFu << slot_index));
+                const uint4*   np             = sc.nodes + 5 * (size_t)(ngroup.x + relative_index);
+                const uint4    n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3),
+                            n4 = __ldg(np + 4);
+                if (STATS) c_nodes++;
+                const uint32_t hitmask = intersect_children(n0, n1, n2, n3, n4, ray, tmin, hit.t);
+                ngroup                 = make_uint2(n1.x, (hitmask & 0xFF000000u) | (n0.w >> 24));
+                tgroup                 = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
+            } else {
+                tgroup = ngroup;
+                ngroup = make_uint2(0u, 0u);
+            }
+
+            while (tgroup.y != 0u) {
+                const uint32_t idx = 31u - (uint32_t)__clz(tgroup.y);
+                tgroup.y &= ~(1u << idx);
+                if (in_blas) {
+                    const float4* tp = sc.tris + 3 * (size_t)(tgroup.x + idx);
+                    const float4  a = __ldg(tp + 0), b = __ldg(tp + 1), c = __ldg(tp + 2);
+                    if (STATS) c_tris++;
+                    intersect_triangle(a, b, c, ray, tmin, cur_ent, hit);
+                    if (ANY_HIT && hit.prim >= 0) break;
+                } else {
+                    // Entity leaf step: gpu_traverse_scene::scene_handle (traversal/mapping_gpu.art:196-222)
+                    const float4*  lp = sc.leaves + 6 * (size_t)(tgroup.x + idx);
+                    const float4   l0 = __ldg(lp + 0), l1 = __ldg(lp + 1), l5 = __ldg(lp + 5);
+                    const uint32_t leaf_flags = __float_as_uint(l5.x);
+                    // check_ray_visibility (traversal/ray.art:51)
+                    if ((ray_flags & 0xFu) != ((ray_flags & leaf_flags) & 0xFu)) continue;
+                    // intersect_ray_box_single_section on the exact leaf box + `tmin <= hit.distance`
+                    const float t0x = (l0.x - ray.org.x) * ray.idir.x, t1x = (l1.x - ray.org.x) * ray.idir.x;
+                    const float t0y = (l0.y - ray.org.y) * ray.idir.y, t1y = (l1.y - ray.org.y) * ray.idir.y;
+                    const float t0z = (l0.z - ray.org.z) * ray.idir.z, t1z = (l1.z - ray.org.z) * ray.idir.z;
+                    const float entry = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tmin));
+                    const float exit_ = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z)) * 1.0000004f;
+                    if (!(entry <= fminf(exit_, hit.t))) continue;
+
+                    const float4 l2 = __ldg(lp + 2), l3 = __ldg(lp + 3), l4 = __ldg(lp + 4);
+                    if (STATS) c_ents++;
+                    cur_ent              = __float_as_int(l0.w) & 0x7FFFFFFF;
+                    const ShapeRef shape = sc.shapes[__float_as_int(l1.w)];
+                    // transform_ray (traversal/ray.art:56-59): matrix columns l2.xyz | l2.w l3.xy | l3.zw l4.x | l4.yzw
+                    TravRay local;
+                    local.org = Vec3{ dot4(l2.x, l2.w, l3.z, l4.y, ray.org.x, ray.org.y, ray.org.z, 1.0f),
+                                      dot4(l2.y, l3.x, l3.w, l4.z, ray.org.x, ray.org.y, ray.org.z, 1.0f),
+                                      dot4(l2.z, l3.y, l4.x, l4.w, ray.org.x, ray.org.y, ray.org.z, 1.0f) };
+                    local.dir = Vec3{ dot4(l2.x, l2.w, l3.z, l4.y, ray.dir.x, ray.dir.y, ray.dir.z, 0.0f),
+                                      dot4(l2.y, l3.x, l3.w, l4.z, ray.dir.x, ray.dir.y, ray.dir.z, 0.0f),
+                                      dot4(l2.z, l3.y, l4.x, l4.w, ray.dir.x, ray.dir.y, ray.dir.z, 0.0f) };
+                    if (shape.type == IGB200_PRIM_SPHERE) {
+                        intersect_sphere(__ldg(sc.spheres + shape.sphere), local, tmin, cur_ent, hit);
+                        if (ANY_HIT && hit.prim >= 0) break;
+                        continue;
+                    }
+                    // Enter the shape's BVH: park the entity-level state and the world ray under a sentinel.
+                    if (ngroup.y > 0x00FFFFFFu) stack[sp++] = ngroup;
+                    if (tgroup.y != 0u) stack[sp++] = tgroup;
+                    stack[sp++] = make_uint2(__float_as_uint(ray.org.x), __float_as_uint(ray.org.y));
+                    stack[sp++] = make_uint2(__float_as_uint(ray.org.z), __float_as_uint(ray.dir.x));
+                    stack[sp++] = make_uint2(__float_as_uint(ray.dir.y), __float_as_uint(ray.dir.z));
+                    stack[sp++] = make_uint2(kSentinel, 0u);
+                    ray         = local;
+                    setup_trav_ray(ray);
+                    in_blas = true;
+                    ngroup  = make_uint2(shape.root_node, 0x80000000u);
+                    tgroup  = make_uint2(0u, 0u);
+                    break;
+                }
+            }
+
+            bool finished = ANY_HIT && hit.prim >= 0;
+            if (!finished && ngroup.y <= 0x00FFFFFFu) {
+                if (sp == 0) {
+                    finished = true;
+                } else {
+                    ngroup = stack[--sp];
+                    if (ngroup.x == kSentinel) {
+                        // Leave the shape: back to world space.
+                        const uint2 c = stack[--sp], b = stack[--sp], a = stack[--sp];
+                        ray.org = Vec3{ __uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(b.x) };
+                        ray.dir = Vec3{ __uint_as_float(b.y), __uint_as_float(c.x), __uint_as_float(c.y) };
+                        setup_trav_ray(ray);
+                        in_blas = false;
+                        if (sp == 0)
+                            finished = true;
+                        else
+                            ngroup = stack[--sp];
+                    }
+                }
+            }
+            if (finished) {
+                io.store(ray_id, hit, s_bins);
+                active = false;
+            }
+        }
+    }
+
+    if (STATS) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            c_nodes += __shfl_xor_sync(0xFFFFFFFFu, c_nodes, o);
+            c_tris += __shfl_xor_sync(0xFFFFFFFFu, c_tris, o);
+            c_ents += __shfl_xor_sync(0xFFFFFFFFu, c_ents, o);
+        }
+        if (lane == 0) {
+            atomicAdd(&counters->nodes, (unsigned long long)c_nodes);
+            atomicAdd(&counters->tris, (unsigned long long)c_tris);
+            atomicAdd(&counters->ents, (unsigned long long)c_ents);
+        }
+    }
+
+    // Self-resetting work counter: the last block to retire rewinds it for the next launch.
+    __shared__ uint32_t s_last;
+    __syncthreads();
+    if (IO::kBins) {
+        uint32_t* gb = io.global_bins();
+        for (uint32_t b = threadIdx.x; b < min(io.bin_count(), (uint32_t)kMaxSmemBins); b += blockDim.x)
+            if (s_bins[b]) atomicAdd(gb + b, s_bins[b]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const uint32_t done = atomicAdd(work + 1, 1u);
+        s_last              = done == gridDim.x - 1 ? 1u : 0u;
+        if (s_last) {
+            work[0] = 0u;
+            work[1] = 0u;
+            __threadfence();
+        }
+    }
+    if (IO::kBins) {
+        // the last block to retire sees every block's histogram: it turns it into scatter offsets
+        __syncthreads();
+        if (s_last) io.finalize_last_block();
+    }
+}
+
+} // namespace core
+} // namespace igb

@@ -1,0 +1,469 @@
+// wavefront.cu -- kernels of the wavefront path tracer (see wavefront.cuh for the design and the reference rows).
+#include "wavefront.cuh"
+
+#include "shade_tech.cuh"
+
+#include <algorithm>
+
+namespace igb {
+namespace {
+
+using namespace core;
+using namespace shade;
+
+constexpr uint32_t kRayCamera = 0x1u, kRayBounce = 0x4u, kRayShadow = 0x8u; // src/artic/traversal/ray.art:21-25
+
+// ---------------------------------------------------------------------------------------------------------
+// Traversal IO policies (trace_core.cuh)
+// ---------------------------------------------------------------------------------------------------------
+
+// K2, gpu_traverse_primary (driver/mapping_gpu.art:45-68): closest hit over the current primary stream; the
+// sort key (material id of the hit entity, n_mat for a miss) and its histogram are produced here
+// (replaces the reset + count launches of gpu_sort_primary, mapping_gpu.art:431-446).
+struct PrimaryIO {
+    static constexpr bool kBins = true;
+    PathStream     s;
+    uint32_t*      keys;
+    const int32_t* ent_mat;
+    WaveControl*   ctl;
+    uint32_t       n_bins; // n_mat + 1
+    __device__ __forceinline__ uint32_t  count() const { return ctl->n_cur; }
+    __device__ __forceinline__ uint32_t  bin_count() const { return n_bins; }
+    __device__ __forceinline__ uint32_t* global_bins() const { return ctl->bins; }
+    __device__ __forceinline__ bool load(uint32_t i, Vec3& org, Vec3& dir, float& tmin, float& tmax, uint32_t& flags) const
+    {
+        const float4 o = s.org_tmin[i], d = s.dir_tmax[i];
+        org   = Vec3{ o.x, o.y, o.z };
+        dir   = Vec3{ d.x, d.y, d.z };
+        tmin  = o.w;
+        tmax  = d.w;
+        flags = s.meta[i].z;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, const HitRec& hit, uint32_t* s_bins) const
+    {
+        s.hit0[i]  = make_uint4((uint32_t)hit.ent, (uint32_t)hit.prim, __float_as_uint(hit.t), __float_as_uint(hit.u));
+        s.hit_v[i] = hit.v;
+        const uint32_t key = hit.prim >= 0 ? (uint32_t)__ldg(ent_mat + hit.ent) : n_bins - 1u;
+        keys[i]            = key;
+        if (n_bins <= (uint32_t)kMaxSmemBins)
+            atomicAdd(s_bins + key, 1u);
+        else
+            atomicAdd(ctl->bins + key, 1u);
+    }
+    // exclusive scan of the histogram -> scatter offsets (replaces the host-side scan between two blocking
+    // copies, mapping_gpu.art:453-461)
+    __device__ __forceinline__ void finalize_last_block() const
+    {
+        if (threadIdx.x < 32u) {
+            uint32_t carry = 0u;
+            for (uint32_t base = 0; base < n_bins; base += 32u) {
+                const uint32_t b = base + threadIdx.x;
+                const uint32_t v = b < n_bins ? __ldcg(ctl->bins + b) : 0u;
+                uint32_t       x = v;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+                    if ((int)threadIdx.x >= o) x += y;
+                }
+                if (b < n_bins) {
+                    ctl->offsets[b] = carry + x - v;
+                    ctl->cursors[b] = 0u;
+                }
+                carry += __shfl_sync(0xFFFFFFFFu, x, 31);
+            }
+        }
+    }
+};
+
+// K3, gpu_traverse_secondary (driver/mapping_gpu.art:70-112): any hit over the shadow stream; an unoccluded ray
+// splats its contribution (simple shadow handling), make_atomic_accumulator (driver/accumulator.art:4-21).
+struct ShadowIO {
+    static constexpr bool kBins = false;
+    ShadowStream s;
+    WaveControl* ctl;
+    float*       film;
+    float        inv_spi;
+    __device__ __forceinline__ uint32_t  count() const { return ctl->n_shadow; }
+    __device__ __forceinline__ uint32_t  bin_count() const { return 0u; }
+    __device__ __forceinline__ uint32_t* global_bins() const { return nullptr; }
+    __device__ __forceinline__ void      finalize_last_block() const {}
+    __device__ __forceinline__ bool load(uint32_t i, Vec3& org, Vec3& dir, float& tmin, float& tmax, uint32_t& flags) const
+    {
+        const float4 o = s.org_tmin[i], d = s.dir_tmax[i];
+        org   = Vec3{ o.x, o.y, o.z };
+        dir   = Vec3{ d.x, d.y, d.z };
+        tmin  = o.w;
+        tmax  = d.w;
+        flags = kRayShadow;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, const HitRec& hit, uint32_t*) const
+    {
+        if (hit.prim < 0) {
+            const float4 c = s.color_pixel[i];
+            float*       p = film + 3 * (size_t)__float_as_uint(c.w);
+            atomicAdd(p + 0, c.x * inv_spi);
+            atomicAdd(p + 1, c.y * inv_spi);
+            atomicAdd(p + 2, c.z * inv_spi);
+        }
+    }
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// Round control + ray generation
+// ---------------------------------------------------------------------------------------------------------
+
+// Head of the loop body of gpu_trace (driver/mapping_gpu.art:756-767): how many rays to regenerate, stream sizes.
+__global__ void begin_round_kernel(WaveControl* ctl, uint32_t capacity, uint32_t n_bins, uint32_t* host_done)
+{
+    if (threadIdx.x == 0) {
+        const uint32_t n_surv = ctl->n_next;
+        ctl->bounce_rays += n_surv;
+        ctl->shadow_rays += ctl->n_shadow;
+        const uint32_t remaining = ctl->total - ctl->next_id;
+        const uint32_t m         = min(remaining, capacity - n_surv);
+        ctl->gen_base  = n_surv;
+        ctl->gen_first = ctl->next_id;
+        ctl->gen_count = m;
+        ctl->next_id += m;
+        ctl->camera_rays += m;
+        ctl->n_cur    = n_surv + m;
+        ctl->n_next   = 0u;
+        ctl->n_shadow = 0u;
+        if (n_surv + m == 0u) {
+            ctl->done = 1u;
+            *reinterpret_cast<volatile uint32_t*>(host_done) = 1u;
+            __threadfence_system();
+        } else {
+            ctl->rounds += 1u;
+        }
+    }
+    for (uint32_t b = threadIdx.x; b < n_bins; b += blockDim.x) ctl->bins[b] = 0u;
+}
+
+__global__ void reset_kernel(WaveControl* ctl, uint32_t total, uint32_t* host_done)
+{
+    ctl->n_cur = ctl->n_next = ctl->n_shadow = 0u;
+    ctl->gen_base = ctl->gen_count = ctl->gen_first = 0u;
+    ctl->next_id = 0u;
+    ctl->total   = total;
+    ctl->done    = 0u;
+    ctl->rounds  = 0u;
+    ctl->work_primary[0] = ctl->work_primary[1] = ctl->work_shadow[0] = ctl->work_shadow[1] = 0u;
+    ctl->camera_rays = ctl->bounce_rays = ctl->shadow_rays = 0ull;
+    *reinterpret_cast<volatile uint32_t*>(host_done) = 0u;
+    __threadfence_system();
+}
+
+// K1, gpu_generate_rays (driver/mapping_gpu.art:618-667) with make_camera_emitter / make_list_emitter
+// (driver/emitter.art:6-31), make_perspective_camera (camera/perspective.art:29-41), make_uniform_pixel_sampler
+// (sampler/pixel_sampler.art:4-10) and init_pt_raypayload (technique/pathtracer.art:33-38).
+__global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __restrict__ ctl, const PathStream s, const ShadeScene sc,
+                                                       const WaveSettings set)
+{
+    const uint32_t count = ctl->gen_count, base = ctl->gen_base, first = ctl->gen_first;
+    const Vec3     eye{ sc.cam.eye[0], sc.cam.eye[1], sc.cam.eye[2] }, cdir{ sc.cam.dir[0], sc.cam.dir[1], sc.cam.dir[2] },
+        up{ sc.cam.up[0], sc.cam.up[1], sc.cam.up[2] };
+    const Mat3 view{ vnormalize(cross3(cdir, up)), up, cdir };
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
+        const uint32_t id     = first + k;
+        const uint32_t sample = id % set.spi, pixel = id / set.spi;
+        const uint32_t y = pixel / set.width, x = pixel - y * set.width;
+        Rnd            rnd{ create_random_seed(sample, set.iter, set.frame, x, y, set.seed), 1u };
+        Vec3           org, dir;
+        float          tmin, tmax;
+        uint32_t       flags;
+        if (set.list_rays) {
+            const float4 r0 = __ldg(set.list_rays + 2 * (size_t)pixel), r1 = __ldg(set.list_rays + 2 * (size_t)pixel + 1);
+            org   = Vec3{ r0.x, r0.y, r0.z };
+            dir   = Vec3{ r0.w, r1.x, r1.y };
+            tmin  = r1.z;
+            tmax  = r1.w;
+            flags = 0u;
+        } else {
+            const float rx = rnd.next_f32();
+            const float ry = rnd.next_f32();
+            // make_pixelcoord_from_xy (driver/camera.art:21-29)
+            const float nx = __fdiv_rn(2.0f * ((float)x + rx), (float)set.width) - 1.0f;
+            const float ny = 1.0f - __fdiv_rn(2.0f * ((float)y + ry), (float)set.height);
+            org   = eye;
+            dir   = vnormalize(mat3_mul(view, Vec3{ sc.cam.scale[0] * nx, sc.cam.scale[1] * ny, 1.0f }));
+            tmin  = sc.cam.tmin;
+            tmax  = sc.cam.tmax;
+            flags = kRayCamera;
+        }
+        const uint32_t slot    = base + k;
+        s.org_tmin[slot]       = make_float4(org.x, org.y, org.z, tmin);
+        s.dir_tmax[slot]       = make_float4(dir.x, dir.y, dir.z, tmax);
+        s.meta[slot]           = make_uint4(id, rnd.counter, flags, 1u);
+        s.contrib_invpdf[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+        s.eta[slot]            = 1.0f;
+    }
+}
+
+// Scatter step of the sort (gpu_sort_primary, driver/mapping_gpu.art:465-471), on indices only: warp-aggregated
+// cursor bump per key (lanes with equal keys are grouped with match.any).
+__global__ void __launch_bounds__(256) scatter_kernel(WaveControl* __restrict__ ctl, const uint32_t* __restrict__ keys,
+                                                      uint32_t* __restrict__ sorted)
+{
+    const uint32_t n    = ctl->n_cur;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t step = gridDim.x * blockDim.x;
+    for (uint32_t i0 = blockIdx.x * blockDim.x; i0 < n; i0 += step) { // warp-uniform trip count
+        const uint32_t i     = i0 + threadIdx.x;
+        const bool     valid = i < n;
+        const uint32_t key   = valid ? keys[i] : 0xFFFFFFFFu;
+        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, key);
+        const uint32_t lead  = __ffs(peers) - 1u;
+        uint32_t       base  = 0u;
+        if (valid && lane == lead) base = ctl->offsets[key] + atomicAdd(ctl->cursors + key, (uint32_t)__popc(peers));
+        base = __shfl_sync(0xFFFFFFFFu, base, lead);
+        if (valid) sorted[base + __popc(peers & ((1u << lane) - 1u))] = i;
+    }
+}
+
+__global__ void film_combine_kernel(float* film, const float* src, uint64_t count, bool overwrite)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) film[i] = overwrite ? src[i] : film[i] + src[i];
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K7 + K8: hit and miss shading in ONE launch over the material-sorted index list
+// (gpu_hit_shade, one launch per material, driver/mapping_gpu.art:114-205,787-795; gpu_miss_shade :229-266).
+// Per ray: surface element -> material -> on_hit splat -> on_shadow (NEE) -> on_bounce, in the reference's order of
+// RNG use (technique/pathtracer.art:52-200).  Survivors go to the OTHER primary stream at a warp-compacted
+// position (this is the compaction pass, gpu_compact_primary :685-714); shadow rays go to the compacted
+// secondary stream.
+// ---------------------------------------------------------------------------------------------------------
+struct NextState {
+    float4 org_tmin, dir_tmax, contrib_invpdf;
+    uint4  meta;
+    float  eta;
+};
+struct ShadowState {
+    float4 org_tmin, dir_tmax, color_pixel;
+};
+
+__device__ __forceinline__ void splat(float* film, uint32_t pixel, Color c, float inv_spi)
+{
+    float* p = film + 3 * (size_t)pixel;
+    atomicAdd(p + 0, c.r * inv_spi);
+    atomicAdd(p + 1, c.g * inv_spi);
+    atomicAdd(p + 2, c.b * inv_spi);
+}
+
+__device__ __noinline__ void shade_one(const ShadeScene& sc, const DeviceScene& geo, const WaveSettings& set, const PathStream& cur,
+                                       uint32_t i, float* film, bool& alive, NextState& nx, bool& has_shadow, ShadowState& sh)
+{
+    const igb200_technique& tech = sc.tech;
+    const float4 o4 = cur.org_tmin[i], d4 = cur.dir_tmax[i];
+    const uint4  meta = cur.meta[i], h0 = cur.hit0[i];
+    const float4 cp  = cur.contrib_invpdf[i];
+    const Vec3   org{ o4.x, o4.y, o4.z }, dir{ d4.x, d4.y, d4.z };
+    const int32_t ent = (int32_t)h0.x, prim = (int32_t)h0.y;
+    const float   t = __uint_as_float(h0.z), u = __uint_as_float(h0.w);
+    const uint32_t id = meta.x, pixel = id / set.spi, sample = id - pixel * set.spi;
+    const int32_t  depth = (int32_t)meta.w;
+    const Color    contrib0{ cp.x, cp.y, cp.z };
+    const float    inv_pdf = cp.w;
+    const float    offset  = 0.001f;
+
+    if (prim < 0 || ent < 0) {
+        // on_miss (technique/pathtracer.art:134-160): every infinite, non-delta light contributes its emission
+        if (tech.type == IGB200_TECH_PATH) {
+            int   inflights = 0;
+            Color col{ 0.0f, 0.0f, 0.0f };
+            for (int32_t k = 0; k < sc.n_inf; ++k) {
+                const igb200_light& l = sc.inf_lights[k];
+                if (light_infinite(l.type) && !light_delta(l.type)) {
+                    ++inflights;
+                    const float pdf_s = __fdiv_rn(1.0f, 4.0f * flt_pi); // env.art:96
+                    const float mis   = tech.enable_nee ? __fdiv_rn(1.0f, 1.0f + inv_pdf * selector_pdf(sc) * pdf_s) : 1.0f;
+                    col               = cadd(col, handle_color(tech, cmulf(cmul(contrib0, light_color(l)), mis)));
+                }
+            }
+            if (inflights > 0) splat(film, pixel, col, set.inv_spi);
+        }
+        return;
+    }
+
+    const float  v = cur.hit_v[i];
+    const Entity e = load_entity(sc, ent);
+    Surf         surf;
+    const uint2  si = sc.shape_info[e.shape_id()];
+    if (si.y == IGB200_PRIM_SPHERE)
+        surf = sphere_surface_element(__ldg(reinterpret_cast<const float4*>(sc.shape_data + si.x)), e, org, dir, t, u, v);
+    else
+        surf = trimesh_surface_element(load_trimesh(sc, e.shape_id()), e, org, dir, t, u, v, prim);
+    const igb200_material mat = sc.materials[e.mat_id()];
+    const Bsdf bsdf{ sc.bsdfs[mat.bsdf], surf.local.c2, (tech.flags & IGB200_TECHFLAG_ONE_SIDED_DIFFUSE) != 0u };
+
+    if (tech.type == IGB200_TECH_DEBUG) { // technique/debugtracer.art:29-177
+        Color out;
+        auto  absv = [](Vec3 a) { return Color{ fabsf(a.x), fabsf(a.y), fabsf(a.z) }; };
+        switch (tech.debug_mode) {
+        case 1: out = absv(surf.local.c0); break;
+        case 2: out = absv(surf.local.c1); break;
+        case 3: out = absv(surf.face_normal); break;
+        case 8: out = Color{ fabsf(surf.tu), fabsf(surf.tv), 0.0f }; break;
+        case 9: out = Color{ fabsf(u), fabsf(v), 0.0f }; break;
+        case 10: out = Color{ surf.point.x, surf.point.y, surf.point.z }; break;
+        case 13: out = Color{ t, t, t }; break;
+        case 14: { const float a = safe_div(1.0f, surf.inv_area); out = Color{ a, a, a }; break; }
+        case 15: { const float f = (float)prim; out = Color{ f, f, f }; break; }
+        case 17: { const float f = (float)ent; out = Color{ f, f, f }; break; }
+        case 19: { const float f = (float)e.mat_id(); out = Color{ f, f, f }; break; }
+        case 21: out = mat.light >= 0 ? Color{ 0.0f, 0.0f, 1.0f } : Color{ 1.0f, 0.0f, 0.0f }; break;
+        case 22: out = bsdf.is_specular() ? Color{ 0.0f, 0.0f, 1.0f } : Color{ 1.0f, 0.0f, 0.0f }; break;
+        case 23: out = surf.is_entering ? Color{ 0.0f, 0.0f, 1.0f } : Color{ 1.0f, 0.0f, 0.0f }; break;
+        default: out = absv(surf.local.c2); break;
+        }
+        splat(film, pixel, out, set.inv_spi);
+        return;
+    }
+
+    // on_hit (pathtracer.art:112-132): emission of area lights with MIS against NEE
+    if (mat.light >= 0 && surf.is_entering) {
+        const float d = -dot3(dir, surf.local.c2);
+        if (d > flt_eps) {
+            const igb200_light& l     = sc.fin_lights[mat.light];
+            const Pdf           pdf   = light_pdf_direct(sc, l, org, surf);
+            const float         pdf_s = pdf.as_solid(d, t * t);
+            const float         mis   = tech.enable_nee ? __fdiv_rn(1.0f, 1.0f + inv_pdf * selector_pdf(sc) * pdf_s) : 1.0f;
+            splat(film, pixel, handle_color(tech, cmulf(cmul(contrib0, light_color(l)), mis)), set.inv_spi);
+        }
+    }
+
+    const uint32_t y = pixel / set.width, x = pixel - y * set.width;
+    Rnd            rnd{ create_random_seed(sample, set.iter, set.frame, x, y, set.seed), meta.y };
+    const Vec3     out_dir = vneg(dir);
+
+    // on_shadow (pathtracer.art:52-110): next event estimation
+    if (tech.enable_nee && !bsdf.is_specular() && (sc.n_inf + sc.n_fin) != 0 && depth + 1 <= tech.max_depth) {
+        const igb200_light& l  = selector_sample(sc, rnd);
+        const DirectSample  ls = light_sample_direct(sc, l, rnd, surf);
+        const float pdf_l_s    = ls.pdf.as_solid(ls.cos, ls.dist * ls.dist) * selector_pdf(sc);
+        if (!(pdf_l_s <= flt_eps) && ls.cos > flt_eps) {
+            const float mis    = light_delta(l.type) ? 1.0f : __fdiv_rn(1.0f, 1.0f + __fdiv_rn(bsdf.pdf(ls.dir), pdf_l_s));
+            const float factor = __fdiv_rn(ls.pdf.value, pdf_l_s);
+            const Color c      = handle_color(tech, cmulf(cmul(ls.intensity, cmul(contrib0, bsdf.eval(ls.dir))), mis * factor));
+            has_shadow         = true;
+            if (light_infinite(l.type)) {
+                sh.org_tmin = make_float4(surf.point.x, surf.point.y, surf.point.z, offset);
+                sh.dir_tmax = make_float4(ls.dir.x, ls.dir.y, ls.dir.z, flt_max);
+            } else {
+                const Vec3 dd = vsub(ls.pos, surf.point);
+                sh.org_tmin   = make_float4(surf.point.x, surf.point.y, surf.point.z, offset);
+                sh.dir_tmax   = make_float4(dd.x, dd.y, dd.z, 1.0f - offset);
+            }
+            sh.color_pixel = make_float4(c.r, c.g, c.b, __uint_as_float(pixel));
+        }
+    }
+
+    // on_bounce (pathtracer.art:162-200)
+    if (depth + 1 > tech.max_depth) return;
+    const BsdfSample ms      = bsdf.sample(rnd, out_dir, surf);
+    const Color      contrib = cmul(contrib0, ms.col);
+    const float      eta0    = cur.eta[i];
+    float            rr_prob = 1.0f;
+    if (depth + 1 > tech.min_depth) {
+        const Color cc = cmulf(contrib, eta0 * eta0);
+        rr_prob        = clampf(fmaxf(fmaxf(cc.r, cc.g), cc.b), 0.05f, 0.95f); // russian_roulette_pbrt
+    }
+    if (rnd.next_f32() >= rr_prob) return;
+    const float new_inv_pdf = bsdf.is_specular() ? 0.0f : __fdiv_rn(1.0f, ms.pdf);
+    const Color nc          = cmulf(contrib, __fdiv_rn(1.0f, rr_prob));
+    alive             = true;
+    nx.org_tmin       = make_float4(surf.point.x, surf.point.y, surf.point.z, offset);
+    nx.dir_tmax       = make_float4(ms.in_dir.x, ms.in_dir.y, ms.in_dir.z, flt_max);
+    nx.meta           = make_uint4(id, rnd.counter, kRayBounce, (uint32_t)(depth + 1));
+    nx.contrib_invpdf = make_float4(nc.r, nc.g, nc.b, new_inv_pdf);
+    nx.eta            = eta0 * ms.eta;
+}
+
+__global__ void __launch_bounds__(128) shade_kernel(WaveControl* __restrict__ ctl, const PathStream cur, const PathStream nxt,
+                                                    const ShadowStream shq, const uint32_t* __restrict__ sorted, const ShadeScene sc,
+                                                    const DeviceScene geo, const WaveSettings set, float* __restrict__ film)
+{
+    const uint32_t n       = ctl->n_cur;
+    const uint32_t lane    = threadIdx.x & 31u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t step    = gridDim.x * blockDim.x;
+    for (uint32_t p0 = blockIdx.x * blockDim.x; p0 < n; p0 += step) { // block-uniform trip count
+        const uint32_t p = p0 + threadIdx.x;
+        bool        alive = false, has_shadow = false;
+        NextState   nx;
+        ShadowState sh;
+        if (p < n) shade_one(sc, geo, set, cur, sorted ? sorted[p] : p, film, alive, nx, has_shadow, sh);
+
+        // stream compaction: one atomic per warp, ranks from the ballot (replaces gpu_compact_primary)
+        const uint32_t am = __ballot_sync(0xFFFFFFFFu, alive);
+        if (am) {
+            uint32_t base = 0u;
+            if (lane == (uint32_t)(__ffs(am) - 1)) base = atomicAdd(&ctl->n_next, (uint32_t)__popc(am));
+            base = __shfl_sync(0xFFFFFFFFu, base, __ffs(am) - 1);
+            if (alive) {
+                const uint32_t slot      = base + __popc(am & lt_mask);
+                nxt.org_tmin[slot]       = nx.org_tmin;
+                nxt.dir_tmax[slot]       = nx.dir_tmax;
+                nxt.meta[slot]           = nx.meta;
+                nxt.contrib_invpdf[slot] = nx.contrib_invpdf;
+                nxt.eta[slot]            = nx.eta;
+            }
+        }
+        const uint32_t sm = __ballot_sync(0xFFFFFFFFu, has_shadow);
+        if (sm) {
+            uint32_t base = 0u;
+            if (lane == (uint32_t)(__ffs(sm) - 1)) base = atomicAdd(&ctl->n_shadow, (uint32_t)__popc(sm));
+            base = __shfl_sync(0xFFFFFFFFu, base, __ffs(sm) - 1);
+            if (has_shadow) {
+                const uint32_t slot    = base + __popc(sm & lt_mask);
+                shq.org_tmin[slot]     = sh.org_tmin;
+                shq.dir_tmax[slot]     = sh.dir_tmax;
+                shq.color_pixel[slot]  = sh.color_pixel;
+            }
+        }
+    }
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------------------
+// Launchers
+// ---------------------------------------------------------------------------------------------------------
+cudaError_t launch_wave_reset(const WaveBuffers& buf, uint32_t total, cudaStream_t stream)
+{
+    reset_kernel<<<1, 1, 0, stream>>>(buf.ctl, total, buf.host_done);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene& sh, const WaveBuffers& buf,
+                              const WaveSettings& set, int parity, bool sort, int sm_count, cudaStream_t stream)
+{
+    const PathStream& cur = buf.stream[parity & 1];
+    const PathStream& nxt = buf.stream[(parity + 1) & 1];
+    const uint32_t    n_bins = (uint32_t)sh.n_mat + 1u;
+    if (n_bins > kWaveMaxBins) return cudaErrorInvalidValue;
+    const int wide = sm_count * 8; // grid-stride kernels: a whole number of waves
+
+    begin_round_kernel<<<1, 256, 0, stream>>>(buf.ctl, set.capacity, n_bins, buf.host_done);
+    generate_kernel<<<wide, 256, 0, stream>>>(buf.ctl, cur, sh, set);
+    const PrimaryIO pio{ cur, buf.keys, buf.ent_mat, buf.ctl, n_bins };
+    trace_kernel<PrimaryIO, false, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, pio, nullptr, buf.ctl->work_primary);
+    if (sort) scatter_kernel<<<wide, 256, 0, stream>>>(buf.ctl, buf.keys, buf.sorted);
+    shade_kernel<<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene, set, buf.film);
+    const ShadowIO sio{ buf.shadow, buf.ctl, buf.film, set.inv_spi };
+    trace_kernel<ShadowIO, true, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, sio, nullptr, buf.ctl->work_shadow);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_film_combine(float* film, const float* src, uint64_t count, bool overwrite, cudaStream_t stream)
+{
+    if (count == 0) return cudaSuccess;
+    film_combine_kernel<<<(uint32_t)((count + 255) / 256), 256, 0, stream>>>(film, src, count, overwrite);
+    return cudaGetLastError();
+}
+
+} // namespace igb

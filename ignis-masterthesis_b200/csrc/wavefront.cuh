@@ -1,0 +1,95 @@
+// wavefront.cuh -- ray streams, counters and launchers of the wavefront path tracer (sm_100a).
+//
+// Replaces the reference's GPU wavefront loop `gpu_trace` (src/artic/driver/mapping_gpu.art:728-870) and its
+// streams (src/artic/driver/streams.art:1-44, sizing src/runtime/device/Device.cpp:474-514).  Differences by design:
+//   * streams are 16-byte-vector SoA (org+tmin, dir+tmax, ...) instead of one float column per component;
+//   * survivors are compacted by the SHADE kernel itself (warp ballot + one atomic per warp) into the other
+//     stream buffer, so there is no separate compaction pass (gpu_compact_primary, mapping_gpu.art:685-714);
+//   * the sort is an index sort by MATERIAL id (histogram fused into the traversal kernel, scan by its last block,
+//     warp-aggregated scatter) -- the reference moves whole 96-byte entries, sorts by entity and scans on the host
+//     through two blocking copies (mapping_gpu.art:403-498);
+//   * all counts live on the device; one wavefront round is a fixed sequence of six launches captured in a CUDA
+//     graph, and the host only polls a mapped "done" flag (no blocking copies per bounce).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+#include "../../include/ignis_b200.h"
+#include "trace.cuh"
+
+namespace igb {
+
+// Primary stream (one of two ping-pong buffers): ray + path state + hit record.  88 bytes per ray.
+struct PathStream {
+    float4* org_tmin;       // ray origin, tmin
+    float4* dir_tmax;       // ray direction, tmax
+    uint4*  meta;           // x: ray id = pixel * spi + sample, y: RNG counter (the `rnd` column), z: ray flags, w: depth
+    float4* contrib_invpdf; // path payload: contrib rgb, inv_pdf (technique/pathtracer.art:7-12)
+    float*  eta;            // path payload: eta
+    uint4*  hit0;           // ent_id, prim_id, t, u (bit patterns)
+    float*  hit_v;
+};
+
+// Secondary (shadow) stream, compacted on write.  48 bytes per ray.
+struct ShadowStream {
+    float4* org_tmin;
+    float4* dir_tmax;
+    float4* color_pixel; // contribution rgb, pixel index (bit pattern)
+};
+
+constexpr uint32_t kWaveMaxBins = 4096; // material bins + miss bin supported by the sort
+
+// Device-resident control block of one render() call.
+struct WaveControl {
+    uint32_t n_cur;     // rays in the current primary stream (survivors + regenerated)
+    uint32_t n_next;    // survivors appended to the other stream by the shade kernel
+    uint32_t n_shadow;  // shadow rays appended by the shade kernel
+    uint32_t gen_base;  // first slot the generator fills this round
+    uint32_t gen_count; // rays the generator creates this round
+    uint32_t gen_first; // id of the first generated ray
+    uint32_t next_id;   // next ray id to generate
+    uint32_t total;     // spi * width * height
+    uint32_t done;      // set when a round starts with nothing to do
+    uint32_t rounds;
+    uint32_t work_primary[2]; // persistent-kernel work counters (self-resetting)
+    uint32_t work_shadow[2];
+    unsigned long long camera_rays, bounce_rays, shadow_rays;
+    uint32_t bins[kWaveMaxBins];    // histogram of sort keys (material id, miss = n_mat)
+    uint32_t offsets[kWaveMaxBins]; // exclusive scan of bins
+    uint32_t cursors[kWaveMaxBins]; // scatter cursors
+};
+
+struct WaveSettings {
+    uint32_t      spi, width, height, iter, frame, seed;
+    float         inv_spi;
+    uint32_t      capacity;
+    const float4* list_rays; // igtrace mode: normalised StreamRays (2 x float4 each), else nullptr
+};
+
+struct WaveBuffers {
+    PathStream     stream[2];
+    ShadowStream   shadow;
+    uint32_t*      keys;   // sort key per primary slot
+    uint32_t*      sorted; // slot indices in key order
+    WaveControl*   ctl;
+    float*         film;   // w * h * 3, RGB sums
+    const int32_t* ent_mat; // material id per entity
+    uint32_t*      host_done; // device alias of a mapped host flag
+};
+
+namespace shade { struct ShadeScene; }
+
+// Enqueues ONE wavefront round (parity selects which stream buffer is current) on `stream`:
+// begin_round, generate, trace_primary(+histogram+scan), scatter, shade, trace_shadow(+splat).
+cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene& sh, const WaveBuffers& buf,
+                              const WaveSettings& set, int parity, bool sort, int sm_count, cudaStream_t stream);
+
+// Resets the control block for a new iteration (total = spi * w * h).
+cudaError_t launch_wave_reset(const WaveBuffers& buf, uint32_t total, cudaStream_t stream);
+
+// film[i] += src[i] (overwrite = false) or film[i] = src[i]
+cudaError_t launch_film_combine(float* film, const float* src, uint64_t count, bool overwrite, cudaStream_t stream);
+
+constexpr int kWaveLaunchesPerRound = 6;
+
+} // namespace igb

@@ -74,6 +74,53 @@ class Device:
         return {"rays": st.rays, "nodes_visited": st.nodes_visited, "tris_tested": st.tris_tested,
                 "entities_entered": st.entities_entered, "kernel_ms": st.kernel_ms}
 
+    # ---- wavefront path tracing: Device::render / getFramebufferForHost (Device.h:53,63-66) ----
+    def assign_shading(self, shading):
+        sh = shading.c_shading()
+        _lib.check(self._lib.igb200_assign_shading(self._h, C.addressof(sh)))
+
+    def render(self, width=0, height=0, spi=1, iteration=0, frame=0, seed=0, rays=None):
+        """One iteration (spi samples per pixel) accumulated into the film. rays != None: igtrace (list) mode."""
+        from .shading import RenderSettings
+        if rays is not None:
+            rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        rs = RenderSettings(rays=rays.ctypes.data if rays is not None else None, ray_count=rays.size if rays is not None else 0,
+                            spi=spi, width=width, height=height, iteration=iteration, frame=frame, user_seed=seed)
+        _lib.check(self._lib.igb200_render(self._h, C.addressof(rs)))
+        self._film = (rays.size, 1) if rays is not None else (width, height)
+
+    def framebuffer(self, copy=True):
+        """(film (h, w, 3) f32 of RGB SUMS over iterations, iteration count)."""
+        ptr, it = C.c_void_p(), C.c_uint64()
+        _lib.check(self._lib.igb200_framebuffer(self._h, None, 0, C.byref(ptr), C.byref(it)))
+        st = self.render_stats()
+        n = st["film"][0] * st["film"][1] * 3
+        arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_float)), shape=(n,)).reshape(st["film"][1], st["film"][0], 3)
+        return (arr.copy() if copy else arr), it.value
+
+    def framebuffer_device(self):
+        ptr, it = C.c_void_p(), C.c_uint64()
+        _lib.check(self._lib.igb200_framebuffer(self._h, None, 1, C.byref(ptr), C.byref(it)))
+        return ptr.value, it.value
+
+    def set_framebuffer(self, d_src, count, iterations):
+        _lib.check(self._lib.igb200_set_framebuffer(self._h, d_src, count, iterations))
+
+    def clear_framebuffer(self):
+        _lib.check(self._lib.igb200_clear_framebuffer(self._h))
+
+    def resize(self, width, height):
+        _lib.check(self._lib.igb200_resize(self._h, width, height))
+        self._film = (width, height)
+
+    def render_stats(self):
+        from .shading import RenderStats
+        st = RenderStats()
+        _lib.check(self._lib.igb200_get_render_stats(self._h, C.addressof(st)))
+        return {"camera_rays": st.camera_rays, "bounce_rays": st.bounce_rays, "shadow_rays": st.shadow_rays,
+                "rounds": st.rounds, "kernel_launches": st.kernel_launches, "device_ms": st.device_ms,
+                "film": getattr(self, "_film", (0, 0))}
+
     def bvh_info(self):
         nb, tb, lb, d = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_uint32()
         _lib.check(self._lib.igb200_get_bvh_info(self._h, C.byref(nb), C.byref(tb), C.byref(lb), C.byref(d)))

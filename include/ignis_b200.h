@@ -290,9 +290,8 @@ int igb200_framebuffer(igb200_device* dev, const char* name, int device, float**
 int igb200_clear_framebuffer(igb200_device* dev);
 int igb200_resize(igb200_device* dev, uint32_t width, uint32_t height);
 
-/* Multi-GPU film combine: adds `count` floats from `src` (a device pointer on this device,
- * e.g. the result of an NCCL reduce) into the film, or overwrites it when overwrite != 0, and sets the
- * iteration count. */
+/* Multi-GPU film combine: overwrites the film with `count` = w*h*3 floats from `d_src` (a device
+ * pointer on this device, e.g. the result of an NCCL reduce over the per-GPU films) and sets the iteration count. */
 int igb200_set_framebuffer(igb200_device* dev, const float* d_src, uint64_t count, uint64_t iterations);
 
 int igb200_get_render_stats(igb200_device* dev, igb200_render_stats* out);
