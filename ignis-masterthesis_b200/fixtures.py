@@ -1,0 +1,55 @@
+"""Golden fixtures: scene tables + shading tables (+ an optional reference image) in one .npz file.
+
+The reference tree does not exist on the GPU box, so scenes taken from it (scenes/evaluation/*.json,
+scenes/diamond_scene.json) travel as the exact table blobs `sceneio.load_scene` produced here, together with
+the reference renderer's image where the reference ships one (scenes/evaluation/references/*.exr).
+Written by scripts/make_golden.py; read by tests/ and bench.py.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import shading as S
+from .tables import LEAF_DTYPE, LOOKUP_DTYPE, SceneTables
+
+
+def _bytes(obj):
+    return np.frombuffer(bytes(obj), np.uint8).copy()
+
+
+def _table(cls, items):
+    return np.concatenate([_bytes(x) for x in items]) if items else np.zeros(0, np.uint8)
+
+
+def save_fixture(path, tables, sh, width, height, ref=None, meta=""):
+    np.savez_compressed(
+        path, lookups=tables.lookups.view(np.uint8), shape_data=tables.shape_data, entities=tables.entities,
+        leaves0=tables.leaves[0].view(np.uint8), leaves1=tables.leaves[1].view(np.uint8), bbox=tables.bbox,
+        material_count=np.int64(tables.material_count), entity_per_material=np.asarray(tables.entity_per_material, np.int64),
+        camera=_bytes(sh.camera), technique=_bytes(sh.technique), bsdfs=_table(S.Bsdf, sh.bsdfs),
+        materials=_table(S.Material, sh.materials), infinite=_table(S.Light, sh.infinite), finite=_table(S.Light, sh.finite),
+        size=np.asarray([width, height], np.int64), ref=np.zeros(0, np.float32) if ref is None else np.asarray(ref, np.float32),
+        meta=np.asarray(meta))
+
+
+def _untable(cls, raw):
+    n = raw.size // C.sizeof(cls)
+    return [cls.from_buffer_copy(raw[i * C.sizeof(cls):(i + 1) * C.sizeof(cls)].tobytes()) for i in range(n)]
+
+
+def load_fixture(path):
+    """Returns (SceneTables, Shading, width, height, ref image or None)."""
+    z = np.load(path)
+    tables = SceneTables(z["lookups"].view(LOOKUP_DTYPE), z["shape_data"], z["entities"],
+                         [z["leaves0"].view(LEAF_DTYPE), z["leaves1"].view(LEAF_DTYPE)], z["bbox"],
+                         int(z["material_count"]), list(z["entity_per_material"]))
+    sh = S.Shading()
+    sh.camera = S.Camera.from_buffer_copy(z["camera"].tobytes())
+    sh.technique = S.Technique.from_buffer_copy(z["technique"].tobytes())
+    sh.bsdfs = _untable(S.Bsdf, z["bsdfs"])
+    sh.materials = _untable(S.Material, z["materials"])
+    sh.infinite = _untable(S.Light, z["infinite"])
+    sh.finite = _untable(S.Light, z["finite"])
+    w, h = [int(x) for x in z["size"]]
+    ref = z["ref"]
+    return tables, sh, w, h, (ref if ref.size else None)

@@ -1,0 +1,33 @@
+"""Generates tests/golden/*.npz from the reference tree (run in the build container only; /root/reference is
+read-only and absent on the GPU box).  Each fixture = the table blobs `sceneio.load_scene` builds from the
+reference's scene file + the reference's own golden image where it ships one."""
+import importlib, os, sys
+os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+import cv2
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+pkg = importlib.import_module("ignis-masterthesis_b200")
+sceneio = importlib.import_module("ignis-masterthesis_b200.sceneio")
+fixtures = importlib.import_module("ignis-masterthesis_b200.fixtures")
+REF = "/root/reference/scenes"
+OUT = os.path.join(ROOT, "tests", "golden")
+os.makedirs(OUT, exist_ok=True)
+
+def exr(name):
+    img = cv2.imread(f"{REF}/evaluation/references/{name}", cv2.IMREAD_UNCHANGED)
+    return np.ascontiguousarray(img[:, :, :3][:, :, ::-1]).astype(np.float32)
+
+JOBS = [  # (fixture, scene file, reference image, width, height)
+    ("cbox-d6", "evaluation/cbox-d6.json", "ref-cbox-d6-4096.exr", None, None),
+    ("cbox-d1", "evaluation/cbox-d1.json", "ref-cbox-d1-4096.exr", None, None),
+    ("point", "evaluation/point.json", "ref-point-4096.exr", None, None),
+    ("emissive-plane", "evaluation/emissive-plane.json", "ref-emissive-plane-4096.exr", None, None),
+    ("plane-d6", "evaluation/plane-d6.json", "ref-plane-d6-4096.exr", None, None),
+    ("diamond", "diamond_scene.json", None, 1920, 1080),
+]
+for name, scene, ref, w, h in JOBS:
+    tables, sh, w, h, info = sceneio.load_scene(f"{REF}/{scene}", width=w, height=h)
+    fixtures.save_fixture(os.path.join(OUT, name + ".npz"), tables, sh, w, h, exr(ref) if ref else None,
+                          meta=f"{scene}; reference image {ref}")
+    print(name, w, h, "entities", tables.entity_count, "materials", tables.material_count, os.path.getsize(os.path.join(OUT, name + ".npz")))
