@@ -54,35 +54,44 @@ def measured_peak():
 
 
 class ClockSampler(threading.Thread):
-    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """Samples SM clocks / throttle reasons during the timed region (B200_PROFILING.md recipe) through NVML
+    (same counters as `nvidia-smi --query-gpu=clocks.sm,clocks.max.sm,clocks_event_reasons.*`), every 5 ms."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self._halt = index, [], threading.Event()
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
 
     def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
         while not self._halt.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                f = [x.strip() for x in out.strip().split(",")]
-                if len(f) >= 6:
-                    self.samples.append(f)
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.samples.append((float(mhz), int(reasons)))
             except Exception:
                 pass
-            self._halt.wait(0.2)
+            self._halt.wait(0.005)
 
     def stop(self):
         self._halt.set()
         self.join(timeout=6)
-        sm = [float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit()]
-        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.samples)}
+        sm = [s[0] for s in self.samples]
+        bits = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40, "sw_power_cap": 0x4}
+        reasons = sorted({n for _, r in self.samples for n, b in bits.items() if r & b})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(self.samples)}
 
 
 def oracle_throughput(pkg, tables, rays, budget_rays):
@@ -96,6 +105,102 @@ def oracle_throughput(pkg, tables, rays, budget_rays):
     osc.trace(sample, threads=cores, normalize=False)
     dt = time.perf_counter() - t0
     return sample.size / dt / 1e6, cores, f"first {sample.size} rays of the c3-instanced batch, closest-hit"
+
+
+PT_WORKLOAD = "c4-diamond"  # BASELINE.json configs[3]: scenes/diamond_scene.json, 1920x1080 (fixture tests/golden/diamond.npz)
+
+
+class _DevArray:
+    """Exposes a raw device pointer to torch through __cuda_array_interface__ (no copy)."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
+
+
+def load_pt_workload(pkg):
+    fx = importlib.import_module("ignis-masterthesis_b200.fixtures")
+    tables, sh, w, h, _ = fx.load_fixture(os.path.join(ROOT, "tests", "golden", "diamond.npz"))
+    spi = max(1, min(64, int(np.ceil(8 / ((w / 1000.0) * (h / 1000.0))))))  # recommendSPI (GPU), Runtime.cpp:61-69
+    return tables, sh, w, h, spi
+
+
+def bench_path_tracer(pkg, local_rank, rank, world, iterations, warmup):
+    """Path-traced samples/s (igcli's definition: spi * w * h / iteration seconds, src/frontend/cli/main.cpp:135).
+    N GPUs: rank r renders the block of iterations [r*K, (r+1)*K) in one wavefront (the seed hashes the iteration
+    index, so the union is the single-GPU sample set), then the films are summed onto rank 0 with one NCCL reduce
+    over NVLink."""
+    import torch
+    import torch.distributed as dist
+    tables, sh, w, h, spi = load_pt_workload(pkg)
+    dev = pkg.Device(local_rank)
+    dev.assign_scene(tables)
+    dev.assign_shading(sh)
+    dev.resize(w, h)
+    for it in range(warmup):
+        dev.render(w, h, spi=spi, iteration=1_000_000 + it)
+    dev.clear_framebuffer()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    dev.render(w, h, spi=spi, iteration=rank * iterations, iterations=iterations)
+    st = dev.render_stats()
+    ms = [st["device_ms"] / iterations]
+    rays = st["camera_rays"] + st["bounce_rays"] + st["shadow_rays"]
+    launches = st["kernel_launches"]
+    rounds = st["rounds"]
+    ptr, n_it = dev.framebuffer_device()
+    film = torch.as_tensor(_DevArray(ptr, w * h * 3), device=f"cuda:{local_rank}")
+    reduce_ms = 0.0
+    if world > 1:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)
+        e1.record()
+        torch.cuda.synchronize()
+        reduce_ms = e0.elapsed_time(e1)
+        if rank == 0:
+            dev.set_framebuffer(ptr, w * h * 3, iterations * world)
+    total_s = time.perf_counter() - t0
+    host_film, n_total = dev.framebuffer()  # D2H of the presented frame: the e2e read
+    e2e_s = time.perf_counter() - t0
+    stats = torch.tensor([total_s, e2e_s, float(rays), float(np.sum(ms)), float(launches)], device="cuda", dtype=torch.float64)
+    if world > 1:
+        mx = stats.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = stats.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        total_s, e2e_s, rays, launches = float(mx[0]), float(mx[1]), float(sm[2]), float(sm[4])
+    samples = float(spi) * w * h * iterations * world
+    out = {
+        "workload": PT_WORKLOAD, "width": w, "height": h, "spi": spi, "iterations": iterations * world,
+        "max_depth": int(sh.technique.max_depth), "metric": "path-traced samples/s", "unit": "Msamples/s",
+        "value": samples / total_s / 1e6, "e2e_value": samples / e2e_s / 1e6,
+        "ms_per_iteration_median": float(np.median(ms)), "mrays_per_s": rays / total_s / 1e6,
+        "rays_per_sample": rays / samples, "film_reduce_ms": reduce_ms, "d2h_bytes": w * h * 3 * 4,
+        "gpu_launches": int(launches), "rounds_rank0": int(rounds), "film_mean": float(host_film.mean() / max(1, n_total)),
+    }
+    dev.close()
+    return out
+
+
+def oracle_samples_per_s(pkg, budget_s=12.0):
+    """The oracle's render iteration on the host cores on a bounded sample of the same workload (a crop-free
+    low-resolution render of the same scene: same rays per sample)."""
+    oracle = load_oracle()
+    tables, sh, w, h, spi = load_pt_workload(pkg)
+    osc = oracle.OracleScene(tables)
+    cw, ch = w // 4, h // 4
+    cores = os.cpu_count() or 1
+    osc.render(sh, cw, ch, spi=1, iterations=1)
+    t0 = time.perf_counter()
+    n = 0
+    while time.perf_counter() - t0 < budget_s:
+        osc.render(sh, cw, ch, spi=spi, iterations=1, first_iteration=n)
+        n += 1
+    dt = time.perf_counter() - t0
+    return {"value": cw * ch * spi * n / dt / 1e6, "unit": "Msamples/s", "cores": cores, "kind": "port",
+            "sample": f"{n} iterations of {PT_WORKLOAD} at {cw}x{ch} (1/16 of the pixels), spi {spi}"}
 
 
 def run_reference(args, rank, world):
@@ -129,6 +234,10 @@ def run_reference(args, rank, world):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if args.pt_iterations > 0:
+        pt = oracle_samples_per_s(pkg)
+        line["path_tracer"] = {"workload": PT_WORKLOAD, "metric": "path-traced samples/s", "unit": "Msamples/s",
+                               "value": pt["value"], "e2e_value": pt["value"], "cpu_baseline": pt}
     print(json.dumps(line), flush=True)
 
 
@@ -211,6 +320,11 @@ def run_ours(args, rank, world, local_rank):
         e2e_s = float(tm.item())
     e2e_val = world * n * e2e_steps / e2e_s / 1e6
     assert int((outs[1] >= 0).sum()) > 0
+    dev.close()
+    del d_rays, d_ent, d_prim, d_t, d_u, d_v
+
+    # ---- second headline metric: path-traced samples/s (all ranks take part) ----
+    pt = bench_path_tracer(pkg, local_rank, rank, world, args.pt_iterations, 2) if args.pt_iterations > 0 else None
 
     if rank == 0:
         # ---- algorithmic bytes per ray: visit counts from a counting pass over a 2 Mi-ray sample (untimed) ----
@@ -244,8 +358,11 @@ def run_ours(args, rank, world, local_rank):
                          "per_ray": {"nodes": n_node, "tris": n_tri, "entities": n_ent}},
             "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         }
+        if pt is not None:
+            pt["cpu_baseline"] = oracle_samples_per_s(pkg)
+            line["path_tracer"] = pt
+            line["gpu_launches"] += pt["gpu_launches"]
         print(json.dumps(line), flush=True)
-    dev.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -253,10 +370,11 @@ def run_ours(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--rays", type=int, default=FULL_RAYS)
     ap.add_argument("--cpu-rays", type=int, default=4_000_000)
+    ap.add_argument("--pt-iterations", type=int, default=16, help="path-traced iterations per GPU (0 disables the leg)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -23,6 +23,7 @@ ABI_SYMBOLS = [
     "igb200_debug_check_bvh8",
     "igb200_assign_shading",
     "igb200_render",
+    "igb200_render_iterations",
     "igb200_framebuffer",
     "igb200_clear_framebuffer",
     "igb200_resize",
@@ -113,6 +114,7 @@ def load():
     lib.igb200_debug_check_bvh8.argtypes = [vp, u32, u32, vp]
     lib.igb200_assign_shading.argtypes = [vp, vp]
     lib.igb200_render.argtypes = [vp, vp]
+    lib.igb200_render_iterations.argtypes = [vp, vp, u32]
     lib.igb200_framebuffer.argtypes = [vp, C.c_char_p, i32, C.POINTER(vp), C.POINTER(u64)]
     lib.igb200_clear_framebuffer.argtypes = [vp]
     lib.igb200_resize.argtypes = [vp, u32, u32]

@@ -123,6 +123,7 @@ struct igb200_device {
     igb::WaveBuffers              wave{};
     uint32_t*                     h_done = nullptr; // mapped pinned host flag
     cudaEvent_t                   round_ev[4] = {};
+    cudaGraphExec_t               round_graph = nullptr; // one round pair; invalidated by assign_scene / assign_shading
     DeviceBuffer<float4>          d_list_rays;
 
     DeviceBuffer<float>           d_film;
@@ -191,6 +192,7 @@ void igb200_destroy(igb200_device* dev)
         if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : dev->round_ev)
         if (e) cudaEventDestroy(e);
+    if (dev->round_graph) cudaGraphExecDestroy(dev->round_graph);
     if (dev->h_done) cudaFreeHost(dev->h_done);
     if (dev->h_film) cudaFreeHost(dev->h_film);
     delete dev; // DeviceBuffer destructors free the allocations (Device::releaseAll, Device.cpp:948-952)
@@ -317,6 +319,7 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
     IGB_CUDA(dev->spheres.upload(all_spheres.data(), all_spheres.size(), dev->stream));
     // tables the shading kernels read (entities FixTable, shapes DynTable data)
     dev->has_shading = false;
+    if (dev->round_graph) { cudaGraphExecDestroy(dev->round_graph); dev->round_graph = nullptr; }
     {
         std::vector<uint2>   info(sc->shape_count);
         for (uint64_t s = 0; s < sc->shape_count; ++s) {
@@ -545,6 +548,7 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
         const float  x = b[3] - b[0], y = b[4] - b[1], z = b[5] - b[2];
         s.scene_radius = std::sqrt(std::fmaf(x, x, std::fmaf(y, y, z * z))) / 2 * 1.01f;
     }
+    if (dev->round_graph) { cudaGraphExecDestroy(dev->round_graph); dev->round_graph = nullptr; }
     dev->has_shading = true;
     return IGB200_OK;
 }
@@ -566,7 +570,7 @@ static int ensure_film(igb200_device* dev, uint32_t w, uint32_t h)
 static int ensure_wave(igb200_device* dev)
 {
     if (dev->wave_capacity) return IGB200_OK;
-    uint32_t cap = 1u << 20; // the reference's GPU stream capacity (mapping_gpu.art:1125)
+    uint32_t cap = 1u << 23; // 8 Mi rays (the reference: 1 Mi, mapping_gpu.art:1125); ~1.9 GB of streams, measured best on B200
     if (const char* e = std::getenv("IGB200_WAVE_CAPACITY")) cap = (uint32_t)std::max(1024l, std::atol(e));
     if (const char* e = std::getenv("IGB200_WAVE_SORT")) dev->wave_sort = std::atoi(e) != 0;
     for (int b = 0; b < 2; ++b) {
@@ -597,14 +601,31 @@ static int ensure_wave(igb200_device* dev)
     return IGB200_OK;
 }
 
-int igb200_render(igb200_device* dev, const igb200_render_settings* rs)
+static int render_batch(igb200_device* dev, const igb200_render_settings* rs, uint32_t count)
 {
     if (!dev || !rs) return fail(IGB200_E_INVALID, "igb200_render: NULL argument");
+    if (count == 0) return IGB200_OK;
     if (!dev->has_scene || !dev->has_shading) return fail(IGB200_E_STATE, "igb200_render: scene and shading must be assigned first");
     const bool     list = rs->rays != nullptr;
     const uint64_t w = list ? rs->ray_count : rs->width, h = list ? 1 : rs->height;
     if (w == 0 || h == 0 || rs->spi == 0) return fail(IGB200_E_INVALID, "igb200_render: empty film or spi == 0");
-    if (w * h * rs->spi >= 0xFFFF0000ull) return fail(IGB200_E_UNSUPPORTED, "igb200_render: more than 2^32 samples per iteration");
+    if (w * h * rs->spi >= 0x7FFF0000ull) return fail(IGB200_E_UNSUPPORTED, "igb200_render: more than 2^31 samples per iteration");
+    const uint64_t per_iter = w * h * rs->spi;
+    {
+        // one wavefront may span several iterations (its queue regenerates across them); split the request so
+        // that a batch has fewer than 2^31 ray ids and fewer than 2^24 iterations
+        const uint64_t max_count = std::max<uint64_t>(1, std::min<uint64_t>(0x7FFF0000ull / per_iter, 1u << 23));
+        if (count > max_count) {
+            igb200_render_settings part = *rs;
+            for (uint32_t done = 0; done < count;) {
+                const uint32_t c = (uint32_t)std::min<uint64_t>(max_count, count - done);
+                part.iteration   = rs->iteration + done;
+                if (int rc = render_batch(dev, &part, c)) return rc;
+                done += c;
+            }
+            return IGB200_OK;
+        }
+    }
     IGB_CUDA(cudaSetDevice(dev->ordinal));
     if (int rc = ensure_wave(dev)) return rc;
     if (int rc = ensure_film(dev, (uint32_t)w, (uint32_t)h)) return rc;
@@ -613,6 +634,7 @@ int igb200_render(igb200_device* dev, const igb200_render_settings* rs)
     igb::WaveSettings set{};
     set.spi = rs->spi; set.width = (uint32_t)w; set.height = (uint32_t)h;
     set.iter = rs->iteration; set.frame = rs->frame; set.seed = rs->user_seed;
+    set.per_iter = (uint32_t)per_iter;
     set.inv_spi  = 1.0f / (float)rs->spi;
     set.capacity = dev->wave_capacity;
     if (list) {
@@ -622,20 +644,33 @@ int igb200_render(igb200_device* dev, const igb200_render_settings* rs)
         IGB_CUDA(igb::launch_normalize_rays(dev->d_list_rays.ptr, rs->ray_count, st));
         set.list_rays = dev->d_list_rays.ptr;
     }
-    dev->wave.film    = dev->d_film.ptr;
+    set.film = dev->d_film.ptr;
     dev->wave.ent_mat = dev->d_ent_mat.ptr;
 
     IGB_CUDA(cudaEventRecord(dev->ev0, st));
-    IGB_CUDA(igb::launch_wave_reset(dev->wave, (uint32_t)(w * h * rs->spi), st));
+    IGB_CUDA(igb::launch_wave_reset(dev->wave, set, (uint32_t)(per_iter * count), st));
     IGB_CUDA(cudaStreamSynchronize(st)); // the mapped flag is cleared before the host starts polling it
     // The host runs ahead of the device by up to kAhead round pairs and polls the mapped `done` flag; rounds
     // enqueued after the queue has drained are no-ops (every kernel reads a zero count).
     constexpr int kAhead = 3;
     uint64_t      pairs  = 0;
     const uint64_t max_pairs = 1ull << 24;
+    // One round pair (12 launches) is captured once into a CUDA graph; per-call settings live in device memory, so
+    // the graph only depends on the scene / shading tables (re-captured when they change).
+    if (!dev->round_graph) {
+        cudaGraph_t g = nullptr;
+        IGB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        cudaError_t e1 = igb::launch_wave_round(dev->view, dev->shade, dev->wave, 0, dev->wave_sort, dev->sm_count, st);
+        cudaError_t e2 = igb::launch_wave_round(dev->view, dev->shade, dev->wave, 1, dev->wave_sort, dev->sm_count, st);
+        cudaError_t e3 = cudaStreamEndCapture(st, &g);
+        if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || !g)
+            return fail(IGB200_E_CUDA, "igb200_render: graph capture failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3)));
+        cudaError_t e4 = cudaGraphInstantiate(&dev->round_graph, g, 0);
+        cudaGraphDestroy(g);
+        if (e4 != cudaSuccess) return fail(IGB200_E_CUDA, "igb200_render: cudaGraphInstantiate failed: %s", cudaGetErrorString(e4));
+    }
     for (; pairs < max_pairs; ++pairs) {
-        IGB_CUDA(igb::launch_wave_round(dev->view, dev->shade, dev->wave, set, 0, dev->wave_sort, dev->sm_count, st));
-        IGB_CUDA(igb::launch_wave_round(dev->view, dev->shade, dev->wave, set, 1, dev->wave_sort, dev->sm_count, st));
+        IGB_CUDA(cudaGraphLaunch(dev->round_graph, st));
         IGB_CUDA(cudaEventRecord(dev->round_ev[pairs % 4], st));
         if (pairs >= (uint64_t)kAhead) IGB_CUDA(cudaEventSynchronize(dev->round_ev[(pairs - kAhead) % 4]));
         if (*reinterpret_cast<volatile uint32_t*>(dev->h_done)) { ++pairs; break; }
@@ -653,9 +688,16 @@ int igb200_render(igb200_device* dev, const igb200_render_settings* rs)
     float ms = 0.0f;
     cudaEventElapsedTime(&ms, dev->ev0, dev->ev1);
     dev->render_stats.device_ms = ms;
-    dev->iterations += 1; // Interface::present, Device.cpp:1460-1472
+    dev->iterations += count; // Interface::present, Device.cpp:1460-1472
     dev->film_mapped = false;
     return IGB200_OK;
+}
+
+int igb200_render(igb200_device* dev, const igb200_render_settings* rs) { return render_batch(dev, rs, 1); }
+
+int igb200_render_iterations(igb200_device* dev, const igb200_render_settings* rs, uint32_t count)
+{
+    return render_batch(dev, rs, count);
 }
 
 int igb200_framebuffer(igb200_device* dev, const char* name, int device, float** data, uint64_t* iterations)

@@ -37,7 +37,7 @@ struct PrimaryIO {
         dir   = Vec3{ d.x, d.y, d.z };
         tmin  = o.w;
         tmax  = d.w;
-        flags = s.meta[i].z;
+        flags = s.meta[i].z & 0xFFu;
         return true;
     }
     __device__ __forceinline__ void store(uint32_t i, const HitRec& hit, uint32_t* s_bins) const
@@ -82,8 +82,6 @@ struct ShadowIO {
     static constexpr bool kBins = false;
     ShadowStream s;
     WaveControl* ctl;
-    float*       film;
-    float        inv_spi;
     __device__ __forceinline__ uint32_t  count() const { return ctl->n_shadow; }
     __device__ __forceinline__ uint32_t  bin_count() const { return 0u; }
     __device__ __forceinline__ uint32_t* global_bins() const { return nullptr; }
@@ -101,8 +99,9 @@ struct ShadowIO {
     __device__ __forceinline__ void store(uint32_t i, const HitRec& hit, uint32_t*) const
     {
         if (hit.prim < 0) {
-            const float4 c = s.color_pixel[i];
-            float*       p = film + 3 * (size_t)__float_as_uint(c.w);
+            const float4 c       = s.color_pixel[i];
+            const float  inv_spi = ctl->set.inv_spi;
+            float*       p       = ctl->set.film + 3 * (size_t)__float_as_uint(c.w);
             atomicAdd(p + 0, c.x * inv_spi);
             atomicAdd(p + 1, c.y * inv_spi);
             atomicAdd(p + 2, c.z * inv_spi);
@@ -115,9 +114,10 @@ struct ShadowIO {
 // ---------------------------------------------------------------------------------------------------------
 
 // Head of the loop body of gpu_trace (driver/mapping_gpu.art:756-767): how many rays to regenerate, stream sizes.
-__global__ void begin_round_kernel(WaveControl* ctl, uint32_t capacity, uint32_t n_bins, uint32_t* host_done)
+__global__ void begin_round_kernel(WaveControl* ctl, uint32_t n_bins, uint32_t* host_done)
 {
     if (threadIdx.x == 0) {
+        const uint32_t capacity = ctl->set.capacity;
         const uint32_t n_surv = ctl->n_next;
         ctl->bounce_rays += n_surv;
         ctl->shadow_rays += ctl->n_shadow;
@@ -142,8 +142,9 @@ __global__ void begin_round_kernel(WaveControl* ctl, uint32_t capacity, uint32_t
     for (uint32_t b = threadIdx.x; b < n_bins; b += blockDim.x) ctl->bins[b] = 0u;
 }
 
-__global__ void reset_kernel(WaveControl* ctl, uint32_t total, uint32_t* host_done)
+__global__ void reset_kernel(WaveControl* ctl, const WaveSettings set, uint32_t total, uint32_t* host_done)
 {
+    ctl->set = set;
     ctl->n_cur = ctl->n_next = ctl->n_shadow = 0u;
     ctl->gen_base = ctl->gen_count = ctl->gen_first = 0u;
     ctl->next_id = 0u;
@@ -159,18 +160,20 @@ __global__ void reset_kernel(WaveControl* ctl, uint32_t total, uint32_t* host_do
 // K1, gpu_generate_rays (driver/mapping_gpu.art:618-667) with make_camera_emitter / make_list_emitter
 // (driver/emitter.art:6-31), make_perspective_camera (camera/perspective.art:29-41), make_uniform_pixel_sampler
 // (sampler/pixel_sampler.art:4-10) and init_pt_raypayload (technique/pathtracer.art:33-38).
-__global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __restrict__ ctl, const PathStream s, const ShadeScene sc,
-                                                       const WaveSettings set)
+__global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __restrict__ ctl, const PathStream s, const ShadeScene sc)
 {
+    const WaveSettings set = ctl->set;
     const uint32_t count = ctl->gen_count, base = ctl->gen_base, first = ctl->gen_first;
     const Vec3     eye{ sc.cam.eye[0], sc.cam.eye[1], sc.cam.eye[2] }, cdir{ sc.cam.dir[0], sc.cam.dir[1], sc.cam.dir[2] },
         up{ sc.cam.up[0], sc.cam.up[1], sc.cam.up[2] };
     const Mat3 view{ vnormalize(cross3(cdir, up)), up, cdir };
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
-        const uint32_t id     = first + k;
+        const uint32_t gid    = first + k;                 // id within the batch of iterations
+        const uint32_t it     = gid / set.per_iter;        // iteration offset: the batch regenerates across iterations
+        const uint32_t id     = gid - it * set.per_iter;   // ray id = (y * w + x) * spi + sample (mapping_gpu.art:655)
         const uint32_t sample = id % set.spi, pixel = id / set.spi;
         const uint32_t y = pixel / set.width, x = pixel - y * set.width;
-        Rnd            rnd{ create_random_seed(sample, set.iter, set.frame, x, y, set.seed), 1u };
+        Rnd            rnd{ create_random_seed(sample, set.iter + it, set.frame, x, y, set.seed), 1u };
         Vec3           org, dir;
         float          tmin, tmax;
         uint32_t       flags;
@@ -196,7 +199,7 @@ __global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __rest
         const uint32_t slot    = base + k;
         s.org_tmin[slot]       = make_float4(org.x, org.y, org.z, tmin);
         s.dir_tmax[slot]       = make_float4(dir.x, dir.y, dir.z, tmax);
-        s.meta[slot]           = make_uint4(id, rnd.counter, flags, 1u);
+        s.meta[slot]           = make_uint4(id, rnd.counter, flags | (it << 8), 1u);
         s.contrib_invpdf[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
         s.eta[slot]            = 1.0f;
     }
@@ -337,7 +340,7 @@ __device__ __noinline__ void shade_one(const ShadeScene& sc, const DeviceScene& 
     }
 
     const uint32_t y = pixel / set.width, x = pixel - y * set.width;
-    Rnd            rnd{ create_random_seed(sample, set.iter, set.frame, x, y, set.seed), meta.y };
+    Rnd            rnd{ create_random_seed(sample, set.iter + (meta.z >> 8), set.frame, x, y, set.seed), meta.y };
     const Vec3     out_dir = vneg(dir);
 
     // on_shadow (pathtracer.art:52-110): next event estimation
@@ -378,16 +381,18 @@ __device__ __noinline__ void shade_one(const ShadeScene& sc, const DeviceScene& 
     alive             = true;
     nx.org_tmin       = make_float4(surf.point.x, surf.point.y, surf.point.z, offset);
     nx.dir_tmax       = make_float4(ms.in_dir.x, ms.in_dir.y, ms.in_dir.z, flt_max);
-    nx.meta           = make_uint4(id, rnd.counter, kRayBounce, (uint32_t)(depth + 1));
+    nx.meta           = make_uint4(id, rnd.counter, kRayBounce | (meta.z & 0xFFFFFF00u), (uint32_t)(depth + 1));
     nx.contrib_invpdf = make_float4(nc.r, nc.g, nc.b, new_inv_pdf);
     nx.eta            = eta0 * ms.eta;
 }
 
 __global__ void __launch_bounds__(128) shade_kernel(WaveControl* __restrict__ ctl, const PathStream cur, const PathStream nxt,
                                                     const ShadowStream shq, const uint32_t* __restrict__ sorted, const ShadeScene sc,
-                                                    const DeviceScene geo, const WaveSettings set, float* __restrict__ film)
+                                                    const DeviceScene geo)
 {
-    const uint32_t n       = ctl->n_cur;
+    const WaveSettings set  = ctl->set;
+    float* const       film = set.film;
+    const uint32_t     n    = ctl->n_cur;
     const uint32_t lane    = threadIdx.x & 31u;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t step    = gridDim.x * blockDim.x;
@@ -433,14 +438,14 @@ __global__ void __launch_bounds__(128) shade_kernel(WaveControl* __restrict__ ct
 // ---------------------------------------------------------------------------------------------------------
 // Launchers
 // ---------------------------------------------------------------------------------------------------------
-cudaError_t launch_wave_reset(const WaveBuffers& buf, uint32_t total, cudaStream_t stream)
+cudaError_t launch_wave_reset(const WaveBuffers& buf, const WaveSettings& set, uint32_t total, cudaStream_t stream)
 {
-    reset_kernel<<<1, 1, 0, stream>>>(buf.ctl, total, buf.host_done);
+    reset_kernel<<<1, 1, 0, stream>>>(buf.ctl, set, total, buf.host_done);
     return cudaGetLastError();
 }
 
-cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene& sh, const WaveBuffers& buf,
-                              const WaveSettings& set, int parity, bool sort, int sm_count, cudaStream_t stream)
+cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene& sh, const WaveBuffers& buf, int parity,
+                              bool sort, int sm_count, cudaStream_t stream)
 {
     const PathStream& cur = buf.stream[parity & 1];
     const PathStream& nxt = buf.stream[(parity + 1) & 1];
@@ -448,13 +453,13 @@ cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene&
     if (n_bins > kWaveMaxBins) return cudaErrorInvalidValue;
     const int wide = sm_count * 8; // grid-stride kernels: a whole number of waves
 
-    begin_round_kernel<<<1, 256, 0, stream>>>(buf.ctl, set.capacity, n_bins, buf.host_done);
-    generate_kernel<<<wide, 256, 0, stream>>>(buf.ctl, cur, sh, set);
+    begin_round_kernel<<<1, 256, 0, stream>>>(buf.ctl, n_bins, buf.host_done);
+    generate_kernel<<<wide, 256, 0, stream>>>(buf.ctl, cur, sh);
     const PrimaryIO pio{ cur, buf.keys, buf.ent_mat, buf.ctl, n_bins };
     trace_kernel<PrimaryIO, false, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, pio, nullptr, buf.ctl->work_primary);
     if (sort) scatter_kernel<<<wide, 256, 0, stream>>>(buf.ctl, buf.keys, buf.sorted);
-    shade_kernel<<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene, set, buf.film);
-    const ShadowIO sio{ buf.shadow, buf.ctl, buf.film, set.inv_spi };
+    shade_kernel<<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene);
+    const ShadowIO sio{ buf.shadow, buf.ctl };
     trace_kernel<ShadowIO, true, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, sio, nullptr, buf.ctl->work_shadow);
     return cudaGetLastError();
 }

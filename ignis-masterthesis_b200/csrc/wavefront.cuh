@@ -23,7 +23,8 @@ namespace igb {
 struct PathStream {
     float4* org_tmin;       // ray origin, tmin
     float4* dir_tmax;       // ray direction, tmax
-    uint4*  meta;           // x: ray id = pixel * spi + sample, y: RNG counter (the `rnd` column), z: ray flags, w: depth
+    uint4*  meta;           // x: ray id = pixel * spi + sample, y: RNG counter (the `rnd` column),
+                            // z: ray flags (bits 0-7) | iteration offset within the batch (bits 8-31), w: depth
     float4* contrib_invpdf; // path payload: contrib rgb, inv_pdf (technique/pathtracer.art:7-12)
     float*  eta;            // path payload: eta
     uint4*  hit0;           // ent_id, prim_id, t, u (bit patterns)
@@ -39,6 +40,17 @@ struct ShadowStream {
 
 constexpr uint32_t kWaveMaxBins = 4096; // material bins + miss bin supported by the sort
 
+// Per-call settings; they live in the control block (device memory) so that the captured CUDA graph of a round
+// pair stays valid from call to call.
+struct WaveSettings {
+    uint32_t      spi, width, height, iter, frame, seed; // iter = first iteration of the batch
+    uint32_t      per_iter;                              // spi * width * height: ray ids per iteration
+    float         inv_spi;
+    uint32_t      capacity;
+    const float4* list_rays; // igtrace mode: normalised StreamRays (2 x float4 each), else nullptr
+    float*        film;      // w * h * 3, RGB sums
+};
+
 // Device-resident control block of one render() call.
 struct WaveControl {
     uint32_t n_cur;     // rays in the current primary stream (survivors + regenerated)
@@ -53,17 +65,11 @@ struct WaveControl {
     uint32_t rounds;
     uint32_t work_primary[2]; // persistent-kernel work counters (self-resetting)
     uint32_t work_shadow[2];
+    WaveSettings set;
     unsigned long long camera_rays, bounce_rays, shadow_rays;
     uint32_t bins[kWaveMaxBins];    // histogram of sort keys (material id, miss = n_mat)
     uint32_t offsets[kWaveMaxBins]; // exclusive scan of bins
     uint32_t cursors[kWaveMaxBins]; // scatter cursors
-};
-
-struct WaveSettings {
-    uint32_t      spi, width, height, iter, frame, seed;
-    float         inv_spi;
-    uint32_t      capacity;
-    const float4* list_rays; // igtrace mode: normalised StreamRays (2 x float4 each), else nullptr
 };
 
 struct WaveBuffers {
@@ -72,7 +78,6 @@ struct WaveBuffers {
     uint32_t*      keys;   // sort key per primary slot
     uint32_t*      sorted; // slot indices in key order
     WaveControl*   ctl;
-    float*         film;   // w * h * 3, RGB sums
     const int32_t* ent_mat; // material id per entity
     uint32_t*      host_done; // device alias of a mapped host flag
 };
@@ -81,11 +86,11 @@ namespace shade { struct ShadeScene; }
 
 // Enqueues ONE wavefront round (parity selects which stream buffer is current) on `stream`:
 // begin_round, generate, trace_primary(+histogram+scan), scatter, shade, trace_shadow(+splat).
-cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene& sh, const WaveBuffers& buf,
-                              const WaveSettings& set, int parity, bool sort, int sm_count, cudaStream_t stream);
+cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene& sh, const WaveBuffers& buf, int parity,
+                              bool sort, int sm_count, cudaStream_t stream);
 
-// Resets the control block for a new iteration (total = spi * w * h).
-cudaError_t launch_wave_reset(const WaveBuffers& buf, uint32_t total, cudaStream_t stream);
+// Resets the control block for a new call (total = spi * w * h * iterations) and stores its settings.
+cudaError_t launch_wave_reset(const WaveBuffers& buf, const WaveSettings& set, uint32_t total, cudaStream_t stream);
 
 // film[i] += src[i] (overwrite = false) or film[i] = src[i]
 cudaError_t launch_film_combine(float* film, const float* src, uint64_t count, bool overwrite, cudaStream_t stream);

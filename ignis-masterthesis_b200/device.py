@@ -79,14 +79,18 @@ class Device:
         sh = shading.c_shading()
         _lib.check(self._lib.igb200_assign_shading(self._h, C.addressof(sh)))
 
-    def render(self, width=0, height=0, spi=1, iteration=0, frame=0, seed=0, rays=None):
-        """One iteration (spi samples per pixel) accumulated into the film. rays != None: igtrace (list) mode."""
+    def render(self, width=0, height=0, spi=1, iteration=0, frame=0, seed=0, rays=None, iterations=1):
+        """`iterations` iterations (spi samples per pixel each) accumulated into the film, in one wavefront.
+        rays != None: igtrace (list) mode."""
         from .shading import RenderSettings
         if rays is not None:
             rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
         rs = RenderSettings(rays=rays.ctypes.data if rays is not None else None, ray_count=rays.size if rays is not None else 0,
                             spi=spi, width=width, height=height, iteration=iteration, frame=frame, user_seed=seed)
-        _lib.check(self._lib.igb200_render(self._h, C.addressof(rs)))
+        if iterations == 1:
+            _lib.check(self._lib.igb200_render(self._h, C.addressof(rs)))
+        else:
+            _lib.check(self._lib.igb200_render_iterations(self._h, C.addressof(rs), iterations))
         self._film = (rays.size, 1) if rays is not None else (width, height)
 
     def framebuffer(self, copy=True):

@@ -281,6 +281,13 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* shading);
 /* Device::render (Device.h:53): synchronous; accumulates into the film and bumps the iteration count. */
 int igb200_render(igb200_device* dev, const igb200_render_settings* settings);
 
+/* `count` consecutive iterations (settings->iteration ... + count - 1) in ONE wavefront: the ray queue regenerates
+ * across iteration boundaries, so the long low-occupancy tail of deep paths (dielectrics, max_depth 64) is paid once
+ * per call instead of once per iteration.  The samples are exactly those of `count` igb200_render calls (the seed
+ * hashes the iteration index, src/artic/core/random.art:34-43); only the order of the f32 film additions differs.
+ * The frontends' loop `for i < spp/spi: runtime.step()` (src/frontend/cli/main.cpp:120-139) maps onto one call. */
+int igb200_render_iterations(igb200_device* dev, const igb200_render_settings* settings, uint32_t count);
+
 /* Device::getFramebufferForHost / ForDevice (Device.h:63-64, Device.cpp:1330-1443): RGB f32, w*h*3, SUM over
  * iterations; *iterations = IterationCount.  name NULL, "" or "Color" = the film.  The pointer is owned by
  * the device and valid until resize / destroy.  device != 0 returns the device pointer (no copy). */

@@ -134,12 +134,31 @@ def test_reproducibility_and_film_lifecycle(ig, dev):
     assert n == 1 and s.shape == (16, 32, 3)
 
 
-def test_capacity_smaller_than_one_iteration(ig, oracle, dev):
-    # regeneration: 256 x 256 x 32 samples = 2 Mi rays flow through the 1 Mi-ray streams
-    tables, sh = room_scene(ig, 256, depth=4)
-    film, stats = _render(dev, tables, sh, 256, 256, 32, 1, seed=9)
+def test_batched_iterations_equal_single_iterations(ig, dev):
+    # igb200_render_iterations: one wavefront over 5 iterations == 5 igb200_render calls (same samples, other add order)
+    tables, sh = room_scene(ig, 96, depth=6)
+    a, sa = _render(dev, tables, sh, 96, 96, 3, 5, seed=8, first=2)
+    dev.resize(96, 96)
+    dev.render(96, 96, spi=3, iteration=2, seed=8, iterations=5)
+    b, n = dev.framebuffer()
+    st = dev.render_stats()
+    assert n == 5
+    np.testing.assert_allclose(a, b, rtol=2e-5, atol=1e-6)
+    assert tuple(sa) == (st["camera_rays"], st["bounce_rays"], st["shadow_rays"])
+
+
+def test_capacity_smaller_than_one_iteration(ig, oracle, monkeypatch):
+    # regeneration: 256 x 256 x 8 samples = 512 Ki rays flow through 64 Ki-ray streams
+    monkeypatch.setenv("IGB200_WAVE_CAPACITY", "65536")
+    small = ig.Device(0)
+    try:
+        tables, sh = room_scene(ig, 256, depth=4)
+        film, stats = _render(small, tables, sh, 256, 256, 8, 1, seed=9)
+        assert small.render_stats()["rounds"] >= 8
+    finally:
+        small.close()
     osc = oracle.OracleScene(tables)
-    ref = osc.render(sh, 256, 256, spi=32, iterations=1, seed=9)
+    ref = osc.render(sh, 256, 256, spi=8, iterations=1, seed=9)
     _assert_parity(film, ref, stats, osc.ray_stats.astype(np.int64))
 
 
