@@ -41,12 +41,16 @@ __device__ __forceinline__ float dot4(float ax, float ay, float az, float aw, fl
     return __fmaf_rn(ax, bx, __fmaf_rn(ay, by, __fmaf_rn(az, bz, aw * bw)));
 }
 
-// Box-test reciprocal: |d| clamped away from zero so 0 * idir never produces NaN.
+// Box-test reciprocal: |d| clamped away from zero so 0 * idir never produces NaN.  One MUFU.RCP (1 ulp): box tests
+// carry no parity requirement and their exit distance has kBoxSlack of head room.
 __device__ __forceinline__ float box_rcp(float d)
 {
     const float eps = 8.271806125530277e-25f; // 2^-80
-    return 1.0f / (fabsf(d) > eps ? d : copysignf(eps, d));
+    float       r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fabsf(d) > eps ? d : copysignf(eps, d)));
+    return r;
 }
+constexpr float kBoxSlack = 1.000002f; // ~17 ulp on the exit distance
 
 __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x)
 {
@@ -111,8 +115,8 @@ __device__ __forceinline__ uint32_t intersect_children(const uint4 n0, const uin
             const float t1y = __fmaf_rn(byte_to_float(fary, j), sy, oy);
             const float t1z = __fmaf_rn(byte_to_float(farz, j), sz, oz);
             const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
-            // 2-ulp slack on the exit distance: the box test must never reject what the triangle test accepts
-            const float cmax = fminf(fminf(fminf(t1x, t1y), t1z) * 1.0000004f, tmax);
+            // slack on the exit distance: the box test must never reject what the triangle test accepts
+            const float cmax = fminf(fminf(fminf(t1x, t1y), t1z) * kBoxSlack, tmax);
             if (cmin <= cmax) hitmask |= extract_byte(child_bits4, j) << extract_byte(bit_index4, j);
         }
     }
@@ -314,7 +318,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                     const float t0y = (l0.y - ray.org.y) * ray.idir.y, t1y = (l1.y - ray.org.y) * ray.idir.y;
                     const float t0z = (l0.z - ray.org.z) * ray.idir.z, t1z = (l1.z - ray.org.z) * ray.idir.z;
                     const float entry = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tmin));
-                    const float exit_ = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z)) * 1.0000004f;
+                    const float exit_ = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z)) * kBoxSlack;
                     if (!(entry <= fminf(exit_, hit.t))) continue;
 
                     const float4 l2 = __ldg(lp + 2), l3 = __ldg(lp + 3), l4 = __ldg(lp + 4);
