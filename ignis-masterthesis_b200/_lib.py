@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libignis_b200.so")
+LIB_PATH = os.environ.get("IGB200_LIB") or os.path.join(_HERE, "lib", "libignis_b200.so")  # IGB200_LIB: experiment builds
 
 # Every symbol include/ignis_b200.h declares (checked by tests/test_abi.py).
 ABI_SYMBOLS = [
