@@ -205,24 +205,55 @@ __global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __rest
     }
 }
 
-// Scatter step of the sort (gpu_sort_primary, driver/mapping_gpu.art:465-471), on indices only: warp-aggregated
-// cursor bump per key (lanes with equal keys are grouped with match.any).
+// Scatter step of the sort (gpu_sort_primary, driver/mapping_gpu.art:465-471), on indices only.  Each block ranks a
+// tile of keys in shared memory (lanes with equal keys are grouped with match.any, one shared atomic per group),
+// reserves one range per key with ONE global atomic per key and tile, then writes the slot indices.
+constexpr int kScatterItems = 8; // keys per thread and tile
 __global__ void __launch_bounds__(256) scatter_kernel(WaveControl* __restrict__ ctl, const uint32_t* __restrict__ keys,
-                                                      uint32_t* __restrict__ sorted)
+                                                      uint32_t* __restrict__ sorted, const uint32_t n_bins)
 {
+    __shared__ uint32_t s_cnt[kMaxSmemBins], s_base[kMaxSmemBins];
     const uint32_t n    = ctl->n_cur;
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t step = gridDim.x * blockDim.x;
-    for (uint32_t i0 = blockIdx.x * blockDim.x; i0 < n; i0 += step) { // warp-uniform trip count
-        const uint32_t i     = i0 + threadIdx.x;
-        const bool     valid = i < n;
-        const uint32_t key   = valid ? keys[i] : 0xFFFFFFFFu;
-        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, key);
-        const uint32_t lead  = __ffs(peers) - 1u;
-        uint32_t       base  = 0u;
-        if (valid && lane == lead) base = ctl->offsets[key] + atomicAdd(ctl->cursors + key, (uint32_t)__popc(peers));
-        base = __shfl_sync(0xFFFFFFFFu, base, lead);
-        if (valid) sorted[base + __popc(peers & ((1u << lane) - 1u))] = i;
+    const uint32_t tile = blockDim.x * kScatterItems;
+    if (n_bins > (uint32_t)kMaxSmemBins) { // many materials: warp-aggregated global cursors
+        for (uint32_t i0 = blockIdx.x * blockDim.x; i0 < n; i0 += gridDim.x * blockDim.x) {
+            const uint32_t i     = i0 + threadIdx.x;
+            const bool     valid = i < n;
+            const uint32_t key   = valid ? keys[i] : 0xFFFFFFFFu;
+            const uint32_t peers = __match_any_sync(0xFFFFFFFFu, key);
+            const uint32_t lead  = __ffs(peers) - 1u;
+            uint32_t       base  = 0u;
+            if (valid && lane == lead) base = ctl->offsets[key] + atomicAdd(ctl->cursors + key, (uint32_t)__popc(peers));
+            base = __shfl_sync(0xFFFFFFFFu, base, lead);
+            if (valid) sorted[base + __popc(peers & ((1u << lane) - 1u))] = i;
+        }
+        return;
+    }
+    for (uint32_t t0 = blockIdx.x * tile; t0 < n; t0 += gridDim.x * tile) { // block-uniform trip count
+        for (uint32_t b = threadIdx.x; b < n_bins; b += blockDim.x) s_cnt[b] = 0u;
+        __syncthreads();
+        uint32_t key[kScatterItems], rank[kScatterItems];
+#pragma unroll
+        for (int k = 0; k < kScatterItems; ++k) {
+            const uint32_t i = t0 + k * blockDim.x + threadIdx.x;
+            key[k]           = i < n ? keys[i] : 0xFFFFFFFFu;
+            const uint32_t peers = __match_any_sync(0xFFFFFFFFu, key[k]);
+            const uint32_t lead  = __ffs(peers) - 1u;
+            uint32_t       base  = 0u;
+            if (i < n && lane == lead) base = atomicAdd(s_cnt + key[k], (uint32_t)__popc(peers));
+            rank[k] = __shfl_sync(0xFFFFFFFFu, base, lead) + __popc(peers & ((1u << lane) - 1u));
+        }
+        __syncthreads();
+        for (uint32_t b = threadIdx.x; b < n_bins; b += blockDim.x)
+            if (s_cnt[b]) s_base[b] = ctl->offsets[b] + atomicAdd(ctl->cursors + b, s_cnt[b]);
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < kScatterItems; ++k) {
+            const uint32_t i = t0 + k * blockDim.x + threadIdx.x;
+            if (i < n) sorted[s_base[key[k]] + rank[k]] = i;
+        }
+        __syncthreads();
     }
 }
 
@@ -257,7 +288,7 @@ __device__ __forceinline__ void splat(float* film, uint32_t pixel, Color c, floa
     atomicAdd(p + 2, c.b * inv_spi);
 }
 
-__device__ __noinline__ void shade_one(const ShadeScene& sc, const DeviceScene& geo, const WaveSettings& set, const PathStream& cur,
+__device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScene& geo, const WaveSettings& set, const PathStream& cur,
                                        uint32_t i, float* film, bool& alive, NextState& nx, bool& has_shadow, ShadowState& sh)
 {
     const igb200_technique& tech = sc.tech;
@@ -457,7 +488,7 @@ cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene&
     generate_kernel<<<wide, 256, 0, stream>>>(buf.ctl, cur, sh);
     const PrimaryIO pio{ cur, buf.keys, buf.ent_mat, buf.ctl, n_bins };
     trace_kernel<PrimaryIO, false, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, pio, nullptr, buf.ctl->work_primary);
-    if (sort) scatter_kernel<<<wide, 256, 0, stream>>>(buf.ctl, buf.keys, buf.sorted);
+    if (sort) scatter_kernel<<<wide / 2, 256, 0, stream>>>(buf.ctl, buf.keys, buf.sorted, n_bins);
     shade_kernel<<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene);
     const ShadowIO sio{ buf.shadow, buf.ctl };
     trace_kernel<ShadowIO, true, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, sio, nullptr, buf.ctl->work_shadow);
