@@ -43,6 +43,16 @@ def load_oracle():
     return pyoracle
 
 
+def measured_traffic(n):
+    """DRAM bytes (read + write) per launch of the dominant kernel from the committed ncu capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            t = json.load(f)
+        return (t["dram_bytes_read"] + t["dram_bytes_write"]) * (n / t["rays_per_launch"])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -353,7 +363,7 @@ def run_ours(args, rank, world, local_rank):
             "gpu_launches": args.steps,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_kind": peak_kind, "kernel": "trace_kernel<closest>",
+                         "traffic": measured_traffic(n), "peak_kind": peak_kind, "kernel": "trace_kernel<closest>",
                          "kernel_ms": kernel_ms, "bytes_per_ray": bytes_per_ray,
                          "per_ray": {"nodes": n_node, "tris": n_tri, "entities": n_ent}},
             "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
