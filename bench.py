@@ -349,7 +349,11 @@ def run_ours(args, rank, world, local_rank):
         peak, peak_kind = measured_peak()
         achieved = bytes_per_ray * n / (kernel_ms * 1e-3) / 1e9
         # ---- CPU baseline: oracle on a bounded sample ----
-        cpu_val, cores, sample = oracle_throughput(pkg, tables, rays, min(n, args.cpu_rays))
+        # (rank 0 at N=1 only: at N>1 the host cores are shared with the other ranks' launch threads)
+        cpu = None
+        if world == 1:
+            cpu_val, cores, sample = oracle_throughput(pkg, tables, rays, min(n, args.cpu_rays))
+            cpu = {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -366,10 +370,10 @@ def run_ours(args, rank, world, local_rank):
                          "traffic": measured_traffic(n), "peak_kind": peak_kind, "kernel": "trace_kernel<closest>",
                          "kernel_ms": kernel_ms, "bytes_per_ray": bytes_per_ray,
                          "per_ray": {"nodes": n_node, "tris": n_tri, "entities": n_ent}},
-            "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "cpu_baseline": cpu,
         }
         if pt is not None:
-            pt["cpu_baseline"] = oracle_samples_per_s(pkg)
+            pt["cpu_baseline"] = oracle_samples_per_s(pkg) if world == 1 else None
             line["path_tracer"] = pt
             line["gpu_launches"] += pt["gpu_launches"]
         print(json.dumps(line), flush=True)

@@ -139,6 +139,205 @@ def make_box(origin, x, y, z):
     return Mesh(vs, fs, ns, ts)
 
 
+# Procedural primitives: vertex and face ORDER follows src/runtime/mesh/TriMesh.cpp:747-1057 (primitive ids are the
+# face order), arithmetic in float32 like the reference's Eigen Vector3f.
+_F = np.float32
+_PI = _F(3.14159265358979323846)
+
+
+def _nrm(v):
+    v = np.asarray(v, _F)
+    return (v / _F(np.sqrt(np.dot(v, v), dtype=_F))).astype(_F)
+
+
+def _frame(n):  # Tangent::frame == frame_duff, src/runtime/math/Tangent.h:50-72
+    n = np.asarray(n, _F)
+    sign = _F(math.copysign(1.0, float(n[2])))
+    a = _F(-1.0) / (sign + n[2])
+    b = n[0] * n[1] * a
+    nx = np.array([_F(1) + sign * n[0] * n[0] * a, sign * b, -sign * n[0]], _F)
+    ny = np.array([b, sign + n[1] * n[1] * a, -n[1]], _F)
+    return nx, ny
+
+
+class _Soup:
+    def __init__(self):
+        self.v, self.n, self.t, self.f = [], [], [], []
+
+    def mesh(self, normals=True):
+        return Mesh(self.v, self.f, self.n if normals else None, self.t)
+
+
+def _add_disk(m, origin, n, nx, ny, radius, sections, fill_cap, flip=False):  # addDisk, TriMesh.cpp:747-780
+    origin, radius = np.asarray(origin, _F), _F(radius)
+    step = _F(1.0) / _F(sections)
+    off = len(m.v)
+    if fill_cap:
+        m.v.append(origin); m.n.append(n); m.t.append((0, 0))
+    for i in range(sections):
+        ang = _F(2) * _PI * step * _F(i)
+        x, y = _F(np.cos(ang, dtype=_F)), _F(np.sin(ang, dtype=_F))
+        m.v.append(radius * nx * x + radius * ny * y + origin)
+        m.n.append(n)
+        m.t.append((_F(0.5) * (x + _F(1)), _F(0.5) * (y + _F(1))))
+    if not fill_cap:
+        return
+    for i in range(sections):
+        c, nc = i + 1, (i + 1 if i + 1 < sections else 0) + 1
+        m.f.append((off, nc + off, c + off) if flip else (off, c + off, nc + off))
+
+
+def make_disk(center, normal, radius, sections):  # MakeDisk :955-965
+    sections = max(3, int(sections))
+    n = np.asarray(normal, _F)
+    nx, ny = _frame(n)
+    m = _Soup()
+    _add_disk(m, center, n, nx, ny, radius, sections, True)
+    return m.mesh()
+
+
+def make_cone(base_center, base_radius, tip, sections, fill_cap):  # MakeCone :1005-1031
+    sections = max(3, int(sections))
+    base_center, tip = np.asarray(base_center, _F), np.asarray(tip, _F)
+    h = _nrm(base_center - tip)
+    nx, ny = _frame(h)
+    m = _Soup()
+    _add_disk(m, base_center, h, nx, ny, base_radius, sections, fill_cap)
+    m.v.append(tip); m.n.append(h); m.t.append((0, 0))
+    start, tp = (1 if fill_cap else 0), len(m.v) - 1
+    for i in range(sections):
+        c, nc = i + start, (i + 1 if i + 1 < sections else 0) + start
+        m.f.append((c, tp, nc))
+    return m.mesh(normals=False)  # computeVertexNormals
+
+
+def make_cylinder(base_center, base_radius, top_center, top_radius, sections, fill_cap):  # MakeCylinder :1033-1057
+    sections = max(3, int(sections))
+    base_center, top_center = np.asarray(base_center, _F), np.asarray(top_center, _F)
+    h = _nrm(base_center - top_center)
+    nx, ny = _frame(h)
+    m = _Soup()
+    _add_disk(m, base_center, h, nx, ny, base_radius, sections, fill_cap)
+    off = len(m.v)
+    _add_disk(m, top_center, h, nx, ny, top_radius, sections, fill_cap, True)
+    start = 1 if fill_cap else 0
+    for i in range(sections):
+        c, nc = i + start, (i + 1 if i + 1 < sections else 0) + start
+        m.f.append((c, c + off, nc))
+        m.f.append((c + off, nc + off, nc))
+    return m.mesh(normals=False)
+
+
+def make_uv_sphere(center, radius, stacks, slices):  # MakeUVSphere :782-835 (keeps its degenerate pole/wrap faces)
+    center, radius = np.asarray(center, _F), _F(radius)
+    drho, dtheta = _F(3.141592) / _F(stacks), _F(2) * _F(3.141592) / _F(slices)
+    m = _Soup()
+    for i in range(stacks + 1):
+        rho = _F(i) * drho
+        srho, crho = _F(np.sin(rho, dtype=_F)), _F(np.cos(rho, dtype=_F))
+        for j in range(slices):
+            theta = _F(j) * dtheta
+            stheta, ctheta = -_F(np.sin(theta, dtype=_F)), _F(np.cos(theta, dtype=_F))
+            n = np.array([stheta * srho, ctheta * srho, crho], _F)
+            m.v.append(n * radius + center); m.n.append(n)
+            m.t.append((_F(0.5) * theta / _PI, rho / _PI))
+    for i in range(stacks + 1):
+        cur, nxt = i * slices, ((i + 1) % (stacks + 1)) * slices
+        for j in range(slices):
+            nj = (j + 1) % slices
+            id0, id1, id2, id3 = cur + j, cur + nj, nxt + j, nxt + nj
+            m.f.append((id2, id3, id1))
+            m.f.append((id2, id1, id0))
+    return m.mesh()
+
+
+def make_ico_sphere(center, radius, subdivisions):  # MakeIcoSphere :838-953
+    golden = _F(1.618033989)
+    v = []
+    for d in range(3):
+        for s1 in (-1, 1):
+            for s2 in (-1, 1):
+                vec = np.zeros(3, _F)
+                vec[(d + 1) % 3] = golden * _F(s1)
+                vec[(d + 2) % 3] = _F(s2)
+                v.append(_nrm(vec))
+    idx = lambda d, s1, s2: d * 4 + (s1 + 1) + ((s2 + 1) >> 1)
+    f = []
+    for s1 in (-1, 1):
+        for s2 in (-1, 1):
+            for s3 in (-1, 1):
+                rev = s1 * s2 * s3 == -1
+                i1, i2, i3 = idx(0, s1, s2), idx(1, s2, s3), idx(2, s3, s1)
+                f.append((i1, i3, i2) if rev else (i1, i2, i3))
+    for d in range(3):
+        for s1 in (-1, 1):
+            for s2 in (-1, 1):
+                rev = s1 * s2 == 1
+                i2, i1, i3 = idx(d, s1, -1), idx(d, s1, 1), idx((d + 2) % 3, s2, s1)
+                f.append((i1, i3, i2) if rev else (i1, i2, i3))
+    for _ in range(int(subdivisions)):
+        edge = {}
+        for tri in f:
+            for j in range(3):
+                i1, i2 = tri[j], tri[(j + 1) % 3]
+                if i1 >= i2:
+                    continue
+                edge[(i1, i2)] = len(v)
+                v.append(_nrm(v[i1] + v[i2]))
+        nf = []
+        for tri in f:
+            ec = [edge[(min(tri[j], tri[(j + 1) % 3]), max(tri[j], tri[(j + 1) % 3]))] for j in range(3)]
+            nf.append((ec[0], ec[1], ec[2]))
+            for j in range(3):
+                nf.append((tri[j], ec[j % 3], ec[(j + 2) % 3]))
+        f = nf
+    v = np.asarray(v, _F)
+    n = np.stack([_nrm(x) for x in v])
+    theta = np.arccos(n[:, 2], dtype=_F)
+    phi = np.arctan2(-n[:, 0], n[:, 1], dtype=_F)
+    phi = np.where(phi < 0, phi + _F(2) * _PI, phi).astype(_F)
+    t = np.stack([phi / (_F(2) * _PI), theta / _PI], axis=1)
+    mesh = Mesh(v, f, n, t)
+    center, radius = np.asarray(center, np.float64), float(radius)
+    if np.any(center != 0) or radius != 1:
+        xf = np.eye(4)
+        xf[:3, :3] *= radius
+        xf[:3, 3] = center
+        mesh.transform(xf)
+    return mesh
+
+
+def subdivide(mesh):  # TriMesh::subdivide without mask, TriMesh.cpp:351-401 (edge ids in first-seen order :300-321)
+    edges = {}
+    for tri in mesh.f:
+        for a, b in ((tri[0], tri[1]), (tri[1], tri[2]), (tri[2], tri[0])):
+            edges.setdefault((min(a, b), max(a, b)), len(edges))
+    nv = mesh.v.shape[0]
+    ea = np.array([k[0] for k in edges], np.int64)
+    eb = np.array([k[1] for k in edges], np.int64)
+    v = np.concatenate([mesh.v, ((mesh.v[ea] + mesh.v[eb]) / _F(2)).astype(_F)])
+    nsum = mesh.n[ea] + mesh.n[eb]
+    n = np.concatenate([mesh.n, (nsum / np.sqrt((nsum * nsum).sum(1, keepdims=True), dtype=_F)).astype(_F)])
+    t = np.concatenate([mesh.t, ((mesh.t[ea] + mesh.t[eb]) / _F(2)).astype(_F)])
+    f = []
+    for v0, v1, v2 in mesh.f:
+        e01 = nv + edges[(min(v0, v1), max(v0, v1))]
+        e12 = nv + edges[(min(v1, v2), max(v1, v2))]
+        e20 = nv + edges[(min(v2, v0), max(v2, v0))]
+        f += [(v0, e01, e20), (v1, e12, e01), (v2, e20, e12), (e01, e12, e20)]
+    return Mesh(v, f, n, t)
+
+
+def face_normals_as_vertex_normals(mesh):  # setupFaceNormalsAsVertexNormals, TriMesh.cpp:152-197
+    idx = mesh.f.reshape(-1)
+    v = mesh.v[idx]
+    t = mesh.t[idx]
+    e1, e2 = v[1::3] - v[0::3], v[2::3] - v[0::3]
+    fn = np.cross(e1, e2).astype(_F)
+    fn = (fn / np.sqrt((fn * fn).sum(1, keepdims=True), dtype=_F)).astype(_F)
+    return Mesh(v, np.arange(v.shape[0], dtype=np.uint32).reshape(-1, 3), np.repeat(fn, 3, axis=0), t)
+
+
 def load_obj(path):
     """OBJ subset: v / vn / vt / f, fan triangulation, vertices numbered by first appearance of the
     (v, vn, vt) triple (ObjFile.cpp:113-173); missing normals -> computeVertexNormals (ObjFile.cpp:193-196)."""
@@ -290,16 +489,42 @@ def build_shape(elem, base):
     elif ty in ("obj", "ply", "external"):
         path = os.path.join(base, elem["filename"])
         mesh = load_obj(path) if path.lower().endswith(".obj") else load_ply(path)
+    elif ty == "icosphere":  # setup_mesh_ico_sphere, TriMeshProvider.cpp:52-58
+        mesh = make_ico_sphere(elem.get("center", (0, 0, 0)), elem.get("radius", 1.0), elem.get("subdivisions", 4))
+    elif ty == "uvsphere":  # :60-67
+        mesh = make_uv_sphere(elem.get("center", (0, 0, 0)), elem.get("radius", 1.0), elem.get("stacks", 32), elem.get("slices", 16))
+    elif ty == "cylinder":  # :69-86
+        r0 = elem.get("radius", 1.0) if "radius" in elem else elem.get("bottom_radius", 1.0)
+        r1 = r0 if "radius" in elem else elem.get("top_radius", r0)
+        mesh = make_cylinder(elem.get("p0", (0, 0, 0)), r0, elem.get("p1", (0, 0, 1)), r1, elem.get("sections", 32),
+                             elem.get("filled", True))
+    elif ty == "cone":  # :88-96
+        mesh = make_cone(elem.get("p0", (0, 0, 0)), elem.get("radius", 1.0), elem.get("p1", (0, 0, 1)), elem.get("sections", 32),
+                         elem.get("filled", True))
+    elif ty == "disk":  # :98-105
+        mesh = make_disk(elem.get("origin", (0, 0, 0)), elem.get("normal", (0, 0, 1)), elem.get("radius", 1.0),
+                         elem.get("sections", 32))
     elif ty == "sphere":
         return ("sphere", np.asarray(elem.get("center", (0, 0, 0)), np.float32), float(elem.get("radius", 1.0)))
     else:
         raise ValueError(f"shape type '{ty}' is outside the supported subset")
     if elem.get("flip_normals", False):
         mesh.flip_normals()
+    if elem.get("face_normals", False):  # TriMeshProvider.cpp:529-536
+        mesh = face_normals_as_vertex_normals(mesh)
+    elif elem.get("smooth_normals", False):
+        mesh.compute_vertex_normals()
     if "transform" in elem:
         m = parse_transform(elem["transform"])
         if not np.allclose(m, np.eye(4)):
             mesh.transform(m)
+    if elem.get("subdivision", 0) > 0:  # handleModification, TriMeshProvider.cpp:435-473 (refinement/displacement: no)
+        for _ in range(int(elem["subdivision"])):
+            mesh = subdivide(mesh)
+        if elem.get("smooth_normals", False):
+            mesh.compute_vertex_normals()
+        else:
+            mesh = face_normals_as_vertex_normals(mesh)
     return ("trimesh", mesh)
 
 

@@ -25,8 +25,12 @@ JOBS = [  # (fixture, scene file, reference image, width, height)
     ("emissive-plane", "evaluation/emissive-plane.json", "ref-emissive-plane-4096.exr", None, None),
     ("plane-d6", "evaluation/plane-d6.json", "ref-plane-d6-4096.exr", None, None),
     ("diamond", "diamond_scene.json", None, 1920, 1080),
+    ("primitives", "primitives.json", None, 1024, 1024),  # BASELINE.json configs[1]
 ]
+only = set(sys.argv[1:])
 for name, scene, ref, w, h in JOBS:
+    if only and name not in only:
+        continue
     tables, sh, w, h, info = sceneio.load_scene(f"{REF}/{scene}", width=w, height=h)
     fixtures.save_fixture(os.path.join(OUT, name + ".npz"), tables, sh, w, h, exr(ref) if ref else None,
                           meta=f"{scene}; reference image {ref}")

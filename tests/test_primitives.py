@@ -1,0 +1,120 @@
+"""Procedural primitives of the scene reader (reference src/runtime/mesh/TriMesh.cpp:747-1057,
+shape/TriMeshProvider.cpp:43-105,435-473): counts, order-sensitive structure and orientation, and the C2 scene
+(scenes/primitives.json as tests/golden/primitives.npz) through the oracle."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+
+from render_common import load_golden
+
+io = importlib.import_module("ignis-masterthesis_b200.sceneio")
+
+
+def _edges(f):
+    e = np.concatenate([f[:, [0, 1]], f[:, [1, 2]], f[:, [2, 0]]])
+    return e
+
+
+def _closed_and_consistent(f):
+    """Every directed edge appears once and its reverse appears once: watertight with consistent winding."""
+    e = _edges(f.astype(np.int64))
+    fwd = set(map(tuple, e))
+    return len(fwd) == len(e) and all((b, a) in fwd for a, b in fwd)
+
+
+def _outward(m, center=(0, 0, 0)):
+    v = m.v.astype(np.float64)
+    fn = np.cross(v[m.f[:, 1]] - v[m.f[:, 0]], v[m.f[:, 2]] - v[m.f[:, 0]])
+    c = v[m.f].mean(axis=1) - np.asarray(center)
+    d = (fn * c).sum(1)
+    return d[np.linalg.norm(fn, axis=1) > 1e-12]
+
+
+def test_ico_sphere():
+    m = io.make_ico_sphere((0, 0, 0), 1.0, 4)
+    assert m.f.shape == (20 * 4 ** 4, 3) and m.v.shape == (10 * 4 ** 4 + 2, 3)
+    assert np.allclose(np.linalg.norm(m.v, axis=1), 1, atol=1e-6) and np.allclose(m.n, m.v, atol=1e-6)
+    assert _closed_and_consistent(m.f) and np.all(_outward(m) > 0)
+    # base icosahedron first: 12 vertices of (0, +-phi, +-1) cyclic, in d / s1 / s2 order (TriMesh.cpp:843-853)
+    g = np.array([0, -1.618033989, -1.0]) / np.linalg.norm([1.618033989, 1.0])
+    assert np.allclose(m.v[0], g, atol=1e-6)
+    m2 = io.make_ico_sphere((1, 2, 3), 0.5, 1)
+    assert m2.f.shape == (80, 3) and np.allclose(np.linalg.norm(m2.v - [1, 2, 3], axis=1), 0.5, atol=1e-6)
+    assert np.all(m.t >= 0) and np.all(m.t <= 1)
+
+
+def test_uv_sphere_keeps_the_reference_layout():
+    m = io.make_uv_sphere((0, 0, 0), 1.0, 32, 16)
+    assert m.v.shape == (33 * 16, 3) and m.f.shape == (33 * 16 * 2, 3)   # incl. the degenerate wrap-around row
+    assert np.allclose(np.linalg.norm(m.v, axis=1), 1, atol=1e-5)
+    assert np.allclose(m.v[0], (0, 0, 1), atol=1e-6) and np.allclose(m.v[-1][2], -1, atol=1e-5)
+    assert tuple(m.f[0]) == (16, 17, 1) and tuple(m.f[1]) == (16, 1, 0)
+    assert np.all(_outward(m)[: 32 * 16 * 2 - 64] >= -1e-9)
+
+
+@pytest.mark.parametrize("filled", [True, False])
+def test_cylinder_and_cone(filled):
+    c = io.make_cylinder((0, 0, 0), 1.0, (0, 0, 1), 1.0, 32, filled)
+    assert c.v.shape[0] == (66 if filled else 64) and c.f.shape[0] == (128 if filled else 64)
+    assert np.all(_outward(c, (0, 0, 0.5)) > 0)
+    if filled:
+        assert _closed_and_consistent(c.f)
+    k = io.make_cone((0, 0, 0), 1.0, (0, 0, 1), 32, filled)
+    assert k.v.shape[0] == (34 if filled else 33) and k.f.shape[0] == (64 if filled else 32)
+    assert np.allclose(k.v[-1], (0, 0, 1)) and np.all(_outward(k, (0, 0, 0.3)) > 0)
+    assert np.allclose(np.linalg.norm(c.n, axis=1), 1, atol=1e-5) and np.allclose(np.linalg.norm(k.n, axis=1), 1, atol=1e-5)
+
+
+def test_disk_and_frame():
+    d = io.make_disk((0, 0, 0), (0, 0, 1), 1.0, 32)
+    assert d.v.shape == (33, 3) and d.f.shape == (32, 3) and np.allclose(d.v[0], 0)
+    assert np.allclose(d.v[1], (1, 0, 0), atol=1e-6)           # frame_duff(+z) = (x, y)
+    assert np.all(_outward(d, (0, 0, -1)) > 0)                  # faces look along +normal
+    assert io.make_disk((0, 0, 0), (0, 0, 1), 1.0, 2).f.shape == (3, 3)   # sections clamped to 3
+    for n in ((0, 0, -1), (0.6, 0, 0.8), (0, 1, 0)):
+        nx, ny = io._frame(np.asarray(n, np.float32))
+        assert abs(np.dot(nx, ny)) < 1e-6 and np.allclose(np.cross(nx, ny), n, atol=1e-6)
+
+
+def test_subdivided_cube_is_the_768_triangle_mesh():
+    kind, m = io.build_shape({"type": "cube", "name": "SubdivBox", "subdivision": 3}, ".")
+    assert kind == "trimesh" and m.f.shape == (768, 3) and m.v.shape == (768 * 3, 3)     # 768 tris
+    assert np.array_equal(m.f.reshape(-1), np.arange(768 * 3))                            # face normals: unshared vertices
+    assert np.all(np.abs(m.v).max(axis=1) == 1.0)                                         # all on the cube surface
+    v = m.v.astype(np.float64)
+    fn = np.cross(v[1::3] - v[0::3], v[2::3] - v[0::3])
+    assert np.allclose(np.linalg.norm(fn, axis=1).sum() / 2, 24.0)                        # area preserved
+    assert np.allclose(m.n[0::3], fn / np.linalg.norm(fn, axis=1, keepdims=True), atol=1e-6)
+    # one level: corner triangles first, centre triangle last (TriMesh.cpp:389-392)
+    one = io.subdivide(io.make_plane((0, 0, 0), (1, 0, 0), (0, 1, 0)))
+    assert one.f.shape == (8, 3) and one.v.shape == (9, 3) and tuple(one.f[3]) == (4, 5, 6)
+
+
+def test_c2_scene_through_the_oracle(ig, oracle):
+    tables, sh, w, h, _ = load_golden(ig, "primitives")
+    assert tables.entity_count == 11 and tables.material_count == 2
+    osc = oracle.OracleScene(tables)
+    a = osc.render(sh, 96, 96, spi=4, iterations=2, seed=42)
+    stats = osc.ray_stats.copy()
+    b = osc.render(sh, 96, 96, spi=4, iterations=2, seed=42, threads=1)
+    assert np.array_equal(a, b)                                   # test_reproducibility.py contract
+    assert stats[0] == 96 * 96 * 8 and stats[1] == stats[2]       # depth 2: one NEE ray per surviving bounce
+    # unit environment, albedo 0.8 / 0.95, literal (two-sided) diffuse: every pixel within (0, 2]
+    assert np.all(np.isfinite(a)) and a.min() >= 0 and 0.5 < a.mean() / 2 < 1.5
+    # the analytic sphere entity is hit (debug entity-id mode 17 -> id 1) next to ten trimesh entities
+    import ctypes
+    sh.set_debug(17)
+    ids = osc.render(sh, 96, 96, spi=1, iterations=1, seed=0)
+    sh.set_path(max_depth=2)
+    seen = set(np.unique(np.round(ids[:, :, 0]).astype(int)))
+    assert 1 in seen and len(seen) >= 5
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/scenes"), reason="reference tree only exists in the build container")
+def test_fixture_is_what_the_reader_builds_from_the_reference_scene(ig):
+    tables, sh, w, h, _ = io.load_scene("/root/reference/scenes/primitives.json", width=1024, height=1024)
+    ft, fsh, fw, fh, _ = load_golden(ig, "primitives")
+    assert (w, h) == (fw, fh) and tables.entity_count == ft.entity_count
+    assert bytes(tables.shape_data) == bytes(ft.shape_data) and np.array_equal(tables.entities, ft.entities)

@@ -60,7 +60,8 @@ def test_room_matches_oracle(ig, oracle, dev, one_sided):
     _assert_parity(film, ref, stats, osc.ray_stats.astype(np.int64))
 
 
-@pytest.mark.parametrize("name,w,h", [("diamond", 240, 135), ("cbox-d6", 128, 128), ("emissive-plane", 96, 96)])
+@pytest.mark.parametrize("name,w,h", [("diamond", 240, 135), ("cbox-d6", 128, 128), ("emissive-plane", 96, 96),
+                                      ("primitives", 192, 192)])
 def test_reference_scenes_match_oracle(ig, oracle, dev, name, w, h):
     tables, sh, _, _, _ = load_golden(ig, name)
     film, stats = _render(dev, tables, sh, w, h, 4, 2, seed=11)
@@ -93,6 +94,28 @@ def test_golden_images(ig, dev, name, one_sided, spp, threshold):
     sh.technique.flags = 1 if one_sided else 0
     film, _ = _render(dev, tables, sh, w, h, 64, spp // 64, seed=2)
     assert eval_error(film / (spp // 64), ref) < threshold
+
+
+def test_c2_primitives_full_size(ig, oracle, dev):
+    # BASELINE.json configs[1]: scenes/primitives.json, 1024 x 1024, 64 spp (8 iterations of spi 8), seed 42, depth 2.
+    # Size-independent properties: ray counters (one camera ray per sample, one shadow ray per bounce at depth 2),
+    # batched == single iterations, and the image mean against the oracle's render of the same scene at 1/16 of
+    # the pixels (both estimate the same integral; 4 Mi vs 67 Mi samples -> 1 % covers the noise).
+    tables, sh, w, h, _ = load_golden(ig, "primitives")
+    assert (w, h) == (1024, 1024)
+    film, stats = _render(dev, tables, sh, w, h, 8, 8, seed=42)
+    assert stats[0] == w * h * 64 and stats[1] == stats[2] and 0 < stats[1] < stats[0]
+    assert np.all(np.isfinite(film)) and film.min() >= 0
+    dev.clear_framebuffer()
+    dev.render(w, h, spi=8, iteration=0, seed=42, iterations=8)
+    batched, n = dev.framebuffer()
+    assert n == 8 and np.allclose(batched, film, rtol=1e-4, atol=1e-5)
+    osc = oracle.OracleScene(tables)
+    ref = osc.render(sh, w // 4, h // 4, spi=8, iterations=8, seed=42)
+    assert film.mean() == pytest.approx(ref.mean(), rel=1e-2)
+    # the image itself: 4 x 4 box-filtered GPU film against the low-resolution oracle render (same camera)
+    small = film.reshape(h // 4, 4, w // 4, 4, 3).mean(axis=(1, 3))
+    assert eval_error(small / 8, ref / 8) < 5e-3
 
 
 def test_igtrace_list_mode(ig, dev):
