@@ -66,10 +66,12 @@ __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x)
     asm("prmt.b32 %0, %1, 0x0, 0x0000BA98;" : "=r"(r) : "r"(x));
     return r;
 }
-// byte j of w as a float in [0, 255]
-__device__ __forceinline__ float byte_to_float(uint32_t w, int j)
+// 32768 + byte j of w, as a float: the byte lands in mantissa bits 8..15 of 2^15 (one PRMT, no arithmetic).  The
+// caller folds the -32768 into the addend of its FMA.
+constexpr float kByteBias = 32768.0f;
+__device__ __forceinline__ float biased_byte_to_float(uint32_t w, int j)
 {
-    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7540u | (uint32_t)j)) - 8388608.0f;
+    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7604u | ((uint32_t)j << 4)));
 }
 __device__ __forceinline__ uint32_t extract_byte(uint32_t w, int j) { return (w >> (8 * j)) & 0xFFu; }
 
@@ -98,6 +100,12 @@ __device__ __forceinline__ uint32_t intersect_children(const uint4 n0, const uin
     const float    ox = (__uint_as_float(n0.x) - r.org.x) * r.idir.x;
     const float    oy = (__uint_as_float(n0.y) - r.org.y) * r.idir.y;
     const float    oz = (__uint_as_float(n0.z) - r.org.z) * r.idir.z;
+    // plane distance = q * s + o = (32768 + q) * s + (o - 32768 s).  Folding the bias costs one rounding of
+    // magnitude <= |s| / 512 (s = one quantisation step in t), so entry planes move 1/256 step out, exit planes in.
+    const float ax = __fmaf_rn(-kByteBias, sx, ox), dx = fabsf(sx) * 0.00390625f;
+    const float ay = __fmaf_rn(-kByteBias, sy, oy), dy = fabsf(sy) * 0.00390625f;
+    const float az = __fmaf_rn(-kByteBias, sz, oz), dz = fabsf(sz) * 0.00390625f;
+    const float o0x = ax - dx, o1x = ax + dx, o0y = ay - dy, o1y = ay + dy, o0z = az - dz, o1z = az + dz;
     const bool     nx = r.dir.x < 0.0f, ny = r.dir.y < 0.0f, nz = r.dir.z < 0.0f;
 
     uint32_t hitmask = 0;
@@ -116,12 +124,12 @@ __device__ __forceinline__ uint32_t intersect_children(const uint4 n0, const uin
         const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const float t0x = __fmaf_rn(byte_to_float(nearx, j), sx, ox);
-            const float t0y = __fmaf_rn(byte_to_float(neary, j), sy, oy);
-            const float t0z = __fmaf_rn(byte_to_float(nearz, j), sz, oz);
-            const float t1x = __fmaf_rn(byte_to_float(farx, j), sx, ox);
-            const float t1y = __fmaf_rn(byte_to_float(fary, j), sy, oy);
-            const float t1z = __fmaf_rn(byte_to_float(farz, j), sz, oz);
+            const float t0x = __fmaf_rn(biased_byte_to_float(nearx, j), sx, o0x);
+            const float t0y = __fmaf_rn(biased_byte_to_float(neary, j), sy, o0y);
+            const float t0z = __fmaf_rn(biased_byte_to_float(nearz, j), sz, o0z);
+            const float t1x = __fmaf_rn(biased_byte_to_float(farx, j), sx, o1x);
+            const float t1y = __fmaf_rn(biased_byte_to_float(fary, j), sy, o1y);
+            const float t1z = __fmaf_rn(biased_byte_to_float(farz, j), sz, o1z);
             const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
             // slack on the exit distance: the box test must never reject what the triangle test accepts
             const float cmax = fminf(fminf(fminf(t1x, t1y), t1z) * kBoxSlack, tmax);
