@@ -114,10 +114,9 @@ struct igb200_device {
     float                         scene_bbox[6] = {};
 
     uint32_t                      wave_capacity = 0;
-    bool                          wave_sort     = true;
-    DeviceBuffer<float4>          w_f4[2][3], w_sh_f4[3];
-    DeviceBuffer<uint4>           w_u4[2][2];
-    DeviceBuffer<float>           w_f1[2][2];
+    int                           wave_sort     = 1; // 0 off, 1 global index sort, 2 tile-local index sort
+    DeviceBuffer<float4>          w_rec[2], w_sh_f4[3];
+    DeviceBuffer<uint8_t>         w_flags[2];
     DeviceBuffer<uint32_t>        w_keys, w_sorted;
     DeviceBuffer<igb::WaveControl> w_ctl;
     igb::WaveBuffers              wave{};
@@ -522,6 +521,8 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
         }
     }
     if (sh->technique.type > IGB200_TECH_DEBUG) return fail(IGB200_E_UNSUPPORTED, "unknown technique %u", sh->technique.type);
+    if (sh->technique.max_depth > 254) // the stream keeps the depth in 8 bits (reference default: 64, PathTechnique.cpp)
+        return fail(IGB200_E_UNSUPPORTED, "technique.max_depth %d exceeds 254", sh->technique.max_depth);
     IGB_CUDA(cudaSetDevice(dev->ordinal));
     IGB_CUDA(dev->d_bsdfs.upload(sh->bsdfs, sh->bsdf_count, dev->stream));
     IGB_CUDA(dev->d_materials.upload(sh->materials, sh->material_count, dev->stream));
@@ -570,17 +571,13 @@ static int ensure_film(igb200_device* dev, uint32_t w, uint32_t h)
 static int ensure_wave(igb200_device* dev)
 {
     if (dev->wave_capacity) return IGB200_OK;
-    uint32_t cap = 1u << 23; // 8 Mi rays (the reference: 1 Mi, mapping_gpu.art:1125); ~1.9 GB of streams, measured best on B200
+    uint32_t cap = 1u << 23; // 8 Mi rays (the reference: 1 Mi, mapping_gpu.art:1125); ~2.1 GB of streams, measured best on B200
     if (const char* e = std::getenv("IGB200_WAVE_CAPACITY")) cap = (uint32_t)std::max(1024l, std::atol(e));
-    if (const char* e = std::getenv("IGB200_WAVE_SORT")) dev->wave_sort = std::atoi(e) != 0;
+    if (const char* e = std::getenv("IGB200_WAVE_SORT")) dev->wave_sort = std::max(0, std::min(2, std::atoi(e)));
     for (int b = 0; b < 2; ++b) {
-        for (int k = 0; k < 3; ++k) IGB_CUDA(dev->w_f4[b][k].ensure(cap));
-        for (int k = 0; k < 2; ++k) IGB_CUDA(dev->w_u4[b][k].ensure(cap));
-        for (int k = 0; k < 2; ++k) IGB_CUDA(dev->w_f1[b][k].ensure(cap));
-        igb::PathStream& s = dev->wave.stream[b];
-        s.org_tmin = dev->w_f4[b][0].ptr; s.dir_tmax = dev->w_f4[b][1].ptr; s.contrib_invpdf = dev->w_f4[b][2].ptr;
-        s.meta = dev->w_u4[b][0].ptr; s.hit0 = dev->w_u4[b][1].ptr;
-        s.eta = dev->w_f1[b][0].ptr; s.hit_v = dev->w_f1[b][1].ptr;
+        IGB_CUDA(dev->w_rec[b].ensure((size_t)cap * igb::kRecVec));
+        IGB_CUDA(dev->w_flags[b].ensure(cap));
+        dev->wave.stream[b] = igb::PathStream{ dev->w_rec[b].ptr, dev->w_flags[b].ptr };
     }
     for (int k = 0; k < 3; ++k) IGB_CUDA(dev->w_sh_f4[k].ensure(cap));
     dev->wave.shadow = igb::ShadowStream{ dev->w_sh_f4[0].ptr, dev->w_sh_f4[1].ptr, dev->w_sh_f4[2].ptr };

@@ -68,6 +68,9 @@ __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x)
 }
 // 32768 + byte j of w, as a float: the byte lands in mantissa bits 8..15 of 2^15 (one PRMT, no arithmetic).  The
 // caller folds the -32768 into the addend of its FMA.
+#ifndef IGB_TLAS_SMEM
+#define IGB_TLAS_SMEM 0 // number of top-level nodes staged in shared memory (0 = off)
+#endif
 constexpr float kByteBias = 32768.0f;
 __device__ __forceinline__ float biased_byte_to_float(uint32_t w, int j)
 {
@@ -234,6 +237,13 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
         for (uint32_t b = threadIdx.x; b < min(io.bin_count(), (uint32_t)kMaxSmemBins); b += blockDim.x) s_bins[b] = 0u;
         __syncthreads();
     }
+#if IGB_TLAS_SMEM
+    // Experiment (north_star item b): top-level nodes staged in shared memory.  See DESIGN.md section 5.1 for the A/B.
+    __shared__ uint4 s_top[IGB_TLAS_SMEM * 5];
+    const uint32_t   n_top = min(sc.tlas_nodes, (uint32_t)IGB_TLAS_SMEM);
+    for (uint32_t i = threadIdx.x; i < n_top * 5u; i += blockDim.x) s_top[i] = sc.nodes[i];
+    __syncthreads();
+#endif
     const uint32_t n = io.count();
     uint32_t       ray_flags = 0;
     const uint32_t lane    = threadIdx.x & 31u;
@@ -301,8 +311,14 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
 
             const uint32_t slot_index     = (child_bit_index - 24u) ^ (ray.octinv4 & 0xFFu);
             const uint32_t relative_index = __popc(imask & ~(0xFFFFFFFFu << slot_index));
+#if IGB_TLAS_SMEM
+            const uint32_t ni             = ngroup.x + relative_index;
+            const uint4*   np             = ni < n_top ? s_top + 5 * ni : sc.nodes + 5 * (size_t)ni; // generic loads
+            const uint4    n0 = np[0], n1 = np[1], n2 = np[2], n3 = np[3], n4 = np[4];
+#else
             const uint4*   np             = sc.nodes + 5 * (size_t)(ngroup.x + relative_index);
             const uint4    n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+#endif
             if (STATS) c_nodes++;
             const uint32_t hitmask = intersect_children(n0, n1, n2, n3, n4, ray, tmin, hit.t);
             ngroup                 = make_uint2(n1.x, (hitmask & 0xFF000000u) | (n0.w >> 24));

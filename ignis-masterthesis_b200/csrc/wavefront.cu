@@ -32,18 +32,20 @@ struct PrimaryIO {
     __device__ __forceinline__ uint32_t* global_bins() const { return ctl->bins; }
     __device__ __forceinline__ bool load(uint32_t i, Vec3& org, Vec3& dir, float& tmin, float& tmax, uint32_t& flags) const
     {
-        const float4 o = s.org_tmin[i], d = s.dir_tmax[i];
+        const float4* r = s.rec + kRecVec * (size_t)i;
+        const float4  o = r[0], d = r[1];
         org   = Vec3{ o.x, o.y, o.z };
         dir   = Vec3{ d.x, d.y, d.z };
         tmin  = o.w;
         tmax  = d.w;
-        flags = s.meta[i].z & 0xFFu;
+        flags = s.flags[i];
         return true;
     }
     __device__ __forceinline__ void store(uint32_t i, const HitRec& hit, uint32_t* s_bins) const
     {
-        s.hit0[i]  = make_uint4((uint32_t)hit.ent, (uint32_t)hit.prim, __float_as_uint(hit.t), __float_as_uint(hit.u));
-        s.hit_v[i] = hit.v;
+        float4* r = s.rec + kRecVec * (size_t)i; // the whole third sector: no partial-sector write
+        r[4] = make_float4(__int_as_float(hit.ent), __int_as_float(hit.prim), hit.t, hit.u);
+        r[5] = make_float4(hit.v, 0.0f, 0.0f, 0.0f);
         const uint32_t key = hit.prim >= 0 ? (uint32_t)__ldg(ent_mat + hit.ent) : n_bins - 1u;
         keys[i]            = key;
         if (n_bins <= (uint32_t)kMaxSmemBins)
@@ -197,11 +199,12 @@ __global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __rest
             flags = kRayCamera;
         }
         const uint32_t slot    = base + k;
-        s.org_tmin[slot]       = make_float4(org.x, org.y, org.z, tmin);
-        s.dir_tmax[slot]       = make_float4(dir.x, dir.y, dir.z, tmax);
-        s.meta[slot]           = make_uint4(id, rnd.counter, flags | (it << 8), 1u);
-        s.contrib_invpdf[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
-        s.eta[slot]            = 1.0f;
+        float4*        r       = s.rec + kRecVec * (size_t)slot;
+        r[0]          = make_float4(org.x, org.y, org.z, tmin);
+        r[1]          = make_float4(dir.x, dir.y, dir.z, tmax);
+        r[2]          = make_float4(__uint_as_float(id), __uint_as_float(rnd.counter), __uint_as_float((it << 8) | 1u), 1.0f);
+        r[3]          = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+        s.flags[slot] = (uint8_t)flags;
     }
 }
 
@@ -210,7 +213,7 @@ __global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __rest
 // reserves one range per key with ONE global atomic per key and tile, then writes the slot indices.
 constexpr int kScatterItems = 8; // keys per thread and tile
 __global__ void __launch_bounds__(256) scatter_kernel(WaveControl* __restrict__ ctl, const uint32_t* __restrict__ keys,
-                                                      uint32_t* __restrict__ sorted, const uint32_t n_bins)
+                                                      uint32_t* __restrict__ sorted, const uint32_t n_bins, const bool tile_local)
 {
     __shared__ uint32_t s_cnt[kMaxSmemBins], s_base[kMaxSmemBins];
     const uint32_t n    = ctl->n_cur;
@@ -245,8 +248,27 @@ __global__ void __launch_bounds__(256) scatter_kernel(WaveControl* __restrict__ 
             rank[k] = __shfl_sync(0xFFFFFFFFu, base, lead) + __popc(peers & ((1u << lane) - 1u));
         }
         __syncthreads();
-        for (uint32_t b = threadIdx.x; b < n_bins; b += blockDim.x)
-            if (s_cnt[b]) s_base[b] = ctl->offsets[b] + atomicAdd(ctl->cursors + b, s_cnt[b]);
+        if (tile_local) {
+            // sort inside the tile only: slots stay within a 2048-ray window, so the shade kernel's gather hits L2
+            if (threadIdx.x < 32u) {
+                uint32_t carry = t0;
+                for (uint32_t b0 = 0; b0 < n_bins; b0 += 32u) {
+                    const uint32_t b = b0 + lane;
+                    const uint32_t c = b < n_bins ? s_cnt[b] : 0u;
+                    uint32_t       x = c;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) {
+                        const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, d);
+                        if ((int)lane >= d) x += y;
+                    }
+                    if (b < n_bins) s_base[b] = carry + x - c;
+                    carry += __shfl_sync(0xFFFFFFFFu, x, 31);
+                }
+            }
+        } else {
+            for (uint32_t b = threadIdx.x; b < n_bins; b += blockDim.x)
+                if (s_cnt[b]) s_base[b] = ctl->offsets[b] + atomicAdd(ctl->cursors + b, s_cnt[b]);
+        }
         __syncthreads();
 #pragma unroll
         for (int k = 0; k < kScatterItems; ++k) {
@@ -272,9 +294,8 @@ __global__ void film_combine_kernel(float* film, const float* src, uint64_t coun
 // secondary stream.
 // ---------------------------------------------------------------------------------------------------------
 struct NextState {
-    float4 org_tmin, dir_tmax, contrib_invpdf;
-    uint4  meta;
-    float  eta;
+    float4  org_tmin, dir_tmax, meta, contrib_invpdf;
+    uint8_t flags;
 };
 struct ShadowState {
     float4 org_tmin, dir_tmax, color_pixel;
@@ -292,14 +313,14 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
                                        uint32_t i, float* film, bool& alive, NextState& nx, bool& has_shadow, ShadowState& sh)
 {
     const igb200_technique& tech = sc.tech;
-    const float4 o4 = cur.org_tmin[i], d4 = cur.dir_tmax[i];
-    const uint4  meta = cur.meta[i], h0 = cur.hit0[i];
-    const float4 cp  = cur.contrib_invpdf[i];
+    const float4* rec = cur.rec + kRecVec * (size_t)i;
+    const float4  o4 = rec[0], d4 = rec[1], meta = rec[2], cp = rec[3], h0 = rec[4];
     const Vec3   org{ o4.x, o4.y, o4.z }, dir{ d4.x, d4.y, d4.z };
-    const int32_t ent = (int32_t)h0.x, prim = (int32_t)h0.y;
-    const float   t = __uint_as_float(h0.z), u = __uint_as_float(h0.w);
-    const uint32_t id = meta.x, pixel = id / set.spi, sample = id - pixel * set.spi;
-    const int32_t  depth = (int32_t)meta.w;
+    const int32_t ent = __float_as_int(h0.x), prim = __float_as_int(h0.y);
+    const float   t = h0.z, u = h0.w;
+    const uint32_t id = __float_as_uint(meta.x), pixel = id / set.spi, sample = id - pixel * set.spi;
+    const uint32_t meta_z = __float_as_uint(meta.z);
+    const int32_t  depth  = (int32_t)(meta_z & 0xFFu);
     const Color    contrib0{ cp.x, cp.y, cp.z };
     const float    inv_pdf = cp.w;
     const float    offset  = 0.001f;
@@ -323,7 +344,7 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
         return;
     }
 
-    const float  v = cur.hit_v[i];
+    const float  v = rec[5].x;
     const Entity e = load_entity(sc, ent);
     Surf         surf;
     const uint2  si = sc.shape_info[e.shape_id()];
@@ -371,7 +392,7 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
     }
 
     const uint32_t y = pixel / set.width, x = pixel - y * set.width;
-    Rnd            rnd{ create_random_seed(sample, set.iter + (meta.z >> 8), set.frame, x, y, set.seed), meta.y };
+    Rnd            rnd{ create_random_seed(sample, set.iter + (meta_z >> 8), set.frame, x, y, set.seed), __float_as_uint(meta.y) };
     const Vec3     out_dir = vneg(dir);
 
     // on_shadow (pathtracer.art:52-110): next event estimation
@@ -400,7 +421,7 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
     if (depth + 1 > tech.max_depth) return;
     const BsdfSample ms      = bsdf.sample(rnd, out_dir, surf);
     const Color      contrib = cmul(contrib0, ms.col);
-    const float      eta0    = cur.eta[i];
+    const float      eta0    = meta.w;
     float            rr_prob = 1.0f;
     if (depth + 1 > tech.min_depth) {
         const Color cc = cmulf(contrib, eta0 * eta0);
@@ -412,12 +433,16 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
     alive             = true;
     nx.org_tmin       = make_float4(surf.point.x, surf.point.y, surf.point.z, offset);
     nx.dir_tmax       = make_float4(ms.in_dir.x, ms.in_dir.y, ms.in_dir.z, flt_max);
-    nx.meta           = make_uint4(id, rnd.counter, kRayBounce | (meta.z & 0xFFFFFF00u), (uint32_t)(depth + 1));
+    nx.meta           = make_float4(meta.x, __uint_as_float(rnd.counter), __uint_as_float((meta_z & 0xFFFFFF00u) | (uint32_t)(depth + 1)),
+                                    eta0 * ms.eta);
     nx.contrib_invpdf = make_float4(nc.r, nc.g, nc.b, new_inv_pdf);
-    nx.eta            = eta0 * ms.eta;
+    nx.flags          = (uint8_t)kRayBounce;
 }
 
-__global__ void __launch_bounds__(128) shade_kernel(WaveControl* __restrict__ ctl, const PathStream cur, const PathStream nxt,
+#ifndef IGB_SHADE_MIN_BLOCKS
+#define IGB_SHADE_MIN_BLOCKS 6 // 85 registers, 80 B of spills: +2 % over 4 blocks (112 registers) on B200
+#endif
+__global__ void __launch_bounds__(128, IGB_SHADE_MIN_BLOCKS) shade_kernel(WaveControl* __restrict__ ctl, const PathStream cur, const PathStream nxt,
                                                     const ShadowStream shq, const uint32_t* __restrict__ sorted, const ShadeScene sc,
                                                     const DeviceScene geo)
 {
@@ -442,11 +467,12 @@ __global__ void __launch_bounds__(128) shade_kernel(WaveControl* __restrict__ ct
             base = __shfl_sync(0xFFFFFFFFu, base, __ffs(am) - 1);
             if (alive) {
                 const uint32_t slot      = base + __popc(am & lt_mask);
-                nxt.org_tmin[slot]       = nx.org_tmin;
-                nxt.dir_tmax[slot]       = nx.dir_tmax;
-                nxt.meta[slot]           = nx.meta;
-                nxt.contrib_invpdf[slot] = nx.contrib_invpdf;
-                nxt.eta[slot]            = nx.eta;
+                float4*        r    = nxt.rec + kRecVec * (size_t)slot;
+                r[0]            = nx.org_tmin;
+                r[1]            = nx.dir_tmax;
+                r[2]            = nx.meta;
+                r[3]            = nx.contrib_invpdf;
+                nxt.flags[slot] = nx.flags;
             }
         }
         const uint32_t sm = __ballot_sync(0xFFFFFFFFu, has_shadow);
@@ -476,7 +502,7 @@ cudaError_t launch_wave_reset(const WaveBuffers& buf, const WaveSettings& set, u
 }
 
 cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene& sh, const WaveBuffers& buf, int parity,
-                              bool sort, int sm_count, cudaStream_t stream)
+                              int sort, int sm_count, cudaStream_t stream)
 {
     const PathStream& cur = buf.stream[parity & 1];
     const PathStream& nxt = buf.stream[(parity + 1) & 1];
@@ -488,7 +514,7 @@ cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene&
     generate_kernel<<<wide, 256, 0, stream>>>(buf.ctl, cur, sh);
     const PrimaryIO pio{ cur, buf.keys, buf.ent_mat, buf.ctl, n_bins };
     trace_kernel<PrimaryIO, false, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, pio, nullptr, buf.ctl->work_primary);
-    if (sort) scatter_kernel<<<wide / 2, 256, 0, stream>>>(buf.ctl, buf.keys, buf.sorted, n_bins);
+    if (sort) scatter_kernel<<<wide / 2, 256, 0, stream>>>(buf.ctl, buf.keys, buf.sorted, n_bins, sort == 2 && n_bins <= kMaxSmemBins);
     shade_kernel<<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene);
     const ShadowIO sio{ buf.shadow, buf.ctl };
     trace_kernel<ShadowIO, true, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, sio, nullptr, buf.ctl->work_shadow);

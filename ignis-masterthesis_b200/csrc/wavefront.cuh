@@ -2,7 +2,8 @@
 //
 // Replaces the reference's GPU wavefront loop `gpu_trace` (src/artic/driver/mapping_gpu.art:728-870) and its
 // streams (src/artic/driver/streams.art:1-44, sizing src/runtime/device/Device.cpp:474-514).  Differences by design:
-//   * streams are 16-byte-vector SoA (org+tmin, dir+tmax, ...) instead of one float column per component;
+//   * the primary stream is an array of 96-byte records (three full sectors per ray) instead of one float column
+//     per component; the shadow stream is 16-byte-vector SoA (it is only ever read and written in order);
 //   * survivors are compacted by the SHADE kernel itself (warp ballot + one atomic per warp) into the other
 //     stream buffer, so there is no separate compaction pass (gpu_compact_primary, mapping_gpu.art:685-714);
 //   * the sort is an index sort by MATERIAL id (histogram fused into the traversal kernel, scan by its last block,
@@ -19,16 +20,19 @@
 
 namespace igb {
 
-// Primary stream (one of two ping-pong buffers): ray + path state + hit record.  88 bytes per ray.
+// Primary stream (one of two ping-pong buffers): one 96-byte RECORD per ray = three 32-byte sectors, so that the
+// shade kernel's gather through the material-sorted index list only ever fetches sectors it uses entirely
+// (16-byte SoA columns made it fetch 210 B per ray where 92 B were needed, ncu r01_s7):
+//   sector 0  [0] org.xyz, tmin        [1] dir.xyz, tmax                       read by traversal, written by generate/shade
+//   sector 1  [2] meta                 [3] contrib.rgb, inv_pdf                written by generate/shade, read by shade
+//   sector 2  [4] ent, prim, t, u      [5] v, -, -, -                          written by traversal, read by shade
+// meta = { ray id = pixel * spi + sample, RNG counter (the `rnd` column), iteration offset in the batch << 8 | depth,
+//          eta (bit pattern) };  path payload: technique/pathtracer.art:7-12.
+// The ray visibility flags live in their own byte column: traversal needs them without touching sector 1.
+constexpr int kRecVec = 6; // float4 per record
 struct PathStream {
-    float4* org_tmin;       // ray origin, tmin
-    float4* dir_tmax;       // ray direction, tmax
-    uint4*  meta;           // x: ray id = pixel * spi + sample, y: RNG counter (the `rnd` column),
-                            // z: ray flags (bits 0-7) | iteration offset within the batch (bits 8-31), w: depth
-    float4* contrib_invpdf; // path payload: contrib rgb, inv_pdf (technique/pathtracer.art:7-12)
-    float*  eta;            // path payload: eta
-    uint4*  hit0;           // ent_id, prim_id, t, u (bit patterns)
-    float*  hit_v;
+    float4*  rec;
+    uint8_t* flags;
 };
 
 // Secondary (shadow) stream, compacted on write.  48 bytes per ray.
@@ -87,7 +91,7 @@ namespace shade { struct ShadeScene; }
 // Enqueues ONE wavefront round (parity selects which stream buffer is current) on `stream`:
 // begin_round, generate, trace_primary(+histogram+scan), scatter, shade, trace_shadow(+splat).
 cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene& sh, const WaveBuffers& buf, int parity,
-                              bool sort, int sm_count, cudaStream_t stream);
+                              int sort, int sm_count, cudaStream_t stream); // sort: 0 off, 1 global, 2 tile-local
 
 // Resets the control block for a new call (total = spi * w * h * iterations) and stores its settings.
 cudaError_t launch_wave_reset(const WaveBuffers& buf, const WaveSettings& set, uint32_t total, cudaStream_t stream);
