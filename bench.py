@@ -388,7 +388,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--rays", type=int, default=FULL_RAYS)
     ap.add_argument("--cpu-rays", type=int, default=4_000_000)
-    ap.add_argument("--pt-iterations", type=int, default=16, help="path-traced iterations per GPU (0 disables the leg)")
+    ap.add_argument("--pt-iterations", type=int, default=64,
+                    help="path-traced iterations per GPU; 64 x spi 4 = the 256 spp of BASELINE.json configs[3] (0 disables the leg)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -116,7 +116,7 @@ struct igb200_device {
     uint32_t                      wave_capacity = 0;
     int                           wave_sort     = 1; // 0 off, 1 global index sort, 2 tile-local index sort
     DeviceBuffer<float4>          w_rec[2], w_sh_f4[3];
-    DeviceBuffer<uint8_t>         w_flags[2];
+    DeviceBuffer<uint16_t>        w_flags[2];
     DeviceBuffer<uint32_t>        w_keys, w_sorted;
     DeviceBuffer<igb::WaveControl> w_ctl;
     igb::WaveBuffers              wave{};

@@ -38,7 +38,7 @@ struct PrimaryIO {
         dir   = Vec3{ d.x, d.y, d.z };
         tmin  = o.w;
         tmax  = d.w;
-        flags = s.flags[i];
+        flags = s.flags[i] & 0xFFu;
         return true;
     }
     __device__ __forceinline__ void store(uint32_t i, const HitRec& hit, uint32_t* s_bins) const
@@ -202,9 +202,9 @@ __global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __rest
         float4*        r       = s.rec + kRecVec * (size_t)slot;
         r[0]          = make_float4(org.x, org.y, org.z, tmin);
         r[1]          = make_float4(dir.x, dir.y, dir.z, tmax);
-        r[2]          = make_float4(__uint_as_float(id), __uint_as_float(rnd.counter), __uint_as_float((it << 8) | 1u), 1.0f);
+        r[2]          = make_float4(__uint_as_float(pixel), __uint_as_float(rnd.counter), __uint_as_float(rnd.seed), 1.0f);
         r[3]          = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
-        s.flags[slot] = (uint8_t)flags;
+        s.flags[slot] = (uint16_t)(flags | (1u << 8)); // depth 1
     }
 }
 
@@ -294,8 +294,8 @@ __global__ void film_combine_kernel(float* film, const float* src, uint64_t coun
 // secondary stream.
 // ---------------------------------------------------------------------------------------------------------
 struct NextState {
-    float4  org_tmin, dir_tmax, meta, contrib_invpdf;
-    uint8_t flags;
+    float4   org_tmin, dir_tmax, meta, contrib_invpdf;
+    uint16_t flags;
 };
 struct ShadowState {
     float4 org_tmin, dir_tmax, color_pixel;
@@ -318,9 +318,8 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
     const Vec3   org{ o4.x, o4.y, o4.z }, dir{ d4.x, d4.y, d4.z };
     const int32_t ent = __float_as_int(h0.x), prim = __float_as_int(h0.y);
     const float   t = h0.z, u = h0.w;
-    const uint32_t id = __float_as_uint(meta.x), pixel = id / set.spi, sample = id - pixel * set.spi;
-    const uint32_t meta_z = __float_as_uint(meta.z);
-    const int32_t  depth  = (int32_t)(meta_z & 0xFFu);
+    const uint32_t pixel = __float_as_uint(meta.x);
+    const int32_t  depth = (int32_t)(cur.flags[i] >> 8);
     const Color    contrib0{ cp.x, cp.y, cp.z };
     const float    inv_pdf = cp.w;
     const float    offset  = 0.001f;
@@ -391,8 +390,7 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
         }
     }
 
-    const uint32_t y = pixel / set.width, x = pixel - y * set.width;
-    Rnd            rnd{ create_random_seed(sample, set.iter + (meta_z >> 8), set.frame, x, y, set.seed), __float_as_uint(meta.y) };
+    Rnd            rnd{ __float_as_uint(meta.z), __float_as_uint(meta.y) }; // seed and counter travel with the ray
     const Vec3     out_dir = vneg(dir);
 
     // on_shadow (pathtracer.art:52-110): next event estimation
@@ -433,10 +431,9 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
     alive             = true;
     nx.org_tmin       = make_float4(surf.point.x, surf.point.y, surf.point.z, offset);
     nx.dir_tmax       = make_float4(ms.in_dir.x, ms.in_dir.y, ms.in_dir.z, flt_max);
-    nx.meta           = make_float4(meta.x, __uint_as_float(rnd.counter), __uint_as_float((meta_z & 0xFFFFFF00u) | (uint32_t)(depth + 1)),
-                                    eta0 * ms.eta);
+    nx.meta           = make_float4(meta.x, __uint_as_float(rnd.counter), meta.z, eta0 * ms.eta);
     nx.contrib_invpdf = make_float4(nc.r, nc.g, nc.b, new_inv_pdf);
-    nx.flags          = (uint8_t)kRayBounce;
+    nx.flags          = (uint16_t)(kRayBounce | ((uint32_t)(depth + 1) << 8));
 }
 
 #ifndef IGB_SHADE_MIN_BLOCKS

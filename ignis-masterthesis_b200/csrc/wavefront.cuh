@@ -26,13 +26,15 @@ namespace igb {
 //   sector 0  [0] org.xyz, tmin        [1] dir.xyz, tmax                       read by traversal, written by generate/shade
 //   sector 1  [2] meta                 [3] contrib.rgb, inv_pdf                written by generate/shade, read by shade
 //   sector 2  [4] ent, prim, t, u      [5] v, -, -, -                          written by traversal, read by shade
-// meta = { ray id = pixel * spi + sample, RNG counter (the `rnd` column), iteration offset in the batch << 8 | depth,
-//          eta (bit pattern) };  path payload: technique/pathtracer.art:7-12.
-// The ray visibility flags live in their own byte column: traversal needs them without touching sector 1.
+// meta = { pixel, RNG counter (the `rnd` column), RNG seed = hash(sample, iteration, frame, x, y, user seed), eta };
+// path payload: technique/pathtracer.art:7-12.  The seed travels with the ray so that a bounce neither re-hashes it
+// nor divides the ray id back into pixel / sample / x / y.
+// The ray visibility flags (low byte) and the path depth (high byte) live in their own 16-bit column: traversal
+// needs the flags without touching sector 1.
 constexpr int kRecVec = 6; // float4 per record
 struct PathStream {
     float4*  rec;
-    uint8_t* flags;
+    uint16_t* flags;
 };
 
 // Secondary (shadow) stream, compacted on write.  48 bytes per ray.
