@@ -107,6 +107,8 @@ struct igb200_device {
     DeviceBuffer<igb200_bsdf>     d_bsdfs;
     DeviceBuffer<igb200_material> d_materials;
     DeviceBuffer<igb200_light>    d_inf_lights, d_fin_lights;
+    DeviceBuffer<igb200_texture>  d_textures;
+    DeviceBuffer<uint8_t>         d_blob;
     igb::shade::ShadeScene        shade{};
     bool                          has_shading = false;
     uint64_t                      entity_count = 0;
@@ -506,14 +508,48 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
         if (m.bsdf < 0 || (uint64_t)m.bsdf >= sh->bsdf_count) return fail(IGB200_E_INVALID, "material %llu: bsdf %d out of range", (unsigned long long)i, m.bsdf);
         if (m.light >= (int64_t)sh->finite_light_count) return fail(IGB200_E_INVALID, "material %llu: light %d out of range", (unsigned long long)i, m.light);
     }
-    for (uint64_t i = 0; i < sh->bsdf_count; ++i)
-        if (sh->bsdfs[i].type > IGB200_BSDF_CONDUCTOR) return fail(IGB200_E_UNSUPPORTED, "bsdf %llu: unknown type %u", (unsigned long long)i, sh->bsdfs[i].type);
+    if ((sh->texture_count && !sh->textures) || (sh->blob_bytes && !sh->blob))
+        return fail(IGB200_E_INVALID, "igb200_assign_shading: texture / blob pointer is NULL");
+    for (uint64_t i = 0; i < sh->texture_count; ++i) {
+        const igb200_texture& t = sh->textures[i];
+        if (t.type > IGB200_TEX_IMAGE) return fail(IGB200_E_UNSUPPORTED, "texture %llu: unknown type %u", (unsigned long long)i, t.type);
+        if (t.type != IGB200_TEX_IMAGE) continue;
+        const uint64_t texel = t.format == IGB200_IMAGE_RGBA32F ? 16 : 4;
+        if (t.format > IGB200_IMAGE_RGBA32F || t.filter > IGB200_FILTER_BICUBIC || t.wrap_u > IGB200_WRAP_CLAMP || t.wrap_v > IGB200_WRAP_CLAMP ||
+            t.width == 0 || t.height == 0 || (t.offset & 15u) || t.offset + texel * t.width * t.height > sh->blob_bytes)
+            return fail(IGB200_E_INVALID, "texture %llu: bad image description", (unsigned long long)i);
+    }
+    for (uint64_t i = 0; i < sh->bsdf_count; ++i) {
+        const igb200_bsdf& b = sh->bsdfs[i];
+        if (b.type > IGB200_BSDF_BUMPMAP) return fail(IGB200_E_UNSUPPORTED, "bsdf %llu: unknown type %u", (unsigned long long)i, b.type);
+        if (b.type == IGB200_BSDF_DIFFUSE && b.q[0].u > sh->texture_count)
+            return fail(IGB200_E_INVALID, "bsdf %llu: texture %u out of range", (unsigned long long)i, b.q[0].u - 1);
+        if (b.type == IGB200_BSDF_BUMPMAP &&
+            (b.q[0].u == 0 || b.q[0].u > sh->texture_count || b.q[1].u == 0 || b.q[1].u > sh->bsdf_count || b.q[1].u - 1 == i))
+            return fail(IGB200_E_INVALID, "bsdf %llu: bump map texture / inner bsdf out of range", (unsigned long long)i);
+    }
+    if (sh->selector > IGB200_SELECTOR_HIERARCHY) return fail(IGB200_E_UNSUPPORTED, "unknown light selector %u", sh->selector);
+    if (sh->selector == IGB200_SELECTOR_HIERARCHY && sh->finite_light_count > 1) {
+        const uint64_t codes = (sh->finite_light_count + 3) / 4 * 4, nodes = 2 * sh->finite_light_count - 1;
+        if ((sh->hierarchy & 3u) || (uint64_t)sh->hierarchy * 4 + codes * 4 + nodes * 32 > sh->blob_bytes)
+            return fail(IGB200_E_INVALID, "igb200_assign_shading: light hierarchy exceeds the blob");
+    }
     for (int t = 0; t < 2; ++t) {
         const igb200_light* ls = t ? sh->finite_lights : sh->infinite_lights;
         const uint64_t      n  = t ? sh->finite_light_count : sh->infinite_light_count;
         for (uint64_t i = 0; i < n; ++i) {
-            const bool inf = ls[i].type == IGB200_LIGHT_ENV || ls[i].type == IGB200_LIGHT_DIRECTIONAL;
-            if (ls[i].type > IGB200_LIGHT_DIRECTIONAL || inf != (t == 0))
+            const bool inf = ls[i].type == IGB200_LIGHT_ENV || ls[i].type == IGB200_LIGHT_DIRECTIONAL || ls[i].type == IGB200_LIGHT_ENV_TEXTURED;
+            if (ls[i].type == IGB200_LIGHT_ENV_TEXTURED) {
+                if (ls[i].tex >= sh->texture_count) return fail(IGB200_E_INVALID, "environment light %llu: texture out of range", (unsigned long long)i);
+                if (ls[i].cdf != IGB200_NO_CDF) {
+                    if ((ls[i].cdf & 3u) || (uint64_t)ls[i].cdf * 4 + 16 > sh->blob_bytes)
+                        return fail(IGB200_E_INVALID, "environment light %llu: CDF out of range", (unsigned long long)i);
+                    const uint32_t* h = reinterpret_cast<const uint32_t*>(sh->blob) + ls[i].cdf;
+                    if (h[0] == 0 || h[1] == 0 || (uint64_t)ls[i].cdf * 4 + 16 + 4ull * h[1] * (1ull + h[0]) > sh->blob_bytes)
+                        return fail(IGB200_E_INVALID, "environment light %llu: CDF exceeds the blob", (unsigned long long)i);
+                }
+            }
+            if (ls[i].type > IGB200_LIGHT_ENV_TEXTURED || inf != (t == 0))
                 return fail(IGB200_E_INVALID, "%s light %llu has type %u", t ? "finite" : "infinite", (unsigned long long)i, ls[i].type);
             if ((ls[i].type == IGB200_LIGHT_AREA_SHAPE || ls[i].type == IGB200_LIGHT_AREA_PLANE) &&
                 (ls[i].entity < 0 || (uint64_t)ls[i].entity >= dev->entity_count))
@@ -528,6 +564,8 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
     IGB_CUDA(dev->d_materials.upload(sh->materials, sh->material_count, dev->stream));
     IGB_CUDA(dev->d_inf_lights.upload(sh->infinite_lights, sh->infinite_light_count, dev->stream));
     IGB_CUDA(dev->d_fin_lights.upload(sh->finite_lights, sh->finite_light_count, dev->stream));
+    IGB_CUDA(dev->d_textures.upload(sh->textures, sh->texture_count, dev->stream));
+    IGB_CUDA(dev->d_blob.upload(sh->blob, sh->blob_bytes, dev->stream));
     IGB_CUDA(cudaStreamSynchronize(dev->stream));
     igb::shade::ShadeScene& s = dev->shade;
     s.entities   = dev->d_entities.ptr;
@@ -543,6 +581,21 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
     s.n_ent      = (int32_t)dev->entity_count;
     s.cam        = sh->camera;
     s.tech       = sh->technique;
+    s.textures   = dev->d_textures.ptr;
+    s.blob       = dev->d_blob.ptr;
+    s.selector   = sh->selector;
+    s.hierarchy  = sh->hierarchy;
+    // The reference specialises its shaders per scene through the JIT; here the shade kernel has two instantiations
+    // and the scene picks one: the extended one only when a feature it adds is actually used.
+    s.extended = sh->selector == IGB200_SELECTOR_HIERARCHY && sh->finite_light_count > 0;
+    for (uint64_t i = 0; i < sh->bsdf_count; ++i) {
+        const igb200_bsdf& b = sh->bsdfs[i];
+        if (b.type == IGB200_BSDF_BUMPMAP || (b.type == IGB200_BSDF_DIFFUSE && b.q[0].u != 0) ||
+            (b.type == IGB200_BSDF_CONDUCTOR && !(b.q[0].f <= 1e-4f || b.q[1].f <= 1e-4f)))
+            s.extended = 1;
+    }
+    for (uint64_t i = 0; i < sh->infinite_light_count; ++i)
+        if (sh->infinite_lights[i].type == IGB200_LIGHT_ENV_TEXTURED) s.extended = 1;
     {
         // bbox_radius(scene_bbox) * 1.01 with vec3_len = sqrt of the fma-chain dot (core/bbox.art:24, vector.art:99)
         const float* b = dev->scene_bbox;

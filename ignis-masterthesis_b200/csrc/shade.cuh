@@ -149,9 +149,19 @@ struct Surf {
     bool  is_entering;
     Vec3  point, face_normal;
     float inv_area;
-    float pu, pv, tu, tv;
+    float pu, pv;        // prim_coords
+    const float2* tex;   // tex_coords are fetched on demand (surf_tex_coords): only textured BSDFs read them.
+    int32_t tix, tiy, tiz; // tex == nullptr: tex_coords = prim_coords (spheres)
     Mat3  local;
 };
+// SurfaceElement::tex_coords (shapes/trimesh.art:31-33, shapes/sphere.art:64)
+__device__ __forceinline__ void surf_tex_coords(const Surf& s, float& tu, float& tv)
+{
+    if (!s.tex) { tu = s.pu; tv = s.pv; return; }
+    const float2 t0 = __ldg(s.tex + s.tix), t1 = __ldg(s.tex + s.tiy), t2 = __ldg(s.tex + s.tiz);
+    tu = lerp2(t0.x, t1.x, t2.x, s.pu, s.pv);
+    tv = lerp2(t0.y, t1.y, t2.y, s.pu, s.pv);
+}
 
 } // namespace shade
 } // namespace igb

@@ -1,7 +1,7 @@
 // shade_lib.cuh -- scene access, surface elements, BSDFs and lights of the wavefront path tracer (sm_100a).
 // Continuation of shade.cuh; same citation and arithmetic conventions.
 #pragma once
-#include "shade.cuh"
+#include "shade_tex.cuh"
 
 namespace igb {
 namespace shade {
@@ -19,6 +19,11 @@ struct ShadeScene {
     igb200_camera          cam;
     igb200_technique       tech;
     float                  scene_radius; // bbox_radius(scene_bbox) * 1.01 (light/env.art:76, light/directional.art:2)
+    const igb200_texture*  textures;
+    const uint8_t*         blob;         // texels, CDFs, light hierarchy (igb200_shading::blob)
+    uint32_t               selector, hierarchy;
+    uint32_t               extended; // host-side: the scene uses textures / rough conductors / bump maps / textured
+                                     // environments / the light hierarchy -> the shade kernel's EXT instantiation
 };
 
 // ---- driver/entity.art:12-29 --------------------------------------------------------------------------
@@ -52,9 +57,9 @@ struct TriMesh {
     {
         return __ldg(reinterpret_cast<const int4*>(data + 12 + 4 * (size_t)nv + 4 * (size_t)nn) + i);
     }
-    __device__ __forceinline__ float2 tex(int32_t i) const
+    __device__ __forceinline__ const float2* tex_base() const
     {
-        return __ldg(reinterpret_cast<const float2*>(data + 12 + 4 * (size_t)nv + 4 * (size_t)nn + 4 * (size_t)nf) + i);
+        return reinterpret_cast<const float2*>(data + 12 + 4 * (size_t)nv + 4 * (size_t)nn + 4 * (size_t)nf);
     }
 };
 __device__ __forceinline__ TriMesh load_trimesh(const ShadeScene& sc, int32_t shape_id)
@@ -84,15 +89,13 @@ __device__ __forceinline__ Surf trimesh_surface_element(const TriMesh& m, const 
                   xform_point(e.global_mat(), m.vertex(idx.z)), fn, area);
     const Vec3   normal   = vnormalize(mat3_mul(e.normal_mat(), lerp2v(m.normal(idx.x), m.normal(idx.y), m.normal(idx.z), u, v)));
     const bool   entering = dot3(dir, fn) <= 0.0f;
-    const float2 t0 = m.tex(idx.x), t1 = m.tex(idx.y), t2 = m.tex(idx.z);
     Surf s;
     s.is_entering = entering;
     s.point       = vadd(org, vmulf(dir, t));
     s.face_normal = entering ? fn : vneg(fn);
     s.inv_area    = __fdiv_rn(1.0f, area);
     s.pu = u; s.pv = v;
-    s.tu = lerp2(t0.x, t1.x, t2.x, u, v);
-    s.tv = lerp2(t0.y, t1.y, t2.y, u, v);
+    s.tex = m.tex_base(); s.tix = idx.x; s.tiy = idx.y; s.tiz = idx.z;
     s.local = make_orthonormal(entering ? normal : vneg(normal));
     return s;
 }
@@ -106,15 +109,13 @@ __device__ __forceinline__ Surf trimesh_surface_element_for_point(const TriMesh&
     float area;
     make_triangle(g0, g1, g2, fn, area);
     const Vec3   normal = vnormalize(mat3_mul(e.normal_mat(), lerp2v(m.normal(idx.x), m.normal(idx.y), m.normal(idx.z), u, v)));
-    const float2 t0 = m.tex(idx.x), t1 = m.tex(idx.y), t2 = m.tex(idx.z);
     Surf s;
     s.is_entering = true;
     s.point       = lerp2v(g0, g1, g2, u, v);
     s.face_normal = fn;
     s.inv_area    = __fdiv_rn(1.0f, area);
     s.pu = u; s.pv = v;
-    s.tu = lerp2(t0.x, t1.x, t2.x, u, v);
-    s.tv = lerp2(t0.y, t1.y, t2.y, u, v);
+    s.tex = m.tex_base(); s.tix = idx.x; s.tiy = idx.y; s.tiz = idx.z;
     s.local = make_orthonormal(normal);
     return s;
 }
@@ -135,8 +136,8 @@ __device__ __forceinline__ Surf sphere_surface_element(float4 sph, const Entity&
     s.point       = point;
     s.face_normal = normal;
     s.inv_area    = __fdiv_rn(1.0f, area);
-    s.pu = s.tu = u;
-    s.pv = s.tv = v;
+    s.pu = u; s.pv = v;
+    s.tex = nullptr; s.tix = s.tiy = s.tiz = 0;
     s.local = make_orthonormal(normal);
     return s;
 }
@@ -159,15 +160,7 @@ __device__ __forceinline__ bool fresnel(float eta, float cos_i, float& cos_t_out
     factor            = fresnel_factor(eta2, fabsf(cos_i), cos_t);
     return true;
 }
-__device__ __forceinline__ float conductor_factor(float n, float k, float cos_i)
-{
-    const float f   = n * n + k * k;
-    const float d1  = f * cos_i * cos_i;
-    const float d2  = 2.0f * n * cos_i;
-    const float R_s = safe_div(d1 - d2, d1 + d2);
-    const float R_p = safe_div(f - d2 + cos_i * cos_i, f + d2 + cos_i * cos_i);
-    return clampf((R_s * R_s + R_p * R_p) * 0.5f, 0.0f, 1.0f);
-}
+// conductor_factor (core/fresnel.art:29-36): shade_tex.cuh
 __device__ __forceinline__ Vec3 reflect(Vec3 v, Vec3 n) { return vsub(vmulf(n, 2.0f * dot3(n, v)), v); }
 __device__ __forceinline__ Vec3 refract(Vec3 v, Vec3 n, float eta, float cos_i, float cos_t)
 {
@@ -176,27 +169,47 @@ __device__ __forceinline__ Vec3 refract(Vec3 v, Vec3 n, float eta, float cos_i, 
 
 struct BsdfSample { Vec3 in_dir; float pdf; Color col; float eta; };
 
+// EXT = false compiles the texture / microfacet / bump paths out (the kernel variant for scenes without them).
+template <bool EXT>
 struct Bsdf {
     igb200_bsdf d;
-    Vec3        n; // surf.local.col(2)
-    bool        one_sided;
-    __device__ __forceinline__ bool  is_specular() const { return d.type != IGB200_BSDF_DIFFUSE; }
-    __device__ __forceinline__ Color kd() const { return Color{ d.color[0], d.color[1], d.color[2] }; }
-    // bsdf/diffuse.art:3-4; specular BSDFs: black / 0 (dielectric.art:3-4, conductor.art:3-4,14-15)
-    __device__ __forceinline__ Color eval(Vec3 in_dir) const
+    Mat3        local; // surf.local, re-oriented by bump maps
+    bool        one_sided, is_entering;
+    Color       kd_;   // DIFFUSE reflectance (constant or texture), ks otherwise
+    __device__ __forceinline__ float au() const { return d.q[0].f; }
+    __device__ __forceinline__ float av() const { return d.q[1].f; }
+    // check_if_delta_distribution, core/microfacet.art:304
+    __device__ __forceinline__ bool  rough() const { return EXT && d.type == IGB200_BSDF_CONDUCTOR && !(au() <= 1e-4f || av() <= 1e-4f); }
+    __device__ __forceinline__ bool  is_specular() const { return d.type != IGB200_BSDF_DIFFUSE && !rough(); }
+    __device__ __forceinline__ Color kd() const { return kd_; }
+    __device__ __forceinline__ Color fresnel_term(float c) const // make_rough_conductor_bsdf, bsdf/conductor.art:102-110
     {
+        return Color{ conductor_factor(d.color2[0], d.p[0], c), conductor_factor(d.color2[1], d.p[1], c),
+                      conductor_factor(d.color2[2], d.p[2], c) };
+    }
+    __device__ __forceinline__ RoughParams rough_params() const
+    {
+        return RoughParams{ local, au(), av(), kd_, Color{ d.color2[0], d.color2[1], d.color2[2] }, Color{ d.p[0], d.p[1], d.p[2] } };
+    }
+    // bsdf/diffuse.art:3-4; specular BSDFs: black / 0 (dielectric.art:3-4, conductor.art:3-4,14-15)
+    __device__ __forceinline__ Color eval(Vec3 in_dir, Vec3 out_dir) const
+    {
+        if (rough()) return rough_eval(rough_params(), in_dir, out_dir);
         if (is_specular()) return Color{ 0.0f, 0.0f, 0.0f };
-        const float c = dot3(in_dir, n);
+        const float c = dot3(in_dir, local.c2);
         return cmulf(kd(), (one_sided ? (c >= 0.0f ? c : 0.0f) : fabsf(c)) * flt_inv_pi);
     }
-    __device__ __forceinline__ float pdf(Vec3 in_dir) const
+    __device__ __forceinline__ float pdf(Vec3 in_dir, Vec3 out_dir) const
     {
+        if (rough()) return rough_pdf(local, au(), av(), in_dir, out_dir);
         if (is_specular()) return 0.0f;
-        const float c = dot3(in_dir, n);
+        const float c = dot3(in_dir, local.c2);
         return __fdiv_rn(c >= 0.0f ? c : 0.0f, flt_pi);
     }
-    __device__ __forceinline__ BsdfSample sample(Rnd& rnd, Vec3 out_dir, const Surf& surf) const
+    // false = reject_bsdf_sample() (the path ends)
+    __device__ __forceinline__ bool sample(Rnd& rnd, Vec3 out_dir, BsdfSample& out) const
     {
+        const Vec3 n = local.c2;
         switch (d.type) {
         default:
         case IGB200_BSDF_DIFFUSE: { // bsdf/diffuse.art:5-9
@@ -204,29 +217,66 @@ struct Bsdf {
             const float v = rnd.next_f32();
             float       pdf;
             const Vec3  l = sample_cosine_hemisphere(u, v, pdf);
-            return BsdfSample{ mat3_mul(surf.local, l), pdf, kd(), 1.0f };
+            out = BsdfSample{ mat3_mul(local, l), pdf, kd(), 1.0f };
+            return true;
         }
         case IGB200_BSDF_DIELECTRIC: { // bsdf/dielectric.art:5-21, adjoint = false
             const float n1 = d.p[0], n2 = d.p[1];
-            const float k     = surf.is_entering ? __fdiv_rn(n1, n2) : __fdiv_rn(n2, n1);
+            const float k     = is_entering ? __fdiv_rn(n1, n2) : __fdiv_rn(n2, n1);
             const float cos_o = dot3(out_dir, n);
             float       cos_t = 0.0f, factor = 1.0f;
             if (!fresnel(k, cos_o, cos_t, factor)) { cos_t = 0.0f; factor = 1.0f; }
             if (rnd.next_f32() > factor)
-                return BsdfSample{ refract(out_dir, n, k, cos_o, cos_t), 1.0f, Color{ d.color2[0], d.color2[1], d.color2[2] }, k };
-            return BsdfSample{ reflect(out_dir, n), 1.0f, kd(), 1.0f };
+                out = BsdfSample{ refract(out_dir, n, k, cos_o, cos_t), 1.0f, Color{ d.color2[0], d.color2[1], d.color2[2] }, k };
+            else
+                out = BsdfSample{ reflect(out_dir, n), 1.0f, kd(), 1.0f };
+            return true;
         }
         case IGB200_BSDF_MIRROR: // bsdf/conductor.art:5-7
-            return BsdfSample{ reflect(out_dir, n), 1.0f, kd(), 1.0f };
-        case IGB200_BSDF_CONDUCTOR: { // bsdf/conductor.art:16-28
-            const float cos_i = dot3(out_dir, n);
-            const Color f{ conductor_factor(d.color2[0], d.p[0], cos_i), conductor_factor(d.color2[1], d.p[1], cos_i),
-                           conductor_factor(d.color2[2], d.p[2], cos_i) };
-            return BsdfSample{ reflect(out_dir, n), 1.0f, cmul(kd(), f), 1.0f };
+            out = BsdfSample{ reflect(out_dir, n), 1.0f, kd(), 1.0f };
+            return true;
+        case IGB200_BSDF_CONDUCTOR: {
+            if (rough()) { // make_rough_base_conductor_bsdf::sample; the two draws of sample_vndf_ggx_11 happen here
+                const float cos_o = fabsf(dot3(out_dir, n));
+                if (cos_o <= flt_eps) return false;
+                const float       u0 = rnd.next_f32();
+                const float       u1 = rnd.next_f32();
+                const RoughSample rs = rough_sample(rough_params(), u0, u1, out_dir);
+                out                  = BsdfSample{ rs.in_dir, rs.pdf, rs.col, 1.0f };
+                return rs.ok;
+            }
+            const float cos_i = dot3(out_dir, n); // make_pure_conductor_bsdf, bsdf/conductor.art:16-28
+            out = BsdfSample{ reflect(out_dir, n), 1.0f, cmul(kd(), fresnel_term(cos_i)), 1.0f };
+            return true;
         }
         }
     }
 };
+
+// Resolves material -> BSDF: bump-map chains re-orient the frame, textures replace constant colours
+// (what the generated `bsdf_<id>` shader closures do, runtime/bsdf/MapBSDF.cpp, DiffuseBSDF.cpp).
+template <bool EXT>
+__device__ __forceinline__ Bsdf<EXT> make_bsdf(const ShadeScene& sc, int32_t id, const Surf& surf, Vec3 ray_dir, bool one_sided)
+{
+    Bsdf<EXT> out;
+    out.local = surf.local;
+    out.d     = sc.bsdfs[id];
+    for (int guard = 0; EXT && guard < 8 && out.d.type == IGB200_BSDF_BUMPMAP; ++guard) {
+        float tu, tv;
+        surf_tex_coords(surf, tu, tv);
+        out.local = bump_frame(sc.textures, sc.blob, out.d.q[0].u - 1u, out.d.p[0], tu, tv, surf.face_normal, ray_dir, out.local);
+        out.d = sc.bsdfs[(int32_t)out.d.q[1].u - 1];
+    }
+    out.one_sided   = one_sided;
+    out.is_entering = surf.is_entering;
+    out.kd_         = Color{ out.d.color[0], out.d.color[1], out.d.color[2] };
+    if (EXT && out.d.type == IGB200_BSDF_DIFFUSE && out.d.q[0].u != 0u) {
+        float tu, tv;
+        surf_tex_coords(surf, tu, tv);
+        out.kd_ = tex_eval(sc.textures, sc.blob, out.d.q[0].u - 1u, tu, tv);
+    }
+    return out;
+}
 
 } // namespace shade
 } // namespace igb

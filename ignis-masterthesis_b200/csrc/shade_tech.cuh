@@ -12,7 +12,10 @@ __device__ __forceinline__ bool light_delta(uint32_t type)
 {
     return type == IGB200_LIGHT_POINT || type == IGB200_LIGHT_SPOT || type == IGB200_LIGHT_DIRECTIONAL;
 }
-__device__ __forceinline__ bool light_infinite(uint32_t type) { return type == IGB200_LIGHT_ENV || type == IGB200_LIGHT_DIRECTIONAL; }
+__device__ __forceinline__ bool light_infinite(uint32_t type)
+{
+    return type == IGB200_LIGHT_ENV || type == IGB200_LIGHT_DIRECTIONAL || type == IGB200_LIGHT_ENV_TEXTURED;
+}
 __device__ __forceinline__ Color light_color(const igb200_light& l) { return Color{ l.color[0], l.color[1], l.color[2] }; }
 
 // make_plane_area_emitter, light/area.art:107-232
@@ -85,7 +88,131 @@ __device__ __forceinline__ Surf shape_emitter_sample(const ShadeScene& sc, const
     return s;
 }
 
+// ---- core/cdf.art on the blob layout of cdf::make_cdf_2d_from_buffer (:156-160) ---------------------------------
+struct Cdf1 { // make_cdf_1d_from_buffer :70-72 + make_cdf_1d :38-68
+    const float* data;
+    int32_t      n;
+    __device__ __forceinline__ float get(int32_t i) const { return i == 0 ? 0.0f : __ldg(data + i - 1); }
+    __device__ __forceinline__ float pdf_discrete(int32_t x) const { return get(x + 1) - get(x); }
+    __device__ __forceinline__ int32_t sample_discrete(float u) const
+    {
+        int32_t first = 0, len_ = n + 1; // interval::binary_search, core/interval.art:7-23
+        while (len_ > 0) {
+            const int32_t half = len_ / 2, middle = first + half;
+            if (get(middle) <= u) { first = middle + 1; len_ -= half + 1; } else { len_ = half; }
+        }
+        return min(min(max(first - 1, 0), n), n - 1);
+    }
+    __device__ __forceinline__ void sample_continuous(float u, int32_t& off, float& pos, float& pdf) const
+    {
+        off             = sample_discrete(u);
+        const float pd  = pdf_discrete(off);
+        const float rem = safe_div(u - get(off), pd);
+        pos             = clampf(((float)off + rem) / (float)n, 0.0f, 1.0f);
+        pdf             = pd * (float)n;
+    }
+    __device__ __forceinline__ void pdf_continuous(float x, int32_t& off, float& pdf) const
+    {
+        off = min(max((int32_t)(x * (float)n), 0), n - 1);
+        pdf = pdf_discrete(off) * (float)n;
+    }
+};
+struct Cdf2 {
+    const float* base;
+    int32_t      sx, sy;
+    __device__ __forceinline__ Cdf1 marginal() const { return Cdf1{ base, sy }; }
+    __device__ __forceinline__ Cdf1 conditional(int32_t i) const { return Cdf1{ base + sy + (size_t)i * sx, sx }; }
+};
+
+// light/env.art:13-21, core/warp.art:44-57
+__device__ __forceinline__ Vec3 switch_env_up(Vec3 v) { return Vec3{ v.x, v.z, v.y }; }
+__device__ __forceinline__ void map_env_uv(Vec3 dir, float& u, float& v)
+{
+    const float theta = acosf(dir.z);
+    float       phi   = atan2f(dir.y, dir.x);
+    if (phi < 0.0f) phi += 2.0f * flt_pi;
+    u = fractf(phi / (2.0f * flt_pi) + 0.25f);
+    v = 1.0f - theta / flt_pi;
+}
+__device__ __forceinline__ Mat3 light_transform(const igb200_light& l)
+{
+    return Mat3{ Vec3{ l.v[0], l.v[1], l.v[2] }, Vec3{ l.v[3], l.v[4], l.v[5] }, Vec3{ l.v[6], l.v[7], l.v[8] } };
+}
+__device__ __forceinline__ Vec3 mat3_left_mul(const Mat3& m, Vec3 v) { return Vec3{ dot3(m.c0, v), dot3(m.c1, v), dot3(m.c2, v) }; }
+
+// Light::emission of an infinite light along `dir` (light/env.art:93,146-151,163-166).  The __noinline__ helpers take
+// the device pointers they need, never the ShadeScene (a reference to the kernel argument would copy it to the stack).
+static __device__ __noinline__ Color env_tex_emission(const igb200_texture* textures, const uint8_t* blob, const igb200_light* l, Vec3 dir)
+{
+    float u, v;
+    map_env_uv(switch_env_up(mat3_mul(light_transform(*l), dir)), u, v);
+    return cmul(light_color(*l), tex_eval(textures, blob, l->tex, u, v));
+}
+template <bool EXT>
+__device__ __forceinline__ Color env_emission(const ShadeScene& sc, const igb200_light& l, Vec3 dir)
+{
+    return EXT && l.type == IGB200_LIGHT_ENV_TEXTURED ? env_tex_emission(sc.textures, sc.blob, &l, dir) : light_color(l);
+}
+__device__ __forceinline__ Cdf2 load_cdf2(const uint8_t* blob, uint32_t off4)
+{
+    const uint32_t* h = reinterpret_cast<const uint32_t*>(blob) + off4;
+    return Cdf2{ reinterpret_cast<const float*>(h + 4), (int32_t)h[0], (int32_t)h[1] };
+}
+// Light::pdf_direct of an infinite light, solid angle (light/env.art:96,121-127,152)
+static __device__ __noinline__ float env_tex_pdf(const uint8_t* blob, const igb200_light* l, Vec3 dir)
+{
+    const Vec3  ldir     = switch_env_up(mat3_mul(light_transform(*l), dir));
+    const float sinTheta = safe_sqrt(1.0f - ldir.z * ldir.z);
+    float       u, v;
+    map_env_uv(ldir, u, v);
+    const Cdf2 cdf = load_cdf2(blob, l->cdf);
+    int32_t    oy, ox;
+    float      p1, p2;
+    cdf.marginal().pdf_continuous(v, oy, p1);
+    cdf.conditional(oy).pdf_continuous(u, ox, p2);
+    return safe_div(p1 * p2, sinTheta * flt_pi * flt_pi * 2.0f);
+}
+template <bool EXT>
+__device__ __forceinline__ float env_pdf(const ShadeScene& sc, const igb200_light& l, Vec3 dir)
+{
+    if (!EXT || l.type != IGB200_LIGHT_ENV_TEXTURED || l.cdf == IGB200_NO_CDF) return __fdiv_rn(1.0f, 4.0f * flt_pi);
+    return env_tex_pdf(sc.blob, &l, dir);
+}
+
+struct EnvSample { Vec3 dir; Color intensity; float pdf; };
+static __device__ __noinline__ EnvSample env_tex_sample_direct(const igb200_texture* textures, const uint8_t* blob, const igb200_light* lp,
+                                                               float u0, float u1)
+{
+    const igb200_light& l = *lp;
+    const Mat3 tr = light_transform(l);
+    EnvSample  out;
+    if (l.cdf == IGB200_NO_CDF) { // make_environment_light -> function_spherical, light/env.art:163-166,82-86
+        const Vec3 d = equal_area_square_to_sphere(u0, u1);
+        out.pdf      = __fdiv_rn(1.0f, 4.0f * flt_pi);
+        float tu, tv;
+        map_env_uv(switch_env_up(mat3_mul(tr, d)), tu, tv);
+        out.intensity = cmulf(cmul(light_color(l), tex_eval(textures, blob, l.tex, tu, tv)), __fdiv_rn(1.0f, out.pdf));
+        out.dir       = d;
+    } else { // make_environment_light_textured::sample_dir, light/env.art:115-133 (radiance NOT scaled, as written)
+        const Cdf2  cdf = load_cdf2(blob, l.cdf);
+        int32_t     oy, ox;
+        float       py, px, p1, p2;
+        cdf.marginal().sample_continuous(u1, oy, py, p1);
+        cdf.conditional(oy).sample_continuous(u0, ox, px, p2);
+        const Color in    = tex_eval(textures, blob, l.tex, px, py);
+        const float theta = (1.0f - py) * flt_pi, phi = (px - 0.25f) * 2.0f * flt_pi;
+        const float st = sinf(theta), ct = cosf(theta);
+        const Vec3  d0{ st * cosf(phi), st * sinf(phi), ct }; // dir_from_spherical
+        const float sinTheta = safe_sqrt(1.0f - d0.z * d0.z);
+        out.pdf       = safe_div(p1 * p2, sinTheta * flt_pi * flt_pi * 2.0f);
+        out.intensity = cmulf(in, 1.0f / out.pdf);
+        out.dir       = mat3_left_mul(tr, switch_env_up(d0));
+    }
+    return out;
+}
+
 // Light::sample_direct of every supported light
+template <bool EXT>
 __device__ __forceinline__ DirectSample light_sample_direct(const ShadeScene& sc, const igb200_light& l, Rnd& rnd, const Surf& from)
 {
     switch (l.type) {
@@ -127,6 +254,13 @@ __device__ __forceinline__ DirectSample light_sample_direct(const ShadeScene& sc
         return DirectSample{ vadd(from.point, vmulf(d, sc.scene_radius)), d, cmulf(light_color(l), __fdiv_rn(1.0f, pdf)), Pdf{ pdf, 0 },
                              1.0f, sc.scene_radius };
     }
+    case IGB200_LIGHT_ENV_TEXTURED: {
+        if (!EXT) break;
+        const float     u0 = rnd.next_f32();
+        const float     u1 = rnd.next_f32();
+        const EnvSample es = env_tex_sample_direct(sc.textures, sc.blob, &l, u0, u1);
+        return DirectSample{ vadd(from.point, vmulf(es.dir, sc.scene_radius)), es.dir, es.intensity, Pdf{ es.pdf, 0 }, 1.0f, sc.scene_radius };
+    }
     case IGB200_LIGHT_AREA_SHAPE:
     case IGB200_LIGHT_AREA_PLANE: { // make_area_light::sample_direct, light/area.art:12-26
         const float u = rnd.next_f32();
@@ -166,17 +300,100 @@ __device__ __forceinline__ Pdf light_pdf_direct(const ShadeScene& sc, const igb2
     return Pdf{ 1.0f, 0 };
 }
 
-// make_uniform_light_selector, light/light_selector.art:26-45
-__device__ __forceinline__ float selector_pdf(const ShadeScene& sc)
+// make_uniform_light_selector / make_hierarchy_light_selector, light/light_selector.art:19-45,76-110
+struct HEntry { Vec3 pos, dir; float flux; int32_t id; bool has_dir, is_leaf; };
+__device__ __forceinline__ const float* hier_nodes(const uint8_t* blob, uint32_t hierarchy, int32_t n_fin)
+{
+    return reinterpret_cast<const float*>(blob) + hierarchy + ((n_fin + 3) / 4) * 4;
+}
+__device__ __forceinline__ HEntry hier_load(const float* nodes, int32_t id) // light_hierarchy.art:24-38
+{
+    const float4  e1 = __ldg(reinterpret_cast<const float4*>(nodes) + 2 * id), e2 = __ldg(reinterpret_cast<const float4*>(nodes) + 2 * id + 1);
+    const int32_t index = __float_as_int(e2.w);
+    return HEntry{ Vec3{ e1.x, e1.y, e1.z }, Vec3{ e2.x, e2.y, e2.z }, fabsf(e1.w), index < 0 ? -index - 1 : index, !signbit(e1.w), index >= 0 };
+}
+__device__ __forceinline__ float hier_cost(const HEntry& e, Vec3 pos) // get_entry_cost :40-52
+{
+    const Vec3  cdir  = vsub(e.pos, pos);
+    const float dist2 = dot3(cdir, cdir);
+    const float cos_d = e.has_dir ? fabsf(dot3(e.dir, vnormalize(cdir))) : 1.0f;
+    return safe_div(e.flux * cos_d, dist2);
+}
+__device__ __forceinline__ float hier_left_prop(const HEntry& l, const HEntry& r, Vec3 pos) // :54-58
+{
+    return 1.0f / (1.0f + hier_cost(r, pos) / hier_cost(l, pos));
+}
+struct HierPick { int32_t id; float pdf; uint32_t counter; };
+static __device__ __noinline__ HierPick hier_sample(const uint8_t* blob, uint32_t hierarchy, int32_t n_fin, Rnd rnd, Vec3 pos) // :65-78
+{
+    float pdf = 1.0f;
+    if (n_fin == 1) return HierPick{ 0, pdf, rnd.counter };
+    const float* nodes = hier_nodes(blob, hierarchy, n_fin);
+    HEntry       e     = hier_load(nodes, 0);
+    while (!e.is_leaf) {
+        const HEntry l = hier_load(nodes, e.id), r = hier_load(nodes, e.id + 1);
+        const float  prop = hier_left_prop(l, r, pos);
+        const bool   left = rnd.next_f32() < prop;
+        e                 = left ? l : r;
+        pdf *= left ? prop : 1.0f - prop;
+    }
+    return HierPick{ e.id, pdf, rnd.counter };
+}
+static __device__ __noinline__ float hier_pdf(const uint8_t* blob, uint32_t hierarchy, int32_t n_fin, int32_t light_id, Vec3 pos) // :80-96
+{
+    if (n_fin == 1) return 1.0f;
+    const float* nodes = hier_nodes(blob, hierarchy, n_fin);
+    uint32_t     code  = __ldg(reinterpret_cast<const uint32_t*>(blob) + hierarchy + light_id);
+    float        pdf   = 1.0f;
+    HEntry       e     = hier_load(nodes, 0);
+    while (!e.is_leaf) {
+        const HEntry l = hier_load(nodes, e.id), r = hier_load(nodes, e.id + 1);
+        const float  prop = hier_left_prop(l, r, pos);
+        const bool   left = (code & 0x1u) == 0u;
+        e                 = left ? l : r;
+        pdf *= left ? prop : 1.0f - prop;
+        code >>= 1;
+    }
+    return pdf;
+}
+template <bool EXT>
+__device__ __forceinline__ bool selector_hierarchical(const ShadeScene& sc) { return EXT && sc.selector == IGB200_SELECTOR_HIERARCHY && sc.n_fin != 0; }
+__device__ __forceinline__ float selector_uniform_pdf(const ShadeScene& sc)
 {
     const int32_t n = sc.n_inf + sc.n_fin;
     return n == 0 ? 1.0f : __fdiv_rn(1.0f, (float)n);
 }
-__device__ __forceinline__ const igb200_light& selector_sample(const ShadeScene& sc, Rnd& rnd)
+template <bool EXT>
+__device__ __forceinline__ float selector_pdf(const ShadeScene& sc, bool infinite, int32_t id, Vec3 pos)
 {
-    const int32_t n  = sc.n_inf + sc.n_fin;
-    const int32_t id = n <= 1 ? 0 : rnd.next_i32(0, n - 1); // pick_light_id :19-25
-    return id < sc.n_inf ? sc.inf_lights[id] : sc.fin_lights[id - sc.n_inf];
+    if (!selector_hierarchical<EXT>(sc)) return selector_uniform_pdf(sc);
+    if (sc.n_inf == 0) return hier_pdf(sc.blob, sc.hierarchy, sc.n_fin, id, pos);
+    return infinite ? (1.0f / (float)sc.n_inf) * 0.5f : hier_pdf(sc.blob, sc.hierarchy, sc.n_fin, id, pos) * (1.0f - 0.5f);
+}
+template <bool EXT>
+__device__ __forceinline__ const igb200_light& selector_sample(const ShadeScene& sc, Rnd& rnd, Vec3 pos, float& pdf)
+{
+    if (!selector_hierarchical<EXT>(sc)) {
+        pdf              = selector_uniform_pdf(sc);
+        const int32_t n  = sc.n_inf + sc.n_fin;
+        const int32_t id = n <= 1 ? 0 : rnd.next_i32(0, n - 1); // pick_light_id :19-25
+        return id < sc.n_inf ? sc.inf_lights[id] : sc.fin_lights[id - sc.n_inf];
+    }
+    if (sc.n_inf == 0) {
+        const HierPick hp = hier_sample(sc.blob, sc.hierarchy, sc.n_fin, rnd, pos);
+        rnd.counter       = hp.counter;
+        pdf               = hp.pdf;
+        return sc.fin_lights[hp.id];
+    }
+    const float q = rnd.next_f32();
+    if (q < 0.5f) {
+        pdf = (1.0f / (float)sc.n_inf) * 0.5f;
+        return sc.inf_lights[sc.n_inf <= 1 ? 0 : rnd.next_i32(0, sc.n_inf - 1)];
+    }
+    const HierPick hp = hier_sample(sc.blob, sc.hierarchy, sc.n_fin, rnd, pos);
+    rnd.counter       = hp.counter;
+    pdf               = hp.pdf * (1.0f - 0.5f);
+    return sc.fin_lights[hp.id];
 }
 
 __device__ __forceinline__ Color handle_color(const igb200_technique& t, Color c) // technique/pathtracer.art:46-50

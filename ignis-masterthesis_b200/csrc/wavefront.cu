@@ -309,6 +309,7 @@ __device__ __forceinline__ void splat(float* film, uint32_t pixel, Color c, floa
     atomicAdd(p + 2, c.b * inv_spi);
 }
 
+template <bool EXT>
 __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScene& geo, const WaveSettings& set, const PathStream& cur,
                                        uint32_t i, float* film, bool& alive, NextState& nx, bool& has_shadow, ShadowState& sh)
 {
@@ -333,9 +334,9 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
                 const igb200_light& l = sc.inf_lights[k];
                 if (light_infinite(l.type) && !light_delta(l.type)) {
                     ++inflights;
-                    const float pdf_s = __fdiv_rn(1.0f, 4.0f * flt_pi); // env.art:96
-                    const float mis   = tech.enable_nee ? __fdiv_rn(1.0f, 1.0f + inv_pdf * selector_pdf(sc) * pdf_s) : 1.0f;
-                    col               = cadd(col, handle_color(tech, cmulf(cmul(contrib0, light_color(l)), mis)));
+                    const float pdf_s = env_pdf<EXT>(sc, l, dir); // env.art:96,152
+                    const float mis   = tech.enable_nee ? __fdiv_rn(1.0f, 1.0f + inv_pdf * selector_pdf<EXT>(sc, true, k, org) * pdf_s) : 1.0f;
+                    col               = cadd(col, handle_color(tech, cmulf(cmul(contrib0, env_emission<EXT>(sc, l, dir)), mis)));
                 }
             }
             if (inflights > 0) splat(film, pixel, col, set.inv_spi);
@@ -352,7 +353,7 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
     else
         surf = trimesh_surface_element(load_trimesh(sc, e.shape_id()), e, org, dir, t, u, v, prim);
     const igb200_material mat = sc.materials[e.mat_id()];
-    const Bsdf bsdf{ sc.bsdfs[mat.bsdf], surf.local.c2, (tech.flags & IGB200_TECHFLAG_ONE_SIDED_DIFFUSE) != 0u };
+    const Bsdf<EXT> bsdf = make_bsdf<EXT>(sc, mat.bsdf, surf, dir, (tech.flags & IGB200_TECHFLAG_ONE_SIDED_DIFFUSE) != 0u);
 
     if (tech.type == IGB200_TECH_DEBUG) { // technique/debugtracer.art:29-177
         Color out;
@@ -361,7 +362,7 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
         case 1: out = absv(surf.local.c0); break;
         case 2: out = absv(surf.local.c1); break;
         case 3: out = absv(surf.face_normal); break;
-        case 8: out = Color{ fabsf(surf.tu), fabsf(surf.tv), 0.0f }; break;
+        case 8: { float tu, tv; surf_tex_coords(surf, tu, tv); out = Color{ fabsf(tu), fabsf(tv), 0.0f }; break; }
         case 9: out = Color{ fabsf(u), fabsf(v), 0.0f }; break;
         case 10: out = Color{ surf.point.x, surf.point.y, surf.point.z }; break;
         case 13: out = Color{ t, t, t }; break;
@@ -385,7 +386,7 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
             const igb200_light& l     = sc.fin_lights[mat.light];
             const Pdf           pdf   = light_pdf_direct(sc, l, org, surf);
             const float         pdf_s = pdf.as_solid(d, t * t);
-            const float         mis   = tech.enable_nee ? __fdiv_rn(1.0f, 1.0f + inv_pdf * selector_pdf(sc) * pdf_s) : 1.0f;
+            const float         mis   = tech.enable_nee ? __fdiv_rn(1.0f, 1.0f + inv_pdf * selector_pdf<EXT>(sc, false, mat.light, org) * pdf_s) : 1.0f;
             splat(film, pixel, handle_color(tech, cmulf(cmul(contrib0, light_color(l)), mis)), set.inv_spi);
         }
     }
@@ -395,13 +396,14 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
 
     // on_shadow (pathtracer.art:52-110): next event estimation
     if (tech.enable_nee && !bsdf.is_specular() && (sc.n_inf + sc.n_fin) != 0 && depth + 1 <= tech.max_depth) {
-        const igb200_light& l  = selector_sample(sc, rnd);
-        const DirectSample  ls = light_sample_direct(sc, l, rnd, surf);
-        const float pdf_l_s    = ls.pdf.as_solid(ls.cos, ls.dist * ls.dist) * selector_pdf(sc);
+        float               sel_pdf;
+        const igb200_light& l  = selector_sample<EXT>(sc, rnd, surf.point, sel_pdf);
+        const DirectSample  ls = light_sample_direct<EXT>(sc, l, rnd, surf);
+        const float pdf_l_s    = ls.pdf.as_solid(ls.cos, ls.dist * ls.dist) * sel_pdf;
         if (!(pdf_l_s <= flt_eps) && ls.cos > flt_eps) {
-            const float mis    = light_delta(l.type) ? 1.0f : __fdiv_rn(1.0f, 1.0f + __fdiv_rn(bsdf.pdf(ls.dir), pdf_l_s));
+            const float mis    = light_delta(l.type) ? 1.0f : __fdiv_rn(1.0f, 1.0f + __fdiv_rn(bsdf.pdf(ls.dir, out_dir), pdf_l_s));
             const float factor = __fdiv_rn(ls.pdf.value, pdf_l_s);
-            const Color c      = handle_color(tech, cmulf(cmul(ls.intensity, cmul(contrib0, bsdf.eval(ls.dir))), mis * factor));
+            const Color c      = handle_color(tech, cmulf(cmul(ls.intensity, cmul(contrib0, bsdf.eval(ls.dir, out_dir))), mis * factor));
             has_shadow         = true;
             if (light_infinite(l.type)) {
                 sh.org_tmin = make_float4(surf.point.x, surf.point.y, surf.point.z, offset);
@@ -417,7 +419,8 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
 
     // on_bounce (pathtracer.art:162-200)
     if (depth + 1 > tech.max_depth) return;
-    const BsdfSample ms      = bsdf.sample(rnd, out_dir, surf);
+    BsdfSample ms;
+    if (!bsdf.sample(rnd, out_dir, ms)) return;
     const Color      contrib = cmul(contrib0, ms.col);
     const float      eta0    = meta.w;
     float            rr_prob = 1.0f;
@@ -439,6 +442,7 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
 #ifndef IGB_SHADE_MIN_BLOCKS
 #define IGB_SHADE_MIN_BLOCKS 6 // 85 registers, 80 B of spills: +2 % over 4 blocks (112 registers) on B200
 #endif
+template <bool EXT>
 __global__ void __launch_bounds__(128, IGB_SHADE_MIN_BLOCKS) shade_kernel(WaveControl* __restrict__ ctl, const PathStream cur, const PathStream nxt,
                                                     const ShadowStream shq, const uint32_t* __restrict__ sorted, const ShadeScene sc,
                                                     const DeviceScene geo)
@@ -454,7 +458,7 @@ __global__ void __launch_bounds__(128, IGB_SHADE_MIN_BLOCKS) shade_kernel(WaveCo
         bool        alive = false, has_shadow = false;
         NextState   nx;
         ShadowState sh;
-        if (p < n) shade_one(sc, geo, set, cur, sorted ? sorted[p] : p, film, alive, nx, has_shadow, sh);
+        if (p < n) shade_one<EXT>(sc, geo, set, cur, sorted ? sorted[p] : p, film, alive, nx, has_shadow, sh);
 
         // stream compaction: one atomic per warp, ranks from the ballot (replaces gpu_compact_primary)
         const uint32_t am = __ballot_sync(0xFFFFFFFFu, alive);
@@ -512,7 +516,10 @@ cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene&
     const PrimaryIO pio{ cur, buf.keys, buf.ent_mat, buf.ctl, n_bins };
     trace_kernel<PrimaryIO, false, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, pio, nullptr, buf.ctl->work_primary);
     if (sort) scatter_kernel<<<wide / 2, 256, 0, stream>>>(buf.ctl, buf.keys, buf.sorted, n_bins, sort == 2 && n_bins <= kMaxSmemBins);
-    shade_kernel<<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene);
+    if (sh.extended)
+        shade_kernel<true><<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene);
+    else
+        shade_kernel<false><<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene);
     const ShadowIO sio{ buf.shadow, buf.ctl };
     trace_kernel<ShadowIO, true, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, sio, nullptr, buf.ctl->work_shadow);
     return cudaGetLastError();

@@ -28,6 +28,8 @@ def save_fixture(path, tables, sh, width, height, ref=None, meta=""):
         material_count=np.int64(tables.material_count), entity_per_material=np.asarray(tables.entity_per_material, np.int64),
         camera=_bytes(sh.camera), technique=_bytes(sh.technique), bsdfs=_table(S.Bsdf, sh.bsdfs),
         materials=_table(S.Material, sh.materials), infinite=_table(S.Light, sh.infinite), finite=_table(S.Light, sh.finite),
+        textures=_table(S.Texture, sh.textures), blob=np.frombuffer(bytes(sh.blob), np.uint8).copy(),
+        selector=np.asarray([sh.selector, sh.hierarchy], np.int64),
         size=np.asarray([width, height], np.int64), ref=np.zeros(0, np.float32) if ref is None else np.asarray(ref, np.float32),
         meta=np.asarray(meta))
 
@@ -50,6 +52,10 @@ def load_fixture(path):
     sh.materials = _untable(S.Material, z["materials"])
     sh.infinite = _untable(S.Light, z["infinite"])
     sh.finite = _untable(S.Light, z["finite"])
+    if "textures" in z.files:  # ABI v3 additions
+        sh.textures = _untable(S.Texture, z["textures"])
+        sh.blob = bytearray(z["blob"].tobytes())
+        sh.selector, sh.hierarchy = [int(x) for x in z["selector"]]
     w, h = [int(x) for x in z["size"]]
     ref = z["ref"]
     return tables, sh, w, h, (ref if ref.size else None)

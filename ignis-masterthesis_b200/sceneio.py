@@ -458,6 +458,12 @@ def _merge_externals(scene, base):
 def _color(v, default):
     if v is None:
         v = default
+    if isinstance(v, str):  # constant PExpr "color(r, g, b[, a])" (loader/Transpiler.cpp); anything else is not folded
+        import re
+        m = re.fullmatch(r"\s*color\(\s*([^,()]+),\s*([^,()]+),\s*([^,()]+)(?:,\s*[^,()]+)?\)\s*", v)
+        if not m:
+            raise ValueError(f"expression '{v}' is outside the supported subset")
+        v = [float(m.group(i)) for i in (1, 2, 3)]
     a = np.asarray(v, np.float32).reshape(-1)
     return np.repeat(a, 3) if a.size == 1 else a[:3]
 
@@ -528,6 +534,144 @@ def build_shape(elem, base):
     return ("trimesh", mesh)
 
 
+# ---------------------------------------------------------------------------------------- images / textures
+def _srgb_byte_to_linear(c):  # byte_color_to_linear, src/runtime/Image.cpp:31-42
+    x = c.astype(np.float32) / np.float32(255.0)
+    lin = np.where(x <= np.float32(0.04045), x / np.float32(12.92),
+                   np.power((x + np.float32(0.055)) / np.float32(1.055), np.float32(2.4), dtype=np.float32))
+    return np.minimum(255, np.floor(lin * np.float32(255))).astype(np.uint8)
+
+
+def load_packed_image(path, linear=False):
+    """Image::loadAsPacked (src/runtime/Image.cpp:565-655): (h, w) uint32 RGBA8, bottom row first, sRGB bytes mapped
+    to linear unless `linear`; returns (pixels, opaque)."""
+    import cv2
+    img = cv2.imread(path, cv2.IMREAD_UNCHANGED)
+    if img is None:
+        raise FileNotFoundError(path)
+    if img.dtype != np.uint8:
+        raise ValueError("packed images are 8 bit")
+    if img.ndim == 2:
+        img = np.repeat(img[:, :, None], 3, axis=2)
+    opaque = img.shape[2] == 3
+    rgb = img[:, :, 2::-1] if img.shape[2] >= 3 else img
+    alpha = img[:, :, 3] if img.shape[2] == 4 else np.full(img.shape[:2], 255, np.uint8)
+    if not linear:
+        rgb = _srgb_byte_to_linear(rgb)
+    px = (rgb[:, :, 0].astype(np.uint32) | (rgb[:, :, 1].astype(np.uint32) << 8) | (rgb[:, :, 2].astype(np.uint32) << 16)
+          | (alpha.astype(np.uint32) << 24))
+    return np.ascontiguousarray(px[::-1]), opaque  # stbi_set_flip_vertically_on_load(1)
+
+
+def _transform2d(t):  # LoaderUtils::inlineTransformAs2d: the 2-D affine part of a transform
+    if t is None:
+        return None
+    m = parse_transform(t)
+    out = np.eye(3)
+    out[:2, :2] = m[:2, :2]
+    out[:2, 2] = m[:2, 3]
+    return out
+
+
+_FILTERS = {"bilinear": 1, "nearest": 0}  # anything else is bicubic (pattern/ImagePattern.cpp:19-31)
+_WRAPS = {"mirror": 1, "clamp": 2}
+
+
+def build_texture(sh, e, base):
+    ty = e["type"]
+    if ty == "checkerboard":  # pattern/CheckerBoardPattern.cpp:14-35
+        return sh.add_checkerboard((e.get("scale_x", 2.0), e.get("scale_y", 2.0)), _color(e.get("color0"), 0.0),
+                                   _color(e.get("color1"), 1.0), _transform2d(e.get("transform")))
+    if ty in ("image", "bitmap"):  # pattern/ImagePattern.cpp
+        path = os.path.join(base, e["filename"])
+        if path.lower().endswith((".exr", ".hdr")):
+            raise ValueError("float image textures are outside the supported subset")
+        px, opaque = load_packed_image(path, e.get("linear", False))
+        if "wrap_mode_u" in e:
+            wrap = (_WRAPS.get(e.get("wrap_mode_u", "repeat"), 0), _WRAPS.get(e.get("wrap_mode_v", "repeat"), 0))
+        else:
+            wrap = (_WRAPS.get(e.get("wrap_mode", "repeat"), 0),) * 2
+        return sh.add_image_texture(px, _FILTERS.get(e.get("filter_type", "bicubic"), 2), wrap, _transform2d(e.get("transform")), opaque)
+    raise ValueError(f"texture type '{ty}' is outside the supported subset")
+
+
+_CONDUCTORS = {"none": ((0.0, 0.0, 0.0), (1.0, 1.0, 1.0))}  # runtime/bsdf/BSDF.cpp:12-42 (named metals: not restated)
+
+
+# ---------------------------------------------------------------------------------------- light hierarchy
+def build_light_hierarchy(entries):
+    """LightHierarchy::setup (src/runtime/light/LightHierarchy.cpp:46-127) over PointBvh::store
+    (src/runtime/container/PointBvh.inl:23-95).  entries: (position, direction or None, flux) per finite light, in id
+    order.  Returns (codes u32[n], nodes float32[m, 8])."""
+    F = np.float32
+    inner, leaves = [], []  # inner: dict(index, lo, hi, mid, axis)
+
+    def descend(i, p):
+        while True:
+            n = inner[i]
+            n["lo"], n["hi"] = np.minimum(n["lo"], p), np.maximum(n["hi"], p)
+            if n["axis"] < 0:
+                return i
+            mid = ((n["hi"] + n["lo"]) / F(2))[n["axis"]]
+            i = n["index"] if p[n["axis"]] < mid else n["index"] + 1
+
+    for k, (pos, direction, flux) in enumerate(entries):
+        p = np.asarray(pos, F)
+        has_dir = direction is not None
+        leaves.append((p, np.asarray(direction if has_dir else (0, 0, 1), F), F(flux) if has_dir else -F(flux), k))
+        if not inner:
+            inner.append(dict(index=0, lo=p.copy(), hi=p.copy(), mid=F(0), axis=-1))
+            continue
+        ni = descend(0, p)
+        node = inner[ni]
+        old_leaf, lo, hi = node["index"], node["lo"].copy(), node["hi"].copy()
+        diam = hi - lo
+        axis = int(np.argmax(diam))
+        mid = diam[axis] / F(2)  # (sic) half the extent, not a position
+        left_idx = len(inner)
+        node.update(index=left_idx, axis=axis, mid=mid)
+        off = (hi[axis] - lo[axis]) * F(0.5)  # BoundingBox::computeSplit
+        lhi, rlo = hi.copy(), lo.copy()
+        lhi[axis] -= off
+        rlo[axis] += off
+        new_leaf = len(leaves) - 1
+        li, ri = (new_leaf, old_leaf) if p[axis] < mid else (old_leaf, new_leaf)
+        inner.append(dict(index=li, lo=lo.copy(), hi=lhi, mid=F(0), axis=-1))
+        inner.append(dict(index=ri, lo=rlo, hi=hi.copy(), mid=F(0), axis=-1))
+
+    nodes = np.zeros((len(inner), 8), F)
+    ids = np.zeros(len(inner), np.int32)
+    codes = np.zeros(len(entries), np.uint32)
+
+    def populate(i, code, depth):  # populateInnerNodes
+        n = inner[i]
+        if n["axis"] < 0:
+            p, d, f, lid = leaves[n["index"]]
+            codes[lid] = code
+            nodes[i, 0:3], nodes[i, 3], nodes[i, 4:7] = p, f, d
+            ids[i] = lid
+            return d, f
+        ld, lf = populate(n["index"], code, depth + 1)
+        rd, rf = populate(n["index"] + 1, code | (1 << depth), depth + 1)
+        nodes[i, 0:3] = (n["hi"] + n["lo"]) / F(2)
+        ids[i] = -(n["index"] + 1)
+        if lf < 0 and rf < 0:
+            d, f = np.array([0, 0, 1], F), lf + rf
+        elif lf < 0:
+            d, f = np.array([0, 0, 1], F), -(-lf + rf)
+        elif rf < 0:
+            d, f = np.array([0, 0, 1], F), -(lf - rf)
+        else:
+            d = ld + rd
+            d, f = (d / np.sqrt(np.dot(d, d), dtype=F)).astype(F), lf + rf
+        nodes[i, 3], nodes[i, 4:7] = f, d
+        return d, f
+
+    populate(0, 0, 0)
+    nodes[:, 7] = ids.view(F)
+    return codes, nodes
+
+
 def load_scene(scene, base=".", width=None, height=None):
     """scene: dict or path. Returns (SceneTables, Shading, width, height, info)."""
     if isinstance(scene, str):
@@ -551,10 +695,23 @@ def load_scene(scene, base=".", width=None, height=None):
             shapes[e["name"]] = b.add_trimesh(m.v, m.f, m.n, m.t)
             shape_mesh[e["name"]] = m
 
+    tex_ids = {e["name"]: build_texture(sh, e, base) for e in scene.get("textures", [])}
+
     bsdf_ids = {}
-    for e in scene.get("bsdfs", []):
+    pending = list(scene.get("bsdfs", []))
+    while pending:  # bump maps refer to other BSDFs by name, in any order
+        e = pending.pop(0)
         ty = e["type"]
-        if ty == "diffuse":
+        if ty == "bumpmap" and e.get("bsdf") not in bsdf_ids:
+            if not any(o["name"] == e.get("bsdf") for o in pending):
+                raise ValueError(f"bumpmap '{e['name']}' refers to an unknown bsdf")
+            pending.append(e)
+            continue
+        if ty == "bumpmap":  # runtime/bsdf/MapBSDF.cpp
+            bsdf_ids[e["name"]] = sh.add_bumpmap(bsdf_ids[e["bsdf"]], tex_ids[e["map"]], e.get("strength", 1.0))
+        elif ty == "diffuse" and isinstance(e.get("reflectance"), str):
+            bsdf_ids[e["name"]] = sh.add_diffuse((0, 0, 0), texture=tex_ids[e["reflectance"]])
+        elif ty == "diffuse":
             bsdf_ids[e["name"]] = sh.add_diffuse(_color(e.get("reflectance"), 0.8))
         elif ty in ("dielectric", "glass"):
             bsdf_ids[e["name"]] = sh.add_dielectric(e.get("int_ior", 1.5046), e.get("ext_ior", 1.0),
@@ -562,9 +719,22 @@ def load_scene(scene, base=".", width=None, height=None):
                                                     _color(e.get("specular_transmittance"), 1.0))
         elif ty == "mirror":
             bsdf_ids[e["name"]] = sh.add_mirror(_color(e.get("specular_reflectance"), 1.0))
-        elif ty == "conductor":
-            bsdf_ids[e["name"]] = sh.add_conductor(_color(e.get("eta"), 0.63660), _color(e.get("k"), 2.7834),
-                                                   _color(e.get("specular_reflectance"), 1.0))
+        elif ty == "conductor":  # runtime/bsdf/ConductorBSDF.cpp:13-36, BSDF.cpp:53-99
+            eta0, k0 = _CONDUCTORS[str(e.get("material", "none")).lower()]
+            eta, k = _color(e.get("eta"), eta0), _color(e.get("k"), k0)
+            ks = _color(e.get("specular_reflectance"), 1.0)
+            old = any(n in e for n in ("alpha", "alpha_u", "alpha_v"))
+            par = "alpha" if old else "roughness"
+            if not any(n in e for n in (par, par + "_u", par + "_v")):
+                # delta distribution: mirror when eta ~ 0 and k ~ 1 (make_conductor_bsdf, bsdf/conductor.art:112-122)
+                if np.all(np.abs(eta) <= 1e-4) and np.all(np.abs(k - 1) <= 1e-4):
+                    bsdf_ids[e["name"]] = sh.add_mirror(ks)
+                else:
+                    bsdf_ids[e["name"]] = sh.add_conductor(eta, k, ks)
+            elif (par + "_u") in e or (par + "_v") in e:
+                bsdf_ids[e["name"]] = sh.add_conductor(eta, k, ks, alpha=(e.get(par + "_u", 0.1), e.get(par + "_v", 0.1)))
+            else:
+                bsdf_ids[e["name"]] = sh.add_conductor(eta, k, ks, roughness=e.get(par, 0.1), anisotropic=e.get("anisotropic", 0.0))
         else:
             raise ValueError(f"bsdf type '{ty}' is outside the supported subset")
 
@@ -593,11 +763,14 @@ def load_scene(scene, base=".", width=None, height=None):
 
     # lights: finite ids are needed by the emissive materials
     area_light_of_entity = {}
+    hier = []  # (position, direction or None, flux) per finite light: Light::position/direction/computeFlux
+    SR = np.float32(4 * math.pi)
     for l in lights:
         ty = l["type"]
         if ty == "point":
-            c = _color(l.get("power"), 4 * math.pi) / np.float32(4 * math.pi) if "power" in l else _color(l.get("intensity"), 1.0)
+            c = _color(l.get("power"), 4 * math.pi) / SR if "power" in l else _color(l.get("intensity"), 1.0)
             sh.add_point_light(l.get("position", (0, 0, 0)), c)
+            hier.append((l.get("position", (0, 0, 0)), None, float(np.mean(c * SR))))  # PointLight.cpp:17-31
         elif ty == "spot":
             cutoff, falloff = l.get("cutoff", 30.0), l.get("falloff", 20.0)
             c = _color(l.get("intensity"), 1.0)
@@ -605,6 +778,9 @@ def load_scene(scene, base=".", width=None, height=None):
                 f = 2 * math.pi * (1 - 0.5 * math.cos(math.radians(falloff)) - 0.5 * math.cos(math.radians(cutoff)))
                 c = _color(l.get("power"), 1.0) / np.float32(f)
             sh.add_spot_light(l.get("position", (0, 0, 0)), l.get("direction", (0, 0, 1)), cutoff, falloff, c)
+            f = 2 * math.pi * (1 - 0.5 * math.cos(math.radians(falloff)) - 0.5 * math.cos(math.radians(cutoff)))
+            d = np.asarray(l.get("direction", (0, 0, 1)), np.float64)
+            hier.append((l.get("position", (0, 0, 0)), d / np.linalg.norm(d), float(np.mean(c) * f)))
         elif ty in ("directional", "direction", "distant"):
             sh.add_directional_light(l.get("direction", (0, 0, 1)), _color(l.get("irradiance"), 1.0))
         elif ty in ("env", "envmap", "uniform", "constant"):
@@ -623,6 +799,18 @@ def load_scene(scene, base=".", width=None, height=None):
                     o = (m[:3, :3] @ pl[0].astype(np.float64) + m[:3, 3])
                     plane = (o, m[:3, :3] @ pl[1].astype(np.float64), m[:3, :3] @ pl[2].astype(np.float64))
             area_light_of_entity[name] = sh.add_area_light(entity_ids[name], _color(l.get("radiance"), 1.0), plane)
+            m = entity_xform[name]
+            if plane is not None:  # AreaLight.cpp:58-71
+                n = np.cross(plane[1], plane[2])
+                area = float(np.linalg.norm(n))
+                hier.append((plane[0] + plane[1] * 0.5 + plane[2] * 0.5, n / area, float(np.mean(_color(l.get("radiance"), 1.0))) * area * math.pi))
+            elif mesh is not None:  # :84-92 (world-space area instead of approximate_area_scale: selection weights only)
+                wv = mesh.v.astype(np.float64) @ m[:3, :3].T + m[:3, 3]
+                area = float(np.linalg.norm(np.cross(wv[mesh.f[:, 1]] - wv[mesh.f[:, 0]], wv[mesh.f[:, 2]] - wv[mesh.f[:, 0]]), axis=1).sum() / 2)
+                c0 = (mesh.v.min(axis=0) + mesh.v.max(axis=0)).astype(np.float64) / 2
+                hier.append((m[:3, :3] @ c0 + m[:3, 3], None, float(np.mean(_color(l.get("radiance"), 1.0))) * area * math.pi))
+            else:
+                raise ValueError("sphere area lights are outside the supported subset")
         else:
             raise ValueError(f"light type '{ty}' is outside the supported subset")
 
@@ -641,6 +829,13 @@ def load_scene(scene, base=".", width=None, height=None):
     tech = scene.get("technique", {"type": "path"})
     if tech.get("type", "path") == "path":
         sh.set_path(tech.get("max_depth", 64), tech.get("min_depth", 2), tech.get("clamp", 0.0), tech.get("nee", True))
+        # LoaderLight::generateLightSelector (loader/LoaderLight.cpp:423-452)
+        selector = tech.get("light_selector", "uniform")
+        if selector == "hierarchy" and len(sh.infinite) + len(sh.finite) > 1 and sh.finite:
+            codes, nodes = build_light_hierarchy(hier)
+            sh.set_hierarchy(codes, nodes)
+        elif selector not in ("uniform", "hierarchy", ""):
+            raise ValueError(f"light selector '{selector}' is outside the supported subset")
     elif tech["type"] == "debug":
         sh.set_debug(tech.get("mode", 0))
     else:

@@ -11,8 +11,14 @@ import math
 
 import numpy as np
 
-BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_MIRROR, BSDF_CONDUCTOR = 0, 1, 2, 3
-LIGHT_POINT, LIGHT_ENV, LIGHT_AREA_SHAPE, LIGHT_AREA_PLANE, LIGHT_SPOT, LIGHT_DIRECTIONAL = 0, 1, 2, 3, 4, 5
+BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_MIRROR, BSDF_CONDUCTOR, BSDF_BUMPMAP = 0, 1, 2, 3, 4
+LIGHT_POINT, LIGHT_ENV, LIGHT_AREA_SHAPE, LIGHT_AREA_PLANE, LIGHT_SPOT, LIGHT_DIRECTIONAL, LIGHT_ENV_TEXTURED = 0, 1, 2, 3, 4, 5, 6
+TEX_CHECKERBOARD, TEX_IMAGE = 0, 1
+FILTER_NEAREST, FILTER_BILINEAR, FILTER_BICUBIC = 0, 1, 2
+WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = 0, 1, 2
+IMAGE_RGBA8, IMAGE_RGBA32F = 0, 1
+SELECTOR_UNIFORM, SELECTOR_HIERARCHY = 0, 1
+NO_CDF = 0xFFFFFFFF
 TECH_PATH, TECH_DEBUG = 0, 1
 TECHFLAG_ONE_SIDED_DIFFUSE = 1
 
@@ -22,8 +28,20 @@ class Camera(C.Structure):
                 ("tmin", C.c_float), ("tmax", C.c_float)]
 
 
+class Word(C.Union):
+    _fields_ = [("f", C.c_float), ("u", C.c_uint32)]
+
+
 class Bsdf(C.Structure):
-    _fields_ = [("type", C.c_uint32), ("color", C.c_float * 3), ("color2", C.c_float * 3), ("p", C.c_float * 5)]
+    _fields_ = [("type", C.c_uint32), ("color", C.c_float * 3), ("color2", C.c_float * 3), ("p", C.c_float * 3),
+                ("q", Word * 2)]
+
+
+class Texture(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("filter", C.c_uint32), ("wrap_u", C.c_uint32), ("wrap_v", C.c_uint32),
+                ("transform", C.c_float * 9), ("color0", C.c_float * 3), ("color1", C.c_float * 3), ("scale", C.c_float * 2),
+                ("width", C.c_uint32), ("height", C.c_uint32), ("format", C.c_uint32), ("opaque", C.c_uint32),
+                ("offset", C.c_uint64), ("_pad", C.c_uint32 * 2)]
 
 
 class Material(C.Structure):
@@ -32,7 +50,7 @@ class Material(C.Structure):
 
 class Light(C.Structure):
     _fields_ = [("type", C.c_uint32), ("entity", C.c_int32), ("color", C.c_float * 3), ("v", C.c_float * 16),
-                ("_pad", C.c_uint32 * 3)]
+                ("tex", C.c_uint32), ("cdf", C.c_uint32), ("_pad", C.c_uint32)]
 
 
 class Technique(C.Structure):
@@ -45,7 +63,9 @@ class ShadingC(C.Structure):
                 ("bsdfs", C.c_void_p), ("bsdf_count", C.c_uint64),
                 ("materials", C.c_void_p), ("material_count", C.c_uint64),
                 ("infinite_lights", C.c_void_p), ("infinite_light_count", C.c_uint64),
-                ("finite_lights", C.c_void_p), ("finite_light_count", C.c_uint64)]
+                ("finite_lights", C.c_void_p), ("finite_light_count", C.c_uint64),
+                ("textures", C.c_void_p), ("texture_count", C.c_uint64), ("blob", C.c_void_p), ("blob_bytes", C.c_uint64),
+                ("selector", C.c_uint32), ("hierarchy", C.c_uint32)]
 
 
 class RenderSettings(C.Structure):
@@ -59,6 +79,7 @@ class RenderStats(C.Structure):
 
 
 assert C.sizeof(Bsdf) == 48 and C.sizeof(Light) == 96 and C.sizeof(Camera) == 52 and C.sizeof(Technique) == 32
+assert C.sizeof(Texture) == 120
 
 
 def _f3(dst, src):
@@ -109,6 +130,8 @@ class Shading:
         self.camera = Camera()
         self.technique = Technique(type=TECH_PATH, max_depth=64, min_depth=2, clamp=0.0, enable_nee=1, debug_mode=0)
         self.bsdfs, self.materials, self.infinite, self.finite = [], [], [], []
+        self.textures, self.blob = [], bytearray()
+        self.selector, self.hierarchy = SELECTOR_UNIFORM, 0
         self._keep = None
 
     # ---- camera: PerspectiveCamera.cpp:27-67 + compute_scale_from_hfov/vfov (camera/perspective.art:1-11) ----
@@ -156,8 +179,12 @@ class Shading:
         self.bsdfs.append(b)
         return len(self.bsdfs) - 1
 
-    def add_diffuse(self, reflectance=(0.8, 0.8, 0.8)):
-        return self._bsdf(BSDF_DIFFUSE, reflectance)
+    def add_diffuse(self, reflectance=(0.8, 0.8, 0.8), texture=None):
+        """texture: id from add_checkerboard / add_image_texture replacing the constant reflectance."""
+        i = self._bsdf(BSDF_DIFFUSE, reflectance)
+        if texture is not None:
+            self.bsdfs[i].q[0].u = texture + 1
+        return i
 
     def add_dielectric(self, int_ior=1.5046, ext_ior=1.0, specular_reflectance=(1, 1, 1), specular_transmittance=(1, 1, 1)):
         # n1 = ext_ior (default vacuum), n2 = int_ior (default bk7): runtime/bsdf/DielectricBSDF.cpp:14-35, BSDF.cpp:8-9
@@ -166,10 +193,80 @@ class Shading:
     def add_mirror(self, specular_reflectance=(1, 1, 1)):
         return self._bsdf(BSDF_MIRROR, specular_reflectance)
 
-    def add_conductor(self, eta, k, specular_reflectance=(1, 1, 1)):
+    def add_conductor(self, eta, k, specular_reflectance=(1, 1, 1), roughness=0.0, anisotropic=0.0, alpha=None):
+        """roughness/anisotropic -> (alpha_u, alpha_v) by microfacet::compute_explicit (core/microfacet.art:409-414);
+        alpha = (u, v) gives them explicitly.  0 = smooth."""
         kk = np.asarray(k, np.float32).reshape(-1)
         kk = np.repeat(kk, 3) if kk.size == 1 else kk
-        return self._bsdf(BSDF_CONDUCTOR, specular_reflectance, eta, tuple(kk[:3]))
+        i = self._bsdf(BSDF_CONDUCTOR, specular_reflectance, eta, tuple(kk[:3]))
+        if alpha is None:
+            r = np.float32(roughness)
+            aspect = np.float32(1) if anisotropic == 0 else np.sqrt(np.float32(1) - np.float32(min(max(anisotropic, 0), 1)) * np.float32(0.99))
+            alpha = (r / aspect, r * aspect)
+        self.bsdfs[i].q[0].f, self.bsdfs[i].q[1].f = float(alpha[0]), float(alpha[1])
+        return i
+
+    def add_bumpmap(self, inner, texture, strength=1.0):
+        i = self._bsdf(BSDF_BUMPMAP, p=(strength,))
+        self.bsdfs[i].q[0].u, self.bsdfs[i].q[1].u = texture + 1, inner + 1
+        return i
+
+    # ---- textures and the blob ----
+    def _blob_append(self, raw):
+        while len(self.blob) % 16:
+            self.blob.append(0)
+        off = len(self.blob)
+        self.blob += bytes(raw)
+        return off
+
+    def add_checkerboard(self, scale=(2, 2), color0=(0, 0, 0), color1=(1, 1, 1), transform=None):
+        t = Texture(type=TEX_CHECKERBOARD)
+        _f3(t.color0, color0)
+        _f3(t.color1, color1)
+        t.scale[0], t.scale[1] = float(scale[0]), float(scale[1])
+        self._tex_transform(t, transform)
+        self.textures.append(t)
+        return len(self.textures) - 1
+
+    @staticmethod
+    def _tex_transform(t, transform):
+        m = np.eye(3, dtype=np.float32) if transform is None else np.asarray(transform, np.float32).reshape(3, 3)
+        for c in range(3):
+            for r in range(3):
+                t.transform[3 * c + r] = float(m[r, c])
+
+    def add_image_texture(self, pixels, filter=FILTER_BICUBIC, wrap=(WRAP_REPEAT, WRAP_REPEAT), transform=None, opaque=False):
+        """pixels: (h, w) uint32 packed RGBA8 (already mapped to linear like Image::loadAsPacked) or (h, w, 4) float32,
+        rows in the reference's in-memory order (bottom row first)."""
+        px = np.ascontiguousarray(pixels)
+        t = Texture(type=TEX_IMAGE, filter=filter, wrap_u=wrap[0], wrap_v=wrap[1], opaque=1 if opaque else 0)
+        if px.dtype == np.uint32 and px.ndim == 2:
+            t.format = IMAGE_RGBA8
+        elif px.dtype == np.float32 and px.ndim == 3 and px.shape[2] == 4:
+            t.format = IMAGE_RGBA32F
+        else:
+            raise ValueError("image textures are (h, w) uint32 RGBA8 or (h, w, 4) float32")
+        t.height, t.width = px.shape[0], px.shape[1]
+        t.offset = self._blob_append(px.tobytes())
+        self._tex_transform(t, transform)
+        self.textures.append(t)
+        return len(self.textures) - 1
+
+    def add_cdf2d(self, marginal, conditional):
+        """The buffer CDF::computeForImage writes (marginal then conditional rows, runtime/CDF.cpp:42-133)."""
+        m, c = np.asarray(marginal, np.float32), np.asarray(conditional, np.float32)
+        head = np.array([c.shape[1], c.shape[0], 0, 0], np.uint32)
+        off = self._blob_append(head.tobytes() + m.tobytes() + c.tobytes())
+        return off // 4
+
+    def set_hierarchy(self, codes, nodes):
+        """codes: u32 per finite light, nodes: (n, 8) float32 rows (LightHierarchy::setup)."""
+        codes = np.asarray(codes, np.uint32)
+        pad = (-codes.size) % 4
+        raw = np.concatenate([codes, np.zeros(pad, np.uint32)]).tobytes() + np.asarray(nodes, np.float32).tobytes()
+        self.hierarchy = self._blob_append(raw) // 4
+        self.selector = SELECTOR_HIERARCHY
+        return self
 
     def add_material(self, bsdf, light=-1):
         self.materials.append(Material(bsdf=bsdf, light=light))
@@ -205,6 +302,14 @@ class Shading:
         c = (np.repeat(r, 3) if r.size == 1 else r) * (np.repeat(s, 3) if s.size == 1 else s)
         return self._light(self.infinite, LIGHT_ENV, c, (1, 0, 0, 0, 1, 0, 0, 0, 1))
 
+    def add_env_textured(self, texture, scale=(1, 1, 1), cdf=None, transform=None):
+        """transform: 3x3 (the loader passes transform.linear().transpose().inverse(), EnvironmentLight.cpp:44)."""
+        m = np.eye(3, dtype=np.float32) if transform is None else np.asarray(transform, np.float32).reshape(3, 3)
+        i = self._light(self.infinite, LIGHT_ENV_TEXTURED, scale, tuple(m.T.reshape(-1)))
+        self.infinite[i].tex = texture
+        self.infinite[i].cdf = NO_CDF if cdf is None else cdf
+        return i
+
     def add_area_light(self, entity, radiance, plane=None):
         """plane = (origin, x_axis, y_axis) in WORLD space selects make_plane_area_emitter
         (AreaLight.cpp:56-70,143-160), otherwise make_shape_area_emitter."""
@@ -219,8 +324,13 @@ class Shading:
     def c_shading(self):
         arr = lambda cls, items: (cls * max(1, len(items)))(*items)
         b, m, i, f = arr(Bsdf, self.bsdfs), arr(Material, self.materials), arr(Light, self.infinite), arr(Light, self.finite)
-        self._keep = (b, m, i, f)
+        t = arr(Texture, self.textures)
+        blob = (C.c_uint8 * max(16, len(self.blob))).from_buffer_copy(bytes(self.blob) + b"\0" * max(0, 16 - len(self.blob)))
+        self._keep = (b, m, i, f, t, blob)
         sh = ShadingC(camera=self.camera, technique=self.technique)
+        sh.textures, sh.texture_count = C.addressof(t), len(self.textures)
+        sh.blob, sh.blob_bytes = C.addressof(blob), len(self.blob)
+        sh.selector, sh.hierarchy = self.selector, self.hierarchy
         sh.bsdfs, sh.bsdf_count = C.addressof(b), len(self.bsdfs)
         sh.materials, sh.material_count = C.addressof(m), len(self.materials)
         sh.infinite_lights, sh.infinite_light_count = C.addressof(i), len(self.infinite)

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define IGB200_ABI_VERSION 2
+#define IGB200_ABI_VERSION 3
 
 enum {
     IGB200_OK            = 0,
@@ -178,14 +178,49 @@ typedef struct igb200_camera {
 #define IGB200_BSDF_DIELECTRIC 1u /* make_pure_dielectric_bsdf(surf, n1 = p[0] (exterior), n2 = p[1] (interior),
                                      ks = color, kt = color2)                          bsdf/dielectric.art:2-23 */
 #define IGB200_BSDF_MIRROR     2u /* make_mirror_bsdf(surf, ks = color)                bsdf/conductor.art:1-9 */
-#define IGB200_BSDF_CONDUCTOR  3u /* make_pure_conductor_bsdf(surf, ior = color2, k = p[0..2], ks = color)
-                                     bsdf/conductor.art:12-30 */
+#define IGB200_BSDF_CONDUCTOR  3u /* make_conductor_bsdf(surf, eta = color2, k = p[0..2], ks = color, micro)
+                                     bsdf/conductor.art:112-122.  micro = make_vndf_ggx_distribution(face_normal,
+                                     local, alpha_u = q[0].f, alpha_v = q[1].f) (core/microfacet.art:383-407; the
+                                     loader's default distribution, runtime/bsdf/BSDF.cpp:75); alpha <= 1e-4 is the
+                                     delta distribution = make_pure_conductor_bsdf (conductor.art:12-30) */
+#define IGB200_BSDF_BUMPMAP    4u /* make_bumpmap(ctx, inner = bsdfs[q[1].u - 1], texture_dx(map).r, texture_dy(map).r,
+                                     strength = p[0]) with map = textures[q[0].u - 1]
+                                     bsdf/map.art:64-68, texture/common.art:28-38, runtime/bsdf/MapBSDF.cpp */
+typedef union igb200_word {
+    float    f;
+    uint32_t u;
+} igb200_word;
 typedef struct igb200_bsdf {
-    uint32_t type;
-    float    color[3];
-    float    color2[3];
-    float    p[5];
+    uint32_t    type;
+    float       color[3];  /* DIFFUSE: reflectance unless q[0].u != 0, then textures[q[0].u - 1] replaces it */
+    float       color2[3];
+    float       p[3];
+    igb200_word q[2];
 } igb200_bsdf; /* 48 bytes */
+
+/* Textures (src/artic/texture/, loader side src/runtime/pattern/).  uv is the surface texture coordinate. */
+#define IGB200_TEX_CHECKERBOARD 0u /* make_checkerboard_texture(scale, color0, color1, transform)  texture/checkerboard.art:4-13 */
+#define IGB200_TEX_IMAGE        1u /* make_image_texture(border, filter, image, transform)         texture/image.art:148-152 */
+#define IGB200_FILTER_NEAREST  0u  /* texture/image.art:81-89 */
+#define IGB200_FILTER_BILINEAR 1u  /* :91-106 */
+#define IGB200_FILTER_BICUBIC  2u  /* :108-146; the loader's default, also for unknown names (pattern/ImagePattern.cpp:19-31) */
+#define IGB200_WRAP_REPEAT 0u      /* texture/image.art:17-26 */
+#define IGB200_WRAP_MIRROR 1u      /* :28-40 */
+#define IGB200_WRAP_CLAMP  2u      /* :9-15 */
+#define IGB200_IMAGE_RGBA8   0u    /* packed u32 per texel, image_rgba_unpack: byte / 255 (driver/image.art:8-14); the sRGB ->
+                                      linear byte mapping was applied by the loader (runtime/Image.cpp:39-42,565-655) */
+#define IGB200_IMAGE_RGBA32F 1u    /* four floats per texel (device.load_image_by_id, EXR / HDR / baked textures) */
+typedef struct igb200_texture {
+    uint32_t type, filter, wrap_u, wrap_v;
+    float    transform[9]; /* 2-D affine transform of uv, column major (LoaderUtils::inlineTransformAs2d) */
+    float    color0[3], color1[3];
+    float    scale[2];
+    uint32_t width, height, format;
+    uint32_t opaque;       /* RGBA8: alpha reads as 1 (three-channel source, `hint_opaque`) */
+    uint64_t offset;       /* byte offset of texel (0, 0) in igb200_shading::blob, 16-byte aligned; row-major, rows in the
+                              order the reference holds them after loading (bottom row first, Image.cpp:559-560,575) */
+    uint32_t _pad[2];
+} igb200_texture; /* 120 bytes */
 
 /* One row per material id (the ids written into the entity table, LoaderEntity.cpp:87-103,171):
  * make_material / make_emissive_material (src/artic/driver/material.art:10-28, ShaderUtils.cpp:95-122). */
@@ -206,12 +241,20 @@ typedef struct igb200_material {
                                       intensity = color)                                   light/spot.art */
 #define IGB200_LIGHT_DIRECTIONAL 5u /* make_directional_light(dir v[0..2], scene_bbox, irradiance = color)
                                       light/directional.art */
+#define IGB200_LIGHT_ENV_TEXTURED 6u /* make_environment_light_textured(scene_bbox, scale = color, tex = textures[tex],
+                                      cdf, transform = v[0..8] column major) when cdf != IGB200_NO_CDF, else
+                                      make_environment_light(scene_bbox, scale, tex, transform)   light/env.art:112-166 */
+#define IGB200_NO_CDF 0xFFFFFFFFu
 typedef struct igb200_light {
     uint32_t type;
     int32_t  entity; /* area lights: the emissive entity id */
     float    color[3];
     float    v[16];
-    uint32_t _pad[3];
+    uint32_t tex;    /* ENV_TEXTURED: texture id */
+    uint32_t cdf;    /* ENV_TEXTURED: offset of the 2-D CDF in igb200_shading::blob in units of 4 bytes: u32 size_x,
+                        size_y, 0, 0, then size_y marginal floats and size_y rows of size_x conditional floats, each
+                        without the leading 0 (cdf::make_cdf_2d_from_buffer, core/cdf.art:70-72,156-160) */
+    uint32_t _pad;
 } igb200_light; /* 96 bytes */
 
 #define IGB200_TECH_PATH  0u /* make_path_renderer (src/artic/technique/pathtracer.art:40-218) */
@@ -235,7 +278,7 @@ typedef struct igb200_technique {
 
 /* The light tables are split exactly like the reference's `infinite_lights` / `finite_lights`
  * (loader/LoaderLight.cpp:118-250); the light selector is make_uniform_light_selector
- * (src/artic/light/light_selector.art:26-45). */
+ * (src/artic/light/light_selector.art:26-45) unless `selector` says otherwise. */
 typedef struct igb200_shading {
     igb200_camera          camera;
     igb200_technique       technique;
@@ -247,7 +290,18 @@ typedef struct igb200_shading {
     uint64_t               infinite_light_count;
     const igb200_light*    finite_lights;
     uint64_t               finite_light_count;
+    /* ---- ABI v3 ---- */
+    const igb200_texture*  textures;
+    uint64_t               texture_count;
+    const uint8_t*         blob;       /* texels, CDFs and the light hierarchy */
+    uint64_t               blob_bytes;
+    uint32_t               selector;   /* IGB200_SELECTOR_* */
+    uint32_t               hierarchy;  /* IGB200_SELECTOR_HIERARCHY: offset of the buffer LightHierarchy::setup writes
+                                          (runtime/light/LightHierarchy.cpp:84-127) in blob, in units of 4 bytes:
+                                          round_up(finite_light_count, 4) u32 codes, then 8 floats per node */
 } igb200_shading;
+#define IGB200_SELECTOR_UNIFORM   0u /* make_uniform_light_selector    light/light_selector.art:26-45 */
+#define IGB200_SELECTOR_HIERARCHY 1u /* make_hierarchy_light_selector  light/light_selector.art:76-110, light_hierarchy.art */
 
 /* Replaces Device::RenderSettings (Device.h:32-42).  One call = one ITERATION = spi samples per pixel
  * (Device::render, Device.cpp:1588-1612).  rays != NULL selects igtrace mode (list emitter,

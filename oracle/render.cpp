@@ -332,39 +332,253 @@ static inline V3 refract(V3 v, V3 n, float eta, float cos_i, float cos_t)      /
     return sub(mulf(n, eta * cos_i - cos_t), mulf(v, eta));
 }
 
+// ---- textures: texture/checkerboard.art, texture/image.art, driver/image.art -------------------------
+struct Tex {
+    const igb200_shading* sh;
+    static float wrapf(float v, float mn, float mx) // math::wrap, core/math.art:88-91
+    {
+        const float range = mx - mn;
+        return range <= flt_eps ? mn : v - (range * floorf((v - mn) / range));
+    }
+    static float fract(float x) { return x - floorf(x); } // core/math.art:74
+    static int32_t border(uint32_t mode, int32_t x, int32_t w) // texture/image.art:9-40
+    {
+        if (mode == IGB200_WRAP_CLAMP) return std::min(std::max(x, 0), w - 1);
+        if (mode == IGB200_WRAP_MIRROR) {
+            const int32_t t = x < 0 ? -1 - x : x;
+            const int32_t i = t / w, k = t - i * w;
+            return (i & 1) == 0 ? w - 1 - k : k;
+        }
+        const int32_t t = x % w;
+        return t < 0 ? t + w : t;
+    }
+    void texel(const igb200_texture& t, int32_t x, int32_t y, float out[4]) const // img.pixels(x, y)
+    {
+        const size_t i = (size_t)y * t.width + (size_t)x;
+        if (t.format == IGB200_IMAGE_RGBA32F) {
+            const float* px = reinterpret_cast<const float*>(sh->blob + t.offset) + 4 * i;
+            out[0] = px[0]; out[1] = px[1]; out[2] = px[2]; out[3] = px[3];
+        } else { // image_rgba_unpack, driver/image.art:8-14
+            const uint32_t q = reinterpret_cast<const uint32_t*>(sh->blob + t.offset)[i];
+            out[0] = (float)(q & 0xFFu) / 255;
+            out[1] = (float)((q & 0xFF00u) >> 8) / 255;
+            out[2] = (float)((q & 0xFF0000u) >> 16) / 255;
+            out[3] = t.opaque ? 1.0f : (float)((q & 0xFF000000u) >> 24) / 255;
+        }
+    }
+    Color eval(uint32_t id, float u, float v) const
+    {
+        const igb200_texture& t = sh->textures[id];
+        // mat3x3_transform_point_affine(transform, uv), core/matrix.art:223-226 (rows dot (u, v, 1))
+        const float* m  = t.transform;
+        const float  tu = fmaf(m[0], u, fmaf(m[3], v, m[6] * 1.0f));
+        const float  tv = fmaf(m[1], u, fmaf(m[4], v, m[7] * 1.0f));
+        if (t.type == IGB200_TEX_CHECKERBOARD) { // texture/checkerboard.art:4-13
+            const float sx = tu * t.scale[0], sy = tv * t.scale[1];
+            const bool  px = ((int32_t)wrapf(sx, 0, 2) % 2) == 0;
+            const bool  py = ((int32_t)wrapf(sy, 0, 2) % 2) == 0;
+            return (px ^ py) ? color(t.color0[0], t.color0[1], t.color0[2]) : color(t.color1[0], t.color1[1], t.color1[2]);
+        }
+        const int32_t w = (int32_t)t.width, h = (int32_t)t.height;
+        float         p[4][4];
+        if (t.filter == IGB200_FILTER_NEAREST) { // map_uv_to_image_pixel_nearest + make_nearest_filter
+            const float fu = tu * (float)w, fv = tv * (float)h;
+            texel(t, border(t.wrap_u, (int32_t)floorf(fu), w), border(t.wrap_v, (int32_t)floorf(fv), h), p[0]);
+            return color(p[0][0], p[0][1], p[0][2]);
+        }
+        const float   fu = tu * (float)w - 0.5f, fv = tv * (float)h - 0.5f; // map_uv_to_image_pixel :70-79
+        const int32_t ix = (int32_t)floorf(fu), iy = (int32_t)floorf(fv);
+        const float   fx = fract(fu), fy = fract(fv);
+        if (t.filter == IGB200_FILTER_BILINEAR) { // :91-106
+            const int32_t x0 = border(t.wrap_u, ix, w), y0 = border(t.wrap_v, iy, h);
+            const int32_t x1 = border(t.wrap_u, ix + 1, w), y1 = border(t.wrap_v, iy + 1, h);
+            texel(t, x0, y0, p[0]); texel(t, x1, y0, p[1]); texel(t, x0, y1, p[2]); texel(t, x1, y1, p[3]);
+            float o[3];
+            for (int k = 0; k < 3; ++k) {
+                const float a = (1 - fx) * p[0][k] + fx * p[1][k], b = (1 - fx) * p[2][k] + fx * p[3][k]; // color_lerp
+                o[k]          = (1 - fy) * a + fy * b;
+            }
+            return color(o[0], o[1], o[2]);
+        }
+        // make_bicubic_filter :108-146
+        auto w0 = [](float a) { return (a * (a * (-a + 3) - 3) + 1) / 6; };
+        auto w1 = [](float a) { return (a * a * (3 * a - 6) + 4) / 6; };
+        auto w2 = [](float a) { return (a * (a * (-3 * a + 3) + 3) + 1) / 6; };
+        auto w3 = [](float a) { return (a * a * a) / 6; };
+        auto g0 = [&](float a) { return w0(a) + w1(a); };
+        auto g1 = [&](float a) { return w2(a) + w3(a); };
+        auto h0 = [&](float a) { return (w1(a) / g0(a)) - 1; };
+        auto h1 = [&](float a) { return (w3(a) / g1(a)) + 1; };
+        const float   g0x = g0(fx), g0y = g0(fy), g1x = g1(fx), g1y = g1(fy);
+        const int32_t ix0 = (int32_t)floorf((float)ix + h0(fx) + 0.5f), iy0 = (int32_t)floorf((float)iy + h0(fy) + 0.5f);
+        const int32_t ix1 = (int32_t)floorf((float)ix + h1(fx) + 0.5f), iy1 = (int32_t)floorf((float)iy + h1(fy) + 0.5f);
+        const int32_t x0 = border(t.wrap_u, ix0, w), y0 = border(t.wrap_v, iy0, h);
+        const int32_t x1 = border(t.wrap_u, ix1, w), y1 = border(t.wrap_v, iy1, h);
+        texel(t, x0, y0, p[0]); texel(t, x1, y0, p[1]); texel(t, x0, y1, p[2]); texel(t, x1, y1, p[3]);
+        float o[3];
+        for (int k = 0; k < 3; ++k)
+            o[k] = (p[0][k] * (g0x * g0y) + p[1][k] * (g1x * g0y)) + (p[2][k] * (g0x * g1y) + p[3][k] * (g1x * g1y));
+        return color(o[0], o[1], o[2]);
+    }
+};
+
+// ---- core/microfacet.art: GGX distribution of visible normals (the loader's default, runtime/bsdf/BSDF.cpp:75) ----
+static inline V3 to_local(const Mat3& l, V3 v) { return v3(dot(l.c0, v), dot(l.c1, v), dot(l.c2, v)); }                // shading.art:9
+static inline V3 to_world(const Mat3& l, V3 v) { return add(add(mulf(l.c0, v.x), mulf(l.c1, v.y)), mulf(l.c2, v.z)); } // :8
+static inline float diff_of_prod(float a, float b, float c, float d) // core/common.art:132-137
+{
+    const float cd = c * d, diff = fmaf(a, b, -cd), err = fmaf(-c, d, cd);
+    return diff + err;
+}
+static float g_1_smith(const Mat3& l, V3 w, float au, float av) // microfacet.art:159-177
+{
+    const float cosZ = dot(l.c2, w);
+    if (fabsf(cosZ) <= flt_eps) return 0;
+    const float kx = au * dot(l.c0, w), ky = av * dot(l.c1, w);
+    const float a2 = kx * kx + ky * ky;
+    if (a2 <= flt_eps) return 1;
+    const float k2 = a2 / (cosZ * cosZ);
+    return 2 / (1 + sqrtf(1 + k2));
+}
+static float ndf_ggx(const Mat3& l, V3 m, float au, float av) // :191-201
+{
+    const float cosZ = dot(l.c2, m), kx = dot(l.c0, m) / au, ky = dot(l.c1, m) / av;
+    const float k = kx * kx + ky * ky + cosZ * cosZ;
+    return safe_div(1, flt_pi * au * av * k * k);
+}
+static float pdf_vndf_ggx(const Mat3& l, V3 w, V3 h, float au, float av) // :378-381
+{
+    const float cosZ = fabsf(dot(l.c2, w));
+    return safe_div(g_1_smith(l, w, au, av) * fabsf(dot(w, h)) * ndf_ggx(l, h, au, av), cosZ);
+}
+static V3 sample_vndf_ggx(Rnd& rnd, const Mat3& l, V3 vN, float au, float av) // :324-376
+{
+    const V3 vL = to_local(l, vN);
+    const V3 sL = normalize(v3(au * vL.x, av * vL.y, vL.z));
+    // shading::sin_cos_phi
+    const float sin_t = safe_sqrt(1 - sL.z * sL.z);
+    float       sin_phi = 0, cos_phi = 1;
+    if (fabsf(sin_t) > flt_eps) { sin_phi = sL.y / sin_t; cos_phi = sL.x / sin_t; }
+    // sample_vndf_ggx_11
+    const float cos_theta = fabsf(sL.z);
+    const float u0 = rnd.next_f32();
+    const float u1 = rnd.next_f32();
+    float       pcx, pcy; // square_to_concentric_disk, core/warp.art:2-22
+    {
+        const float a = 2 * u0 - 1, b = 2 * u1 - 1;
+        if (a == 0 && b == 0) { pcx = 0; pcy = 0; }
+        else if (a * a > b * b) { const float phi = (flt_pi / 4) * safe_div(b, a); pcx = cosf(phi) * a; pcy = sinf(phi) * a; }
+        else { const float phi = (flt_pi / 2) - (flt_pi / 4) * safe_div(a, b); pcx = cosf(phi) * b; pcy = sinf(phi) * b; }
+    }
+    const float s  = 0.5f * (1 + cos_theta);
+    const float y  = (1 - s) * safe_sqrt(1 - pcx * pcx) + s * pcy;
+    const float z  = safe_sqrt(1 - y * y - pcx * pcx);
+    const float st = safe_sqrt(1 - cos_theta * cos_theta);
+    const float nm = safe_div(1, sum_of_prod(st, y, cos_theta, z));
+    const float slx = diff_of_prod(cos_theta, y, st, z) * nm, sly = pcx * nm;
+    const float s2x = (cos_phi * slx - sin_phi * sly) * au, s2y = (sin_phi * slx + cos_phi * sly) * av;
+    const V3    Nh  = !std::isfinite(s2x) ? v3(0, 0, 0) : normalize(v3(-s2x, -s2y, 1));
+    return to_world(l, Nh);
+}
+
+// core/sampling.art:120-165
+static V3 ensure_valid_reflection(V3 Ng, V3 I, V3 N)
+{
+    const V3    R         = reflect(I, N);
+    const float threshold = fminf(0.9f * dot(Ng, I), 0.01f);
+    if (dot(Ng, R) >= threshold) return N;
+    const float NdotNg = dot(N, Ng);
+    const V3    X      = normalize(sub(N, mulf(Ng, NdotNg)));
+    const float Ix = dot(I, X), Iz = dot(I, Ng), Ix2 = Ix * Ix, Iz2 = Iz * Iz, a = Ix2 + Iz2;
+    const float b = safe_sqrt(Ix2 * (a - threshold * threshold)), c = Iz * threshold + a;
+    const float fac = 0.5f / a, N1_z2 = fac * (b + c), N2_z2 = fac * (-b + c);
+    const bool  valid1 = (N1_z2 > 1e-5f) && (N1_z2 <= (1.0f + 1e-5f)), valid2 = (N2_z2 > 1e-5f) && (N2_z2 <= (1.0f + 1e-5f));
+    float nx, ny;
+    if (valid1 && valid2) {
+        const float n1x = safe_sqrt(1 - N1_z2), n1y = safe_sqrt(N1_z2), n2x = safe_sqrt(1 - N2_z2), n2y = safe_sqrt(N2_z2);
+        const float R1 = 2 * (n1x * Ix + n1y * Iz) * n1y - Iz, R2 = 2 * (n2x * Ix + n2y * Iz) * n2y - Iz;
+        const bool  valid3 = R1 >= 1e-5f, valid4 = R2 >= 1e-5f;
+        const bool  first  = (valid3 && valid4) ? (R1 < R2) : (R1 > R2);
+        nx = first ? n1x : n2x; ny = first ? n1y : n2y;
+    } else if (valid1 || valid2) {
+        const float Nz2 = valid1 ? N1_z2 : N2_z2;
+        nx = safe_sqrt(1 - Nz2); ny = safe_sqrt(Nz2);
+    } else { nx = 0; ny = 1; }
+    return add(mulf(X, nx), mulf(Ng, ny));
+}
+// core/matrix.art:247-270 and :110-113
+static Mat3 align_vectors(V3 a, V3 b)
+{
+    const V3    ax   = cross(b, a);
+    const float cosA = dot(a, b);
+    if (cosA <= -1) return Mat3{ v3(-1, 0, 0), v3(0, -1, 0), v3(0, 0, -1) };
+    const float k = 1 / (1 + cosA);
+    return Mat3{ v3((ax.x * ax.x * k) + cosA, (ax.y * ax.x * k) - ax.z, (ax.z * ax.x * k) + ax.y),
+                 v3((ax.x * ax.y * k) + ax.z, (ax.y * ax.y * k) + cosA, (ax.z * ax.y * k) - ax.x),
+                 v3((ax.x * ax.z * k) - ax.y, (ax.y * ax.z * k) + ax.x, (ax.z * ax.z * k) + cosA) };
+}
+static Mat3 matmul(const Mat3& a, const Mat3& b) { return Mat3{ mat3_mul(a, b.c0), mat3_mul(a, b.c1), mat3_mul(a, b.c2) }; }
+
 struct Bsdf {
     const igb200_bsdf* d;
-    const Surf*        surf;
-    bool               one_sided; // IGB200_TECHFLAG_ONE_SIDED_DIFFUSE (not in the reference)
-    bool is_specular() const { return d->type != IGB200_BSDF_DIFFUSE; }
-    Color kd() const { return color(d->color[0], d->color[1], d->color[2]); }
-    // eval / pdf: bsdf/diffuse.art:3-4; specular BSDFs return black / 0 (dielectric.art:3-4, conductor.art:3-4,14-15)
-    Color eval(V3 in_dir, V3) const
+    Mat3               local;       // surf.local, re-oriented by bump maps
+    V3                 face_normal;
+    bool               is_entering;
+    bool               one_sided;   // IGB200_TECHFLAG_ONE_SIDED_DIFFUSE (not in the reference)
+    Color              kd_;         // DIFFUSE reflectance (constant or texture), ks otherwise
+    float              au, av;      // CONDUCTOR roughness
+    bool rough() const { return d->type == IGB200_BSDF_CONDUCTOR && !(au <= 1e-4f || av <= 1e-4f); } // check_if_delta_distribution
+    bool is_specular() const { return d->type != IGB200_BSDF_DIFFUSE && !rough(); }
+    Color kd() const { return kd_; }
+    Color fresnel_term(float c) const // make_rough_conductor_bsdf, bsdf/conductor.art:102-110
     {
+        return color(conductor_factor(d->color2[0], d->p[0], c), conductor_factor(d->color2[1], d->p[1], c),
+                     conductor_factor(d->color2[2], d->p[2], c));
+    }
+    // eval / pdf: bsdf/diffuse.art:3-4; specular BSDFs return black / 0 (dielectric.art:3-4, conductor.art:3-4,14-15)
+    Color eval(V3 in_dir, V3 out_dir) const
+    {
+        if (rough()) { // make_rough_base_conductor_bsdf::eval (kd = black), bsdf/conductor.art:53-66
+            const V3    N     = local.c2;
+            const float cos_o = fabsf(dot(out_dir, N)), cos_i = fabsf(dot(in_dir, N));
+            if (cos_o <= flt_eps || cos_i <= flt_eps) return black;
+            const V3    H = normalize(add(in_dir, out_dir));
+            const float D = ndf_ggx(local, H, au, av);
+            const float G = g_1_smith(local, in_dir, au, av) * g_1_smith(local, out_dir, au, av);
+            const Color F = fresnel_term(fabsf(dot(out_dir, H)));
+            const Color IF = color(1 - F.r, 1 - F.g, 1 - F.b);
+            return cmulf(cadd(cmul(black, IF), cmul(kd_, F)), D * G / (4 * cos_o));
+        }
         if (is_specular()) return black;
-        const float c = dot(in_dir, surf->local.c2);
+        const float c = dot(in_dir, local.c2);
         return cmulf(kd(), (one_sided ? (c >= 0 ? c : 0.0f) : fabsf(c)) * flt_inv_pi); // absolute_cos unless flagged
     }
-    float pdf(V3 in_dir, V3) const
+    float pdf(V3 in_dir, V3 out_dir) const
     {
+        if (rough()) { // bsdf/conductor.art:70-75
+            const V3    H       = normalize(add(in_dir, out_dir));
+            const float cos_h_o = fabsf(dot(out_dir, H));
+            return pdf_vndf_ggx(local, out_dir, H, au, av) * safe_div(1, 4 * cos_h_o);
+        }
         if (is_specular()) return 0.0f;
-        const float c = dot(in_dir, surf->local.c2);
+        const float c = dot(in_dir, local.c2);
         return (c >= 0 ? c : 0.0f) / flt_pi; // cosine_hemisphere_pdf(positive_cos(..))
     }
     BsdfSample sample(Rnd& rnd, V3 out_dir) const
     {
-        const V3 n = surf->local.c2;
+        const V3         n = local.c2;
+        const BsdfSample reject{ false, v3(0, 0, 0), 0, black, 1 };
         switch (d->type) {
         default:
         case IGB200_BSDF_DIFFUSE: { // bsdf/diffuse.art:5-9
             const float     u = rnd.next_f32();
             const float     v = rnd.next_f32();
             const DirSample s = sample_cosine_hemisphere(u, v);
-            return BsdfSample{ true, mat3_mul(surf->local, s.dir), s.pdf, kd(), 1.0f };
+            return BsdfSample{ true, mat3_mul(local, s.dir), s.pdf, kd(), 1.0f };
         }
         case IGB200_BSDF_DIELECTRIC: { // bsdf/dielectric.art:5-21 (adjoint = false)
             const float n1 = d->p[0], n2 = d->p[1];
-            const float k     = surf->is_entering ? n1 / n2 : n2 / n1;
+            const float k     = is_entering ? n1 / n2 : n2 / n1;
             const float cos_o = dot(out_dir, n);
             float       cos_t = 0, factor = 1;
             if (!fresnel(k, cos_o, cos_t, factor)) { cos_t = 0; factor = 1; }
@@ -376,15 +590,56 @@ struct Bsdf {
         }
         case IGB200_BSDF_MIRROR: // bsdf/conductor.art:5-7
             return BsdfSample{ true, reflect(out_dir, n), 1.0f, kd(), 1.0f };
-        case IGB200_BSDF_CONDUCTOR: { // bsdf/conductor.art:16-28
-            const float cos_i = dot(out_dir, n);
-            const Color f = color(conductor_factor(d->color2[0], d->p[0], cos_i), conductor_factor(d->color2[1], d->p[1], cos_i),
-                                  conductor_factor(d->color2[2], d->p[2], cos_i));
-            return BsdfSample{ true, reflect(out_dir, n), 1.0f, cmul(kd(), f), 1.0f };
+        case IGB200_BSDF_CONDUCTOR: {
+            if (!rough()) { // make_pure_conductor_bsdf, bsdf/conductor.art:16-28
+                const float cos_i = dot(out_dir, n);
+                return BsdfSample{ true, reflect(out_dir, n), 1.0f, cmul(kd(), fresnel_term(cos_i)), 1.0f };
+            }
+            // make_rough_base_conductor_bsdf::sample, bsdf/conductor.art:76-97
+            const float cos_o = fabsf(dot(out_dir, n));
+            if (cos_o <= flt_eps) return reject;
+            const V3    m    = sample_vndf_ggx(rnd, local, out_dir, au, av);
+            const float spdf = pdf_vndf_ggx(local, out_dir, m, au, av);
+            if (dot(m, m) <= flt_eps) return reject;
+            const V3 oH     = normalize(m);
+            const V3 H      = std::signbit(dot(oH, out_dir)) ? neg(oH) : oH;
+            const V3 in_dir = reflect(out_dir, H);
+            const float cos_i = fabsf(dot(in_dir, n));
+            if (cos_i <= flt_eps) return reject;
+            const float cos_h_o = fabsf(dot(out_dir, H));
+            const float jacob   = 1 / (4 * cos_h_o);
+            const float pdfv    = spdf * jacob;
+            return BsdfSample{ true, in_dir, pdfv, cmulf(eval(in_dir, out_dir), safe_div(1, pdfv)), 1.0f };
         }
         }
     }
 };
+
+struct Ctx;
+static Bsdf make_bsdf(const igb200_shading& sh, int32_t id, const Surf& surf, V3 ray_dir, bool one_sided)
+{
+    const Tex tex{ &sh };
+    Mat3      local = surf.local;
+    // make_bumpmap -> make_normal_set (bsdf/map.art:36-44,64-68): only the shading frame changes (adjoint = false)
+    for (int guard = 0; guard < 8 && sh.bsdfs[id].type == IGB200_BSDF_BUMPMAP; ++guard) {
+        const igb200_bsdf& b     = sh.bsdfs[id];
+        const uint32_t     map   = b.q[0].u - 1u;
+        const float        delta = 0.001f; // texture_dx / texture_dy, texture/common.art:28-38
+        const Color        t0 = tex.eval(map, surf.tu, surf.tv);
+        const float        dx = (tex.eval(map, surf.tu + delta, surf.tv).r - t0.r) * (1 / delta);
+        const float        dy = (tex.eval(map, surf.tu, surf.tv + delta).r - t0.r) * (1 / delta);
+        const V3 N     = normalize(sub(local.c2, mulf(add(mulf(local.c0, dx), mulf(local.c1, dy)), b.p[0])));
+        const V3 nn    = ensure_valid_reflection(surf.face_normal, neg(ray_dir), normalize(N));
+        const Mat3 trans = align_vectors(local.c2, nn);
+        local          = matmul(trans, local);
+        id             = (int32_t)b.q[1].u - 1;
+    }
+    const igb200_bsdf& d = sh.bsdfs[id];
+    Bsdf               out{ &d, local, surf.face_normal, surf.is_entering, one_sided, color(d.color[0], d.color[1], d.color[2]), 0, 0 };
+    if (d.type == IGB200_BSDF_DIFFUSE && d.q[0].u != 0) out.kd_ = tex.eval(d.q[0].u - 1u, surf.tu, surf.tv);
+    if (d.type == IGB200_BSDF_CONDUCTOR) { out.au = d.q[0].f; out.av = d.q[1].f; }
+    return out;
+}
 
 // ---- lights --------------------------------------------------------------------------------------
 struct DirectSample { V3 pos, dir; Color intensity; Pdf pdf; float cos, dist; };
@@ -399,7 +654,10 @@ static inline bool light_delta(const igb200_light& l)
 {
     return l.type == IGB200_LIGHT_POINT || l.type == IGB200_LIGHT_SPOT || l.type == IGB200_LIGHT_DIRECTIONAL;
 }
-static inline bool light_infinite(const igb200_light& l) { return l.type == IGB200_LIGHT_ENV || l.type == IGB200_LIGHT_DIRECTIONAL; }
+static inline bool light_infinite(const igb200_light& l)
+{
+    return l.type == IGB200_LIGHT_ENV || l.type == IGB200_LIGHT_DIRECTIONAL || l.type == IGB200_LIGHT_ENV_TEXTURED;
+}
 static inline Color light_color(const igb200_light& l) { return color(l.color[0], l.color[1], l.color[2]); }
 
 // make_plane_area_emitter::compute_sq, light/area.art:117-160
@@ -476,6 +734,83 @@ static void shape_emitter_sample(const Ctx& c, const igb200_light& l, float ux_,
     weight = (float)m.nf / surf.inv_area;
 }
 
+// ---- core/cdf.art on the blob layout of cdf::make_cdf_2d_from_buffer (:156-160) ---------------------------
+struct Cdf1 { // make_cdf_1d_from_buffer :70-72 + make_cdf_1d :38-68
+    const float* data;
+    int32_t      n;
+    float get(int32_t i) const { return i == 0 ? 0.0f : data[i - 1]; }
+    float pdf_discrete(int32_t x) const { return get(x + 1) - get(x); }
+    int32_t sample_discrete(float u) const
+    {
+        int32_t first = 0, len_ = n + 1; // interval::binary_search(func_size + 1, get(i) <= u), core/interval.art:7-23
+        while (len_ > 0) {
+            const int32_t half = len_ / 2, middle = first + half;
+            if (get(middle) <= u) { first = middle + 1; len_ -= half + 1; } else { len_ = half; }
+        }
+        return std::min(std::min(std::max(first - 1, 0), n), n - 1);
+    }
+    void sample_continuous(float u, int32_t& off, float& pos, float& pdf) const
+    {
+        off              = sample_discrete(u);
+        const float pd   = pdf_discrete(off);
+        const float rem  = safe_div(u - get(off), pd);
+        pos              = clampf(((float)off + rem) / (float)n, 0, 1);
+        pdf              = pd * (float)n;
+    }
+    void pdf_continuous(float x, int32_t& off, float& pdf) const
+    {
+        off = std::min(std::max((int32_t)(x * (float)n), 0), n - 1);
+        pdf = pdf_discrete(off) * (float)n;
+    }
+};
+struct Cdf2 {
+    const float* base;
+    int32_t      sx, sy;
+    Cdf1 marginal() const { return Cdf1{ base, sy }; }
+    Cdf1 conditional(int32_t i) const { return Cdf1{ base + sy + (size_t)i * sx, sx }; }
+};
+static inline Cdf2 load_cdf2(const igb200_shading& sh, uint32_t off4)
+{
+    const uint32_t* h = reinterpret_cast<const uint32_t*>(sh.blob) + off4;
+    return Cdf2{ reinterpret_cast<const float*>(h + 4), (int32_t)h[0], (int32_t)h[1] };
+}
+
+// light/env.art:13-21, core/warp.art:44-57
+static inline V3 switch_env_up(V3 v) { return v3(v.x, v.z, v.y); }
+static inline void map_env_uv(V3 dir, float& u, float& v)
+{
+    const float theta = acosf(dir.z);
+    float       phi   = atan2f(dir.y, dir.x);
+    if (phi < 0) phi += 2 * flt_pi;
+    u = Tex::fract(phi / (2 * flt_pi) + 0.25f);
+    v = 1 - theta / flt_pi;
+}
+static inline Mat3 light_transform(const igb200_light& l) { return Mat3{ v3(l.v[0], l.v[1], l.v[2]), v3(l.v[3], l.v[4], l.v[5]), v3(l.v[6], l.v[7], l.v[8]) }; }
+
+// Light::emission of an infinite light along `dir` (light/env.art:93,146-151,163-166)
+static Color env_emission(const igb200_shading& sh, const igb200_light& l, V3 dir)
+{
+    if (l.type != IGB200_LIGHT_ENV_TEXTURED) return light_color(l);
+    float u, v;
+    map_env_uv(switch_env_up(mat3_mul(light_transform(l), dir)), u, v);
+    return cmul(light_color(l), Tex{ &sh }.eval(l.tex, u, v));
+}
+// Light::pdf_direct of an infinite light, solid angle (light/env.art:96,121-127,152)
+static float env_pdf(const igb200_shading& sh, const igb200_light& l, V3 dir)
+{
+    if (l.type != IGB200_LIGHT_ENV_TEXTURED || l.cdf == IGB200_NO_CDF) return 1 / (4 * flt_pi);
+    const V3    ldir     = switch_env_up(mat3_mul(light_transform(l), dir));
+    const float sinTheta = safe_sqrt(1 - ldir.z * ldir.z);
+    float       u, v;
+    map_env_uv(ldir, u, v);
+    const Cdf2 cdf = load_cdf2(sh, l.cdf);
+    int32_t    oy, ox;
+    float      p1, p2;
+    cdf.marginal().pdf_continuous(v, oy, p1);
+    cdf.conditional(oy).pdf_continuous(u, ox, p2);
+    return safe_div(p1 * p2, sinTheta * flt_pi * flt_pi * 2);
+}
+
 static DirectSample light_sample_direct(const Ctx& c, const igb200_light& l, Rnd& rnd, const Surf& from)
 {
     switch (l.type) {
@@ -516,6 +851,35 @@ static DirectSample light_sample_direct(const Ctx& c, const igb200_light& l, Rnd
         const float pdf = 1 / (4 * flt_pi);
         return DirectSample{ add(from.point, mulf(d, c.scene_radius)), d, cmulf(light_color(l), 1 / pdf), solid_pdf(pdf), 1.0f, c.scene_radius };
     }
+    case IGB200_LIGHT_ENV_TEXTURED: {
+        const Mat3 tr = light_transform(l);
+        if (l.cdf == IGB200_NO_CDF) { // make_environment_light -> function_spherical, light/env.art:163-166,82-86
+            const float u = rnd.next_f32();
+            const float v = rnd.next_f32();
+            const V3    d = equal_area_square_to_sphere(u, v);
+            const float pdf = 1 / (4 * flt_pi);
+            float       tu, tv;
+            map_env_uv(switch_env_up(mat3_mul(tr, d)), tu, tv);
+            const Color in = cmul(light_color(l), Tex{ c.sh }.eval(l.tex, tu, tv));
+            return DirectSample{ add(from.point, mulf(d, c.scene_radius)), d, cmulf(in, 1 / pdf), solid_pdf(pdf), 1.0f, c.scene_radius };
+        }
+        // make_environment_light_textured::sample_dir / sample_direct, light/env.art:115-133 (the radiance is NOT scaled here)
+        const float u0 = rnd.next_f32();
+        const float u1 = rnd.next_f32();
+        const Cdf2  cdf = load_cdf2(*c.sh, l.cdf);
+        int32_t     oy, ox;
+        float       py, px, p1, p2;
+        cdf.marginal().sample_continuous(u1, oy, py, p1);
+        cdf.conditional(oy).sample_continuous(u0, ox, px, p2);
+        const Color in    = Tex{ c.sh }.eval(l.tex, px, py);
+        const float theta = (1 - py) * flt_pi, phi = (px - 0.25f) * 2 * flt_pi;
+        const float st = sinf(theta), ct = cosf(theta);
+        const V3    dir = v3(st * cosf(phi), st * sinf(phi), ct); // dir_from_spherical
+        const float sinTheta = safe_sqrt(1 - dir.z * dir.z);
+        const float pdf_dir  = safe_div(p1 * p2, sinTheta * flt_pi * flt_pi * 2);
+        const V3    d        = mat3_left_mul(tr, switch_env_up(dir));
+        return DirectSample{ add(from.point, mulf(d, c.scene_radius)), d, cmulf(in, 1 / pdf_dir), solid_pdf(pdf_dir), 1.0f, c.scene_radius };
+    }
     case IGB200_LIGHT_AREA_SHAPE:
     case IGB200_LIGHT_AREA_PLANE: { // make_area_light::sample_direct, light/area.art:12-26
         const float u = rnd.next_f32();
@@ -555,17 +919,88 @@ static Pdf light_pdf_direct(const Ctx& c, const igb200_light& l, const Ray& ray,
     }
 }
 
-// make_uniform_light_selector, light/light_selector.art:26-45 (pick_light_id :19-25)
+// make_uniform_light_selector / make_hierarchy_light_selector, light/light_selector.art:19-45,76-110
+struct HEntry { V3 pos, dir; float flux; int32_t id; bool has_dir, is_leaf; };
 struct Selector {
     const Ctx* c;
     int32_t    n_inf, n_fin;
     int32_t count() const { return n_inf + n_fin; }
-    float   pdf() const { return count() == 0 ? 1.0f : 1 / (float)count(); }
-    const igb200_light& sample(Rnd& rnd) const
+    bool    hierarchical() const { return c->sh->selector == IGB200_SELECTOR_HIERARCHY && n_fin != 0; }
+    float   uniform_pdf() const { return count() == 0 ? 1.0f : 1 / (float)count(); }
+    int32_t pick(Rnd& rnd, int32_t n) const { return n <= 1 ? 0 : rnd.next_i32(0, n - 1); }
+
+    // ---- light/light_hierarchy.art ----
+    const uint32_t* codes() const { return reinterpret_cast<const uint32_t*>(c->sh->blob) + c->sh->hierarchy; }
+    const float*    nodes() const { return reinterpret_cast<const float*>(codes() + ((n_fin + 3) / 4) * 4); }
+    HEntry load(int32_t id) const // load_entry :24-38
     {
-        const int32_t n  = count();
-        const int32_t id = n <= 1 ? 0 : rnd.next_i32(0, n - 1);
-        return id < n_inf ? c->sh->infinite_lights[id] : c->sh->finite_lights[id - n_inf];
+        const float* e = nodes() + 8 * (size_t)id;
+        int32_t      index;
+        memcpy(&index, e + 7, 4);
+        return HEntry{ v3(e[0], e[1], e[2]), v3(e[4], e[5], e[6]), fabsf(e[3]), index < 0 ? -index - 1 : index, !std::signbit(e[3]), index >= 0 };
+    }
+    static float cost(const HEntry& e, V3 pos) // get_entry_cost :40-52
+    {
+        const V3    cdir  = sub(e.pos, pos);
+        const float dist2 = dot(cdir, cdir);
+        const float cos_d = e.has_dir ? fabsf(dot(e.dir, normalize(cdir))) : 1.0f;
+        return safe_div(e.flux * cos_d, dist2);
+    }
+    static float left_prop(const HEntry& l, const HEntry& r, V3 pos) { return 1 / (1 + cost(r, pos) / cost(l, pos)); } // :54-58
+    int32_t hierarchy_sample(Rnd& rnd, V3 pos, float& pdf) const // sample_light_id :65-78, make_light_hierarchy :105-112
+    {
+        pdf = 1.0f;
+        if (n_fin == 1) return 0;
+        HEntry e = load(0);
+        while (!e.is_leaf) {
+            const HEntry l = load(e.id), r = load(e.id + 1);
+            const float  prop = left_prop(l, r, pos);
+            const bool   left = rnd.next_f32() < prop;
+            e                 = left ? l : r;
+            pdf *= left ? prop : 1 - prop;
+        }
+        return e.id;
+    }
+    float hierarchy_pdf(int32_t light_id, V3 pos) const // compute_pdf :80-96
+    {
+        if (n_fin == 1) return 1.0f;
+        uint32_t code = codes()[light_id];
+        float    pdf  = 1.0f;
+        HEntry   e    = load(0);
+        while (!e.is_leaf) {
+            const HEntry l = load(e.id), r = load(e.id + 1);
+            const float  prop = left_prop(l, r, pos);
+            const bool   left = (code & 0x1u) == 0;
+            e                 = left ? l : r;
+            pdf *= left ? prop : 1 - prop;
+            code >>= 1;
+        }
+        return pdf;
+    }
+
+    const igb200_light& sample(Rnd& rnd, V3 pos, float& pdf) const
+    {
+        if (!hierarchical()) {
+            pdf              = uniform_pdf();
+            const int32_t id = pick(rnd, count());
+            return id < n_inf ? c->sh->infinite_lights[id] : c->sh->finite_lights[id - n_inf];
+        }
+        if (n_inf == 0) return c->sh->finite_lights[hierarchy_sample(rnd, pos, pdf)];
+        const float q = rnd.next_f32();
+        if (q < 0.5f) {
+            pdf = (1 / (float)n_inf) * 0.5f;
+            return c->sh->infinite_lights[pick(rnd, n_inf)];
+        }
+        float               p;
+        const igb200_light& l = c->sh->finite_lights[hierarchy_sample(rnd, pos, p)];
+        pdf                   = p * (1 - 0.5f);
+        return l;
+    }
+    float pdf(bool infinite, int32_t id, V3 pos) const
+    {
+        if (!hierarchical()) return uniform_pdf();
+        if (n_inf == 0) return hierarchy_pdf(id, pos);
+        return infinite ? (1 / (float)n_inf) * 0.5f : hierarchy_pdf(id, pos) * (1 - 0.5f);
     }
 };
 
@@ -613,9 +1048,9 @@ static void trace_path(const Ctx& c, const igb200_render_settings& rs, int32_t x
                     const igb200_light& l = c.sh->infinite_lights[i];
                     if (light_infinite(l) && !light_delta(l)) {
                         ++inflights;
-                        const Color emit  = light_color(l); // env emission: func(transform * dir) with constant func
-                        const float pdf_s = 1 / (4 * flt_pi);
-                        const float mis   = tech.enable_nee ? 1 / (1 + pt.inv_pdf * sel.pdf() * pdf_s) : 1.0f;
+                        const Color emit  = env_emission(*c.sh, l, ray.dir);
+                        const float pdf_s = env_pdf(*c.sh, l, ray.dir);
+                        const float mis   = tech.enable_nee ? 1 / (1 + pt.inv_pdf * sel.pdf(true, (int32_t)i, ray.org) * pdf_s) : 1.0f;
                         col               = cadd(col, handle_color(tech, cmulf(cmul(pt.contrib, emit), mis)));
                     }
                 }
@@ -631,7 +1066,7 @@ static void trace_path(const Ctx& c, const igb200_render_settings& rs, int32_t x
         else
             surf = trimesh_surface_element(load_trimesh(*c.scene, ent.shape_id), ent, ray, hit);
         const igb200_material& mat = c.sh->materials[ent.mat_id];
-        const Bsdf             bsdf{ &c.sh->bsdfs[mat.bsdf], &surf, (tech.flags & IGB200_TECHFLAG_ONE_SIDED_DIFFUSE) != 0 };
+        const Bsdf bsdf = make_bsdf(*c.sh, mat.bsdf, surf, ray.dir, (tech.flags & IGB200_TECHFLAG_ONE_SIDED_DIFFUSE) != 0);
         const bool             emissive = mat.light >= 0;
 
         if (tech.type == IGB200_TECH_DEBUG) { // technique/debugtracer.art:29-177
@@ -667,7 +1102,7 @@ static void trace_path(const Ctx& c, const igb200_render_settings& rs, int32_t x
                 const Color         emit  = light_color(l);
                 const Pdf           pdf   = light_pdf_direct(c, l, ray, surf);
                 const float         pdf_s = pdf.as_solid(d, hit.distance * hit.distance);
-                const float         mis   = tech.enable_nee ? 1 / (1 + pt.inv_pdf * sel.pdf() * pdf_s) : 1.0f;
+                const float         mis   = tech.enable_nee ? 1 / (1 + pt.inv_pdf * sel.pdf(false, mat.light, ray.org) * pdf_s) : 1.0f;
                 film.splat(pixel, handle_color(tech, cmulf(cmul(pt.contrib, emit), mis)));
             }
         }
@@ -675,9 +1110,10 @@ static void trace_path(const Ctx& c, const igb200_render_settings& rs, int32_t x
         // on_shadow, pathtracer.art:52-110
         const V3 out_dir = neg(ray.dir);
         if (tech.enable_nee && !bsdf.is_specular() && sel.count() != 0 && pt.depth + 1 <= tech.max_depth) {
-            const igb200_light& l  = sel.sample(rnd);
+            float               sel_pdf;
+            const igb200_light& l  = sel.sample(rnd, surf.point, sel_pdf);
             const DirectSample  ls = light_sample_direct(c, l, rnd, surf);
-            const float pdf_l_s    = ls.pdf.as_solid(ls.cos, ls.dist * ls.dist) * sel.pdf();
+            const float pdf_l_s    = ls.pdf.as_solid(ls.cos, ls.dist * ls.dist) * sel_pdf;
             if (!(pdf_l_s <= flt_eps) && ls.cos > flt_eps) {
                 const V3    in_dir = ls.dir;
                 const float mis    = light_delta(l) ? 1.0f : 1 / (1 + bsdf.pdf(in_dir, out_dir) / pdf_l_s);
