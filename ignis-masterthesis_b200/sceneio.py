@@ -595,6 +595,33 @@ def build_texture(sh, e, base):
     raise ValueError(f"texture type '{ty}' is outside the supported subset")
 
 
+def compute_cdf2d(image, premultiply_sin=True, compensate=False):
+    """CDF::computeForImage (src/runtime/CDF.cpp:42-133): image (h, w, >=3) float32 -> (marginal[h], conditional[h, w])."""
+    F = np.float32
+    img = np.asarray(image, F)
+    h, w = img.shape[:2]
+    defect = np.zeros(3, F)
+    if compensate:
+        defect = (np.maximum(img[:, :, :3], 0).reshape(-1, 3) / F(w)).sum(axis=0, dtype=F) / F(h)
+    lum = (np.maximum(img[:, :, 0] - defect[0], 0) + np.maximum(img[:, :, 1] - defect[1], 0) + np.maximum(img[:, :, 2] - defect[2], 0)) / F(3)
+    cond = np.cumsum(lum.astype(F), axis=1, dtype=F)
+    sums = cond[:, -1].copy()
+    marginal = sums * np.sin(F(math.pi) * (np.arange(h, dtype=F) + F(0.5)) / F(h), dtype=F) if premultiply_sin else sums.copy()
+    for y in range(h):
+        if sums[y] > 1e-5:
+            cond[y] *= F(1.0) / sums[y]
+        else:
+            cond[y] = np.arange(w, dtype=F) * (F(1.0) / F(w - 1))
+        cond[y, -1] = 1
+    marginal = np.cumsum(marginal.astype(F), dtype=F)
+    if marginal[-1] > 1e-5:
+        marginal *= F(1.0) / marginal[-1]
+    else:
+        marginal = np.arange(h, dtype=F) * (F(1.0) / F(h - 1))
+    marginal[-1] = 1
+    return marginal.astype(F), cond.astype(F)
+
+
 _CONDUCTORS = {"none": ((0.0, 0.0, 0.0), (1.0, 1.0, 1.0))}  # runtime/bsdf/BSDF.cpp:12-42 (named metals: not restated)
 
 

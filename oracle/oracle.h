@@ -82,6 +82,9 @@ int igo_render(const igo_scene* scene, const igb200_shading* shading, const igb2
 void igo_kat_rng(int32_t sample, int32_t iter, int32_t frame, int32_t x, int32_t y, int32_t user, uint32_t n,
                  uint32_t* out_seed, uint32_t* out_raw, float* out_f32);
 
+/* Texture lookups on their own: n (u, v) pairs -> n rgb triples; -1 if the id is out of range. */
+int igo_texture_eval(const igb200_shading* shading, uint32_t id, const float* uv, uint64_t n, float* rgb);
+
 /* Structure statistics for reports. */
 void igo_scene_info(const igo_scene* s, uint64_t* node4_count, uint64_t* tri4_count, uint64_t* tri_count);
 

@@ -118,6 +118,18 @@ class OracleScene:
         return {"node4": a.value, "tri4": b.value, "tris": c.value}
 
 
+def texture_eval(shading, tex_id, uv):
+    """rgb of texture `tex_id` of an ignis-masterthesis_b200 Shading at the (n, 2) coordinates `uv`."""
+    uv = np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
+    out = np.zeros((uv.shape[0], 3), np.float32)
+    sh = shading.c_shading()
+    lib = load()
+    lib.igo_texture_eval.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p]
+    if lib.igo_texture_eval(C.addressof(sh), tex_id, uv.ctypes.data, uv.shape[0], out.ctypes.data) != 0:
+        raise ValueError("texture id out of range")
+    return out
+
+
 def kat_rng(sample, it, frame, x, y, user, n=8):
     seed = C.c_uint32()
     raw, f32 = np.zeros(n, np.uint32), np.zeros(n, np.float32)

@@ -1155,6 +1155,18 @@ static void trace_path(const Ctx& c, const igb200_render_settings& rs, int32_t x
 
 using namespace igo;
 
+// Texture lookups on their own (tests pin them against an independent numpy restatement).
+extern "C" int igo_texture_eval(const igb200_shading* sh, uint32_t id, const float* uv, uint64_t n, float* rgb)
+{
+    if (!sh || !uv || !rgb || id >= sh->texture_count) return -1;
+    const Tex tex{ sh };
+    for (uint64_t i = 0; i < n; ++i) {
+        const Color c = tex.eval(id, uv[2 * i], uv[2 * i + 1]);
+        rgb[3 * i] = c.r; rgb[3 * i + 1] = c.g; rgb[3 * i + 2] = c.b;
+    }
+    return 0;
+}
+
 // One render iteration (Device::render, src/runtime/device/Device.cpp:1588-1612 -> cpu_trace).
 // film: w*h*3 floats, accumulated into (the caller keeps the iteration count).  stats3 = camera / bounce / shadow rays.
 extern "C" int igo_render(const igo_scene* scene, const igb200_shading* sh, const igb200_render_settings* rs, float* film,

@@ -26,6 +26,8 @@ JOBS = [  # (fixture, scene file, reference image, width, height)
     ("plane-d6", "evaluation/plane-d6.json", "ref-plane-d6-4096.exr", None, None),
     ("diamond", "diamond_scene.json", None, 1920, 1080),
     ("primitives", "primitives.json", None, 1024, 1024),  # BASELINE.json configs[1]
+    ("multilight-uniform", "evaluation/multilight-uniform.json", "ref-multilight-4096.exr", None, None),
+    ("multilight-hierarchy", "evaluation/multilight-hierarchy.json", "ref-multilight-4096.exr", None, None),
 ]
 only = set(sys.argv[1:])
 for name, scene, ref, w, h in JOBS:

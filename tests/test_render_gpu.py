@@ -12,7 +12,7 @@ at most 0.5 % of the pixel channels further than 1e-3 relative from the oracle, 
 import numpy as np
 import pytest
 
-from render_common import eval_error, flat_scene, load_golden, room_scene
+from render_common import eval_error, features_scene, flat_scene, load_golden, room_scene
 
 pytestmark = pytest.mark.gpu
 
@@ -60,8 +60,21 @@ def test_room_matches_oracle(ig, oracle, dev, one_sided):
     _assert_parity(film, ref, stats, osc.ray_stats.astype(np.int64))
 
 
+@pytest.mark.parametrize("selector", ["hierarchy", "uniform"])
+def test_features_scene_matches_oracle(ig, oracle, dev, selector):
+    # ABI v3 paths (extended shade kernel): textures, rough / bump-mapped conductors, textured environment + CDF,
+    # light hierarchy.  Same tolerance as the other parity tests.
+    tables, sh = features_scene(ig, 160)
+    if selector == "uniform":
+        sh.selector = ig.shading.SELECTOR_UNIFORM
+    film, stats = _render(dev, tables, sh, 160, 160, 4, 3, seed=21)
+    osc = oracle.OracleScene(tables)
+    ref = osc.render(sh, 160, 160, spi=4, iterations=3, seed=21)
+    _assert_parity(film, ref, stats, osc.ray_stats.astype(np.int64))
+
+
 @pytest.mark.parametrize("name,w,h", [("diamond", 240, 135), ("cbox-d6", 128, 128), ("emissive-plane", 96, 96),
-                                      ("primitives", 192, 192)])
+                                      ("primitives", 192, 192), ("multilight-hierarchy", 128, 128)])
 def test_reference_scenes_match_oracle(ig, oracle, dev, name, w, h):
     tables, sh, _, _, _ = load_golden(ig, name)
     film, stats = _render(dev, tables, sh, w, h, 4, 2, seed=11)
@@ -88,6 +101,8 @@ def test_flat_scene_closed_forms_full_size(ig, dev, light, one_sided, expected, 
     ("cbox-d1", False, 256, 5e-3),
     ("plane-d6", True, 1024, 1e-3),
     ("cbox-d6", True, 4096, 5e-3),         # the reference's own sample count and threshold (RunEvaluations.py:91-93)
+    ("multilight-uniform", True, 1024, 3e-4),
+    ("multilight-hierarchy", True, 1024, 3e-4),
 ])
 def test_golden_images(ig, dev, name, one_sided, spp, threshold):
     tables, sh, w, h, ref = load_golden(ig, name)

@@ -1,0 +1,119 @@
+"""ABI v3 shading paths in the oracle: textures against an independent numpy restatement, the light hierarchy
+builder, the 2-D CDF, and the reference's golden image for the hierarchy / uniform selectors
+(scenes/evaluation/multilight-*.json, threshold 3e-4 of scripts/RunEvaluations.py:91-108)."""
+import importlib
+
+import numpy as np
+import pytest
+
+from render_common import eval_error, features_scene, load_golden
+
+io = importlib.import_module("ignis-masterthesis_b200.sceneio")
+
+
+def _np_texel(img, x, y):
+    q = img[y, x]
+    return np.array([q & 255, (q >> 8) & 255, (q >> 16) & 255], np.float32) / np.float32(255)
+
+
+def test_checkerboard_and_nearest_bilinear_against_numpy(ig, oracle):
+    S = ig.shading
+    sh = ig.Shading()
+    rng = np.random.default_rng(1)
+    img8 = rng.integers(0, 256, (8, 16, 4), dtype=np.uint32)
+    img = (img8[:, :, 0] | (img8[:, :, 1] << 8) | (img8[:, :, 2] << 16) | (img8[:, :, 3] << 24)).astype(np.uint32)
+    t_chk = sh.add_checkerboard((10, 5), (0.3, 0.3, 0.3), (1, 1, 1))
+    t_near = sh.add_image_texture(img, S.FILTER_NEAREST)
+    t_bil = sh.add_image_texture(img, S.FILTER_BILINEAR, (S.WRAP_CLAMP, S.WRAP_MIRROR))
+    t_cub = sh.add_image_texture(np.full((4, 4), 0x80808080, np.uint32), S.FILTER_BICUBIC)
+    uv = rng.uniform(-1.5, 2.5, (400, 2)).astype(np.float32)
+    # checkerboard: texture/checkerboard.art:4-13
+    got = oracle.texture_eval(sh, t_chk, uv)
+    su, sv = uv[:, 0] * np.float32(10), uv[:, 1] * np.float32(5)
+    par = lambda s: (np.floor(s - 2 * np.floor(s / 2)).astype(int) % 2) == 0
+    want = np.where((par(su) ^ par(sv))[:, None], np.float32(0.3), np.float32(1.0)) * np.ones((1, 3), np.float32)
+    assert np.array_equal(got, want)
+    # nearest with repeat: floor(uv * size) mod size
+    got = oracle.texture_eval(sh, t_near, uv)
+    ix = np.floor(uv[:, 0] * np.float32(16)).astype(int) % 16
+    iy = np.floor(uv[:, 1] * np.float32(8)).astype(int) % 8
+    assert np.array_equal(got, np.stack([_np_texel(img, x, y) for x, y in zip(ix, iy)]))
+    # bilinear with clamp (u) and mirror (v)
+    got = oracle.texture_eval(sh, t_bil, uv)
+    clamp = lambda x, w: min(max(x, 0), w - 1)
+
+    def mirror(x, w):
+        t = -1 - x if x < 0 else x
+        i, k = divmod(t, w)
+        return w - 1 - k if i % 2 == 0 else k
+
+    for (u, v), g in zip(uv[:50], got[:50]):
+        fu, fv = np.float32(u) * np.float32(16) - np.float32(0.5), np.float32(v) * np.float32(8) - np.float32(0.5)
+        x, y = int(np.floor(fu)), int(np.floor(fv))
+        fx, fy = fu - np.floor(fu), fv - np.floor(fv)
+        p = [[_np_texel(img, clamp(x + dx, 16), mirror(y + dy, 8)) for dx in (0, 1)] for dy in (0, 1)]
+        want = (1 - fy) * ((1 - fx) * p[0][0] + fx * p[0][1]) + fy * ((1 - fx) * p[1][0] + fx * p[1][1])
+        assert np.allclose(g, want, atol=2e-6)
+    # the cubic B-spline weights are a partition of unity: a constant image stays constant
+    assert np.allclose(oracle.texture_eval(sh, t_cub, uv), 128 / 255, atol=1e-6)
+
+
+def test_packed_image_mapping_matches_the_loader_formula():
+    # byte_color_to_linear, src/runtime/Image.cpp:31-42
+    c = np.arange(256, dtype=np.uint8)
+    lin = io._srgb_byte_to_linear(c)
+    assert lin[0] == 0 and lin[255] == 255 and np.all(np.diff(lin.astype(int)) >= 0)
+    x = 128 / 255
+    assert lin[128] == int(np.floor(((x + 0.055) / 1.055) ** 2.4 * 255))
+    assert lin[5] == int(np.floor(5 / 255 / 12.92 * 255))
+
+
+def test_light_hierarchy_builder_and_pdf(ig, oracle):
+    # four point lights: a binary tree with 7 nodes; leaf codes walk back to their leaf (light_hierarchy.art:80-96)
+    ent = [((-1, 0, 0), None, 2.0), ((1, 0, 0), None, 1.0), ((1, 2, 0), None, 4.0), ((-1, 0.5, 3), (0, 0, 1), 3.0)]
+    codes, nodes = io.build_light_hierarchy(ent)
+    assert nodes.shape == (7, 8) and codes.shape == (4,)
+    ids = nodes[:, 7].view(np.int32)
+    for lid in range(4):
+        i, code = 0, int(codes[lid])
+        while ids[i] < 0:
+            i = (-ids[i] - 1) + (code & 1)
+            code >>= 1
+        assert ids[i] == lid
+    assert np.isclose(abs(nodes[0, 3]), 10.0)            # the root carries the total flux
+    assert nodes[0, 3] < 0                                # delta lights below: no direction (LightHierarchy.cpp:62-76)
+    leaf = {int(ids[i]): i for i in range(7) if ids[i] >= 0}
+    assert nodes[leaf[0], 3] == -2.0 and nodes[leaf[3], 3] == 3.0
+
+
+def test_cdf2d_is_the_loader_table():
+    img = np.zeros((4, 8, 4), np.float32)
+    img[1, 2, :3] = 3.0
+    img[2, 5, :3] = (1.0, 2.0, 3.0)
+    m, c = io.compute_cdf2d(img, premultiply_sin=False)
+    assert np.allclose(m, [0, 0.6, 1, 1]) and m[-1] == 1
+    assert np.allclose(c[1], [0, 0, 1, 1, 1, 1, 1, 1]) and np.allclose(c[0], np.arange(8) / 7)
+    m2, _ = io.compute_cdf2d(img, premultiply_sin=True)
+    assert np.isclose(m2[1], 3 * np.sin(np.pi * 1.5 / 4) / (3 * np.sin(np.pi * 1.5 / 4) + 2 * np.sin(np.pi * 2.5 / 4)))
+
+
+@pytest.mark.parametrize("name", ["multilight-uniform", "multilight-hierarchy"])
+def test_multilight_golden(ig, oracle, name):
+    tables, sh, w, h, ref = load_golden(ig, name)
+    assert (sh.selector == ig.shading.SELECTOR_HIERARCHY) == name.endswith("hierarchy")
+    sh.technique.flags = ig.shading.TECHFLAG_ONE_SIDED_DIFFUSE  # see DESIGN.md section 4.1, note 2
+    film = oracle.OracleScene(tables).render(sh, w, h, spi=64, iterations=4, seed=1)
+    assert eval_error(film / 4, ref) < 3e-4
+
+
+def test_features_scene_renders_and_both_selectors_agree(ig, oracle):
+    # the hierarchy only changes the sampling density: the expectation must not move
+    tables, sh = features_scene(ig, 64)
+    osc = oracle.OracleScene(tables)
+    a = osc.render(sh, 64, 64, spi=64, iterations=4, seed=2)
+    assert np.all(np.isfinite(a)) and a.min() >= 0
+    sh.selector = ig.shading.SELECTOR_UNIFORM
+    b = osc.render(sh, 64, 64, spi=64, iterations=4, seed=9)
+    assert a.mean() == pytest.approx(b.mean(), rel=3e-2)
+    sm = lambda x: x.reshape(8, 8, 8, 8, 3).mean(axis=(1, 3))
+    assert np.allclose(sm(a), sm(b), rtol=0.25, atol=0.05 * 4)
