@@ -622,6 +622,90 @@ def compute_cdf2d(image, premultiply_sin=True, compensate=False):
     return marginal.astype(F), cond.astype(F)
 
 
+# ---------------------------------------------------------------------------------------- sky (loader side, N3)
+def compute_sun_ea(year=2020, month=5, day=6, hour=12, minute=0, seconds=0.0, longitude=-6.9965744, latitude=49.235422, timezone=-2.0):
+    """computeSunEA (src/runtime/skysun/SunLocation.cpp:17-103) with the defaults of SunLocation.h:8-36.
+    Returns (elevation, azimuth west of south) in radians, float32 like ElevationAzimuth."""
+    F = np.float32
+    dec_hours = hour + F(timezone) + (minute + F(seconds) / 60.0) / 60.0
+    aux1 = int((month - 14) / 12)
+    aux2 = int((1461 * (year + 4800 + aux1)) / 4) + int((367 * (month - 2 - 12 * aux1)) / 12) - int((3 * int((year + 4900 + aux1) / 100)) / 4) + day - 32075
+    elapsed = (float(aux2) - 0.5 + dec_hours / 24.0) - 2451545.0
+    omega = 2.1429 - 0.0010394594 * elapsed
+    mean_long = 4.8950630 + 0.017202791698 * elapsed
+    anomaly = 6.2400600 + 0.0172019699 * elapsed
+    ecl_long = mean_long + 0.03341607 * math.sin(anomaly) + 0.00034894 * math.sin(2 * anomaly) - 0.0001134 - 0.0000203 * math.sin(omega)
+    ecl_obl = 0.4090928 - 6.2140e-9 * elapsed + 0.0000396 * math.cos(omega)
+    s_el = math.sin(ecl_long)
+    ra = math.atan2(math.cos(ecl_obl) * s_el, math.cos(ecl_long))
+    PI = float(F(3.14159265358979323846))
+    if ra < 0:
+        ra += 2 * PI
+    decl = math.asin(math.sin(ecl_obl) * s_el)
+    gmst = 6.6974243242 + 0.0657098283 * elapsed + dec_hours
+    deg2rad = float(F(PI / 180))
+    lmst = deg2rad * float(F(gmst * 15 - float(F(longitude))))
+    lat = deg2rad * float(F(latitude))
+    ha = lmst - ra
+    zenith = math.acos(math.cos(lat) * math.cos(ha) * math.cos(decl) + math.sin(decl) * math.sin(lat))
+    az = math.atan2(-math.sin(ha), math.tan(decl) * math.cos(lat) - math.sin(lat) * math.cos(ha))
+    if az < 0:
+        az += 2 * PI
+    zenith += (6371.01 / 149597890) * math.sin(zenith)
+    return F(F(PI / 2) - F(zenith)), F(math.fmod(float(F(az) + F(PI)), 2 * PI))
+
+
+def ea_from_direction_yup(d):  # ElevationAzimuth::fromDirectionYUp
+    d = np.asarray(d, np.float64)
+    d = d / np.linalg.norm(d)
+    phi = math.atan2(d[0], -d[2])
+    return np.float32(math.pi / 2 - math.acos(d[1])), np.float32(phi + 2 * math.pi if phi < 0 else phi)
+
+
+def bake_sky(light, hosek_lib):
+    """SkyModel::SkyModel (src/runtime/skysun/SkyModel.cpp:9-55) at RES_AZ x RES_EL = 512 x 256 over the reference's own
+    ArHosekSkyModel (compiled from the reference tree into oracle/_ref/libhosek.so), followed by the EXR round trip of
+    SkyLight.cpp:33-50: float32 on disk, flipped vertically when loaded (Image.cpp:559-560), alpha 1.
+    Returns the (256, 512, 4) float32 image as the device sees it."""
+    import ctypes as C
+    F = np.float32
+    lib = C.CDLL(hosek_lib)
+    init = getattr(lib, "_Z36arhosek_rgb_skymodelstate_alloc_initddd")
+    init.restype, init.argtypes = C.c_void_p, [C.c_double] * 3
+    rad = getattr(lib, "_Z33arhosek_tristim_skymodel_radianceP20ArHosekSkyModelStateddi")
+    rad.restype, rad.argtypes = C.c_double, [C.c_void_p, C.c_double, C.c_double, C.c_int]
+    if "direction" in light or "sun_direction" in light:
+        el, az = ea_from_direction_yup(light.get("direction", light.get("sun_direction")))
+    elif "elevation" in light or "azimuth" in light:
+        el, az = F(light.get("elevation", 0)), F(light.get("azimuth", 0))
+    else:
+        el, az = compute_sun_ea(*[light.get(k, d) for k, d in (("year", 2020), ("month", 5), ("day", 6), ("hour", 12), ("minute", 0),
+                                                               ("seconds", 0.0), ("longitude", -6.9965744), ("latitude", 49.235422),
+                                                               ("timezone", -2.0))])
+    ground = _color(light.get("ground"), 0.8)
+    turbidity = F(light.get("turbidity", 3.0))
+    PI = F(3.14159265358979323846)
+    solar_elevation = F(PI / 2) - el  # (sic) SkyModel.cpp:13
+    sun_se, sun_ce = F(math.sin(solar_elevation)), F(math.cos(solar_elevation))
+    states = [init(float(turbidity), float(ground[k]), float(solar_elevation)) for k in range(3)]
+    H, Wd = 256, 512
+    data = np.zeros((H, Wd, 4), F)
+    for y in range(H):
+        theta = F(PI / 2) * F(y) / F(H)
+        st, ct = F(math.sin(theta)), F(math.cos(theta))
+        for x in range(Wd):
+            azimuth = F(2 * PI) * F(x) / F(Wd) - F(PI / 4)
+            if azimuth < 0:
+                azimuth += F(2) * PI
+            cos_gamma = ct * sun_ce + st * sun_se * F(math.cos(azimuth - az))
+            gamma = F(math.acos(min(1.0, max(-1.0, float(cos_gamma)))))
+            for k in range(3):
+                data[y, x, k] = max(0.0, F(rad(states[k], float(theta), float(gamma), k)) / F(106.856980))
+    img = data[::-1].copy()
+    img[:, :, 3] = 1
+    return np.ascontiguousarray(img)
+
+
 _CONDUCTORS = {"none": ((0.0, 0.0, 0.0), (1.0, 1.0, 1.0))}  # runtime/bsdf/BSDF.cpp:12-42 (named metals: not restated)
 
 
@@ -699,7 +783,7 @@ def build_light_hierarchy(entries):
     return codes, nodes
 
 
-def load_scene(scene, base=".", width=None, height=None):
+def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
     """scene: dict or path. Returns (SceneTables, Shading, width, height, info)."""
     if isinstance(scene, str):
         base = os.path.dirname(os.path.abspath(scene))
@@ -814,6 +898,14 @@ def load_scene(scene, base=".", width=None, height=None):
             if isinstance(l.get("radiance"), str):
                 raise ValueError("textured environment lights are outside the supported subset")
             sh.add_env_light(_color(l.get("radiance"), 1.0), _color(l.get("scale"), 1.0))
+        elif ty == "sky":  # runtime/light/SkyLight.cpp:52-77
+            if hosek_lib is None:
+                raise ValueError("sky lights need the reference's Hosek model (oracle/_ref/libhosek.so, build container only)")
+            img = bake_sky(l, hosek_lib)
+            tex = sh.add_image_texture(img, 1, (0, 0))  # make_repeat_border(), make_bilinear_filter()
+            marginal, cond = compute_cdf2d(img, True, False)
+            m3 = parse_transform(l.get("transform"))[:3, :3]
+            sh.add_env_textured(tex, _color(l.get("scale"), 1.0), sh.add_cdf2d(marginal, cond), np.linalg.inv(m3.T))
         elif ty == "area":
             name = l["entity"]
             ent = next(e for e in scene["entities"] if e["name"] == name)

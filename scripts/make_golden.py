@@ -28,12 +28,14 @@ JOBS = [  # (fixture, scene file, reference image, width, height)
     ("primitives", "primitives.json", None, 1024, 1024),  # BASELINE.json configs[1]
     ("multilight-uniform", "evaluation/multilight-uniform.json", "ref-multilight-4096.exr", None, None),
     ("multilight-hierarchy", "evaluation/multilight-hierarchy.json", "ref-multilight-4096.exr", None, None),
+    ("many-point-lights", "many_point_lights.json", None, 3840, 2160),  # BASELINE.json configs[4]
 ]
+HOSEK = os.path.join(ROOT, "oracle", "_ref", "libhosek.so")  # `make -C oracle ref`
 only = set(sys.argv[1:])
 for name, scene, ref, w, h in JOBS:
     if only and name not in only:
         continue
-    tables, sh, w, h, info = sceneio.load_scene(f"{REF}/{scene}", width=w, height=h)
+    tables, sh, w, h, info = sceneio.load_scene(f"{REF}/{scene}", width=w, height=h, hosek_lib=HOSEK if os.path.exists(HOSEK) else None)
     fixtures.save_fixture(os.path.join(OUT, name + ".npz"), tables, sh, w, h, exr(ref) if ref else None,
                           meta=f"{scene}; reference image {ref}")
     print(name, w, h, "entities", tables.entity_count, "materials", tables.material_count, os.path.getsize(os.path.join(OUT, name + ".npz")))

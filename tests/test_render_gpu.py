@@ -38,16 +38,16 @@ def _render(dev, tables, sh, w, h, spi, iters, seed=0, first=0):
     return film, stats
 
 
-def _assert_parity(film, ref, stats, ostats):
+def _assert_parity(film, ref, stats, ostats, far_limit=5e-3, count_tol=2e-3):
     assert np.all(np.isfinite(film))
     scale = np.maximum(np.abs(ref), 1e-3 * max(float(np.abs(ref).mean()), 1e-12))
     rel = np.abs(film - ref) / scale
     far = rel > 1e-3
-    assert float(far.mean()) <= 5e-3, f"{far.mean():.4%} of the pixels differ by more than 1e-3"
+    assert float(far.mean()) <= far_limit, f"{far.mean():.4%} of the pixels differ by more than 1e-3"
     near_rrmse = float(np.sqrt(np.mean(np.square(rel[~far]))))
     assert near_rrmse <= 1e-4 and float(np.median(rel)) <= 1e-5, (near_rrmse, float(np.median(rel)))
     assert abs(float(film.sum()) - float(ref.sum())) <= 1e-2 * float(np.abs(ref).sum()) + 1e-12
-    assert np.all(np.abs(stats - ostats) <= 2e-3 * np.maximum(ostats, 1)), (stats, ostats)
+    assert np.all(np.abs(stats - ostats) <= count_tol * np.maximum(ostats, 1)), (stats, ostats)
 
 
 @pytest.mark.parametrize("one_sided", [False, True])
@@ -131,6 +131,63 @@ def test_c2_primitives_full_size(ig, oracle, dev):
     # the image itself: 4 x 4 box-filtered GPU film against the low-resolution oracle render (same camera)
     small = film.reshape(h // 4, 4, w // 4, 4, 3).mean(axis=(1, 3))
     assert eval_error(small / 8, ref / 8) < 5e-3
+
+
+@pytest.mark.parametrize("max_depth,far_limit,count_tol", [(2, 5e-3, 0.0), (64, 4e-2, 1.5e-2)])
+def test_c5_many_point_lights_matches_oracle(ig, oracle, dev, max_depth, far_limit, count_tol):
+    # Up to depth 2 (every ABI v3 feature evaluated once per path) the standard tolerance holds.  Deeper paths bounce
+    # between bump-mapped surfaces: the finite-difference normal (texture_dx, delta = 1e-3, over a 500 x 500 noise
+    # map) amplifies a 1e-7 difference of the hit point ~5e4 times, so like the glass of C4 a few percent of the pixels
+    # take another path (measured: 2.2 % of the pixels, ray counters 0.8 % apart on one seed).  That this is
+    # decorrelation and not bias is what test_c5_expectation_is_the_oracles checks with independent seeds.
+    tables, sh, _, _, _ = load_golden(ig, "many-point-lights")
+    sh.technique.max_depth = max_depth
+    film, stats = _render(dev, tables, sh, 192, 108, 4, 2, seed=11)
+    osc = oracle.OracleScene(tables)
+    ref = osc.render(sh, 192, 108, spi=4, iterations=2, seed=11)
+    _assert_parity(film, ref, stats, osc.ray_stats.astype(np.int64), far_limit, count_tol)
+
+
+def test_c5_expectation_is_the_oracles(ig, oracle, dev):
+    # independent seeds on both sides: bounce-ray count and film sum agree within 4 standard errors
+    tables, sh, _, _, _ = load_golden(ig, "many-point-lights")
+    osc = oracle.OracleScene(tables)
+    g, o = [], []
+    for k in range(10):
+        dev.clear_framebuffer()
+        film, stats = _render(dev, tables, sh, 192, 108, 16, 2, seed=100 + k)
+        g.append((stats[1], film.sum()))
+        ref = osc.render(sh, 192, 108, spi=16, iterations=2, seed=200 + k)
+        o.append((int(osc.ray_stats[1]), ref.sum()))
+    g, o = np.asarray(g, np.float64), np.asarray(o, np.float64)
+    se = np.sqrt(g.var(axis=0, ddof=1) / len(g) + o.var(axis=0, ddof=1) / len(o))
+    assert np.all(np.abs(g.mean(axis=0) - o.mean(axis=0)) <= 4 * se), (g.mean(axis=0), o.mean(axis=0), se)
+
+
+def test_c5_many_point_lights_full_size(ig, oracle, dev):
+    # BASELINE.json configs[4]: scenes/many_point_lights.json at 3840 x 2160 (checkerboard ground, bump-mapped rough
+    # conductor, ten point lights + baked Hosek sky, light hierarchy).  Full-size properties: one camera ray per
+    # sample, batched == single iterations, and the image against the oracle's render at 1/10 of the resolution.
+    tables, sh, w, h, _ = load_golden(ig, "many-point-lights")
+    assert (w, h) == (3840, 2160) and sh.selector == ig.shading.SELECTOR_HIERARCHY
+    film, stats = _render(dev, tables, sh, w, h, 1, 4, seed=42)
+    assert stats[0] == w * h * 4 and 0 < stats[2] <= stats[0] + stats[1]
+    assert np.all(np.isfinite(film)) and film.min() >= 0
+    dev.clear_framebuffer()
+    dev.render(w, h, spi=1, iteration=0, seed=42, iterations=4)
+    batched, n = dev.framebuffer()
+    assert n == 4 and np.allclose(batched, film, rtol=1e-4, atol=1e-5)
+    osc = oracle.OracleScene(tables)
+    ref = osc.render(sh, w // 10, h // 10, spi=8, iterations=4, seed=42)
+    assert film.mean() == pytest.approx(ref.mean(), rel=2e-2)
+    # the image itself, on a 9 x 16 grid of block means (the highlights on the pillar are far too noisy per pixel
+    # at the 32 spp the oracle gets here)
+    coarse = lambda img: img.reshape(9, img.shape[0] // 9, 16, img.shape[1] // 16, 3).mean(axis=(1, 3))
+    # (two oracle renders with different seeds differ by up to 12 % in the pillar's blocks, < 1 % elsewhere)
+    assert np.allclose(coarse(film), coarse(ref), rtol=0.25, atol=1e-2 * float(ref.mean()))
+    sky = np.ones((9, 16), bool)
+    sky[:, 6:10] = False
+    assert np.allclose(coarse(film)[sky], coarse(ref)[sky], rtol=2e-2)
 
 
 def test_igtrace_list_mode(ig, dev):

@@ -117,3 +117,25 @@ def test_features_scene_renders_and_both_selectors_agree(ig, oracle):
     assert a.mean() == pytest.approx(b.mean(), rel=3e-2)
     sm = lambda x: x.reshape(8, 8, 8, 8, 3).mean(axis=(1, 3))
     assert np.allclose(sm(a), sm(b), rtol=0.25, atol=0.05 * 4)
+
+
+def test_c5_fixture_through_the_oracle(ig, oracle):
+    # scenes/many_point_lights.json as baked by scripts/make_golden.py: checkerboard + bicubic bump image + sky image
+    tables, sh, w, h, _ = load_golden(ig, "many-point-lights")
+    S = ig.shading
+    assert (w, h) == (3840, 2160) and len(sh.finite) == 10 and len(sh.infinite) == 1 and sh.selector == S.SELECTOR_HIERARCHY
+    assert [b.type for b in sh.bsdfs] == [S.BSDF_DIFFUSE, S.BSDF_CONDUCTOR, S.BSDF_BUMPMAP]
+    assert sh.bsdfs[1].q[0].f == pytest.approx(0.16) and sh.bsdfs[2].p[0] == pytest.approx(0.2)
+    bump, check, sky = sh.textures
+    assert (bump.width, bump.height, bump.filter) == (500, 500, S.FILTER_BICUBIC)   # "trilinear" is not a filter name -> default
+    assert (sky.width, sky.height, sky.format, sky.filter) == (512, 256, S.IMAGE_RGBA32F, S.FILTER_BILINEAR)
+    assert sh.infinite[0].type == S.LIGHT_ENV_TEXTURED and sh.infinite[0].cdf != S.NO_CDF
+    film = oracle.OracleScene(tables).render(sh, 96, 54, spi=8, iterations=1, seed=1)
+    assert np.all(np.isfinite(film)) and film.min() >= 0 and 0.3 < film.mean() < 1.5
+    assert film[:10].mean(axis=(0, 1))[2] > film[:10].mean(axis=(0, 1))[0]           # a blue sky above the pillar
+
+
+def test_default_sun_position_is_the_documented_one():
+    # src/runtime/skysun/SunLocation.h:31: "Default is Saarbruecken, Elevation: 52.87 Azimuth: 323.271 (west of south)"
+    el, az = io.compute_sun_ea()
+    assert np.degrees(el) == pytest.approx(52.87, abs=0.02) and np.degrees(az) == pytest.approx(323.271, abs=0.03)
