@@ -127,21 +127,25 @@ class _DevArray:
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
 
 
-def load_pt_workload(pkg):
+PT_FIXTURE = {"c4-diamond": "diamond", "c5-many-point-lights": "many-point-lights"}
+
+
+def load_pt_workload(pkg, workload=None):
     fx = importlib.import_module("ignis-masterthesis_b200.fixtures")
-    tables, sh, w, h, _ = fx.load_fixture(os.path.join(ROOT, "tests", "golden", "diamond.npz"))
+    tables, sh, w, h, _ = fx.load_fixture(os.path.join(ROOT, "tests", "golden", PT_FIXTURE[workload or PT_WORKLOAD] + ".npz"))
     spi = max(1, min(64, int(np.ceil(8 / ((w / 1000.0) * (h / 1000.0))))))  # recommendSPI (GPU), Runtime.cpp:61-69
     return tables, sh, w, h, spi
 
 
-def bench_path_tracer(pkg, local_rank, rank, world, iterations, warmup):
+def bench_path_tracer(pkg, local_rank, rank, world, iterations, warmup, workload=None, first=None):
     """Path-traced samples/s (igcli's definition: spi * w * h / iteration seconds, src/frontend/cli/main.cpp:135).
     N GPUs: rank r renders the block of iterations [r*K, (r+1)*K) in one wavefront (the seed hashes the iteration
     index, so the union is the single-GPU sample set), then the films are summed onto rank 0 with one NCCL reduce
     over NVLink."""
     import torch
     import torch.distributed as dist
-    tables, sh, w, h, spi = load_pt_workload(pkg)
+    workload = workload or PT_WORKLOAD
+    tables, sh, w, h, spi = load_pt_workload(pkg, workload)
     dev = pkg.Device(local_rank)
     dev.assign_scene(tables)
     dev.assign_shading(sh)
@@ -149,11 +153,15 @@ def bench_path_tracer(pkg, local_rank, rank, world, iterations, warmup):
     for it in range(warmup):
         dev.render(w, h, spi=spi, iteration=1_000_000 + it)
     dev.clear_framebuffer()
+    its = torch.tensor([float(iterations)], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(its, op=dist.ReduceOp.SUM)
+    total_iterations = int(its.item())
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
-    dev.render(w, h, spi=spi, iteration=rank * iterations, iterations=iterations)
+    dev.render(w, h, spi=spi, iteration=rank * iterations if first is None else first, iterations=iterations)
     st = dev.render_stats()
     ms = [st["device_ms"] / iterations]
     rays = st["camera_rays"] + st["bounce_rays"] + st["shadow_rays"]
@@ -170,7 +178,7 @@ def bench_path_tracer(pkg, local_rank, rank, world, iterations, warmup):
         torch.cuda.synchronize()
         reduce_ms = e0.elapsed_time(e1)
         if rank == 0:
-            dev.set_framebuffer(ptr, w * h * 3, iterations * world)
+            dev.set_framebuffer(ptr, w * h * 3, total_iterations)
     total_s = time.perf_counter() - t0
     host_film, n_total = dev.framebuffer()  # D2H of the presented frame: the e2e read
     e2e_s = time.perf_counter() - t0
@@ -181,9 +189,9 @@ def bench_path_tracer(pkg, local_rank, rank, world, iterations, warmup):
         sm = stats.clone()
         dist.all_reduce(sm, op=dist.ReduceOp.SUM)
         total_s, e2e_s, rays, launches = float(mx[0]), float(mx[1]), float(sm[2]), float(sm[4])
-    samples = float(spi) * w * h * iterations * world
+    samples = float(spi) * w * h * total_iterations
     out = {
-        "workload": PT_WORKLOAD, "width": w, "height": h, "spi": spi, "iterations": iterations * world,
+        "workload": workload, "width": w, "height": h, "spi": spi, "iterations": total_iterations,
         "max_depth": int(sh.technique.max_depth), "metric": "path-traced samples/s", "unit": "Msamples/s",
         "value": samples / total_s / 1e6, "e2e_value": samples / e2e_s / 1e6,
         "ms_per_iteration_median": float(np.median(ms)), "mrays_per_s": rays / total_s / 1e6,
@@ -194,11 +202,12 @@ def bench_path_tracer(pkg, local_rank, rank, world, iterations, warmup):
     return out
 
 
-def oracle_samples_per_s(pkg, budget_s=12.0):
+def oracle_samples_per_s(pkg, budget_s=12.0, workload=None):
     """The oracle's render iteration on the host cores on a bounded sample of the same workload (a crop-free
     low-resolution render of the same scene: same rays per sample)."""
     oracle = load_oracle()
-    tables, sh, w, h, spi = load_pt_workload(pkg)
+    workload = workload or PT_WORKLOAD
+    tables, sh, w, h, spi = load_pt_workload(pkg, workload)
     osc = oracle.OracleScene(tables)
     cw, ch = w // 4, h // 4
     cores = os.cpu_count() or 1
@@ -210,7 +219,7 @@ def oracle_samples_per_s(pkg, budget_s=12.0):
         n += 1
     dt = time.perf_counter() - t0
     return {"value": cw * ch * spi * n / dt / 1e6, "unit": "Msamples/s", "cores": cores, "kind": "port",
-            "sample": f"{n} iterations of {PT_WORKLOAD} at {cw}x{ch} (1/16 of the pixels), spi {spi}"}
+            "sample": f"{n} iterations of {workload} at {cw}x{ch} (1/16 of the pixels), spi {spi}"}
 
 
 def run_reference(args, rank, world):
@@ -248,6 +257,10 @@ def run_reference(args, rank, world):
         pt = oracle_samples_per_s(pkg)
         line["path_tracer"] = {"workload": PT_WORKLOAD, "metric": "path-traced samples/s", "unit": "Msamples/s",
                                "value": pt["value"], "e2e_value": pt["value"], "cpu_baseline": pt}
+    if args.c5_spp > 0:
+        c5 = oracle_samples_per_s(pkg, 8.0, "c5-many-point-lights")
+        line["path_tracer_c5"] = {"workload": "c5-many-point-lights", "metric": "path-traced samples/s", "unit": "Msamples/s",
+                                  "value": c5["value"], "e2e_value": c5["value"], "cpu_baseline": c5}
     print(json.dumps(line), flush=True)
 
 
@@ -336,6 +349,18 @@ def run_ours(args, rank, world, local_rank):
     # ---- second headline metric: path-traced samples/s (all ranks take part) ----
     pt = bench_path_tracer(pkg, local_rank, rank, world, args.pt_iterations, 2) if args.pt_iterations > 0 else None
 
+    # ---- BASELINE.json configs[4]: many_point_lights at 3840x2160, a FIXED number of samples per pixel split across
+    # the ranks by iteration index (strong scaling); rank r renders iterations [r*K, (r+1)*K) (+ the remainder on the last)
+    c5 = None
+    if args.c5_spp > 0:
+        _, _, _, _, c5_spi = load_pt_workload(pkg, "c5-many-point-lights")
+        total_it = max(world, args.c5_spp // c5_spi)
+        per = total_it // world
+        mine = per + (total_it - per * world if rank == world - 1 else 0)
+        c5 = bench_path_tracer(pkg, local_rank, rank, world, mine, 2, "c5-many-point-lights", first=rank * per)
+        c5["scaling"] = "strong"
+        c5["spp"] = int(c5["iterations"] * c5["spi"])
+
     if rank == 0:
         # ---- algorithmic bytes per ray: visit counts from a counting pass over a 2 Mi-ray sample (untimed) ----
         sdev = pkg.Device(local_rank, acquire_stats=True)
@@ -376,6 +401,10 @@ def run_ours(args, rank, world, local_rank):
             pt["cpu_baseline"] = oracle_samples_per_s(pkg) if world == 1 else None
             line["path_tracer"] = pt
             line["gpu_launches"] += pt["gpu_launches"]
+        if c5 is not None:
+            c5["cpu_baseline"] = oracle_samples_per_s(pkg, 8.0, "c5-many-point-lights") if world == 1 else None
+            line["path_tracer_c5"] = c5
+            line["gpu_launches"] += c5["gpu_launches"]
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -390,6 +419,8 @@ def main():
     ap.add_argument("--cpu-rays", type=int, default=4_000_000)
     ap.add_argument("--pt-iterations", type=int, default=64,
                     help="path-traced iterations per GPU; 64 x spi 4 = the 256 spp of BASELINE.json configs[3] (0 disables the leg)")
+    ap.add_argument("--c5-spp", type=int, default=1024,
+                    help="samples per pixel of the many_point_lights leg (BASELINE.json configs[4]: 1024), split across ranks; 0 disables")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

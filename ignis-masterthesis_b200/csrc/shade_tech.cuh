@@ -128,7 +128,9 @@ struct Cdf2 {
 __device__ __forceinline__ Vec3 switch_env_up(Vec3 v) { return Vec3{ v.x, v.z, v.y }; }
 __device__ __forceinline__ void map_env_uv(Vec3 dir, float& u, float& v)
 {
-    const float theta = acosf(dir.z);
+    // acos argument clamped: a direction whose length rounds to 1 + 1 ulp gives acos(1.0000001) = NaN in the reference
+    // (core/warp.art:45) and poisons the pixel for good; this is the only deviation, and only where that NaN would be
+    const float theta = acosf(clampf(dir.z, -1.0f, 1.0f));
     float       phi   = atan2f(dir.y, dir.x);
     if (phi < 0.0f) phi += 2.0f * flt_pi;
     u = fractf(phi / (2.0f * flt_pi) + 0.25f);

@@ -4,6 +4,7 @@
 #include "shade_tech.cuh"
 
 #include <algorithm>
+#include <cstdio>
 
 namespace igb {
 namespace {
@@ -339,6 +340,11 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
                     col               = cadd(col, handle_color(tech, cmulf(cmul(contrib0, env_emission<EXT>(sc, l, dir)), mis)));
                 }
             }
+#ifdef IGB_DEBUG_NAN
+            if (!isfinite(col.r + col.g + col.b))
+                printf("NAN miss px %u depth %d contrib %g %g %g inv_pdf %g dir %g %g %g\n", pixel, depth, contrib0.r, contrib0.g, contrib0.b,
+                       inv_pdf, dir.x, dir.y, dir.z);
+#endif
             if (inflights > 0) splat(film, pixel, col, set.inv_spi);
         }
         return;
@@ -413,6 +419,12 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
                 sh.org_tmin   = make_float4(surf.point.x, surf.point.y, surf.point.z, offset);
                 sh.dir_tmax   = make_float4(dd.x, dd.y, dd.z, 1.0f - offset);
             }
+#ifdef IGB_DEBUG_NAN
+            if (!isfinite(c.r + c.g + c.b))
+                printf("NAN nee px %u depth %d contrib0 %g %g %g ls.int %g %g %g pdf_l_s %g lspdf %g mis %g eval %g bsdfpdf %g type %u au %g\n", pixel,
+                       depth, contrib0.r, contrib0.g, contrib0.b, ls.intensity.r, ls.intensity.g, ls.intensity.b, pdf_l_s, ls.pdf.value, mis,
+                       bsdf.eval(ls.dir, out_dir).r, bsdf.pdf(ls.dir, out_dir), bsdf.d.type, bsdf.au());
+#endif
             sh.color_pixel = make_float4(c.r, c.g, c.b, __uint_as_float(pixel));
         }
     }
@@ -421,6 +433,12 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
     if (depth + 1 > tech.max_depth) return;
     BsdfSample ms;
     if (!bsdf.sample(rnd, out_dir, ms)) return;
+#ifdef IGB_DEBUG_NAN
+    if (!isfinite(ms.col.r + ms.col.g + ms.col.b + ms.pdf + ms.in_dir.x + ms.in_dir.y + ms.in_dir.z))
+        printf("NAN sample px %u depth %d col %g %g %g pdf %g in %g %g %g out %g %g %g n %g %g %g type %u\n", pixel, depth, ms.col.r, ms.col.g,
+               ms.col.b, ms.pdf, ms.in_dir.x, ms.in_dir.y, ms.in_dir.z, out_dir.x, out_dir.y, out_dir.z, bsdf.local.c2.x, bsdf.local.c2.y,
+               bsdf.local.c2.z, bsdf.d.type);
+#endif
     const Color      contrib = cmul(contrib0, ms.col);
     const float      eta0    = meta.w;
     float            rr_prob = 1.0f;

@@ -779,7 +779,9 @@ static inline Cdf2 load_cdf2(const igb200_shading& sh, uint32_t off4)
 static inline V3 switch_env_up(V3 v) { return v3(v.x, v.z, v.y); }
 static inline void map_env_uv(V3 dir, float& u, float& v)
 {
-    const float theta = acosf(dir.z);
+    // acos argument clamped: |dir.z| can round to 1 + 1 ulp, for which the reference's acos (core/warp.art:45) is NaN;
+    // the CUDA path clamps the same way (note 3)
+    const float theta = acosf(clampf(dir.z, -1, 1));
     float       phi   = atan2f(dir.y, dir.x);
     if (phi < 0) phi += 2 * flt_pi;
     u = Tex::fract(phi / (2 * flt_pi) + 0.25f);
