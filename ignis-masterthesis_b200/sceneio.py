@@ -706,6 +706,42 @@ def bake_sky(light, hosek_lib):
     return np.ascontiguousarray(img)
 
 
+def bake_image_texture(px, opaque, filt, wrap, width, height):
+    """bake_texture2d (src/artic/entrypoints/bake.art): the texture at uv = (x / (w - 1), y / (h - 1)); the loader
+    bakes environment radiance at >= 1024 x 512 before building its CDF (EnvironmentLight.cpp:37-41,
+    ShadingTree.h:78-85).  Nearest and bilinear lookups of packed RGBA8 images with identity transform only."""
+    F = np.float32
+    ih, iw = px.shape
+    rgba = np.stack([(px >> s) & 255 for s in (0, 8, 16, 24)], axis=-1).astype(F) / F(255)
+    if opaque:
+        rgba[:, :, 3] = 1
+
+    def border(mode, x, n):
+        if mode == 2:
+            return np.clip(x, 0, n - 1)
+        if mode == 1:
+            t = np.where(x < 0, -1 - x, x)
+            i, k = t // n, t % n
+            return np.where(i % 2 == 0, n - 1 - k, k)
+        return np.mod(x, n)
+
+    u = (np.arange(width, dtype=F) / F(width - 1))[None, :].repeat(height, 0)
+    v = (np.arange(height, dtype=F) / F(height - 1))[:, None].repeat(width, 1)
+    if filt == 0:
+        ix = border(wrap[0], np.floor(u * F(iw)).astype(np.int64), iw)
+        iy = border(wrap[1], np.floor(v * F(ih)).astype(np.int64), ih)
+        return rgba[iy, ix]
+    if filt == 1:
+        fu, fv = u * F(iw) - F(0.5), v * F(ih) - F(0.5)
+        x0, y0 = np.floor(fu).astype(np.int64), np.floor(fv).astype(np.int64)
+        fx, fy = (fu - np.floor(fu))[..., None], (fv - np.floor(fv))[..., None]
+        g = lambda xx, yy: rgba[border(wrap[1], yy, ih), border(wrap[0], xx, iw)]
+        a = (1 - fx) * g(x0, y0) + fx * g(x0 + 1, y0)
+        b = (1 - fx) * g(x0, y0 + 1) + fx * g(x0 + 1, y0 + 1)
+        return ((1 - fy) * a + fy * b).astype(F)
+    raise ValueError("baking bicubic textures is outside the supported subset")
+
+
 _CONDUCTORS = {"none": ((0.0, 0.0, 0.0), (1.0, 1.0, 1.0))}  # runtime/bsdf/BSDF.cpp:12-42 (named metals: not restated)
 
 
@@ -895,9 +931,22 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
         elif ty in ("directional", "direction", "distant"):
             sh.add_directional_light(l.get("direction", (0, 0, 1)), _color(l.get("irradiance"), 1.0))
         elif ty in ("env", "envmap", "uniform", "constant"):
-            if isinstance(l.get("radiance"), str):
-                raise ValueError("textured environment lights are outside the supported subset")
-            sh.add_env_light(_color(l.get("radiance"), 1.0), _color(l.get("scale"), 1.0))
+            if isinstance(l.get("radiance"), str) and l["radiance"] in tex_ids:  # EnvironmentLight.cpp:27-76
+                tid = tex_ids[l["radiance"]]
+                t = sh.textures[tid]
+                te = next(e for e in scene["textures"] if e["name"] == l["radiance"])
+                cdf = None
+                if l.get("cdf", True) and t.type == 1 and t.format == 0 and "transform" not in te:
+                    px = np.frombuffer(bytes(sh.blob[t.offset:t.offset + 4 * t.width * t.height]), np.uint32).reshape(t.height, t.width)
+                    baked = bake_image_texture(px, bool(t.opaque), t.filter, (t.wrap_u, t.wrap_v), max(1024, t.width), max(512, t.height))
+                    cdf = sh.add_cdf2d(*compute_cdf2d(baked, True, l.get("compensate", True)))
+                m3 = parse_transform(l.get("transform"))[:3, :3]
+                sh.add_env_textured(tid, _color(l.get("scale"), 1.0), cdf, np.linalg.inv(m3.T))
+            elif isinstance(l.get("radiance"), str):
+                c = _color(l["radiance"], 1.0)  # constant expression
+                sh.add_env_light(c, _color(l.get("scale"), 1.0))
+            else:
+                sh.add_env_light(_color(l.get("radiance"), 1.0), _color(l.get("scale"), 1.0))
         elif ty == "sky":  # runtime/light/SkyLight.cpp:52-77
             if hosek_lib is None:
                 raise ValueError("sky lights need the reference's Hosek model (oracle/_ref/libhosek.so, build container only)")

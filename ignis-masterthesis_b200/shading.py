@@ -21,6 +21,7 @@ SELECTOR_UNIFORM, SELECTOR_HIERARCHY = 0, 1
 NO_CDF = 0xFFFFFFFF
 TECH_PATH, TECH_DEBUG = 0, 1
 TECHFLAG_ONE_SIDED_DIFFUSE = 1
+LIGHTFLAG_SCALED_NEE = 1
 
 
 class Camera(C.Structure):
@@ -50,7 +51,7 @@ class Material(C.Structure):
 
 class Light(C.Structure):
     _fields_ = [("type", C.c_uint32), ("entity", C.c_int32), ("color", C.c_float * 3), ("v", C.c_float * 16),
-                ("tex", C.c_uint32), ("cdf", C.c_uint32), ("_pad", C.c_uint32)]
+                ("tex", C.c_uint32), ("cdf", C.c_uint32), ("flags", C.c_uint32)]
 
 
 class Technique(C.Structure):
@@ -302,12 +303,14 @@ class Shading:
         c = (np.repeat(r, 3) if r.size == 1 else r) * (np.repeat(s, 3) if s.size == 1 else s)
         return self._light(self.infinite, LIGHT_ENV, c, (1, 0, 0, 0, 1, 0, 0, 0, 1))
 
-    def add_env_textured(self, texture, scale=(1, 1, 1), cdf=None, transform=None):
-        """transform: 3x3 (the loader passes transform.linear().transpose().inverse(), EnvironmentLight.cpp:44)."""
+    def add_env_textured(self, texture, scale=(1, 1, 1), cdf=None, transform=None, scaled_nee=False):
+        """transform: 3x3 (the loader passes transform.linear().transpose().inverse(), EnvironmentLight.cpp:44).
+        scaled_nee sets IGB200_LIGHTFLAG_SCALED_NEE (the reference omits the scale in sample_direct, light/env.art:139)."""
         m = np.eye(3, dtype=np.float32) if transform is None else np.asarray(transform, np.float32).reshape(3, 3)
         i = self._light(self.infinite, LIGHT_ENV_TEXTURED, scale, tuple(m.T.reshape(-1)))
         self.infinite[i].tex = texture
         self.infinite[i].cdf = NO_CDF if cdf is None else cdf
+        self.infinite[i].flags = LIGHTFLAG_SCALED_NEE if scaled_nee else 0
         return i
 
     def add_area_light(self, entity, radiance, plane=None):

@@ -245,6 +245,11 @@ typedef struct igb200_material {
                                       cdf, transform = v[0..8] column major) when cdf != IGB200_NO_CDF, else
                                       make_environment_light(scene_bbox, scale, tex, transform)   light/env.art:112-166 */
 #define IGB200_NO_CDF 0xFFFFFFFFu
+/* make_environment_light_textured::sample_direct returns the UNSCALED texture radiance (light/env.art:138-139 uses
+ * `intensity` where emission, :150, uses scale * tex), so next event estimation under-weights a scaled environment map;
+ * the reference's own Mitsuba golden for this light (scenes/evaluation/env.json, scale 100, ref-env-4096.exr) only holds
+ * with the scale applied.  This light flag applies it; 0 restates the reference's code as written. */
+#define IGB200_LIGHTFLAG_SCALED_NEE 0x1u
 typedef struct igb200_light {
     uint32_t type;
     int32_t  entity; /* area lights: the emissive entity id */
@@ -254,7 +259,7 @@ typedef struct igb200_light {
     uint32_t cdf;    /* ENV_TEXTURED: offset of the 2-D CDF in igb200_shading::blob in units of 4 bytes: u32 size_x,
                         size_y, 0, 0, then size_y marginal floats and size_y rows of size_x conditional floats, each
                         without the leading 0 (cdf::make_cdf_2d_from_buffer, core/cdf.art:70-72,156-160) */
-    uint32_t _pad;
+    uint32_t flags;  /* IGB200_LIGHTFLAG_*; 0 = the reference's behaviour */
 } igb200_light; /* 96 bytes */
 
 #define IGB200_TECH_PATH  0u /* make_path_renderer (src/artic/technique/pathtracer.art:40-218) */

@@ -873,7 +873,8 @@ static DirectSample light_sample_direct(const Ctx& c, const igb200_light& l, Rnd
         float       py, px, p1, p2;
         cdf.marginal().sample_continuous(u1, oy, py, p1);
         cdf.conditional(oy).sample_continuous(u0, ox, px, p2);
-        const Color in    = Tex{ c.sh }.eval(l.tex, px, py);
+        Color       in    = Tex{ c.sh }.eval(l.tex, px, py);
+        if (l.flags & IGB200_LIGHTFLAG_SCALED_NEE) in = cmul(light_color(l), in);
         const float theta = (1 - py) * flt_pi, phi = (px - 0.25f) * 2 * flt_pi;
         const float st = sinf(theta), ct = cosf(theta);
         const V3    dir = v3(st * cosf(phi), st * sinf(phi), ct); // dir_from_spherical
@@ -1015,6 +1016,9 @@ struct Film {
     float    inv_spi;
     void splat(int32_t pixel, Color c) const // make_standard_accumulator, driver/accumulator.art:23-30
     {
+        // non-finite contributions (0 * inf in the reference's MIS weights) are dropped, as in the CUDA path:
+        // DESIGN.md section 4.1, note 6
+        if (!std::isfinite(c.r + c.g + c.b)) return;
         px[3 * (size_t)pixel + 0] += c.r * inv_spi;
         px[3 * (size_t)pixel + 1] += c.g * inv_spi;
         px[3 * (size_t)pixel + 2] += c.b * inv_spi;

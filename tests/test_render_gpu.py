@@ -83,6 +83,23 @@ def test_reference_scenes_match_oracle(ig, oracle, dev, name, w, h):
     _assert_parity(film, ref, stats, osc.ray_stats.astype(np.int64))
 
 
+@pytest.mark.parametrize("scaled_nee", [False, True])
+def test_textured_environment_matches_oracle_and_closed_form(ig, oracle, dev, scaled_nee):
+    # scenes/evaluation/env.json: one lit texel, nearest filter, compensated 2-D CDF from the 1024 x 512 bake
+    tables, sh, w, h, _ = load_golden(ig, "env")
+    sh.infinite[0].flags = ig.shading.LIGHTFLAG_SCALED_NEE if scaled_nee else 0
+    film, stats = _render(dev, tables, sh, w, h, 4, 2, seed=11)
+    osc = oracle.OracleScene(tables)
+    ref = osc.render(sh, w, h, spi=4, iterations=2, seed=11)
+    _assert_parity(film, ref, stats, osc.ray_stats.astype(np.int64))
+    if scaled_nee:  # tests/test_shading_ext.py::_env_floor_radiance at 4096 spp
+        film, _ = _render(dev, tables, sh, w, h, 64, 64, seed=3)
+        t1, t2, dphi = 13 / 50 * np.pi, 14 / 50 * np.pi, 2 * np.pi / 100
+        want = np.array([0.885809, 0.698859, 0.666422]) / np.pi * 100 * dphi * (np.sin(t2) ** 2 - np.sin(t1) ** 2) / 2
+        assert np.all(np.isfinite(film))
+        assert np.allclose(film[205:245, 60:196].reshape(-1, 3).mean(axis=0) / 64, want, rtol=1e-2)
+
+
 @pytest.mark.parametrize("light,one_sided,expected,tol", [
     ("none", False, 0.0, 0.0),
     ("point", False, 0.005100456, 1e-4),   # src/tests/integrator/test_lights.py:13-24 at its own size and tolerance

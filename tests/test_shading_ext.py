@@ -106,6 +106,41 @@ def test_multilight_golden(ig, oracle, name):
     assert eval_error(film / 4, ref) < 3e-4
 
 
+def _env_floor_radiance():
+    # scenes/evaluation/env.json: a 100 x 50 map, one white texel (row 13 from the top, nearest filter), scale 100, over a
+    # diffuse floor.  L_o = kd / pi * scale * integral of cos over the texel = kd / pi * scale * dphi * (sin^2 t2 - sin^2 t1) / 2
+    t1, t2, dphi = 13 / 50 * np.pi, 14 / 50 * np.pi, 2 * np.pi / 100
+    return np.array([0.885809, 0.698859, 0.666422]) / np.pi * 100 * dphi * (np.sin(t2) ** 2 - np.sin(t1) ** 2) / 2
+
+
+def test_textured_environment_against_the_closed_form(ig, oracle):
+    """The CDF-sampled environment (light/env.art:112-157) on the reference's env.json: with the scale applied in next
+    event estimation the floor radiance is the closed form; as written (no scale, :139) NEE carries 1/100 of it and the
+    MIS weight of the BSDF-sampled hits stays below the texel's tiny share.  No sample may be NaN (0 * inf in the MIS
+    weight on a miss through a zero-mass CDF cell)."""
+    tables, sh, w, h, mitsuba = load_golden(ig, "env")
+    S = ig.shading
+    env = sh.infinite[0]
+    assert env.type == S.LIGHT_ENV_TEXTURED and env.cdf != S.NO_CDF and env.flags == 0 and tuple(env.color) == (100, 100, 100)
+    assert (sh.textures[env.tex].width, sh.textures[env.tex].height, sh.textures[env.tex].filter) == (100, 50, S.FILTER_NEAREST)
+    osc = oracle.OracleScene(tables)
+    want = _env_floor_radiance()
+    floor = lambda f: f[205:245, 60:196].reshape(-1, 3).mean(axis=0)
+    as_written = osc.render(sh, w, h, spi=64, iterations=4, seed=1) / 4
+    assert np.all(np.isfinite(as_written))
+    med = np.median(as_written[205:245, 60:196].reshape(-1, 3), axis=0)   # the rare BSDF-sampled hits are fireflies
+    assert np.allclose(med, 0.01 * want, rtol=0.1) and np.all(floor(as_written) < 0.1 * want)
+    env.flags = S.LIGHTFLAG_SCALED_NEE
+    scaled = osc.render(sh, w, h, spi=64, iterations=4, seed=1) / 4
+    assert np.all(np.isfinite(scaled))
+    # the 1024 x 512 CDF cells do not line up with the 100 x 50 texels: ~2 % of the texel has density 0 after compensation
+    # and arrives through BSDF-sampled hits (MIS weight 1) as rare bright samples
+    assert np.allclose(floor(scaled), want, rtol=3e-2)
+    assert np.allclose(np.median(scaled[205:245, 60:196].reshape(-1, 3), axis=0), 0.977 * want, rtol=1e-2)
+    # the shipped Mitsuba image is not a pin for either variant: it sits 2.16x below the closed form (DESIGN.md 4.1, note 5)
+    assert np.allclose(floor(mitsuba) * 2.16, want, rtol=2e-2)
+
+
 def test_features_scene_renders_and_both_selectors_agree(ig, oracle):
     # the hierarchy only changes the sampling density: the expectation must not move
     tables, sh = features_scene(ig, 64)
