@@ -26,6 +26,8 @@ ABI_SYMBOLS = [
     "igb200_render_iterations",
     "igb200_framebuffer",
     "igb200_clear_framebuffer",
+    "igb200_clear_aov",
+    "igb200_tonemap",
     "igb200_resize",
     "igb200_set_framebuffer",
     "igb200_get_render_stats",
@@ -117,6 +119,8 @@ def load():
     lib.igb200_render_iterations.argtypes = [vp, vp, u32]
     lib.igb200_framebuffer.argtypes = [vp, C.c_char_p, i32, C.POINTER(vp), C.POINTER(u64)]
     lib.igb200_clear_framebuffer.argtypes = [vp]
+    lib.igb200_clear_aov.argtypes = [vp, C.c_char_p]
+    lib.igb200_tonemap.argtypes = [vp, vp, vp]
     lib.igb200_resize.argtypes = [vp, u32, u32]
     lib.igb200_set_framebuffer.argtypes = [vp, vp, u64, u64]
     lib.igb200_get_render_stats.argtypes = [vp, vp]

@@ -133,7 +133,21 @@ struct igb200_device {
     uint64_t                      iterations = 0;
     bool                          film_mapped = false; // host copy is current
     igb200_render_stats           render_stats{};
+
+    // Named AOV images next to the film (Interface::aovs, Device.cpp:95-100,1300-1307): allocated at film size the first
+    // time a technique that enables them renders, each with its own iteration count (markAOVAsUsed / present,
+    // Device.cpp:1389-1403,1468-1471).
+    struct Aov {
+        DeviceBuffer<float> d;
+        float*              h = nullptr; // pinned host copy, lazily filled
+        uint64_t            iterations = 0;
+        bool                mapped = false;
+    };
+    static constexpr int kAovCount = 5;
+    Aov                  aov[kAovCount];
+    DeviceBuffer<uint32_t> d_tonemap;
 };
+static const char* const kAovNames[igb200_device::kAovCount] = { "Direct Weights", "NEE Weights", "Normals", "Albedo", "Depth" };
 
 extern "C" {
 
@@ -196,6 +210,8 @@ void igb200_destroy(igb200_device* dev)
     if (dev->round_graph) cudaGraphExecDestroy(dev->round_graph);
     if (dev->h_done) cudaFreeHost(dev->h_done);
     if (dev->h_film) cudaFreeHost(dev->h_film);
+    for (auto& a : dev->aov)
+        if (a.h) cudaFreeHost(a.h);
     delete dev; // DeviceBuffer destructors free the allocations (Device::releaseAll, Device.cpp:948-952)
 }
 
@@ -556,7 +572,7 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
                 return fail(IGB200_E_INVALID, "area light %llu: entity %d out of range", (unsigned long long)i, ls[i].entity);
         }
     }
-    if (sh->technique.type > IGB200_TECH_DEBUG) return fail(IGB200_E_UNSUPPORTED, "unknown technique %u", sh->technique.type);
+    if (sh->technique.type > IGB200_TECH_INFOBUFFER) return fail(IGB200_E_UNSUPPORTED, "unknown technique %u", sh->technique.type);
     if (sh->technique.max_depth > 254) // the stream keeps the depth in 8 bits (reference default: 64, PathTechnique.cpp)
         return fail(IGB200_E_UNSUPPORTED, "technique.max_depth %d exceeds 254", sh->technique.max_depth);
     IGB_CUDA(cudaSetDevice(dev->ordinal));
@@ -618,7 +634,34 @@ static int ensure_film(igb200_device* dev, uint32_t w, uint32_t h)
     dev->film_w = w; dev->film_h = h;
     dev->iterations  = 0;
     dev->film_mapped = false;
+    for (auto& a : dev->aov) { // AOVs follow the film size (Device.cpp:306-321): dropped here, re-created on use
+        a.d.release();
+        if (a.h) { cudaFreeHost(a.h); a.h = nullptr; }
+        a.iterations = 0;
+        a.mapped     = false;
+    }
     return IGB200_OK;
+}
+
+static int ensure_aov(igb200_device* dev, int k)
+{
+    igb200_device::Aov& a = dev->aov[k];
+    if (a.d.ptr) return IGB200_OK;
+    const size_t n = (size_t)dev->film_w * dev->film_h * 3;
+    IGB_CUDA(a.d.ensure(n));
+    IGB_CUDA(cudaMemsetAsync(a.d.ptr, 0, n * sizeof(float), dev->stream));
+    a.iterations = 0;
+    a.mapped     = false;
+    return IGB200_OK;
+}
+
+// index into igb200_device::aov, or -1 for the film, or -2 if the name is not an AOV
+static int find_image(const char* name)
+{
+    if (!name || name[0] == '\0' || std::strcmp(name, "Color") == 0) return -1;
+    for (int k = 0; k < igb200_device::kAovCount; ++k)
+        if (std::strcmp(name, kAovNames[k]) == 0) return k;
+    return -2;
 }
 
 static int ensure_wave(igb200_device* dev)
@@ -695,6 +738,21 @@ static int render_batch(igb200_device* dev, const igb200_render_settings* rs, ui
         set.list_rays = dev->d_list_rays.ptr;
     }
     set.film = dev->d_film.ptr;
+    // the technique's AOVs (TechniqueInfo::EnabledAOVs: PathTechnique.cpp:23-27, InfoBufferTechnique.cpp:30-33)
+    const igb200_technique& tech = dev->shade.tech;
+    const bool infobuffer = tech.type == IGB200_TECH_INFOBUFFER;
+    int        used[3]    = { -1, -1, -1 };
+    if (infobuffer) {
+        used[0] = 2; used[1] = 3; used[2] = 4;
+    } else if (tech.type == IGB200_TECH_PATH && (tech.flags & IGB200_TECHFLAG_AOV_MIS)) {
+        used[0] = 0; used[1] = 1;
+    }
+    for (int k = 0; k < 3; ++k) {
+        set.aov[k] = nullptr;
+        if (used[k] < 0) continue;
+        if (int rc = ensure_aov(dev, used[k])) return rc;
+        set.aov[k] = dev->aov[used[k]].d.ptr;
+    }
     dev->wave.ent_mat = dev->d_ent_mat.ptr;
 
     IGB_CUDA(cudaEventRecord(dev->ev0, st));
@@ -738,8 +796,16 @@ static int render_batch(igb200_device* dev, const igb200_render_settings* rs, ui
     float ms = 0.0f;
     cudaEventElapsedTime(&ms, dev->ev0, dev->ev1);
     dev->render_stats.device_ms = ms;
-    dev->iterations += count; // Interface::present, Device.cpp:1460-1472
-    dev->film_mapped = false;
+    // Interface::present, Device.cpp:1460-1472: the film counts unless the technique locks it, every used AOV counts
+    if (!infobuffer) {
+        dev->iterations += count;
+        dev->film_mapped = false;
+    }
+    for (int k = 0; k < 3; ++k)
+        if (used[k] >= 0) {
+            dev->aov[used[k]].iterations += count;
+            dev->aov[used[k]].mapped = false;
+        }
     return IGB200_OK;
 }
 
@@ -755,10 +821,28 @@ int igb200_framebuffer(igb200_device* dev, const char* name, int device, float**
     if (!dev || !data) return fail(IGB200_E_INVALID, "igb200_framebuffer: NULL argument");
     *data = nullptr;
     if (iterations) *iterations = 0;
-    if (name && name[0] != '\0' && std::strcmp(name, "Color") != 0)
+    const int img = find_image(name);
+    if (img == -2 || (img >= 0 && !dev->aov[img].d.ptr))
         return fail(IGB200_E_INVALID, "igb200_framebuffer: unknown AOV '%s'", name); // Device.cpp:1303-1305
     if (!dev->d_film.ptr) return fail(IGB200_E_STATE, "igb200_framebuffer: nothing rendered yet");
     IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (img >= 0) {
+        igb200_device::Aov& a = dev->aov[img];
+        if (iterations) *iterations = a.iterations;
+        if (device) {
+            *data = a.d.ptr;
+            return IGB200_OK;
+        }
+        const size_t bytes = (size_t)dev->film_w * dev->film_h * 3 * sizeof(float);
+        if (!a.h) IGB_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&a.h), std::max<size_t>(bytes, 4), cudaHostAllocDefault));
+        if (!a.mapped) {
+            IGB_CUDA(cudaMemcpyAsync(a.h, a.d.ptr, bytes, cudaMemcpyDeviceToHost, dev->stream));
+            IGB_CUDA(cudaStreamSynchronize(dev->stream));
+            a.mapped = true;
+        }
+        *data = a.h;
+        return IGB200_OK;
+    }
     if (iterations) *iterations = dev->iterations;
     if (device) {
         *data = dev->d_film.ptr;
@@ -774,16 +858,63 @@ int igb200_framebuffer(igb200_device* dev, const char* name, int device, float**
     return IGB200_OK;
 }
 
+static int clear_image(igb200_device* dev, int img)
+{
+    const size_t bytes = (size_t)dev->film_w * dev->film_h * 3 * sizeof(float);
+    if (img < 0) {
+        if (dev->d_film.ptr) IGB_CUDA(cudaMemsetAsync(dev->d_film.ptr, 0, bytes, dev->stream));
+        dev->iterations  = 0;
+        dev->film_mapped = false;
+    } else {
+        igb200_device::Aov& a = dev->aov[img];
+        if (a.d.ptr) IGB_CUDA(cudaMemsetAsync(a.d.ptr, 0, bytes, dev->stream));
+        a.iterations = 0;
+        a.mapped     = false;
+    }
+    return IGB200_OK;
+}
+
 int igb200_clear_framebuffer(igb200_device* dev)
 {
     if (!dev) return fail(IGB200_E_INVALID, "igb200_clear_framebuffer: NULL device");
     IGB_CUDA(cudaSetDevice(dev->ordinal));
-    if (dev->d_film.ptr) {
-        IGB_CUDA(cudaMemsetAsync(dev->d_film.ptr, 0, (size_t)dev->film_w * dev->film_h * 3 * sizeof(float), dev->stream));
-        IGB_CUDA(cudaStreamSynchronize(dev->stream));
-    }
-    dev->iterations  = 0;
-    dev->film_mapped = false;
+    for (int img = -1; img < igb200_device::kAovCount; ++img) // clearAllAOVs, Device.cpp:1406-1411
+        if (int rc = clear_image(dev, img)) return rc;
+    IGB_CUDA(cudaStreamSynchronize(dev->stream));
+    return IGB200_OK;
+}
+
+int igb200_clear_aov(igb200_device* dev, const char* name)
+{
+    if (!dev) return fail(IGB200_E_INVALID, "igb200_clear_aov: NULL device");
+    const int img = find_image(name);
+    if (img == -2 || (img >= 0 && !dev->aov[img].d.ptr)) return fail(IGB200_E_INVALID, "igb200_clear_aov: unknown AOV '%s'", name);
+    IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (int rc = clear_image(dev, img)) return rc;
+    IGB_CUDA(cudaStreamSynchronize(dev->stream));
+    return IGB200_OK;
+}
+
+int igb200_tonemap(igb200_device* dev, const igb200_tonemap_settings* ts, uint32_t* out_pixels)
+{
+    if (!dev || !ts || !out_pixels) return fail(IGB200_E_INVALID, "igb200_tonemap: NULL argument");
+    const int img = find_image(ts->aov);
+    if (img == -2 || (img >= 0 && !dev->aov[img].d.ptr)) return fail(IGB200_E_INVALID, "igb200_tonemap: unknown AOV '%s'", ts->aov);
+    if (!dev->d_film.ptr) return fail(IGB200_E_STATE, "igb200_tonemap: nothing rendered yet");
+    IGB_CUDA(cudaSetDevice(dev->ordinal));
+    const uint64_t n     = (uint64_t)dev->film_w * dev->film_h;
+    const uint64_t iters = img < 0 ? dev->iterations : dev->aov[img].iterations;
+    const float*   in    = img < 0 ? dev->d_film.ptr : dev->aov[img].d.ptr;
+    igb::TonemapParams p{};
+    p.method          = ts->method;
+    p.use_gamma       = ts->use_gamma;
+    p.scale           = ts->scale * (iters > 0 ? 1.0f / (float)iters : 0.0f); // Device.cpp:1668,1677
+    p.exposure_factor = ts->exposure_factor;
+    p.exposure_offset = ts->exposure_offset;
+    IGB_CUDA(dev->d_tonemap.ensure(n));
+    IGB_CUDA(igb::launch_tonemap(in, dev->d_tonemap.ptr, n, p, dev->stream));
+    IGB_CUDA(cudaMemcpyAsync(out_pixels, dev->d_tonemap.ptr, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, dev->stream));
+    IGB_CUDA(cudaStreamSynchronize(dev->stream));
     return IGB200_OK;
 }
 

@@ -109,6 +109,12 @@ struct ShadowIO {
             atomicAdd(p + 0, c.x * inv_spi);
             atomicAdd(p + 1, c.y * inv_spi);
             atomicAdd(p + 2, c.z * inv_spi);
+            if (float* a = ctl->set.aov[1]) { // on_shadow_miss: aov_nee (pathtracer.art:202-208)
+                a += 3 * (size_t)__float_as_uint(c.w);
+                atomicAdd(a + 0, c.x * inv_spi);
+                atomicAdd(a + 1, c.y * inv_spi);
+                atomicAdd(a + 2, c.z * inv_spi);
+            }
         }
     }
 };
@@ -316,7 +322,7 @@ __device__ __forceinline__ void splat(float* film, uint32_t pixel, Color c, floa
     atomicAdd(p + 2, c.b * inv_spi);
 }
 
-template <bool EXT>
+template <bool EXT, bool IB>
 __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScene& geo, const WaveSettings& set, const PathStream& cur,
                                        uint32_t i, float* film, bool& alive, NextState& nx, bool& has_shadow, ShadowState& sh)
 {
@@ -351,7 +357,10 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
                 printf("NAN miss px %u depth %d contrib %g %g %g inv_pdf %g dir %g %g %g\n", pixel, depth, contrib0.r, contrib0.g, contrib0.b,
                        inv_pdf, dir.x, dir.y, dir.z);
 #endif
-            if (inflights > 0) splat(film, pixel, col, set.inv_spi);
+            if (inflights > 0) {
+                splat(film, pixel, col, set.inv_spi);
+                if (set.aov[0]) splat(set.aov[0], pixel, col, set.inv_spi); // aov_di, pathtracer.art:158
+            }
         }
         return;
     }
@@ -366,6 +375,39 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
         surf = trimesh_surface_element(load_trimesh(sc, e.shape_id()), e, org, dir, t, u, v, prim);
     const igb200_material mat = sc.materials[e.mat_id()];
     const Bsdf<EXT> bsdf = make_bsdf<EXT>(sc, mat.bsdf, surf, dir, (tech.flags & IGB200_TECHFLAG_ONE_SIDED_DIFFUSE) != 0u);
+
+    if constexpr (IB) { // make_infobuffer_renderer, technique/infobuffer.art:28-104; the payload's distance rides in cp.w
+        const bool handle_specular = (tech.flags & IGB200_TECHFLAG_IB_HANDLE_SPECULAR) != 0u;
+        const Vec3 out_dir         = vneg(dir);
+        const bool specular        = bsdf.is_specular();
+        if (!handle_specular || !specular) { // on_hit :36-63
+            Color albedo{ 0.0f, 0.0f, 0.0f };
+            Rnd   arnd{ hash_combine(0x811C9DC5u, pixel), 1u }; // create_random_generator(hash_combine(hash_init(), pixel.linear))
+            for (int k = 0; k < 16; ++k) {
+                BsdfSample ms;
+                if (bsdf.sample(arnd, out_dir, ms)) {
+                    const float c = fabsf(dot3(ms.in_dir, surf.local.c2));
+                    albedo        = cadd(albedo, cmulf(ms.col, safe_div(ms.pdf, 16.0f * c))); // without the cosine term
+                }
+            }
+            const float d = t + (handle_specular ? inv_pdf : 0.0f);
+            splat(set.aov[0], pixel, Color{ surf.local.c2.x, surf.local.c2.y, surf.local.c2.z }, set.inv_spi);
+            splat(set.aov[1], pixel, Color{ fminf(albedo.r, 1.0f), fminf(albedo.g, 1.0f), fminf(albedo.b, 1.0f) }, set.inv_spi);
+            splat(set.aov[2], pixel, Color{ d, d, d }, set.inv_spi);
+        }
+        // on_bounce :65-91
+        if (!(handle_specular && specular) || !(depth <= tech.max_depth)) return;
+        Rnd        rnd{ __float_as_uint(meta.z), __float_as_uint(meta.y) };
+        BsdfSample ms;
+        if (!bsdf.sample(rnd, out_dir, ms)) return;
+        alive             = true;
+        nx.org_tmin       = make_float4(surf.point.x, surf.point.y, surf.point.z, offset);
+        nx.dir_tmax       = make_float4(ms.in_dir.x, ms.in_dir.y, ms.in_dir.z, flt_max);
+        nx.meta           = make_float4(meta.x, __uint_as_float(rnd.counter), meta.z, meta.w);
+        nx.contrib_invpdf = make_float4(cp.x, cp.y, cp.z, inv_pdf + t);
+        nx.flags          = (uint16_t)(kRayBounce | ((uint32_t)(depth + 1) << 8));
+        return;
+    }
 
     if (tech.type == IGB200_TECH_DEBUG) { // technique/debugtracer.art:29-177
         Color out;
@@ -399,7 +441,9 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
             const Pdf           pdf   = light_pdf_direct(sc, l, org, surf);
             const float         pdf_s = pdf.as_solid(d, t * t);
             const float         mis   = tech.enable_nee ? __fdiv_rn(1.0f, 1.0f + inv_pdf * selector_pdf<EXT>(sc, false, mat.light, org) * pdf_s) : 1.0f;
-            splat(film, pixel, handle_color(tech, cmulf(cmul(contrib0, light_color(l)), mis)), set.inv_spi);
+            const Color         c     = handle_color(tech, cmulf(cmul(contrib0, light_color(l)), mis));
+            splat(film, pixel, c, set.inv_spi);
+            if (set.aov[0]) splat(set.aov[0], pixel, c, set.inv_spi); // aov_di, pathtracer.art:128
         }
     }
 
@@ -466,7 +510,7 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
 #ifndef IGB_SHADE_MIN_BLOCKS
 #define IGB_SHADE_MIN_BLOCKS 6 // 85 registers, 80 B of spills: +2 % over 4 blocks (112 registers) on B200
 #endif
-template <bool EXT>
+template <bool EXT, bool IB>
 __global__ void __launch_bounds__(128, IGB_SHADE_MIN_BLOCKS) shade_kernel(WaveControl* __restrict__ ctl, const PathStream cur, const PathStream nxt,
                                                     const ShadowStream shq, const uint32_t* __restrict__ sorted, const ShadeScene sc,
                                                     const DeviceScene geo)
@@ -482,7 +526,7 @@ __global__ void __launch_bounds__(128, IGB_SHADE_MIN_BLOCKS) shade_kernel(WaveCo
         bool        alive = false, has_shadow = false;
         NextState   nx;
         ShadowState sh;
-        if (p < n) shade_one<EXT>(sc, geo, set, cur, sorted ? sorted[p] : p, film, alive, nx, has_shadow, sh);
+        if (p < n) shade_one<EXT, IB>(sc, geo, set, cur, sorted ? sorted[p] : p, film, alive, nx, has_shadow, sh);
 
         // stream compaction: one atomic per warp, ranks from the ballot (replaces gpu_compact_primary)
         const uint32_t am = __ballot_sync(0xFFFFFFFFu, alive);
@@ -540,10 +584,19 @@ cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene&
     const PrimaryIO pio{ cur, buf.keys, buf.ent_mat, buf.ctl, n_bins };
     trace_kernel<PrimaryIO, false, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, pio, nullptr, buf.ctl->work_primary);
     if (sort) scatter_kernel<<<wide / 2, 256, 0, stream>>>(buf.ctl, buf.keys, buf.sorted, n_bins, sort == 2 && n_bins <= kMaxSmemBins);
+    // four instantiations: {lean, extended material set} x {path / debug, infobuffer}, picked per scene and technique
+#define SHADE_LAUNCH(EXT)                                                                                                           \
+    do {                                                                                                                            \
+        if (sh.tech.type == IGB200_TECH_INFOBUFFER)                                                                                 \
+            shade_kernel<EXT, true><<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene); \
+        else                                                                                                                        \
+            shade_kernel<EXT, false><<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene); \
+    } while (0)
     if (sh.extended)
-        shade_kernel<true><<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene);
+        SHADE_LAUNCH(true);
     else
-        shade_kernel<false><<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene);
+        SHADE_LAUNCH(false);
+#undef SHADE_LAUNCH
     const ShadowIO sio{ buf.shadow, buf.ctl };
     trace_kernel<ShadowIO, true, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, sio, nullptr, buf.ctl->work_shadow);
     return cudaGetLastError();

@@ -55,6 +55,8 @@ struct WaveSettings {
     uint32_t      capacity;
     const float4* list_rays; // igtrace mode: normalised StreamRays (2 x float4 each), else nullptr
     float*        film;      // w * h * 3, RGB sums
+    float*        aov[3];    // technique AOVs, same layout, or nullptr: path + aov_mis: Direct Weights, NEE Weights;
+                             // infobuffer: Normals, Albedo, Depth
 };
 
 // Device-resident control block of one render() call.
@@ -99,6 +101,13 @@ cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene&
 cudaError_t launch_wave_reset(const WaveBuffers& buf, const WaveSettings& set, uint32_t total, cudaStream_t stream);
 
 // film[i] += src[i] (overwrite = false) or film[i] = src[i]
+// Device::tonemap (Device.cpp:1662-1687): scale already carries 1 / IterationCount
+struct TonemapParams {
+    uint32_t method;    // 0 none, 1 reinhard, 2 reinhard_modified, 3 aces, else uncharted2 (entrypoints/tonemap.art:31-37)
+    int32_t  use_gamma;
+    float    scale, exposure_factor, exposure_offset;
+};
+cudaError_t launch_tonemap(const float* in, uint32_t* out, uint64_t n, const TonemapParams& p, cudaStream_t stream);
 cudaError_t launch_film_combine(float* film, const float* src, uint64_t count, bool overwrite, cudaStream_t stream);
 
 constexpr int kWaveLaunchesPerRound = 6;

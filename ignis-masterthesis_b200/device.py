@@ -93,10 +93,10 @@ class Device:
             _lib.check(self._lib.igb200_render_iterations(self._h, C.addressof(rs), iterations))
         self._film = (rays.size, 1) if rays is not None else (width, height)
 
-    def framebuffer(self, copy=True):
-        """(film (h, w, 3) f32 of RGB SUMS over iterations, iteration count)."""
+    def framebuffer(self, copy=True, name=None):
+        """(film or AOV `name` (h, w, 3) f32 of RGB SUMS over iterations, iteration count of that image)."""
         ptr, it = C.c_void_p(), C.c_uint64()
-        _lib.check(self._lib.igb200_framebuffer(self._h, None, 0, C.byref(ptr), C.byref(it)))
+        _lib.check(self._lib.igb200_framebuffer(self._h, name.encode() if name else None, 0, C.byref(ptr), C.byref(it)))
         st = self.render_stats()
         n = st["film"][0] * st["film"][1] * 3
         arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_float)), shape=(n,)).reshape(st["film"][1], st["film"][0], 3)
@@ -110,8 +110,22 @@ class Device:
     def set_framebuffer(self, d_src, count, iterations):
         _lib.check(self._lib.igb200_set_framebuffer(self._h, d_src, count, iterations))
 
-    def clear_framebuffer(self):
-        _lib.check(self._lib.igb200_clear_framebuffer(self._h))
+    def clear_framebuffer(self, name=None):
+        """Device::clearAllFramebuffer, or Device::clearFramebuffer(name) when a name is given ("Color" = the film)."""
+        if name is None:
+            _lib.check(self._lib.igb200_clear_framebuffer(self._h))
+        else:
+            _lib.check(self._lib.igb200_clear_aov(self._h, name.encode()))
+
+    def tonemap(self, aov=None, method=0, use_gamma=True, scale=1.0, exposure_factor=1.0, exposure_offset=0.0):
+        """Device::tonemap: (h, w) u32 packed ARGB of the film or AOV divided by its iteration count."""
+        from .shading import TonemapSettings
+        ts = TonemapSettings(aov=aov.encode() if aov else None, method=method, use_gamma=1 if use_gamma else 0, scale=scale,
+                             exposure_factor=exposure_factor, exposure_offset=exposure_offset)
+        w, h = self._film
+        out = np.empty((h, w), np.uint32)
+        _lib.check(self._lib.igb200_tonemap(self._h, C.addressof(ts), out.ctypes.data))
+        return out
 
     def resize(self, width, height):
         _lib.check(self._lib.igb200_resize(self._h, width, height))

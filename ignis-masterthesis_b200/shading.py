@@ -19,8 +19,10 @@ WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = 0, 1, 2
 IMAGE_RGBA8, IMAGE_RGBA32F = 0, 1
 SELECTOR_UNIFORM, SELECTOR_HIERARCHY = 0, 1
 NO_CDF = 0xFFFFFFFF
-TECH_PATH, TECH_DEBUG = 0, 1
+TECH_PATH, TECH_DEBUG, TECH_INFOBUFFER = 0, 1, 2
 TECHFLAG_ONE_SIDED_DIFFUSE = 1
+TECHFLAG_AOV_MIS = 2
+TECHFLAG_IB_HANDLE_SPECULAR = 4
 LIGHTFLAG_SCALED_NEE = 1
 
 
@@ -72,6 +74,11 @@ class ShadingC(C.Structure):
 class RenderSettings(C.Structure):
     _fields_ = [("rays", C.c_void_p), ("ray_count", C.c_uint64), ("spi", C.c_uint32), ("width", C.c_uint32),
                 ("height", C.c_uint32), ("iteration", C.c_uint32), ("frame", C.c_uint32), ("user_seed", C.c_uint32)]
+
+
+class TonemapSettings(C.Structure):
+    _fields_ = [("aov", C.c_char_p), ("method", C.c_uint32), ("use_gamma", C.c_int32), ("scale", C.c_float),
+                ("exposure_factor", C.c_float), ("exposure_offset", C.c_float)]
 
 
 class RenderStats(C.Structure):
@@ -160,10 +167,17 @@ class Shading:
         m = np.asarray(m, np.float64).reshape(-1, 4)
         return self.set_perspective(m[:3, 3], m[:3, 2], m[:3, 1], fov_deg, width, height, near, far, vertical)
 
-    def set_path(self, max_depth=64, min_depth=2, clamp=0.0, nee=True, one_sided_diffuse=False):
+    def set_path(self, max_depth=64, min_depth=2, clamp=0.0, nee=True, one_sided_diffuse=False, aov_mis=False):
+        """PathTechnique.cpp:8-17; aov_mis adds the AOVs "Direct Weights" and "NEE Weights" (:23-27)."""
         self.technique = Technique(type=TECH_PATH, max_depth=max_depth, min_depth=min_depth, clamp=clamp,
                                    enable_nee=1 if nee else 0, debug_mode=0,
-                                   flags=TECHFLAG_ONE_SIDED_DIFFUSE if one_sided_diffuse else 0)
+                                   flags=(TECHFLAG_ONE_SIDED_DIFFUSE if one_sided_diffuse else 0) | (TECHFLAG_AOV_MIS if aov_mis else 0))
+        return self
+
+    def set_infobuffer(self, max_depth=64, handle_specular=False):
+        """InfoBufferTechnique.cpp:6-12: AOVs "Normals", "Albedo", "Depth"; the film is locked."""
+        self.technique = Technique(type=TECH_INFOBUFFER, max_depth=max_depth, min_depth=1, clamp=0.0, enable_nee=0, debug_mode=0,
+                                   flags=TECHFLAG_IB_HANDLE_SPECULAR if handle_specular else 0)
         return self
 
     def set_debug(self, mode):

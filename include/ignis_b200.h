@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define IGB200_ABI_VERSION 3
+#define IGB200_ABI_VERSION 4
 
 enum {
     IGB200_OK            = 0,
@@ -264,12 +264,23 @@ typedef struct igb200_light {
 
 #define IGB200_TECH_PATH  0u /* make_path_renderer (src/artic/technique/pathtracer.art:40-218) */
 #define IGB200_TECH_DEBUG 1u /* make_debug_renderer (src/artic/technique/debugtracer.art), mode = debug_mode */
+#define IGB200_TECH_INFOBUFFER 2u /* make_infobuffer_renderer (src/artic/technique/infobuffer.art:28-104): the denoiser's
+                                     AOVs "Normals", "Albedo", "Depth"; the film is locked (not written, iteration count
+                                     unchanged: InfoBufferTechnique.cpp:36, Device.cpp:1463-1466); max_depth =
+                                     __tech_ib_max_depth.  The reference runs it with spi 1 (OverrideSPI). */
 /* The reference's lambertian eval is kd*|cos|/pi for ANY incoming direction (bsdf/diffuse.art:3), so next event
  * estimation lets light through one-sided geometry from behind (e.g. a full-sphere environment sample below a
  * ground plane, light/env.art:82-86).  The reference's own golden values that involve this case
  * (tests/integrator/test_lights.py:37-44 expects 1.0; scenes/evaluation plane-d6 vs Mitsuba) only hold with a
  * one-sided eval kd*max(cos,0)/pi; this flag selects it.  Default (0) restates the reference's code as written. */
 #define IGB200_TECHFLAG_ONE_SIDED_DIFFUSE 0x1u
+/* PathTechnique `aov_mis` (runtime/technique/PathTechnique.cpp:16,23-27,54-57): the AOVs "Direct Weights" (every
+ * contribution a BSDF-sampled path collects: emission on hit, environment on miss; pathtracer.art:128,158) and
+ * "NEE Weights" (unoccluded next-event contributions, pathtracer.art:202-208) are accumulated next to the film. */
+#define IGB200_TECHFLAG_AOV_MIS 0x2u
+/* IGB200_TECH_INFOBUFFER: `handle_specular` -- follow specular bounces and record the first non-specular hit
+ * (runtime/technique/InfoBufferTechnique.cpp:11,77). */
+#define IGB200_TECHFLAG_IB_HANDLE_SPECULAR 0x4u
 typedef struct igb200_technique {
     uint32_t type;
     int32_t  max_depth;  /* __tech_max_depth, default 64 (runtime/technique/Technique.h:8) */
@@ -348,13 +359,31 @@ int igb200_render(igb200_device* dev, const igb200_render_settings* settings);
 int igb200_render_iterations(igb200_device* dev, const igb200_render_settings* settings, uint32_t count);
 
 /* Device::getFramebufferForHost / ForDevice (Device.h:63-64, Device.cpp:1330-1443): RGB f32, w*h*3, SUM over
- * iterations; *iterations = IterationCount.  name NULL, "" or "Color" = the film.  The pointer is owned by
+ * iterations; *iterations = IterationCount of that image.  name NULL, "" or "Color" = the film; "Direct Weights",
+ * "NEE Weights" (path with IGB200_TECHFLAG_AOV_MIS) and "Normals", "Albedo", "Depth" (IGB200_TECH_INFOBUFFER) exist
+ * once a technique that enables them has rendered; anything else is an error (Device.cpp:1303-1305).  The pointer is owned by
  * the device and valid until resize / destroy.  device != 0 returns the device pointer (no copy). */
 int igb200_framebuffer(igb200_device* dev, const char* name, int device, float** data, uint64_t* iterations);
 
-/* Device::clearAllFramebuffer / resize (Device.h:65-66, Device.cpp:306-313,1407-1443). */
+/* Device::clearAllFramebuffer / resize (Device.h:65-66, Device.cpp:306-313,1407-1443): the film and every AOV. */
 int igb200_clear_framebuffer(igb200_device* dev);
 int igb200_resize(igb200_device* dev, uint32_t width, uint32_t height);
+/* Device::clearFramebuffer(name) (Device.h:65, Device.cpp:1413-1441): one image and its iteration count. */
+int igb200_clear_aov(igb200_device* dev, const char* name);
+
+/* Device::tonemap (Device.h:70, Device.cpp:1662-1687, src/artic/entrypoints/tonemap.art): the film or an AOV, divided
+ * by its iteration count and multiplied by `scale`, to packed 8-bit ARGB (a << 24 | r << 16 | g << 8 | b), w*h
+ * words written to the HOST buffer `out_pixels`.  NaN pixels come out cyan, infinite ones pink, negative ones
+ * yellow, as in the reference.  This is the headless target for the viewer's display path. */
+typedef struct igb200_tonemap_settings {
+    const char* aov;             /* NULL, "" or "Color" = the film (RuntimeStructs.h:6-13) */
+    uint32_t    method;          /* 0 none, 1 reinhard, 2 modified reinhard, 3 ACES, 4 uncharted2 */
+    int32_t     use_gamma;       /* sRGB transfer curve on the output */
+    float       scale;
+    float       exposure_factor;
+    float       exposure_offset;
+} igb200_tonemap_settings;
+int igb200_tonemap(igb200_device* dev, const igb200_tonemap_settings* settings, uint32_t* out_pixels);
 
 /* Multi-GPU film combine: overwrites the film with `count` = w*h*3 floats from `d_src` (a device
  * pointer on this device, e.g. the result of an NCCL reduce over the per-GPU films) and sets the iteration count. */

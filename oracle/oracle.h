@@ -77,6 +77,17 @@ int igo_kat_ray_box(const float* box, const float* org, const float* dir, float 
 int igo_render(const igo_scene* scene, const igb200_shading* shading, const igb200_render_settings* settings,
                float* film, uint64_t* stats3, int threads);
 
+/* igo_render plus the technique's AOV images (each w*h*3 f32 sums, or NULL): path with IGB200_TECHFLAG_AOV_MIS adds into
+ * aov0 = "Direct Weights" and aov1 = "NEE Weights" (pathtracer.art:128,158,206); IGB200_TECH_INFOBUFFER adds into
+ * aov0..2 = "Normals", "Albedo", "Depth" (technique/infobuffer.art:28-104) and does not touch the film. */
+int igo_render_aov(const igo_scene* scene, const igb200_shading* shading, const igb200_render_settings* settings,
+                   float* film, float* aov0, float* aov1, float* aov2, uint64_t* stats3, int threads);
+
+/* Restated tonemap pipeline (src/artic/entrypoints/tonemap.art, core/color.art:77-142): n pixels of RGB sums ->
+ * packed 8-bit ARGB; `scale` carries 1 / IterationCount as Device::tonemap computes it (Device.cpp:1668,1677). */
+void igo_tonemap(const float* in, uint64_t n, uint32_t method, int use_gamma, float scale, float exposure_factor,
+                 float exposure_offset, uint32_t* out);
+
 /* Integer RNG known answers (src/artic/core/random.art): seed = create_random_seed(...), then n draws of
  * sample_tea_u32(seed, counter++) from counter 1, raw and as next_f32. */
 void igo_kat_rng(int32_t sample, int32_t iter, int32_t frame, int32_t x, int32_t y, int32_t user, uint32_t n,

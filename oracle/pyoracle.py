@@ -42,6 +42,8 @@ def load():
         lib.igo_scene_info.argtypes = [vp, vp, vp, vp]
         lib.igo_render.argtypes = [vp, vp, vp, vp, vp, C.c_int]
         lib.igo_render.restype = C.c_int
+        lib.igo_render_aov.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, C.c_int]
+        lib.igo_render_aov.restype = C.c_int
         lib.igo_kat_rng.argtypes = [C.c_int32] * 6 + [C.c_uint32, vp, vp, vp]
         _lib = lib
     return _lib
@@ -89,9 +91,10 @@ class OracleScene:
         return ent, prim, t, u, v, tie.astype(bool), second
 
     def render(self, shading, width, height, spi, iterations=1, seed=0, frame=0, rays=None, threads=0, film=None,
-               first_iteration=0):
+               first_iteration=0, aovs=None):
         """Restated Device::render: adds `iterations` iterations into a (h, w, 3) f32 film of RGB SUMS.
-        `shading` is an ignis-masterthesis_b200.shading.Shading; rays != None selects igtrace (list) mode."""
+        `shading` is an ignis-masterthesis_b200.shading.Shading; rays != None selects igtrace (list) mode.
+        aovs: list of up to three (h, w, 3) f32 arrays the technique's AOVs are added into (igo_render_aov)."""
         from importlib import import_module
         S = import_module("ignis-masterthesis_b200").shading
         if rays is not None:
@@ -106,7 +109,9 @@ class OracleScene:
             rs = S.RenderSettings(rays=rays.ctypes.data if rays is not None else None,
                                   ray_count=rays.size if rays is not None else 0, spi=spi, width=width, height=height,
                                   iteration=it, frame=frame, user_seed=seed)
-            rc = self._lib.igo_render(self._h, C.addressof(sh), C.addressof(rs), film.ctypes.data, stats.ctypes.data, threads)
+            a = [x.ctypes.data if x is not None else None for x in (list(aovs or []) + [None] * 3)[:3]]
+            rc = self._lib.igo_render_aov(self._h, C.addressof(sh), C.addressof(rs), film.ctypes.data, a[0], a[1], a[2],
+                                          stats.ctypes.data, threads)
             if rc != 0:
                 raise ValueError("oracle rejected the shading tables / settings")
             self.ray_stats += stats
@@ -116,6 +121,19 @@ class OracleScene:
         a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
         self._lib.igo_scene_info(self._h, C.addressof(a), C.addressof(b), C.addressof(c))
         return {"node4": a.value, "tri4": b.value, "tris": c.value}
+
+
+def tonemap(image_sum, iterations, method=0, use_gamma=True, scale=1.0, exposure_factor=1.0, exposure_offset=0.0):
+    """Restated Device::tonemap of an (h, w, 3) f32 image of sums -> (h, w) u32 packed ARGB."""
+    img = np.ascontiguousarray(image_sum, np.float32)
+    out = np.empty(img.shape[:2], np.uint32)
+    lib = load()
+    lib.igo_tonemap.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_float, C.c_float, C.c_float, C.c_void_p]
+    lib.igo_tonemap.restype = None
+    inv = np.float32(1.0) / np.float32(iterations) if iterations > 0 else np.float32(0)
+    lib.igo_tonemap(img.ctypes.data, img.shape[0] * img.shape[1], method, 1 if use_gamma else 0, float(np.float32(scale) * inv),
+                    exposure_factor, exposure_offset, out.ctypes.data)
+    return out
 
 
 def texture_eval(shading, tex_id, uv):

@@ -1014,15 +1014,18 @@ struct Film {
     float*   px;
     uint32_t w, h;
     float    inv_spi;
-    void splat(int32_t pixel, Color c) const // make_standard_accumulator, driver/accumulator.art:23-30
+    float*   aov[3]; // path + aov_mis: Direct Weights, NEE Weights; infobuffer: Normals, Albedo, Depth (else null)
+    static void add(float* img, int32_t pixel, Color c, float inv_spi) // make_standard_accumulator, driver/accumulator.art:23-30
     {
         // non-finite contributions (0 * inf in the reference's MIS weights) are dropped, as in the CUDA path:
         // DESIGN.md section 4.1, note 6
-        if (!std::isfinite(c.r + c.g + c.b)) return;
-        px[3 * (size_t)pixel + 0] += c.r * inv_spi;
-        px[3 * (size_t)pixel + 1] += c.g * inv_spi;
-        px[3 * (size_t)pixel + 2] += c.b * inv_spi;
+        if (!img || !std::isfinite(c.r + c.g + c.b)) return;
+        img[3 * (size_t)pixel + 0] += c.r * inv_spi;
+        img[3 * (size_t)pixel + 1] += c.g * inv_spi;
+        img[3 * (size_t)pixel + 2] += c.b * inv_spi;
     }
+    void splat(int32_t pixel, Color c) const { add(px, pixel, c, inv_spi); }
+    void splat_aov(int k, int32_t pixel, Color c) const { add(aov[k], pixel, c, inv_spi); } // make_atomic_aov_image, driver/aov.art:22-36
 };
 
 struct Stats { uint64_t camera = 0, bounce = 0, shadow = 0; };
@@ -1041,6 +1044,7 @@ static void trace_path(const Ctx& c, const igb200_render_settings& rs, int32_t x
     const float             offset = 0.001f;
     const int32_t           pixel  = y * (int32_t)rs.width + x;
     Payload                 pt{ 0.0f, color(1, 1, 1), 1, 1.0f }; // init_pt_raypayload, pathtracer.art:33-38
+    float                   ib_distance = 0.0f;                  // init_ib_raypayload, infobuffer.art:19-22 (depth = pt.depth)
     (void)sample;
 
     for (;;) {
@@ -1060,7 +1064,10 @@ static void trace_path(const Ctx& c, const igb200_render_settings& rs, int32_t x
                         col               = cadd(col, handle_color(tech, cmulf(cmul(pt.contrib, emit), mis)));
                     }
                 }
-                if (inflights > 0) film.splat(pixel, col);
+                if (inflights > 0) {
+                    film.splat_aov(0, pixel, col); // aov_di, pathtracer.art:158
+                    film.splat(pixel, col);
+                }
             }
             return;
         }
@@ -1100,6 +1107,36 @@ static void trace_path(const Ctx& c, const igb200_render_settings& rs, int32_t x
             return; // TechniqueNoBounceFunction
         }
 
+        if (tech.type == IGB200_TECH_INFOBUFFER) { // make_infobuffer_renderer, technique/infobuffer.art:28-104
+            const bool handle_specular = (tech.flags & IGB200_TECHFLAG_IB_HANDLE_SPECULAR) != 0;
+            const V3   out_dir         = neg(ray.dir);
+            if (!handle_specular || !bsdf.is_specular()) { // on_hit :36-63
+                Color     albedo  = black;
+                const int samples = 16;
+                Rnd       arnd{ hash_combine(0x811C9DC5u, (uint32_t)pixel), 1u }; // create_random_generator(hash_combine(hash_init(), pixel))
+                for (int i = 0; i < samples; ++i) {
+                    const BsdfSample ms = bsdf.sample(arnd, out_dir);
+                    if (ms.valid) {
+                        const float cos = fabsf(dot(ms.in_dir, surf.local.c2));
+                        albedo          = cadd(albedo, cmulf(ms.col, safe_div(ms.pdf, (float)samples * cos))); // without the cosine term
+                    }
+                }
+                const float d = hit.distance + (handle_specular ? ib_distance : 0.0f);
+                film.splat_aov(0, pixel, color(surf.local.c2.x, surf.local.c2.y, surf.local.c2.z));
+                film.splat_aov(1, pixel, color(fminf_(albedo.r, 1), fminf_(albedo.g, 1), fminf_(albedo.b, 1))); // color_saturate
+                film.splat_aov(2, pixel, color(d, d, d));
+            }
+            // on_bounce :65-91
+            if (!(handle_specular && bsdf.is_specular()) || !(pt.depth <= tech.max_depth)) return;
+            const BsdfSample ms = bsdf.sample(rnd, out_dir);
+            if (!ms.valid) return;
+            pt.depth    = pt.depth + 1;
+            ib_distance = ib_distance + hit.distance;
+            ray         = make_ray(surf.point, ms.in_dir, offset, flt_max, ray_flag_bounce);
+            st.bounce++;
+            continue;
+        }
+
         // on_hit, pathtracer.art:112-132
         if (emissive && surf.is_entering) {
             const float d = -dot(ray.dir, surf.local.c2);
@@ -1109,7 +1146,9 @@ static void trace_path(const Ctx& c, const igb200_render_settings& rs, int32_t x
                 const Pdf           pdf   = light_pdf_direct(c, l, ray, surf);
                 const float         pdf_s = pdf.as_solid(d, hit.distance * hit.distance);
                 const float         mis   = tech.enable_nee ? 1 / (1 + pt.inv_pdf * sel.pdf(false, mat.light, ray.org) * pdf_s) : 1.0f;
-                film.splat(pixel, handle_color(tech, cmulf(cmul(pt.contrib, emit), mis)));
+                const Color         contrib = handle_color(tech, cmulf(cmul(pt.contrib, emit), mis));
+                film.splat_aov(0, pixel, contrib); // aov_di, pathtracer.art:128
+                film.splat(pixel, contrib);
             }
         }
 
@@ -1132,7 +1171,10 @@ static void trace_path(const Ctx& c, const igb200_render_settings& rs, int32_t x
                 st.shadow++;
                 // cpu_traverse_secondary + the simple-shadow splat loop (driver/mapping_cpu.art:395-424,816-829)
                 const Hit sh = trace_one(*c.scene, shadow, true);
-                if (sh.prim_id < 0) film.splat(pixel, contrib);
+                if (sh.prim_id < 0) {
+                    film.splat_aov(1, pixel, contrib); // on_shadow_miss: aov_nee, pathtracer.art:202-208
+                    film.splat(pixel, contrib);
+                }
             }
         }
 
@@ -1178,6 +1220,15 @@ extern "C" int igo_texture_eval(const igb200_shading* sh, uint32_t id, const flo
 extern "C" int igo_render(const igo_scene* scene, const igb200_shading* sh, const igb200_render_settings* rs, float* film,
                           uint64_t* stats3, int threads)
 {
+    return igo_render_aov(scene, sh, rs, film, nullptr, nullptr, nullptr, stats3, threads);
+}
+
+// The same with the technique's AOV images (each w*h*3 floats or NULL): path + IGB200_TECHFLAG_AOV_MIS writes
+// aov0 = "Direct Weights", aov1 = "NEE Weights"; IGB200_TECH_INFOBUFFER writes aov0..2 = "Normals", "Albedo", "Depth"
+// and leaves the film alone (LockFramebuffer).
+extern "C" int igo_render_aov(const igo_scene* scene, const igb200_shading* sh, const igb200_render_settings* rs, float* film,
+                              float* aov0, float* aov1, float* aov2, uint64_t* stats3, int threads)
+{
     if (!scene || !sh || !rs || !film) return -1;
     const bool     list = rs->rays != nullptr;
     const uint32_t w = list ? (uint32_t)rs->ray_count : rs->width, h = list ? 1u : rs->height;
@@ -1194,7 +1245,12 @@ extern "C" int igo_render(const igo_scene* scene, const igb200_shading* sh, cons
     }
     igb200_render_settings s = *rs;
     s.width = w; s.height = h;
-    const Film film_{ film, w, h, 1 / (float)rs->spi };
+    Film film_{ film, w, h, 1 / (float)rs->spi, { nullptr, nullptr, nullptr } };
+    if (sh->technique.type == IGB200_TECH_INFOBUFFER) {
+        film_.aov[0] = aov0; film_.aov[1] = aov1; film_.aov[2] = aov2;
+    } else if (sh->technique.type == IGB200_TECH_PATH && (sh->technique.flags & IGB200_TECHFLAG_AOV_MIS)) {
+        film_.aov[0] = aov0; film_.aov[1] = aov1;
+    }
 
     // make_perspective_camera, camera/perspective.art:29-41
     const igb200_camera& cam = sh->camera;
@@ -1254,6 +1310,55 @@ extern "C" int igo_render(const igo_scene* scene, const igb200_shading* sh, cons
         for (auto& p : per) { stats3[0] += p.camera; stats3[1] += p.bounce; stats3[2] += p.shadow; }
     }
     return 0;
+}
+
+// ig_tonemap_pipeline (src/artic/entrypoints/tonemap.art:1-70) over n pixels of RGB sums; `scale` already carries
+// 1 / IterationCount (Device::tonemap, Device.cpp:1662-1687).  Packed colour = a << 24 | r << 16 | g << 8 | b.
+extern "C" void igo_tonemap(const float* in, uint64_t n, uint32_t method, int use_gamma, float scale, float exposure_factor,
+                            float exposure_offset, uint32_t* out)
+{
+    auto pack = [](uint32_t r, uint32_t g, uint32_t b, uint32_t a) { return (a << 24) | (r << 16) | (g << 8) | b; };
+    auto byte = [](float c) { return (uint32_t)(clampf(c, 0.0f, 1.0f) * 255.0f) & 0xFFu; }; // make_byte_color: `as u8` truncates
+    auto gamma = [](float x) { return x <= 0.0031308f ? 12.92f * x : 1.055f * powf(x, 0.416666667f) - 0.055f; }; // core/color.art:136-142
+    auto curve = [&](float L) -> float { // mod tonemapping, core/color.art:101-134
+        switch (method) {
+        case 0: return L;
+        case 1: return safe_div(L, 1.0f + L);
+        case 2: return safe_div(L * (1.0f + L / (4.0f * 4.0f)), 1.0f + L);
+        case 3: return safe_div(L * (2.51f * L + 0.03f), L * (2.43f * L + 0.59f) + 0.14f);
+        default: {
+            auto f = [](float x) {
+                const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
+                return ((x * (A * x + C * B) + D * E) / (x * (A * x + B) + D * F)) - E / F;
+            };
+            return f(L) / f(11.2f);
+        }
+        }
+    };
+    for (uint64_t i = 0; i < n; ++i) {
+        const float r = in[3 * i] * scale, g = in[3 * i + 1] * scale, b = in[3 * i + 2] * scale;
+        const float X = 0.4124564f * r + 0.3575761f * g + 0.1804375f * b; // srgb_to_xyY, core/color.art:84-99
+        const float Y = 0.2126729f * r + 0.7151522f * g + 0.0721750f * b;
+        const float Z = 0.0193339f * r + 0.1191920f * g + 0.9503041f * b;
+        const float s = X + Y + Z;
+        float       cx = 0, cy = 0, cY = 0;
+        if (!(s <= flt_eps)) { cx = X / s; cy = Y / s; cY = Y; }
+        if (std::isnan(cY)) out[i] = pack(0, 255, 255, 255);
+        else if (!std::isfinite(cY)) out[i] = pack(255, 0, 150, 255);
+        else if (cx < 0 || cy < 0 || cY < 0) out[i] = pack(255, 255, 0, 255);
+        else {
+            const float nL = curve(exposure_factor * cY + exposure_offset);
+            float       R = 0, G = 0, B = 0; // xyY_to_srgb, core/color.art:77-93
+            if (!(cy <= flt_eps)) {
+                const float x2 = cx * nL / cy, y2 = nL, z2 = (1 - cx - cy) * nL / cy;
+                R = 3.2404542f * x2 - 1.5371385f * y2 - 0.4985314f * z2;
+                G = -0.9692660f * x2 + 1.8760108f * y2 + 0.0415560f * z2;
+                B = 0.0556434f * x2 - 0.2040259f * y2 + 1.0572252f * z2;
+            }
+            if (use_gamma) { R = gamma(R); G = gamma(G); B = gamma(B); }
+            out[i] = pack(byte(R), byte(G), byte(B), 255);
+        }
+    }
 }
 
 // Known-answer hooks for the integer RNG (bit-exact on every platform): seed and the first `n` raw draws.
