@@ -322,6 +322,41 @@ def run_ours(args, rank, world, local_rank):
     value = world * n * args.steps / (total_ms * 1e-3) / 1e6
     hits = int((d_prim >= 0).sum().item())
 
+    # ---- BASELINE.json configs[2] also names any-hit on the same batch, and SURVEY 8(d) a flattened variant of the
+    # same triangles (one 1 M-triangle BVH, ~75 MB of nodes + triangles: L2- instead of L1-resident) ----
+    def timed_variant(device, any_hit, steps):
+        def one():
+            device.trace_device(d_rays.data_ptr(), n, d_ent.data_ptr(), d_prim.data_ptr(), d_t.data_ptr(), d_u.data_ptr(),
+                                d_v.data_ptr(), any_hit=any_hit, stream=stream.cuda_stream)
+        for _ in range(3):
+            one()
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(steps):
+            one()
+        b.record(stream)
+        barrier()
+        ms = a.elapsed_time(b) / steps
+        if world > 1:
+            tm = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            ms = float(tm.item())
+        return {"value": world * n / (ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms, "steps": steps,
+                "hit_rate": float((d_prim >= 0).sum().item()) / n}
+
+    variants = None
+    if args.variant_steps > 0:
+        variants = {"c3-instanced any-hit": timed_variant(dev, True, args.variant_steps)}
+        fdev = pkg.Device(local_rank)
+        ftables = W.c3_scene(flat=True)
+        fdev.assign_scene(ftables)
+        variants["c3-flat closest-hit"] = timed_variant(fdev, False, args.variant_steps)
+        variants["c3-flat any-hit"] = timed_variant(fdev, True, args.variant_steps)
+        variants["c3-flat bvh"] = fdev.bvh_info()
+        fdev.close()
+        del ftables
+
     # ---- end to end through the host-buffer C-ABI call (pinned host memory in, pinned host memory out) ----
     h_rays = torch.from_numpy(rays.view(np.float32).reshape(-1, 8)).pin_memory()
     h_i = [torch.empty(n, dtype=torch.int32).pin_memory() for _ in range(2)]
@@ -397,6 +432,9 @@ def run_ours(args, rank, world, local_rank):
                          "per_ray": {"nodes": n_node, "tris": n_tri, "entities": n_ent}},
             "cpu_baseline": cpu,
         }
+        if variants is not None:
+            line["trace_variants"] = variants
+            line["gpu_launches"] += 3 * (args.variant_steps + 3)
         if pt is not None:
             pt["cpu_baseline"] = oracle_samples_per_s(pkg) if world == 1 else None
             line["path_tracer"] = pt
@@ -421,6 +459,8 @@ def main():
                     help="path-traced iterations per GPU; 64 x spi 4 = the 256 spp of BASELINE.json configs[3] (0 disables the leg)")
     ap.add_argument("--c5-spp", type=int, default=1024,
                     help="samples per pixel of the many_point_lights leg (BASELINE.json configs[4]: 1024), split across ranks; 0 disables")
+    ap.add_argument("--variant-steps", type=int, default=10,
+                    help="timed steps of the any-hit and flattened-mesh variants of the C3 batch (0 disables)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

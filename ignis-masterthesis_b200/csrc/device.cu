@@ -710,12 +710,21 @@ static int render_batch(igb200_device* dev, const igb200_render_settings* rs, ui
         const uint64_t max_count = std::max<uint64_t>(1, std::min<uint64_t>(0x7FFF0000ull / per_iter, 1u << 23));
         if (count > max_count) {
             igb200_render_settings part = *rs;
+            igb200_render_stats    sum{};
             for (uint32_t done = 0; done < count;) {
                 const uint32_t c = (uint32_t)std::min<uint64_t>(max_count, count - done);
                 part.iteration   = rs->iteration + done;
                 if (int rc = render_batch(dev, &part, c)) return rc;
                 done += c;
+                // the counters describe the whole call, not its last batch
+                sum.camera_rays += dev->render_stats.camera_rays;
+                sum.bounce_rays += dev->render_stats.bounce_rays;
+                sum.shadow_rays += dev->render_stats.shadow_rays;
+                sum.rounds += dev->render_stats.rounds;
+                sum.kernel_launches += dev->render_stats.kernel_launches;
+                sum.device_ms += dev->render_stats.device_ms;
             }
+            dev->render_stats = sum;
             return IGB200_OK;
         }
     }

@@ -338,9 +338,9 @@ typedef struct igb200_render_stats {
     uint64_t camera_rays;
     uint64_t bounce_rays;
     uint64_t shadow_rays;
-    uint64_t rounds;        /* wavefront rounds (generate/trace/sort/shade/shadow) of the last iteration */
+    uint64_t rounds;        /* wavefront rounds (generate/trace/sort/shade/shadow) of the last render call */
     uint64_t kernel_launches;
-    float    device_ms;     /* device time of the last iteration */
+    float    device_ms;     /* device time of the last render call */
     float    _pad;
 } igb200_render_stats;
 
