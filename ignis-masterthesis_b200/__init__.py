@@ -3,7 +3,7 @@
 The directory name contains a hyphen (it is the repo's required package name), so import it with
 ``importlib.import_module("ignis-masterthesis_b200")`` -- see ``tests/conftest.py``.
 """
-from . import _lib, shading, tables, workloads  # noqa: F401
+from . import _lib, fixtures, shading, tables, workloads  # noqa: F401
 from .device import Device  # noqa: F401
 from .shading import Shading  # noqa: F401
 from .tables import SceneBuilder, SceneTables, make_rays  # noqa: F401

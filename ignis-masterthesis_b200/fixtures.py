@@ -34,6 +34,31 @@ def save_fixture(path, tables, sh, width, height, ref=None, meta=""):
         meta=np.asarray(meta))
 
 
+def save_igdb(path, tables, sh, width, height):
+    """The same tables as one `.igdb` file for the C++ frontends (layout: host/SceneFile.h)."""
+    sections = [
+        ("lookups", tables.lookups.view(np.uint8)), ("shape_data", tables.shape_data), ("entities", tables.entities.view(np.uint8)),
+        ("leaves0", tables.leaves[0].view(np.uint8)), ("leaves1", tables.leaves[1].view(np.uint8)),
+        ("bbox", np.asarray(tables.bbox, "<f4").view(np.uint8)), ("material_count", np.asarray([tables.material_count], "<u8").view(np.uint8)),
+        ("entity_per_material", np.asarray(tables.entity_per_material, "<i4").view(np.uint8)),
+        ("camera", _bytes(sh.camera)), ("technique", _bytes(sh.technique)), ("bsdfs", _table(S.Bsdf, sh.bsdfs)),
+        ("materials", _table(S.Material, sh.materials)), ("infinite", _table(S.Light, sh.infinite)),
+        ("finite", _table(S.Light, sh.finite)), ("textures", _table(S.Texture, sh.textures)),
+        ("blob", np.frombuffer(bytes(sh.blob), np.uint8)), ("selector", np.asarray([sh.selector, sh.hierarchy], "<u4").view(np.uint8)),
+        ("film", np.asarray([width, height], "<u4").view(np.uint8)),
+    ]
+    align = lambda x: (x + 15) // 16 * 16
+    offset = align(16 + 40 * len(sections))
+    toc, payload = bytearray(), bytearray()
+    for name, data in sections:
+        raw = np.ascontiguousarray(data).reshape(-1).tobytes()
+        toc += name.encode().ljust(24, b"\0") + np.asarray([len(raw), offset + len(payload)], "<u8").tobytes()
+        payload += raw + b"\0" * (align(len(raw)) - len(raw))
+    head = b"IGB200DB" + np.asarray([1, len(sections)], "<u4").tobytes() + bytes(toc)
+    with open(path, "wb") as f:
+        f.write(head.ljust(offset, b"\0") + bytes(payload))
+
+
 def _untable(cls, raw):
     n = raw.size // C.sizeof(cls)
     return [cls.from_buffer_copy(raw[i * C.sizeof(cls):(i + 1) * C.sizeof(cls)].tobytes()) for i in range(n)]

@@ -1,0 +1,87 @@
+// Device.h -- `IG::Device` with the reference's public interface (src/runtime/device/Device.h:14-74), implemented by
+// forwarding to the C ABI of include/ignis_b200.h.  Same member names, argument meaning and error behaviour
+// (no error codes out of the class: fatal conditions log and abort, unknown AOVs log and return {nullptr, 0} --
+// Device.cpp:271-274,1303-1305), so `IG::Runtime` and the frontends compile against it unchanged.
+// One addition: `assignShading`, the POD replacement of the per-scene shader JIT.
+#pragma once
+
+#ifdef IG_B200_IN_REFERENCE_TREE // building inside the reference: its own headers define these types
+#include "RuntimeStructs.h"
+#include "Target.h"
+#include "technique/TechniqueInfo.h"
+#include "technique/TechniqueVariant.h"
+#else
+#include "IgTypes.h"
+#endif
+
+#include <ignis_b200.h>
+
+namespace IG {
+class Device {
+public:
+    struct SetupSettings { // Device.h:18-23
+        Target target;
+        bool   AcquireStats  = false;
+        bool   DebugTrace    = false;
+        bool   IsInteractive = false;
+    };
+    struct SceneSettings { // Device.h:25-30; borrowed pointers, read during assignScene only (the backend copies to HBM)
+        SceneDatabase*                  database            = nullptr;
+        const std::vector<std::string>* aov_map             = nullptr;
+        const std::vector<std::string>* resource_map        = nullptr;
+        const std::vector<int32>*       entity_per_material = nullptr;
+    };
+    struct RenderSettings { // Device.h:32-42
+        const Ray* rays      = nullptr; // non-null: width = number of rays, height = 1
+        size_t     spi       = 8;
+        size_t     width     = 0;
+        size_t     height    = 0;
+        size_t     iteration = 0;
+        size_t     frame     = 0;
+        size_t     user_seed = 0;
+        TechniqueVariantInfo info;
+        bool       denoise = false;
+    };
+    struct AOVAccessor { // Device.h:44-47
+        float* Data;
+        size_t IterationCount;
+    };
+
+    explicit Device(const SetupSettings& settings);
+    ~Device();
+    Device(const Device&)            = delete;
+    Device& operator=(const Device&) = delete;
+
+    void assignScene(const SceneSettings& settings);
+    void assignShading(const igb200_shading& shading); // widened seam: replaces Runtime::compileShaders (Runtime.cpp:542-626)
+    void render(const TechniqueVariantShaderSet& shader_set, const RenderSettings& settings, const ParameterSet* parameter_set);
+    // `count` consecutive iterations in one wavefront (igb200_render_iterations); same film as `count` render() calls
+    void renderIterations(const RenderSettings& settings, size_t count);
+    void resize(size_t width, size_t height);
+    void releaseAll();
+
+    [[nodiscard]] Target target() const { return mSetup.target; }
+    [[nodiscard]] size_t framebufferWidth() const { return mWidth; }
+    [[nodiscard]] size_t framebufferHeight() const { return mHeight; }
+    [[nodiscard]] bool   isInteractive() const { return mSetup.IsInteractive; }
+
+    [[nodiscard]] AOVAccessor getFramebufferForHost(const std::string& name);
+    [[nodiscard]] AOVAccessor getFramebufferForDevice(const std::string& name);
+    void clearFramebuffer(const std::string& name);
+    void clearAllFramebuffer();
+
+    [[nodiscard]] const Statistics* getStatistics() { return nullptr; } // ray counters: renderStats()
+    [[nodiscard]] igb200_render_stats renderStats() const;
+
+    void tonemap(uint32_t* out, const TonemapSettings& settings);
+    // evaluateGlare / imageinfo / bake: out of scope (SURVEY.md 8(b) "Utility"); the reference's frontends on this
+    // path run with EnableTonemapping = false (cli/main.cpp:62, trace/main.cpp:77) and never call them.
+
+    [[nodiscard]] igb200_device* handle() const { return mHandle; }
+
+private:
+    SetupSettings  mSetup;
+    igb200_device* mHandle = nullptr;
+    size_t         mWidth = 0, mHeight = 0;
+};
+} // namespace IG
