@@ -36,6 +36,10 @@ constexpr int      kChunk       = 64; // rays a warp claims per atomic on the gl
 #endif
 constexpr int      kVoteTri     = IGB_VOTE_TRI; // lanes that must wait for a triangle phase before it runs
 constexpr int      kVoteEnt     = IGB_VOTE_ENT; // same for the entity-leaf phase
+#ifndef IGB_VOTE_REFILL
+#define IGB_VOTE_REFILL 1
+#endif
+constexpr int      kVoteRefill  = IGB_VOTE_REFILL; // idle lanes that must wait before the warp fetches new rays
 
 struct Vec3 { float x, y, z; };
 
@@ -267,7 +271,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
 
     for (;;) {
         const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !active);
-        if (idle != 0u) {
+        if (idle != 0u && (kVoteRefill <= 1 || exhausted || __popc(idle) >= kVoteRefill)) {
             if (!exhausted) {
                 if (pool_next == pool_end) {
                     uint32_t base = 0;

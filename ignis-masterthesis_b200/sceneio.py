@@ -996,7 +996,8 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
                                       cam.get("near_clip", 0.0), cam.get("far_clip", float(np.finfo(np.float32).max)), vertical)
     tech = scene.get("technique", {"type": "path"})
     if tech.get("type", "path") == "path":
-        sh.set_path(tech.get("max_depth", 64), tech.get("min_depth", 2), tech.get("clamp", 0.0), tech.get("nee", True))
+        sh.set_path(tech.get("max_depth", 64), tech.get("min_depth", 2), tech.get("clamp", 0.0), tech.get("nee", True),
+                    aov_mis=bool(tech.get("aov_mis", False)))  # PathTechnique.cpp:16
         # LoaderLight::generateLightSelector (loader/LoaderLight.cpp:423-452)
         selector = tech.get("light_selector", "uniform")
         if selector == "hierarchy" and len(sh.infinite) + len(sh.finite) > 1 and sh.finite:
@@ -1006,6 +1007,8 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
             raise ValueError(f"light selector '{selector}' is outside the supported subset")
     elif tech["type"] == "debug":
         sh.set_debug(tech.get("mode", 0))
+    elif tech["type"] == "infobuffer":  # InfoBufferTechnique.cpp:9-12
+        sh.set_infobuffer(tech.get("max_depth", 64), bool(tech.get("handle_specular", False)))
     else:
         raise ValueError(f"technique '{tech['type']}' is outside the supported subset")
     return tables, sh, width, height, {"entities": entity_ids, "materials": keys}
