@@ -544,7 +544,10 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
             (b.q[0].u == 0 || b.q[0].u > sh->texture_count || b.q[1].u == 0 || b.q[1].u > sh->bsdf_count || b.q[1].u - 1 == i))
             return fail(IGB200_E_INVALID, "bsdf %llu: bump map texture / inner bsdf out of range", (unsigned long long)i);
     }
-    if (sh->selector > IGB200_SELECTOR_HIERARCHY) return fail(IGB200_E_UNSUPPORTED, "unknown light selector %u", sh->selector);
+    if (sh->selector > IGB200_SELECTOR_CDF) return fail(IGB200_E_UNSUPPORTED, "unknown light selector %u", sh->selector);
+    if (sh->selector == IGB200_SELECTOR_CDF && sh->finite_light_count > 0 &&
+        ((uint64_t)sh->hierarchy * 4 + sh->finite_light_count * 4 > sh->blob_bytes))
+        return fail(IGB200_E_INVALID, "igb200_assign_shading: light CDF exceeds the blob");
     if (sh->selector == IGB200_SELECTOR_HIERARCHY && sh->finite_light_count > 1) {
         const uint64_t codes = (sh->finite_light_count + 3) / 4 * 4, nodes = 2 * sh->finite_light_count - 1;
         if ((sh->hierarchy & 3u) || (uint64_t)sh->hierarchy * 4 + codes * 4 + nodes * 32 > sh->blob_bytes)
@@ -603,7 +606,7 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
     s.hierarchy  = sh->hierarchy;
     // The reference specialises its shaders per scene through the JIT; here the shade kernel has two instantiations
     // and the scene picks one: the extended one only when a feature it adds is actually used.
-    s.extended = sh->selector == IGB200_SELECTOR_HIERARCHY && sh->finite_light_count > 0;
+    s.extended = (sh->selector == IGB200_SELECTOR_HIERARCHY || sh->selector == IGB200_SELECTOR_CDF) && sh->finite_light_count > 0;
     for (uint64_t i = 0; i < sh->bsdf_count; ++i) {
         const igb200_bsdf& b = sh->bsdfs[i];
         if (b.type == IGB200_BSDF_BUMPMAP || (b.type == IGB200_BSDF_DIFFUSE && b.q[0].u != 0) ||

@@ -304,7 +304,7 @@ __device__ __forceinline__ Pdf light_pdf_direct(const ShadeScene& sc, const igb2
     return Pdf{ 1.0f, 0 };
 }
 
-// make_uniform_light_selector / make_hierarchy_light_selector, light/light_selector.art:19-45,76-110
+// make_uniform_light_selector / make_cdf_light_selector / make_hierarchy_light_selector, light/light_selector.art:19-110
 struct HEntry { Vec3 pos, dir; float flux; int32_t id; bool has_dir, is_leaf; };
 __device__ __forceinline__ const float* hier_nodes(const uint8_t* blob, uint32_t hierarchy, int32_t n_fin)
 {
@@ -362,42 +362,64 @@ static __device__ __noinline__ float hier_pdf(const uint8_t* blob, uint32_t hier
 }
 template <bool EXT>
 __device__ __forceinline__ bool selector_hierarchical(const ShadeScene& sc) { return EXT && sc.selector == IGB200_SELECTOR_HIERARCHY && sc.n_fin != 0; }
+template <bool EXT>
+__device__ __forceinline__ bool selector_cdf(const ShadeScene& sc) { return EXT && sc.selector == IGB200_SELECTOR_CDF && sc.n_fin != 0; }
+__device__ __forceinline__ Cdf1 selector_cdf_table(const ShadeScene& sc) // cdf::make_cdf_1d_from_buffer(buffer, finite_lights.count, 0)
+{
+    return Cdf1{ reinterpret_cast<const float*>(sc.blob) + sc.hierarchy, sc.n_fin };
+}
 __device__ __forceinline__ float selector_uniform_pdf(const ShadeScene& sc)
 {
     const int32_t n = sc.n_inf + sc.n_fin;
     return n == 0 ? 1.0f : __fdiv_rn(1.0f, (float)n);
 }
+// pdf of the finite-light part of the non-uniform selectors (hierarchy: position dependent; cdf: flux table)
+template <bool EXT>
+__device__ __forceinline__ float selector_finite_pdf(const ShadeScene& sc, int32_t id, Vec3 pos)
+{
+    if (selector_cdf<EXT>(sc)) return selector_cdf_table(sc).pdf_discrete(id);
+    return hier_pdf(sc.blob, sc.hierarchy, sc.n_fin, id, pos);
+}
 template <bool EXT>
 __device__ __forceinline__ float selector_pdf(const ShadeScene& sc, bool infinite, int32_t id, Vec3 pos)
 {
-    if (!selector_hierarchical<EXT>(sc)) return selector_uniform_pdf(sc);
-    if (sc.n_inf == 0) return hier_pdf(sc.blob, sc.hierarchy, sc.n_fin, id, pos);
-    return infinite ? (1.0f / (float)sc.n_inf) * 0.5f : hier_pdf(sc.blob, sc.hierarchy, sc.n_fin, id, pos) * (1.0f - 0.5f);
+    if (!selector_hierarchical<EXT>(sc) && !selector_cdf<EXT>(sc)) return selector_uniform_pdf(sc);
+    if (sc.n_inf == 0) return selector_finite_pdf<EXT>(sc, id, pos);
+    return infinite ? (1.0f / (float)sc.n_inf) * 0.5f : selector_finite_pdf<EXT>(sc, id, pos) * (1.0f - 0.5f);
+}
+template <bool EXT>
+__device__ __forceinline__ int32_t selector_finite_sample(const ShadeScene& sc, Rnd& rnd, Vec3 pos, float& pdf)
+{
+    if (selector_cdf<EXT>(sc)) { // make_cdf_light_selector: sampler.sample_discrete(rnd.next_f32()), light_selector.art:51,66
+        const Cdf1    cdf = selector_cdf_table(sc);
+        const int32_t off = cdf.sample_discrete(rnd.next_f32());
+        pdf               = cdf.pdf_discrete(off);
+        return off;
+    }
+    const HierPick hp = hier_sample(sc.blob, sc.hierarchy, sc.n_fin, rnd, pos);
+    rnd.counter       = hp.counter;
+    pdf               = hp.pdf;
+    return hp.id;
 }
 template <bool EXT>
 __device__ __forceinline__ const igb200_light& selector_sample(const ShadeScene& sc, Rnd& rnd, Vec3 pos, float& pdf)
 {
-    if (!selector_hierarchical<EXT>(sc)) {
+    if (!selector_hierarchical<EXT>(sc) && !selector_cdf<EXT>(sc)) {
         pdf              = selector_uniform_pdf(sc);
         const int32_t n  = sc.n_inf + sc.n_fin;
         const int32_t id = n <= 1 ? 0 : rnd.next_i32(0, n - 1); // pick_light_id :19-25
         return id < sc.n_inf ? sc.inf_lights[id] : sc.fin_lights[id - sc.n_inf];
     }
-    if (sc.n_inf == 0) {
-        const HierPick hp = hier_sample(sc.blob, sc.hierarchy, sc.n_fin, rnd, pos);
-        rnd.counter       = hp.counter;
-        pdf               = hp.pdf;
-        return sc.fin_lights[hp.id];
-    }
+    if (sc.n_inf == 0) return sc.fin_lights[selector_finite_sample<EXT>(sc, rnd, pos, pdf)];
     const float q = rnd.next_f32();
     if (q < 0.5f) {
         pdf = (1.0f / (float)sc.n_inf) * 0.5f;
         return sc.inf_lights[sc.n_inf <= 1 ? 0 : rnd.next_i32(0, sc.n_inf - 1)];
     }
-    const HierPick hp = hier_sample(sc.blob, sc.hierarchy, sc.n_fin, rnd, pos);
-    rnd.counter       = hp.counter;
-    pdf               = hp.pdf * (1.0f - 0.5f);
-    return sc.fin_lights[hp.id];
+    float               p;
+    const igb200_light& l = sc.fin_lights[selector_finite_sample<EXT>(sc, rnd, pos, p)];
+    pdf                   = p * (1.0f - 0.5f);
+    return l;
 }
 
 __device__ __forceinline__ Color handle_color(const igb200_technique& t, Color c) // technique/pathtracer.art:46-50

@@ -40,6 +40,10 @@ constexpr int      kVoteEnt     = IGB_VOTE_ENT; // same for the entity-leaf phas
 #define IGB_VOTE_REFILL 1
 #endif
 constexpr int      kVoteRefill  = IGB_VOTE_REFILL; // idle lanes that must wait before the warp fetches new rays
+#ifndef IGB_TRI_PER_TRIP
+#define IGB_TRI_PER_TRIP 2
+#endif
+constexpr int      kTriPerTrip  = IGB_TRI_PER_TRIP; // triangles a lane tests per triangle phase (0 = all it has pending)
 
 struct Vec3 { float x, y, z; };
 
@@ -339,7 +343,8 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
         const uint32_t free_v = __ballot_sync(0xFFFFFFFFu, active && tgroup.y == 0u);
         if (tri_v != 0u && (__popc(tri_v) >= kVoteTri || free_v == 0u)) {
             if (want_p && in_blas) {
-                while (tgroup.y != 0u) {
+                int budget = kTriPerTrip > 0 ? kTriPerTrip : 32;
+                while (tgroup.y != 0u && budget-- > 0) {
                     const uint32_t idx = 31u - (uint32_t)__clz(tgroup.y);
                     tgroup.y &= ~(1u << idx);
                     const float4* tp = sc.tris + 3 * (size_t)(tgroup.x + idx);

@@ -1003,7 +1003,9 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
         if selector == "hierarchy" and len(sh.infinite) + len(sh.finite) > 1 and sh.finite:
             codes, nodes = build_light_hierarchy(hier)
             sh.set_hierarchy(codes, nodes)
-        elif selector not in ("uniform", "hierarchy", ""):
+        elif selector == "simple" and len(sh.infinite) + len(sh.finite) > 1 and sh.finite:
+            sh.set_light_cdf([h[2] for h in hier])  # LoaderLight::generateLightSelectionCDF: computeFlux per finite light
+        elif selector not in ("uniform", "hierarchy", "simple", ""):
             raise ValueError(f"light selector '{selector}' is outside the supported subset")
     elif tech["type"] == "debug":
         sh.set_debug(tech.get("mode", 0))

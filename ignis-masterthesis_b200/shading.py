@@ -17,7 +17,7 @@ TEX_CHECKERBOARD, TEX_IMAGE = 0, 1
 FILTER_NEAREST, FILTER_BILINEAR, FILTER_BICUBIC = 0, 1, 2
 WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = 0, 1, 2
 IMAGE_RGBA8, IMAGE_RGBA32F = 0, 1
-SELECTOR_UNIFORM, SELECTOR_HIERARCHY = 0, 1
+SELECTOR_UNIFORM, SELECTOR_HIERARCHY, SELECTOR_CDF = 0, 1, 2
 NO_CDF = 0xFFFFFFFF
 TECH_PATH, TECH_DEBUG, TECH_INFOBUFFER = 0, 1, 2
 TECHFLAG_ONE_SIDED_DIFFUSE = 1
@@ -281,6 +281,23 @@ class Shading:
         raw = np.concatenate([codes, np.zeros(pad, np.uint32)]).tobytes() + np.asarray(nodes, np.float32).tobytes()
         self.hierarchy = self._blob_append(raw) // 4
         self.selector = SELECTOR_HIERARCHY
+        return self
+
+    def set_light_cdf(self, fluxes):
+        """The "simple" selector: CDF::computeForArray (runtime/CDF.cpp:11-40) over the finite lights' estimated flux."""
+        v = np.asarray(fluxes, np.float32)
+        cdf = np.empty_like(v)
+        acc = np.float32(0)
+        for i, x in enumerate(v):  # f32 running sum, like the reference
+            acc = np.float32(acc + x)
+            cdf[i] = acc
+        if acc > np.float32(1e-5):
+            cdf = (cdf * (np.float32(1) / acc)).astype(np.float32)
+        else:
+            cdf = (np.arange(v.size, dtype=np.float32) * (np.float32(1) / np.float32(v.size))).astype(np.float32)
+        cdf[-1] = 1
+        self.hierarchy = self._blob_append(cdf.tobytes()) // 4
+        self.selector = SELECTOR_CDF
         return self
 
     def add_material(self, bsdf, light=-1):

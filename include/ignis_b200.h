@@ -318,6 +318,10 @@ typedef struct igb200_shading {
 } igb200_shading;
 #define IGB200_SELECTOR_UNIFORM   0u /* make_uniform_light_selector    light/light_selector.art:26-45 */
 #define IGB200_SELECTOR_HIERARCHY 1u /* make_hierarchy_light_selector  light/light_selector.art:76-110, light_hierarchy.art */
+#define IGB200_SELECTOR_CDF       2u /* make_cdf_light_selector ("simple")  light/light_selector.art:47-74: `hierarchy` is then the
+                                        offset (units of 4 bytes) in blob of finite_light_count floats, the running sum of the lights'
+                                        estimated flux normalised to end at 1, without the leading 0 (CDF::computeForArray,
+                                        runtime/CDF.cpp:11-40; loader/LoaderLight.cpp:454-478) */
 
 /* Replaces Device::RenderSettings (Device.h:32-42).  One call = one ITERATION = spi samples per pixel
  * (Device::render, Device.cpp:1588-1612).  rays != NULL selects igtrace mode (list emitter,

@@ -922,13 +922,26 @@ static Pdf light_pdf_direct(const Ctx& c, const igb200_light& l, const Ray& ray,
     }
 }
 
-// make_uniform_light_selector / make_hierarchy_light_selector, light/light_selector.art:19-45,76-110
+// make_uniform_light_selector / make_cdf_light_selector / make_hierarchy_light_selector, light/light_selector.art:19-110
 struct HEntry { V3 pos, dir; float flux; int32_t id; bool has_dir, is_leaf; };
 struct Selector {
     const Ctx* c;
     int32_t    n_inf, n_fin;
     int32_t count() const { return n_inf + n_fin; }
     bool    hierarchical() const { return c->sh->selector == IGB200_SELECTOR_HIERARCHY && n_fin != 0; }
+    bool    by_cdf() const { return c->sh->selector == IGB200_SELECTOR_CDF && n_fin != 0; } // make_cdf_light_selector :47-74
+    Cdf1    cdf() const { return Cdf1{ reinterpret_cast<const float*>(c->sh->blob) + c->sh->hierarchy, n_fin }; }
+    // the finite-light half of the two non-uniform selectors
+    int32_t finite_sample(Rnd& rnd, V3 pos, float& pdf) const
+    {
+        if (by_cdf()) {
+            const int32_t off = cdf().sample_discrete(rnd.next_f32());
+            pdf               = cdf().pdf_discrete(off);
+            return off;
+        }
+        return hierarchy_sample(rnd, pos, pdf);
+    }
+    float finite_pdf(int32_t id, V3 pos) const { return by_cdf() ? cdf().pdf_discrete(id) : hierarchy_pdf(id, pos); }
     float   uniform_pdf() const { return count() == 0 ? 1.0f : 1 / (float)count(); }
     int32_t pick(Rnd& rnd, int32_t n) const { return n <= 1 ? 0 : rnd.next_i32(0, n - 1); }
 
@@ -983,27 +996,27 @@ struct Selector {
 
     const igb200_light& sample(Rnd& rnd, V3 pos, float& pdf) const
     {
-        if (!hierarchical()) {
+        if (!hierarchical() && !by_cdf()) {
             pdf              = uniform_pdf();
             const int32_t id = pick(rnd, count());
             return id < n_inf ? c->sh->infinite_lights[id] : c->sh->finite_lights[id - n_inf];
         }
-        if (n_inf == 0) return c->sh->finite_lights[hierarchy_sample(rnd, pos, pdf)];
+        if (n_inf == 0) return c->sh->finite_lights[finite_sample(rnd, pos, pdf)];
         const float q = rnd.next_f32();
         if (q < 0.5f) {
             pdf = (1 / (float)n_inf) * 0.5f;
             return c->sh->infinite_lights[pick(rnd, n_inf)];
         }
         float               p;
-        const igb200_light& l = c->sh->finite_lights[hierarchy_sample(rnd, pos, p)];
+        const igb200_light& l = c->sh->finite_lights[finite_sample(rnd, pos, p)];
         pdf                   = p * (1 - 0.5f);
         return l;
     }
     float pdf(bool infinite, int32_t id, V3 pos) const
     {
-        if (!hierarchical()) return uniform_pdf();
-        if (n_inf == 0) return hierarchy_pdf(id, pos);
-        return infinite ? (1 / (float)n_inf) * 0.5f : hierarchy_pdf(id, pos) * (1 - 0.5f);
+        if (!hierarchical() && !by_cdf()) return uniform_pdf();
+        if (n_inf == 0) return finite_pdf(id, pos);
+        return infinite ? (1 / (float)n_inf) * 0.5f : finite_pdf(id, pos) * (1 - 0.5f);
     }
 };
 

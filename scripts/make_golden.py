@@ -28,6 +28,7 @@ JOBS = [  # (fixture, scene file, reference image, width, height)
     ("primitives", "primitives.json", None, 1024, 1024),  # BASELINE.json configs[1]
     ("multilight-uniform", "evaluation/multilight-uniform.json", "ref-multilight-4096.exr", None, None),
     ("multilight-hierarchy", "evaluation/multilight-hierarchy.json", "ref-multilight-4096.exr", None, None),
+    ("multilight-simple", "evaluation/multilight-simple.json", "ref-multilight-4096.exr", None, None),  # CDF ("simple") selector
     ("many-point-lights", "many_point_lights.json", None, 3840, 2160),  # BASELINE.json configs[4]
     # textured environment + 2-D CDF.  The shipped Mitsuba image (ref-env-4096.exr) is kept for the record but is NOT a
     # pin: it is 2.16x below the analytic irradiance of the one lit texel (note 5).

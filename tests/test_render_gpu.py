@@ -74,7 +74,8 @@ def test_features_scene_matches_oracle(ig, oracle, dev, selector):
 
 
 @pytest.mark.parametrize("name,w,h", [("diamond", 240, 135), ("cbox-d6", 128, 128), ("emissive-plane", 96, 96),
-                                      ("primitives", 192, 192), ("multilight-hierarchy", 128, 128)])
+                                      ("primitives", 192, 192), ("multilight-hierarchy", 128, 128),
+                                      ("multilight-simple", 128, 128)])
 def test_reference_scenes_match_oracle(ig, oracle, dev, name, w, h):
     tables, sh, _, _, _ = load_golden(ig, name)
     film, stats = _render(dev, tables, sh, w, h, 4, 2, seed=11)
@@ -120,6 +121,7 @@ def test_flat_scene_closed_forms_full_size(ig, dev, light, one_sided, expected, 
     ("cbox-d6", True, 4096, 5e-3),         # the reference's own sample count and threshold (RunEvaluations.py:91-93)
     ("multilight-uniform", True, 1024, 3e-4),
     ("multilight-hierarchy", True, 1024, 3e-4),
+    ("multilight-simple", True, 1024, 3e-4),   # make_cdf_light_selector, light_selector.art:47-74
 ])
 def test_golden_images(ig, dev, name, one_sided, spp, threshold):
     tables, sh, w, h, ref = load_golden(ig, name)

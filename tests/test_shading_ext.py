@@ -97,10 +97,23 @@ def test_cdf2d_is_the_loader_table():
     assert np.isclose(m2[1], 3 * np.sin(np.pi * 1.5 / 4) / (3 * np.sin(np.pi * 1.5 / 4) + 2 * np.sin(np.pi * 2.5 / 4)))
 
 
-@pytest.mark.parametrize("name", ["multilight-uniform", "multilight-hierarchy"])
+def test_light_cdf_table_is_compute_for_array(ig):
+    # CDF::computeForArray (runtime/CDF.cpp:11-40): running sum / total, last entry forced to 1, no leading 0
+    sh = ig.Shading()
+    sh.set_light_cdf([3.0, 1.0, 0.0, 4.0])
+    assert sh.selector == ig.shading.SELECTOR_CDF
+    table = np.frombuffer(bytes(sh.blob), np.float32)[sh.hierarchy:sh.hierarchy + 4]
+    assert np.allclose(table, [3 / 8, 4 / 8, 4 / 8, 1.0]) and table[-1] == 1.0
+    sh = ig.Shading()
+    sh.set_light_cdf([0.0, 0.0])  # degenerate: uniform ramp x / n, then the forced 1
+    assert np.allclose(np.frombuffer(bytes(sh.blob), np.float32)[sh.hierarchy:sh.hierarchy + 2], [0.0, 1.0])
+
+
+@pytest.mark.parametrize("name", ["multilight-uniform", "multilight-hierarchy", "multilight-simple"])
 def test_multilight_golden(ig, oracle, name):
     tables, sh, w, h, ref = load_golden(ig, name)
     assert (sh.selector == ig.shading.SELECTOR_HIERARCHY) == name.endswith("hierarchy")
+    assert (sh.selector == ig.shading.SELECTOR_CDF) == name.endswith("simple")
     sh.technique.flags = ig.shading.TECHFLAG_ONE_SIDED_DIFFUSE  # see DESIGN.md section 4.1, note 2
     film = oracle.OracleScene(tables).render(sh, w, h, spi=64, iterations=4, seed=1)
     assert eval_error(film / 4, ref) < 3e-4
