@@ -76,7 +76,8 @@ struct igb200_device {
     cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
     int          sm_count = 0;
     static constexpr int      kPipe      = 3;         // streams of the host-buffer pipeline
-    static constexpr uint64_t kChunkRays = 1u << 20;  // rays per pipeline chunk (32 MiB up, 20 MiB down)
+    uint64_t                 chunk_rays = 1u << 20;   // rays per bulk chunk of the host-buffer pipeline (32 MiB up, 20 MiB down)
+    uint64_t                 chunk_min  = 1u << 18;   // first / last chunk of the ramp (IGB200_TRACE_CHUNK / _MIN override both)
     cudaStream_t             pipe[kPipe] = {};
     std::vector<cudaEvent_t> chunk_events;
     DeviceBuffer<uint32_t>   d_work; // persistent-kernel work counters (self-resetting): pair k for pipe[k], last pair for `stream`
@@ -189,6 +190,10 @@ int igb200_create(const igb200_setup* setup, igb200_device** out)
         delete dev;
         return fail(IGB200_E_OOM, "igb200_create: work counter allocation failed");
     }
+    if (const char* e = std::getenv("IGB200_TRACE_CHUNK")) // experiment switch: rays per chunk of the host-buffer pipeline
+        dev->chunk_rays = std::max<uint64_t>(1u << 12, std::min<uint64_t>(1u << 26, std::strtoull(e, nullptr, 10)));
+    if (const char* e = std::getenv("IGB200_TRACE_CHUNK_MIN"))
+        dev->chunk_min = std::max<uint64_t>(1u << 12, std::min<uint64_t>(1u << 26, std::strtoull(e, nullptr, 10)));
     *out = dev;
     return IGB200_OK;
 }
@@ -425,35 +430,62 @@ int igb200_trace_rays(igb200_device* dev, const igb200_ray* rays, uint64_t n, ui
         counters = dev->d_counters.ptr;
     }
 
-    // Chunked software pipeline over kPipe streams: upload of chunk k+1, traversal of chunk k and download of
-    // chunk k-1 overlap (PCIe is full duplex), instead of the reference's upload-all / trace / download-all
-    // (Device.cpp:573-611, 1330-1363).  Chunks use disjoint slices of the staging buffers.
-    const uint64_t chunk   = igb200_device::kChunkRays;
-    const uint64_t nchunks = (n + chunk - 1) / chunk;
-    if (dev->chunk_events.size() < 2 * nchunks) {
+    // Chunked software pipeline over three streams by ROLE -- upload, traversal, download -- chained by events: upload of
+    // chunk k+1, traversal of chunk k and download of chunk k-1 overlap (PCIe is full duplex), instead of the
+    // reference's upload-all / trace / download-all (Device.cpp:573-611, 1330-1363).  Chunks use disjoint slices of the
+    // staging buffers; small chunks keep the un-overlapped head (first upload) and tail (last download) short.
+    // Chunk schedule: sizes double from chunk_min up to chunk_rays and halve again at the end, so the un-overlapped
+    // head (the first upload) and tail (the last download) are those of a small chunk while the bulk moves in large
+    // ones (a chunk costs ~13 driver calls, ~0.1 ms of host time: small chunks throughout would be issue-bound).
+    std::vector<uint64_t> sizes;
+    {
+        const uint64_t big = dev->chunk_rays, small = std::min(big, dev->chunk_min);
+        std::vector<uint64_t> up;
+        uint64_t              ramp = 0;
+        for (uint64_t s = small; s < big; s *= 2) {
+            up.push_back(s);
+            ramp += s;
+        }
+        if (n > 2 * ramp + big) {
+            sizes = up;
+            uint64_t mid = n - 2 * ramp;
+            for (; mid > big; mid -= big) sizes.push_back(big);
+            sizes.push_back(mid);
+            sizes.insert(sizes.end(), up.rbegin(), up.rend());
+        } else {
+            for (uint64_t left = n; left > 0;) {
+                sizes.push_back(std::min(big, left));
+                left -= sizes.back();
+            }
+        }
+    }
+    const uint64_t nchunks = sizes.size();
+    if (dev->chunk_events.size() < 3 * nchunks) {
         const size_t old = dev->chunk_events.size();
-        dev->chunk_events.resize(2 * nchunks, nullptr);
+        dev->chunk_events.resize(3 * nchunks, nullptr);
         for (size_t i = old; i < dev->chunk_events.size(); ++i) IGB_CUDA(cudaEventCreate(&dev->chunk_events[i]));
     }
-    for (uint64_t c = 0; c < nchunks; ++c) {
-        const int      slot = (int)(c % igb200_device::kPipe);
-        cudaStream_t   s    = dev->pipe[slot];
-        const uint64_t off = c * chunk, m = std::min(chunk, n - off);
+    cudaStream_t s_up = dev->pipe[0], s_trace = dev->pipe[1], s_down = dev->pipe[2];
+    uint64_t     off  = 0;
+    for (uint64_t c = 0; c < nchunks; off += sizes[c], ++c) {
+        const uint64_t m  = sizes[c];
         float4*        dr = dev->d_rays.ptr + 2 * off;
-        IGB_CUDA(cudaMemcpyAsync(dr, rays + off, m * sizeof(igb200_ray), cudaMemcpyHostToDevice, s));
-        IGB_CUDA(igb::launch_normalize_rays(dr, m, s));
+        IGB_CUDA(cudaMemcpyAsync(dr, rays + off, m * sizeof(igb200_ray), cudaMemcpyHostToDevice, s_up));
+        IGB_CUDA(cudaEventRecord(dev->chunk_events[3 * c + 2], s_up));
+        IGB_CUDA(cudaStreamWaitEvent(s_trace, dev->chunk_events[3 * c + 2], 0));
         const igb::TraceOutputs out{ ent_id ? dev->d_ent.ptr + off : nullptr, prim_id ? dev->d_prim.ptr + off : nullptr,
                                      t ? dev->d_t.ptr + off : nullptr, u ? dev->d_u.ptr + off : nullptr,
                                      v ? dev->d_v.ptr + off : nullptr };
-        IGB_CUDA(cudaEventRecord(dev->chunk_events[2 * c], s));
-        IGB_CUDA(igb::launch_trace(dev->view, dr, m, ray_flags, any_hit, out, counters, dev->d_work.ptr + 2 * slot,
-                                   dev->sm_count, s));
-        IGB_CUDA(cudaEventRecord(dev->chunk_events[2 * c + 1], s));
-        if (ent_id) IGB_CUDA(cudaMemcpyAsync(ent_id + off, out.ent_id, m * 4, cudaMemcpyDeviceToHost, s));
-        if (prim_id) IGB_CUDA(cudaMemcpyAsync(prim_id + off, out.prim_id, m * 4, cudaMemcpyDeviceToHost, s));
-        if (t) IGB_CUDA(cudaMemcpyAsync(t + off, out.t, m * 4, cudaMemcpyDeviceToHost, s));
-        if (u) IGB_CUDA(cudaMemcpyAsync(u + off, out.u, m * 4, cudaMemcpyDeviceToHost, s));
-        if (v) IGB_CUDA(cudaMemcpyAsync(v + off, out.v, m * 4, cudaMemcpyDeviceToHost, s));
+        IGB_CUDA(cudaEventRecord(dev->chunk_events[3 * c], s_trace));
+        // Interface::loadRayList's direction normalisation (Device.cpp:588-592) happens in the kernel's ray load
+        IGB_CUDA(igb::launch_trace(dev->view, dr, m, ray_flags, any_hit, out, counters, dev->d_work.ptr, dev->sm_count, s_trace, true));
+        IGB_CUDA(cudaEventRecord(dev->chunk_events[3 * c + 1], s_trace));
+        IGB_CUDA(cudaStreamWaitEvent(s_down, dev->chunk_events[3 * c + 1], 0));
+        if (ent_id) IGB_CUDA(cudaMemcpyAsync(ent_id + off, out.ent_id, m * 4, cudaMemcpyDeviceToHost, s_down));
+        if (prim_id) IGB_CUDA(cudaMemcpyAsync(prim_id + off, out.prim_id, m * 4, cudaMemcpyDeviceToHost, s_down));
+        if (t) IGB_CUDA(cudaMemcpyAsync(t + off, out.t, m * 4, cudaMemcpyDeviceToHost, s_down));
+        if (u) IGB_CUDA(cudaMemcpyAsync(u + off, out.u, m * 4, cudaMemcpyDeviceToHost, s_down));
+        if (v) IGB_CUDA(cudaMemcpyAsync(v + off, out.v, m * 4, cudaMemcpyDeviceToHost, s_down));
     }
     for (int k = 0; k < igb200_device::kPipe; ++k) IGB_CUDA(cudaStreamSynchronize(dev->pipe[k]));
 
@@ -461,7 +493,7 @@ int igb200_trace_rays(igb200_device* dev, const igb200_ray* rays, uint64_t n, ui
     dev->last_stats.rays = n;
     for (uint64_t c = 0; c < nchunks; ++c) {
         float ms = 0.0f;
-        if (cudaEventElapsedTime(&ms, dev->chunk_events[2 * c], dev->chunk_events[2 * c + 1]) == cudaSuccess)
+        if (cudaEventElapsedTime(&ms, dev->chunk_events[3 * c], dev->chunk_events[3 * c + 1]) == cudaSuccess)
             dev->last_stats.kernel_ms += ms;
     }
     if (dev->stats) {

@@ -12,6 +12,7 @@ namespace {
 using namespace core;
 
 // Ray list in (32 B StreamRay, two 128-bit loads), five hit columns out (src/artic/driver/streams.art:80-100).
+template <bool NORMALIZE> // host-buffer path: Interface::loadRayList's normalisation (Device.cpp:588-592) fused into the load
 struct ListIO {
     static constexpr bool kBins = false;
     const float4* rays;
@@ -28,6 +29,11 @@ struct ListIO {
         const float4 r1 = __ldg(rays + 2 * (size_t)i + 1);
         org   = Vec3{ r0.x, r0.y, r0.z };
         dir   = Vec3{ r0.w, r1.x, r1.y };
+        if (NORMALIZE) { // same arithmetic as normalize_rays_kernel below
+            float norm = __fsqrt_rn(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
+            if (norm < kFltEps) norm = 1.0f;
+            dir = Vec3{ __fdiv_rn(dir.x, norm), __fdiv_rn(dir.y, norm), __fdiv_rn(dir.z, norm) };
+        }
         tmin  = r1.z;
         tmax  = r1.w;
         flags = ray_flags;
@@ -59,29 +65,38 @@ __global__ void normalize_rays_kernel(float4* rays, uint64_t n)
     rays[2 * i + 1] = r1;
 }
 
+template <bool NORMALIZE>
+void launch_list(const DeviceScene& scene, const ListIO<NORMALIZE>& io, int any_hit, TraceCounters* d_counters, uint32_t* d_work,
+                 uint32_t grid, cudaStream_t stream)
+{
+    if (d_counters) {
+        if (any_hit)
+            trace_kernel<ListIO<NORMALIZE>, true, true><<<grid, kBlock, 0, stream>>>(scene, io, d_counters, d_work);
+        else
+            trace_kernel<ListIO<NORMALIZE>, false, true><<<grid, kBlock, 0, stream>>>(scene, io, d_counters, d_work);
+    } else {
+        if (any_hit)
+            trace_kernel<ListIO<NORMALIZE>, true, false><<<grid, kBlock, 0, stream>>>(scene, io, nullptr, d_work);
+        else
+            trace_kernel<ListIO<NORMALIZE>, false, false><<<grid, kBlock, 0, stream>>>(scene, io, nullptr, d_work);
+    }
+}
+
 } // namespace
 
 cudaError_t launch_trace(const DeviceScene& scene, const float4* d_rays, uint64_t n, uint32_t ray_flags, int any_hit,
                          const TraceOutputs& out, TraceCounters* d_counters, uint32_t* d_work, int sm_count,
-                         cudaStream_t stream)
+                         cudaStream_t stream, bool normalize)
 {
     if (n == 0) return cudaSuccess;
     if (n > 0xFFFF0000ull) return cudaErrorInvalidValue;
     // persistent grid: one wave of resident CTAs (a multiple of the SM count), fewer for tiny batches
     const uint64_t want = (n + kChunk - 1) / kChunk; // warps that can get at least one chunk
     const uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)sm_count * kBlocksPerSM, (want + 3) / 4));
-    const ListIO io{ d_rays, (uint32_t)n, ray_flags, out };
-    if (d_counters) {
-        if (any_hit)
-            trace_kernel<ListIO, true, true><<<grid, kBlock, 0, stream>>>(scene, io, d_counters, d_work);
-        else
-            trace_kernel<ListIO, false, true><<<grid, kBlock, 0, stream>>>(scene, io, d_counters, d_work);
-    } else {
-        if (any_hit)
-            trace_kernel<ListIO, true, false><<<grid, kBlock, 0, stream>>>(scene, io, nullptr, d_work);
-        else
-            trace_kernel<ListIO, false, false><<<grid, kBlock, 0, stream>>>(scene, io, nullptr, d_work);
-    }
+    if (normalize)
+        launch_list<true>(scene, ListIO<true>{ d_rays, (uint32_t)n, ray_flags, out }, any_hit, d_counters, d_work, grid, stream);
+    else
+        launch_list<false>(scene, ListIO<false>{ d_rays, (uint32_t)n, ray_flags, out }, any_hit, d_counters, d_work, grid, stream);
     return cudaGetLastError();
 }
 

@@ -44,7 +44,7 @@ constexpr int kStackSize = 44; // traversal stack entries per ray (uint2 each)
 // so only one trace launch per handle may be in flight at a time.
 cudaError_t launch_trace(const DeviceScene& scene, const float4* d_rays, uint64_t n, uint32_t ray_flags, int any_hit,
                          const TraceOutputs& out, TraceCounters* d_counters, uint32_t* d_work, int sm_count,
-                         cudaStream_t stream);
+                         cudaStream_t stream, bool normalize = false);
 
 // In-place normalisation of ray directions (Interface::loadRayList, src/runtime/device/Device.cpp:585-607).
 cudaError_t launch_normalize_rays(float4* d_rays, uint64_t n, cudaStream_t stream);
