@@ -329,7 +329,7 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
         }
         shape_refs[s] = ref;
     }
-    if (tlas.max_depth + blas_depth + 7 > (uint32_t)kStackSize)
+    if (tlas.max_depth + blas_depth + 9 > (uint32_t)kStackSize)
         return fail(IGB200_E_UNSUPPORTED, "BVH too deep for the traversal stack (%u + %u levels)", tlas.max_depth, blas_depth);
 
     // ---- upload ----
