@@ -270,6 +270,9 @@ def run_ours(args, rank, world, local_rank):
 
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # NCCL prints its version banner to STDOUT at NCCL_DEBUG=VERSION; stdout carries exactly one JSON line
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     pkg = load_pkg()
     W = pkg.workloads
