@@ -66,9 +66,11 @@ bool Runtime::loadFromFile(const std::string& path)
         // the camera's image-plane scale follows the film's aspect ratio (PerspectiveCamera.cpp:40-54); the .igdb holds
         // the scale of its own film, so an override keeps the horizontal field of view and rescales the vertical one
         igb200_camera& cam = mScene.shading.camera;
-        if (!mOptions.IsTracer && mScene.width && mScene.height)
+        const bool same_aspect = mScene.width * mFilmHeight == mScene.height * mFilmWidth;
+        if (!mOptions.IsTracer && mScene.width && mScene.height && !same_aspect) {
             cam.scale[1] = cam.scale[0] * (float)mFilmHeight / (float)mFilmWidth;
-        mDevice->assignShading(mScene.shading.view());
+            mDevice->assignShading(mScene.shading.view());
+        }
     }
     mSamplesPerIteration = mOptions.SPI ? mOptions.SPI : recommendSPI(mFilmWidth, mFilmHeight, false);
     if (mOptions.IsTracer) mSamplesPerIteration = mOptions.SPI ? mOptions.SPI : 1; // trace/main.cpp:79-81

@@ -99,25 +99,26 @@ def test_igtrace_path_contributions_match_the_binding(ig, host_bin, tmp_path):
     np.testing.assert_allclose(got, film[0].astype(np.float64) / 4, rtol=2e-6, atol=1e-9)
 
 
-@pytest.mark.parametrize("batch", [False, True])
-def test_igcli_image_matches_the_binding(ig, host_bin, tmp_path, batch):
+@pytest.mark.parametrize("name,size,batch", [("cbox-d6", (128, 128), False), ("cbox-d6", (128, 128), True),
+                                             ("many-point-lights", (480, 270), True)])  # textures, sky, hierarchy in the blob
+def test_igcli_image_matches_the_binding(ig, host_bin, tmp_path, name, size, batch):
     os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
     import cv2
-    tables, sh, w, h, _ = load_golden(ig, "cbox-d6")
-    scene, out = str(tmp_path / "cbox.igdb"), str(tmp_path / "out.exr")
+    tables, sh, w, h, _ = load_golden(ig, name)
+    scene, out = str(tmp_path / "scene.igdb"), str(tmp_path / "out.exr")
     ig.fixtures.save_igdb(scene, tables, sh, w, h)
-    size = 128
-    cmd = [os.path.join(host_bin, "igcli"), scene, "-o", out, "--spp", "8", "--spi", "4", "--seed", "7", "--width", str(size), "--height", str(size)]
+    sw, sh_ = size
+    cmd = [os.path.join(host_bin, "igcli"), scene, "-o", out, "--spp", "8", "--spi", "4", "--seed", "7", "--width", str(sw), "--height", str(sh_)]
     r = _run(*(cmd + (["--batch"] if batch else [])))
     assert "Iterations: 2" in r.stdout and "SPP: 8" in r.stdout and "(min/med/max Msamples/s)" in r.stdout  # cli/main.cpp:170-196
     img = cv2.imread(out, cv2.IMREAD_UNCHANGED)[:, :, ::-1]
     with ig.Device(0) as dev:
         dev.assign_scene(tables)
         dev.assign_shading(sh)
-        dev.resize(size, size)
+        dev.resize(sw, sh_)
         for it in range(2):
-            dev.render(size, size, spi=4, iteration=it, seed=7)
+            dev.render(sw, sh_, spi=4, iteration=it, seed=7)
         film, iters = dev.framebuffer()
-    assert iters == 2 and img.shape == (size, size, 3) and img.mean() > 0.01
+    assert iters == 2 and img.shape == (sh_, sw, 3) and img.mean() > 0.01
     # the same samples; only the order of the f32 atomic additions into the film differs
     np.testing.assert_allclose(img, film / 2, rtol=1e-4, atol=1e-6)
