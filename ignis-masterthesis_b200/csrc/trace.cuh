@@ -36,7 +36,10 @@ struct TraceCounters { // device-side, 3 x u64
     unsigned long long nodes, tris, ents;
 };
 
-constexpr int kStackSize = 46; // traversal stack entries per ray (uint2 each)
+#ifndef IGB_STACK
+#define IGB_STACK 46
+#endif
+constexpr int kStackSize = IGB_STACK; // traversal stack entries per ray (uint2 each)
 
 // Launches the closest-hit (any_hit = 0) or any-hit traversal of `n` rays on `stream`.
 // counters may be nullptr (then the non-counting kernel variant is used).  d_work: two zero-initialised

@@ -40,6 +40,9 @@ constexpr int      kVoteEnt     = IGB_VOTE_ENT; // same for the entity-leaf phas
 #define IGB_VOTE_REFILL 1
 #endif
 constexpr int      kVoteRefill  = IGB_VOTE_REFILL; // idle lanes that must wait before the warp fetches new rays
+#ifndef IGB_PARK_PRIMS
+#define IGB_PARK_PRIMS 0 // 1: park triangle groups, 2: entity-leaf groups too (measured: see DESIGN.md section 7)
+#endif
 #ifndef IGB_TRI_PER_TRIP
 #define IGB_TRI_PER_TRIP 2
 #endif
@@ -309,6 +312,14 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
             }
         }
 
+#if IGB_PARK_PRIMS
+        // Experiment: a lane with both inner children and primitives pending parks the primitive group on the stack and
+        // keeps descending (it is tested when popped) instead of waiting for the primitive vote.
+        if (active && tgroup.y != 0u && ngroup.y > 0x00FFFFFFu && (IGB_PARK_PRIMS == 2 || in_blas)) {
+            stack[sp++] = tgroup;
+            tgroup      = make_uint2(0u, 0u);
+        }
+#endif
         // ---- node phase: lanes with inner children pending and no primitives waiting
         if (active && tgroup.y == 0u && ngroup.y > 0x00FFFFFFu) {
             const uint32_t hits            = ngroup.y;
