@@ -600,9 +600,9 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
                         return fail(IGB200_E_INVALID, "environment light %llu: CDF exceeds the blob", (unsigned long long)i);
                 }
             }
-            if (ls[i].type > IGB200_LIGHT_ENV_TEXTURED || inf != (t == 0))
+            if (ls[i].type > IGB200_LIGHT_AREA_SPHERE || inf != (t == 0))
                 return fail(IGB200_E_INVALID, "%s light %llu has type %u", t ? "finite" : "infinite", (unsigned long long)i, ls[i].type);
-            if ((ls[i].type == IGB200_LIGHT_AREA_SHAPE || ls[i].type == IGB200_LIGHT_AREA_PLANE) &&
+            if ((ls[i].type == IGB200_LIGHT_AREA_SHAPE || ls[i].type == IGB200_LIGHT_AREA_PLANE || ls[i].type == IGB200_LIGHT_AREA_SPHERE) &&
                 (ls[i].entity < 0 || (uint64_t)ls[i].entity >= dev->entity_count))
                 return fail(IGB200_E_INVALID, "area light %llu: entity %d out of range", (unsigned long long)i, ls[i].entity);
         }
@@ -647,6 +647,8 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
     }
     for (uint64_t i = 0; i < sh->infinite_light_count; ++i)
         if (sh->infinite_lights[i].type == IGB200_LIGHT_ENV_TEXTURED) s.extended = 1;
+    for (uint64_t i = 0; i < sh->finite_light_count; ++i)
+        if (sh->finite_lights[i].type == IGB200_LIGHT_AREA_SPHERE) s.extended = 1; // the sphere emitter lives in the extended kernel
     {
         // bbox_radius(scene_bbox) * 1.01 with vec3_len = sqrt of the fma-chain dot (core/bbox.art:24, vector.art:99)
         const float* b = dev->scene_bbox;

@@ -119,15 +119,20 @@ __device__ __forceinline__ Surf trimesh_surface_element_for_point(const TriMesh&
     s.local = make_orthonormal(normal);
     return s;
 }
-// compute_ellipsoid_area + make_sphere_shape::surface_element, shapes/sphere.art:22-29,48-67
-__device__ __forceinline__ Surf sphere_surface_element(float4 sph, const Entity& e, Vec3 org, Vec3 dir, float t, float u, float v)
+// compute_ellipsoid_area, shapes/sphere.art:22-29
+__device__ __forceinline__ float ellipsoid_area(float radius, const Entity& e)
 {
     const float* g = e.global_mat();
     const Mat3   lin{ Vec3{ g[0], g[1], g[2] }, Vec3{ g[3], g[4], g[5] }, Vec3{ g[6], g[7], g[8] } };
-    const float  l1 = vlen(mat3_mul(lin, Vec3{ sph.w, 0.0f, 0.0f })), l2 = vlen(mat3_mul(lin, Vec3{ 0.0f, sph.w, 0.0f })),
-                l3 = vlen(mat3_mul(lin, Vec3{ 0.0f, 0.0f, sph.w }));
+    const float  l1 = vlen(mat3_mul(lin, Vec3{ radius, 0.0f, 0.0f })), l2 = vlen(mat3_mul(lin, Vec3{ 0.0f, radius, 0.0f })),
+                l3 = vlen(mat3_mul(lin, Vec3{ 0.0f, 0.0f, radius }));
     const float P    = 1.6f;
-    const float area = 4.0f * flt_pi * powf(__fdiv_rn(powf(l1 * l2, P) + powf(l1 * l3, P) + powf(l2 * l3, P), 3.0f), __fdiv_rn(1.0f, P));
+    return 4.0f * flt_pi * powf(__fdiv_rn(powf(l1 * l2, P) + powf(l1 * l3, P) + powf(l2 * l3, P), 3.0f), __fdiv_rn(1.0f, P));
+}
+// make_sphere_shape::surface_element, shapes/sphere.art:48-67
+__device__ __forceinline__ Surf sphere_surface_element(float4 sph, const Entity& e, Vec3 org, Vec3 dir, float t, float u, float v)
+{
+    const float area   = ellipsoid_area(sph.w, e);
     const Vec3  point  = vadd(org, vmulf(dir, t));
     const Vec3  d      = vsub(point, xform_point(e.global_mat(), Vec3{ sph.x, sph.y, sph.z }));
     const Vec3  normal = vmulf(d, __fdiv_rn(1.0f, vlen(d)));
@@ -140,6 +145,13 @@ __device__ __forceinline__ Surf sphere_surface_element(float4 sph, const Entity&
     s.tex = nullptr; s.tix = s.tiy = s.tiz = 0;
     s.local = make_orthonormal(normal);
     return s;
+}
+// sphere_compute_surface_element_for_normal, shapes/sphere.art:31-45: the point and normal an emitter sample needs
+// (prim / tex coords feed only textured emission, which this backend does not have)
+struct SpherePoint { Vec3 point, normal; };
+__device__ __forceinline__ SpherePoint sphere_point_for_normal(Vec3 normal, Vec3 origin, float radius, const Entity& e)
+{
+    return SpherePoint{ xform_point(e.global_mat(), vadd(origin, vmulf(normal, radius))), vnormalize(mat3_mul(e.normal_mat(), normal)) };
 }
 
 // ---- BSDFs ------------------------------------------------------------------------------------------------

@@ -72,6 +72,23 @@ struct PlaneEmitter {
     __device__ __forceinline__ Pdf pdf_direct(Vec3 from) const { return Pdf{ safe_div(1.0f, compute_sq(from).s), 0 }; }
 };
 
+// make_sphere_area_emitter::sample_direct, light/area.art:248-273: uniform on the sphere, mirrored through the centre onto
+// the half facing `from`; pdf = 2 / area, weight = area / 2
+static __device__ __noinline__ SpherePoint sphere_emitter_sample(const float* entities, int32_t entity, Vec3 origin, float radius, float u, float v,
+                                                                 Vec3 from, float* inv_area)
+{
+    const Entity e{ entities + 36 * (size_t)entity };
+    const Vec3   glb_org = xform_point(e.global_mat(), origin);
+    SpherePoint  sp      = sphere_point_for_normal(equal_area_square_to_sphere(u, v), origin, radius, e);
+    const Vec3   os = vsub(from, glb_org), ps = vsub(from, sp.point);
+    if (!(dot3(ps, ps) <= dot3(os, os))) {
+        const Vec3 op = vsub(sp.point, glb_org);
+        const Vec3 np = vsub(sp.point, vmulf(op, 2.0f));
+        sp            = sphere_point_for_normal(vnormalize(vsub(np, glb_org)), origin, radius, e);
+    }
+    *inv_area = __fdiv_rn(1.0f, ellipsoid_area(radius, e));
+    return sp;
+}
 // make_shape_area_emitter::sample, light/area.art:48-58 (sample_triangle core/sampling.art:33-35)
 __device__ __forceinline__ Surf shape_emitter_sample(const ShadeScene& sc, const igb200_light& l, float ux_, float uy, float& pdfv,
                                                     float& weight)
@@ -265,6 +282,7 @@ __device__ __forceinline__ DirectSample light_sample_direct(const ShadeScene& sc
         return DirectSample{ vadd(from.point, vmulf(es.dir, sc.scene_radius)), es.dir, es.intensity, Pdf{ es.pdf, 0 }, 1.0f, sc.scene_radius };
     }
     case IGB200_LIGHT_AREA_SHAPE:
+    case IGB200_LIGHT_AREA_SPHERE:
     case IGB200_LIGHT_AREA_PLANE: { // make_area_light::sample_direct, light/area.art:12-26
         const float u = rnd.next_f32();
         const float v = rnd.next_f32();
@@ -275,6 +293,13 @@ __device__ __forceinline__ DirectSample light_sample_direct(const ShadeScene& sc
             const PlaneEmitter pe(l);
             pe.sample_direct(u, v, from.point, to_point, pdf, weight);
             to_normal = pe.normal;
+        } else if (EXT && l.type == IGB200_LIGHT_AREA_SPHERE) {
+            float             inv_area;
+            const SpherePoint sp = sphere_emitter_sample(sc.entities, l.entity, Vec3{ l.v[0], l.v[1], l.v[2] }, l.v[3], u, v, from.point, &inv_area);
+            to_point  = sp.point;
+            to_normal = sp.normal;
+            pdf       = Pdf{ 2.0f * inv_area, 1 };
+            weight    = __fdiv_rn(1.0f, 2.0f * inv_area);
         } else {
             float      pdfv;
             const Surf to = shape_emitter_sample(sc, l, u, v, pdfv, weight);
@@ -296,6 +321,8 @@ __device__ __forceinline__ DirectSample light_sample_direct(const ShadeScene& sc
 __device__ __forceinline__ Pdf light_pdf_direct(const ShadeScene& sc, const igb200_light& l, Vec3 ray_org, const Surf& surf)
 {
     if (l.type == IGB200_LIGHT_AREA_PLANE) return PlaneEmitter(l).pdf_direct(ray_org);
+    if (l.type == IGB200_LIGHT_AREA_SPHERE) // light/area.art:280-282
+        return Pdf{ __fdiv_rn(2.0f, ellipsoid_area(l.v[3], load_entity(sc, l.entity))), 1 };
     if (l.type == IGB200_LIGHT_AREA_SHAPE) {
         float pdfv, w;
         shape_emitter_sample(sc, l, surf.pu, surf.pv, pdfv, w); // prim_coords reinterpreted as the sampling square

@@ -48,6 +48,8 @@ def _rot(axis, deg):
 def parse_transform(t):
     if t is None:
         return np.eye(4)
+    if isinstance(t, dict):  # a single object of ops, e.g. {"scale": 0.5} (Parser.cpp: ops applied in key order)
+        t = [t]
     if isinstance(t, list) and t and isinstance(t[0], dict):
         m = np.eye(4)
         for op in t:
@@ -448,8 +450,18 @@ def _merge_externals(scene, base):
         sub = _merge_externals(sub, os.path.dirname(path))
         for k, v in sub.items():
             if isinstance(v, list):
-                scene.setdefault(k, [])
-                scene[k] = scene[k] + v
+                # externals are handled first "such that the current file can replace parts of it later on" (Parser.cpp:446);
+                # objects live in name-keyed maps (Scene.h:43-48), so a later definition of a name replaces the earlier one
+                merged, slot = [], {}
+                for obj in v + scene.get(k, []):
+                    name = obj.get("name") if isinstance(obj, dict) else None
+                    if name is not None and name in slot:
+                        merged[slot[name]] = obj
+                    else:
+                        if name is not None:
+                            slot[name] = len(merged)
+                        merged.append(obj)
+                scene[k] = merged
             elif k not in scene:
                 scene[k] = v
     return scene
@@ -832,11 +844,12 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
     b = SceneBuilder()
     sh = Shading()
 
-    shapes, shape_mesh = {}, {}
+    shapes, shape_mesh, shape_sphere = {}, {}, {}
     for e in scene.get("shapes", []):
         built = build_shape(e, base)
         if built[0] == "sphere":
             shapes[e["name"]] = b.add_sphere(built[1], built[2])
+            shape_sphere[e["name"]] = (built[1], built[2])
         else:
             m = built[1]
             shapes[e["name"]] = b.add_trimesh(m.v, m.f, m.n, m.t)
@@ -966,8 +979,16 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
                     m = entity_xform[name]
                     o = (m[:3, :3] @ pl[0].astype(np.float64) + m[:3, 3])
                     plane = (o, m[:3, :3] @ pl[1].astype(np.float64), m[:3, :3] @ pl[2].astype(np.float64))
-            area_light_of_entity[name] = sh.add_area_light(entity_ids[name], _color(l.get("radiance"), 1.0), plane)
             m = entity_xform[name]
+            sphere = shape_sphere.get(ent["shape"])
+            if sphere is not None and l.get("optimize", True):  # AreaLight.cpp:54-55,73-82: analytic sphere sampler
+                area_light_of_entity[name] = sh.add_sphere_area_light(entity_ids[name], _color(l.get("radiance"), 1.0), sphere[0], sphere[1])
+                w, h_, d = (np.linalg.norm(m[:3, :3] @ (np.eye(3)[k] * sphere[1])) for k in range(3))
+                P = 1.6075  # approximate_ellipsoid_area, AreaLight.cpp:26-35
+                area = 4 * math.pi * (((w * h_) ** P + (w * d) ** P + (h_ * d) ** P) / 3) ** (1 / P)
+                hier.append((m[:3, :3] @ np.asarray(sphere[0], np.float64) + m[:3, 3], None, float(np.mean(_color(l.get("radiance"), 1.0))) * area * math.pi))
+                continue
+            area_light_of_entity[name] = sh.add_area_light(entity_ids[name], _color(l.get("radiance"), 1.0), plane)
             if plane is not None:  # AreaLight.cpp:58-71
                 n = np.cross(plane[1], plane[2])
                 area = float(np.linalg.norm(n))

@@ -13,6 +13,7 @@ import numpy as np
 
 BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_MIRROR, BSDF_CONDUCTOR, BSDF_BUMPMAP = 0, 1, 2, 3, 4
 LIGHT_POINT, LIGHT_ENV, LIGHT_AREA_SHAPE, LIGHT_AREA_PLANE, LIGHT_SPOT, LIGHT_DIRECTIONAL, LIGHT_ENV_TEXTURED = 0, 1, 2, 3, 4, 5, 6
+LIGHT_AREA_SPHERE = 7
 TEX_CHECKERBOARD, TEX_IMAGE = 0, 1
 FILTER_NEAREST, FILTER_BILINEAR, FILTER_BICUBIC = 0, 1, 2
 WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = 0, 1, 2
@@ -343,6 +344,10 @@ class Shading:
         self.infinite[i].cdf = NO_CDF if cdf is None else cdf
         self.infinite[i].flags = LIGHTFLAG_SCALED_NEE if scaled_nee else 0
         return i
+
+    def add_sphere_area_light(self, entity, radiance, origin, radius):
+        """make_sphere_area_emitter (light/area.art:241-296): `entity` is an analytic sphere entity; origin / radius in object space."""
+        return self._light(self.finite, LIGHT_AREA_SPHERE, radiance, list(np.asarray(origin, np.float32)) + [np.float32(radius)], entity)
 
     def add_area_light(self, entity, radiance, plane=None):
         """plane = (origin, x_axis, y_axis) in WORLD space selects make_plane_area_emitter

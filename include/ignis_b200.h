@@ -244,6 +244,9 @@ typedef struct igb200_material {
 #define IGB200_LIGHT_ENV_TEXTURED 6u /* make_environment_light_textured(scene_bbox, scale = color, tex = textures[tex],
                                       cdf, transform = v[0..8] column major) when cdf != IGB200_NO_CDF, else
                                       make_environment_light(scene_bbox, scale, tex, transform)   light/env.art:112-166 */
+#define IGB200_LIGHT_AREA_SPHERE 7u /* make_area_light(make_sphere_area_emitter(entity, Sphere{origin v[0..2], radius v[3]}),
+                                      radiance = color): analytic sphere entity as emitter, sampled on the side facing the
+                                      shading point          light/area.art:241-296, runtime/light/AreaLight.cpp:73-82,153-160 */
 #define IGB200_NO_CDF 0xFFFFFFFFu
 /* make_environment_light_textured::sample_direct returns the UNSCALED texture radiance (light/env.art:138-139 uses
  * `intensity` where emission, :150, uses scale * tex), so next event estimation under-weights a scaled environment map;

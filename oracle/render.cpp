@@ -274,14 +274,19 @@ static Surf trimesh_surface_element_for_point(const TriMesh& m, const Entity& e,
     s.local = make_orthonormal(normal);
     return s;
 }
-// compute_ellipsoid_area + make_sphere_shape::surface_element, shapes/sphere.art:22-29,48-67
-static Surf sphere_surface_element(const Sphere& sp, const Entity& e, const Ray& ray, const Hit& hit)
+// compute_ellipsoid_area, shapes/sphere.art:22-29
+static float ellipsoid_area(float radius, const Entity& e)
 {
     const float* g  = e.global_mat;
     auto to_gdir    = [&](V3 p) { return mat3_mul(Mat3{ v3(g[0], g[1], g[2]), v3(g[3], g[4], g[5]), v3(g[6], g[7], g[8]) }, p); };
-    const float l1 = len(to_gdir(v3(sp.radius, 0, 0))), l2 = len(to_gdir(v3(0, sp.radius, 0))), l3 = len(to_gdir(v3(0, 0, sp.radius)));
+    const float l1 = len(to_gdir(v3(radius, 0, 0))), l2 = len(to_gdir(v3(0, radius, 0))), l3 = len(to_gdir(v3(0, 0, radius)));
     const float P    = 1.6f;
-    const float area = 4 * flt_pi * powf((powf(l1 * l2, P) + powf(l1 * l3, P) + powf(l2 * l3, P)) / 3, 1 / P);
+    return 4 * flt_pi * powf((powf(l1 * l2, P) + powf(l1 * l3, P) + powf(l2 * l3, P)) / 3, 1 / P);
+}
+// make_sphere_shape::surface_element, shapes/sphere.art:48-67
+static Surf sphere_surface_element(const Sphere& sp, const Entity& e, const Ray& ray, const Hit& hit)
+{
+    const float area   = ellipsoid_area(sp.radius, e);
     const V3    point  = add(ray.org, mulf(ray.dir, hit.distance));
     const V3    dir    = sub(point, xform_point(e.global_mat, sp.origin));
     const V3    normal = mulf(dir, 1 / len(dir));
@@ -293,6 +298,24 @@ static Surf sphere_surface_element(const Sphere& sp, const Entity& e, const Ray&
     s.pu = s.tu = hit.u;
     s.pv = s.tv = hit.v;
     s.local = make_orthonormal(normal);
+    return s;
+}
+// sphere_map_uv + sphere_compute_surface_element_for_normal, shapes/sphere.art:1-6,31-45
+static Surf sphere_surface_element_for_normal(V3 normal, const Sphere& sp, const Entity& e)
+{
+    const V3    d     = v3(normal.y, -normal.x, normal.z);
+    const float theta = acosf(d.z); // spherical_from_dir, core/common.art
+    float       phi   = atan2f(d.y, d.x);
+    if (phi < 0) phi += 2 * flt_pi;
+    const V3 gn = normalize(mat3_mul(e.normal_mat, normal));
+    Surf s;
+    s.is_entering = true;
+    s.point       = xform_point(e.global_mat, add(sp.origin, mulf(normal, sp.radius)));
+    s.face_normal = gn;
+    s.inv_area    = 1 / ellipsoid_area(sp.radius, e);
+    s.pu = s.tu = phi / (2 * flt_pi);
+    s.pv = s.tv = theta / flt_pi;
+    s.local = make_orthonormal(gn);
     return s;
 }
 
@@ -720,6 +743,25 @@ struct PlaneEmitter {
     Pdf pdf_direct(V3 from) const { return solid_pdf(safe_div(1, compute_sq(from).s)); }
 };
 
+// make_sphere_area_emitter::sample_direct, light/area.art:248-273: uniform on the sphere, mirrored through the centre
+// onto the half facing `from`; pdf = 2 / area
+static void sphere_emitter_sample(const Ctx& c, const igb200_light& l, float u, float v, V3 from, Surf& surf, float& pdfv, float& weight)
+{
+    const Entity e = load_entity(*c.scene, l.entity);
+    const Sphere sp{ v3(l.v[0], l.v[1], l.v[2]), l.v[3] };
+    const V3     glb_org = xform_point(e.global_mat, sp.origin);
+    surf = sphere_surface_element_for_normal(equal_area_square_to_sphere(u, v), sp, e);
+    const V3 p  = surf.point;
+    const V3 os = sub(from, glb_org), ps = sub(from, p);
+    pdfv   = 2 * surf.inv_area;
+    weight = 1 / (2 * surf.inv_area);
+    if (!(dot(ps, ps) <= dot(os, os))) {
+        const V3 op   = sub(p, glb_org);
+        const V3 np   = sub(p, mulf(op, 2));
+        const V3 norm = normalize(sub(np, glb_org));
+        surf          = sphere_surface_element_for_normal(norm, sp, e);
+    }
+}
 // make_shape_area_emitter::sample / pdf, light/area.art:48-68 (sample_triangle core/sampling.art:33-35)
 static void shape_emitter_sample(const Ctx& c, const igb200_light& l, float ux_, float uy, Surf& surf, float& pdfv, float& weight)
 {
@@ -884,6 +926,7 @@ static DirectSample light_sample_direct(const Ctx& c, const igb200_light& l, Rnd
         return DirectSample{ add(from.point, mulf(d, c.scene_radius)), d, cmulf(in, 1 / pdf_dir), solid_pdf(pdf_dir), 1.0f, c.scene_radius };
     }
     case IGB200_LIGHT_AREA_SHAPE:
+    case IGB200_LIGHT_AREA_SPHERE:
     case IGB200_LIGHT_AREA_PLANE: { // make_area_light::sample_direct, light/area.art:12-26
         const float u = rnd.next_f32();
         const float v = rnd.next_f32();
@@ -892,6 +935,10 @@ static DirectSample light_sample_direct(const Ctx& c, const igb200_light& l, Rnd
         float weight;
         if (l.type == IGB200_LIGHT_AREA_PLANE) {
             PlaneEmitter(l).sample_direct(u, v, from.point, to, pdf, weight);
+        } else if (l.type == IGB200_LIGHT_AREA_SPHERE) {
+            float pdfv;
+            sphere_emitter_sample(c, l, u, v, from.point, to, pdfv, weight);
+            pdf = area_pdf(pdfv);
         } else {
             float pdfv;
             shape_emitter_sample(c, l, u, v, to, pdfv, weight);
@@ -912,6 +959,8 @@ static Pdf light_pdf_direct(const Ctx& c, const igb200_light& l, const Ray& ray,
     switch (l.type) {
     case IGB200_LIGHT_ENV: return solid_pdf(1 / (4 * flt_pi)); // light/env.art:96
     case IGB200_LIGHT_AREA_PLANE: return PlaneEmitter(l).pdf_direct(ray.org); // light/area.art:206-210
+    case IGB200_LIGHT_AREA_SPHERE: // light/area.art:280-282: 2 / area
+        return area_pdf(2 / ellipsoid_area(l.v[3], load_entity(*c.scene, l.entity)));
     case IGB200_LIGHT_AREA_SHAPE: { // light/area.art:60-68,83: prim_coords reinterpreted as the sampling square
         Surf  s;
         float pdfv, w;

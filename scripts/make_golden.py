@@ -28,6 +28,14 @@ JOBS = [  # (fixture, scene file, reference image, width, height)
     ("primitives", "primitives.json", None, 1024, 1024),  # BASELINE.json configs[1]
     ("multilight-uniform", "evaluation/multilight-uniform.json", "ref-multilight-4096.exr", None, None),
     ("multilight-hierarchy", "evaluation/multilight-hierarchy.json", "ref-multilight-4096.exr", None, None),
+    # more of scripts/RunEvaluations.py's scene list that needs nothing beyond the supported subset
+    ("plane-d1", "evaluation/plane-d1.json", "ref-plane-d1-4096.exr", None, None),
+    ("room", "evaluation/room.json", "ref-room-4096.exr", None, None),
+    ("flipped-prim-glass", "evaluation/flipped-prim-glass.json", "ref-flipped-prim-glass-4096.exr", None, None),
+    ("emissive-plane-scale", "evaluation/emissive-plane-scale.json", "ref-emissive-plane-scale-4096.exr", None, None),
+    ("sphere-light-ico", "evaluation/sphere-light-ico.json", "ref-sphere-light-4096.exr", None, None),  # mesh area light
+    ("sphere-light-pure", "evaluation/sphere-light-pure.json", "ref-sphere-light-4096.exr", None, None),  # analytic sphere emitter
+    ("two-planes-mirror", "evaluation/two-planes-mirror.json", "ref-two-planes-mirror-rad.exr", None, None),  # sphere light + mirror, Radiance reference
     ("multilight-simple", "evaluation/multilight-simple.json", "ref-multilight-4096.exr", None, None),  # CDF ("simple") selector
     ("many-point-lights", "many_point_lights.json", None, 3840, 2160),  # BASELINE.json configs[4]
     # textured environment + 2-D CDF.  The shipped Mitsuba image (ref-env-4096.exr) is kept for the record but is NOT a

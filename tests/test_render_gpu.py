@@ -75,7 +75,8 @@ def test_features_scene_matches_oracle(ig, oracle, dev, selector):
 
 @pytest.mark.parametrize("name,w,h", [("diamond", 240, 135), ("cbox-d6", 128, 128), ("emissive-plane", 96, 96),
                                       ("primitives", 192, 192), ("multilight-hierarchy", 128, 128),
-                                      ("multilight-simple", 128, 128)])
+                                      ("multilight-simple", 128, 128), ("sphere-light-pure", 128, 128),
+                                      ("two-planes-mirror", 128, 128), ("room", 128, 128)])
 def test_reference_scenes_match_oracle(ig, oracle, dev, name, w, h):
     tables, sh, _, _, _ = load_golden(ig, name)
     film, stats = _render(dev, tables, sh, w, h, 4, 2, seed=11)
@@ -122,6 +123,13 @@ def test_flat_scene_closed_forms_full_size(ig, dev, light, one_sided, expected, 
     ("multilight-uniform", True, 1024, 3e-4),
     ("multilight-hierarchy", True, 1024, 3e-4),
     ("multilight-simple", True, 1024, 3e-4),   # make_cdf_light_selector, light_selector.art:47-74
+    ("plane-d1", False, 256, 1e-3),
+    ("flipped-prim-glass", False, 256, 1e-3),
+    ("emissive-plane-scale", False, 1024, 1e-3),
+    ("room", False, 4096, 1e-3),               # the reference's own sample count (ref-room-4096)
+    ("sphere-light-ico", False, 4096, 2e-3),
+    ("sphere-light-pure", False, 4096, 3e-3),
+    ("two-planes-mirror", False, 1024, 1e-3),
 ])
 def test_golden_images(ig, dev, name, one_sided, spp, threshold):
     tables, sh, w, h, ref = load_golden(ig, name)

@@ -75,6 +75,13 @@ def test_spot_light_against_quadrature(ig, oracle):
     ("cbox-d1", False, 32, 5e-3),          # predef_eps, RunEvaluations.py:91-93
     ("plane-d6", True, 64, 1e-3),
     ("cbox-d6", True, 512, 8e-3),          # 5e-3 is met at 1024 spp (GPU test); CPU budget here is 512 spp
+    ("plane-d1", False, 64, 1e-3),
+    ("flipped-prim-glass", False, 64, 1e-3),      # mirrored entity transform (negative determinant) around a dielectric
+    ("emissive-plane-scale", False, 256, 1e-3),   # area light on a scaled entity ({"scale": 0.5} transform form)
+    ("room", False, 512, 1e-3),                   # predef_eps "room", RunEvaluations.py:97
+    ("sphere-light-ico", False, 1024, 2e-3),      # icosphere mesh as area light; predef_eps "sphere-light-ico"
+    ("sphere-light-pure", False, 256, 3e-3),      # make_sphere_area_emitter; predef_eps "sphere-light-pure"
+    ("two-planes-mirror", False, 256, 1e-3),      # sphere emitter + mirror against the Radiance reference
 ])
 def test_golden_images(ig, oracle, name, one_sided, spp, threshold):
     tables, sh, w, h, ref = load_golden(ig, name)
