@@ -1,0 +1,104 @@
+"""Size limits and error behaviour of the render ABI on the device: what the reference answers with IG_LOG(L_ERROR) /
+abort (Device.cpp:271-274,1303-1305) comes back as an IGB200_E_* code with a message; oversized requests are split or
+refused, never truncated."""
+import numpy as np
+import pytest
+
+from render_common import flat_scene
+
+pytestmark = pytest.mark.gpu
+
+E_INVALID, E_STATE, E_UNSUPPORTED = -2, -5, -6
+
+
+@pytest.fixture()
+def dev(ig):
+    d = ig.Device(0)
+    yield d
+    d.close()
+
+
+def test_render_before_scene_or_shading_is_a_state_error(ig, dev):
+    with pytest.raises(ig._lib.BackendError) as e:
+        dev.render(8, 8, spi=1)
+    assert e.value.code == E_STATE
+    tables, sh = flat_scene(ig, "point", 8)
+    dev.assign_scene(tables)
+    with pytest.raises(ig._lib.BackendError) as e:
+        dev.render(8, 8, spi=1)
+    assert e.value.code == E_STATE and "shading" in str(e.value)
+
+
+def test_empty_film_and_oversized_iteration_are_refused(ig, dev):
+    tables, sh = flat_scene(ig, "point", 8)
+    dev.assign_scene(tables)
+    dev.assign_shading(sh)
+    for w, h, spi in ((0, 8, 1), (8, 0, 1), (8, 8, 0)):
+        with pytest.raises(ig._lib.BackendError) as e:
+            dev.render(w, h, spi=spi)
+        assert e.value.code == E_INVALID
+    with pytest.raises(ig._lib.BackendError) as e:    # 2^31 samples in ONE iteration: ray ids are 31 bits
+        dev.render(32768, 32768, spi=2)
+    assert e.value.code == E_UNSUPPORTED and "2^31" in str(e.value)
+
+
+def test_shading_tables_are_validated(ig, dev):
+    S = ig.shading
+    tables, sh = flat_scene(ig, "point", 8)
+    dev.assign_scene(tables)
+
+    def refused(mutate, code):
+        _, bad = flat_scene(ig, "point", 8)
+        mutate(bad)
+        with pytest.raises(ig._lib.BackendError) as e:
+            dev.assign_shading(bad)
+        assert e.value.code == code, str(e.value)
+
+    refused(lambda s: setattr(s.technique, "max_depth", 300), E_UNSUPPORTED)        # depth travels in 8 bits
+    refused(lambda s: setattr(s.technique, "type", 9), E_UNSUPPORTED)
+    refused(lambda s: setattr(s, "selector", 7), E_UNSUPPORTED)
+    refused(lambda s: (s.add_point_light((0, 0, -3)), setattr(s, "selector", S.SELECTOR_CDF), setattr(s, "hierarchy", 1 << 20)), E_INVALID)
+    refused(lambda s: s.add_area_light(5, (1, 1, 1)), E_INVALID)                     # entity 5 of a one-entity scene
+    refused(lambda s: s.add_sphere_area_light(-1, (1, 1, 1), (0, 0, 0), 1.0), E_INVALID)
+    refused(lambda s: setattr(s.bsdfs[0], "type", 99), E_UNSUPPORTED)
+    refused(lambda s: s.add_diffuse((1, 1, 1), texture=3), E_INVALID)                # texture id out of range
+    dev.assign_shading(sh)                                                           # the untouched tables still load
+    dev.render(8, 8, spi=1)
+
+
+def test_unknown_aov_and_framebuffer_before_render(ig, dev):
+    tables, sh = flat_scene(ig, "point", 8)
+    dev.assign_scene(tables)
+    dev.assign_shading(sh)
+    with pytest.raises(ig._lib.BackendError) as e:
+        dev.framebuffer()
+    assert e.value.code == E_STATE
+    dev.render(8, 8, spi=1)
+    with pytest.raises(ig._lib.BackendError, match="unknown AOV") as e:                # Device.cpp:1303-1305
+        dev.framebuffer(name="No Such Image")
+    assert e.value.code == E_INVALID
+
+
+def test_a_request_beyond_2_31_samples_is_split_and_the_counters_cover_all_of_it(ig, dev):
+    """igb200_render_iterations splits a call whose ray ids would not fit 31 bits into several wavefronts; film, iteration
+    count and the ray counters must describe the whole call (the counters used to describe only the last batch)."""
+    tables, sh = flat_scene(ig, "point", 8)
+    dev.assign_scene(tables)
+    dev.assign_shading(sh)
+    w = h = 2048
+    spi, count = 64, 9                      # 268 M samples per iteration, 2.4 G in the call -> two batches (7 + 2)
+    dev.resize(w, h)
+    dev.render(w, h, spi=spi, iteration=0, seed=5, iterations=count)
+    st = dev.render_stats()
+    film, n = dev.framebuffer()
+    assert n == count
+    assert st["camera_rays"] == w * h * spi * count        # one camera ray per sample, summed over the batches
+    assert st["shadow_rays"] > 0 and st["rounds"] > 0 and st["device_ms"] > 0
+    # the same samples as `count` single iterations (the seed hashes the iteration index): compare two of them exactly enough
+    dev.clear_framebuffer()
+    for it in (0, 8):                       # first iteration of the first batch, last of the second
+        dev.render(w, h, spi=spi, iteration=it, seed=5)
+    two, n2 = dev.framebuffer()
+    assert n2 == 2
+    assert film.mean() / count == pytest.approx(two.mean() / 2, rel=2e-3)
+    assert np.all(np.isfinite(film))
