@@ -127,7 +127,11 @@ class _DevArray:
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
 
 
-PT_FIXTURE = {"c4-diamond": "diamond", "c5-many-point-lights": "many-point-lights"}
+PT_FIXTURE = {"c4-diamond": "diamond", "c5-many-point-lights": "many-point-lights", "office-fisheye": "office"}
+# The reference's only published timing: `igcli --spp 16384` on scenes/radiance/office/office_scene.json
+# (256 x 256 fisheye, depth 8) took 13.516 s on a GeForce RTX 3080 -- WHOLE igcli wall clock, scene load + JIT + save included.
+OFFICE_PUBLISHED = {"value": 256 * 256 * 16384 / 13.516 / 1e6, "unit": "Msamples/s", "hardware": "GeForce RTX 3080 12 GB",
+                    "source": "scenes/radiance/office/benchmark.txt:17", "includes": "whole igcli wall clock: scene load + shader JIT + render + save"}
 
 
 def load_pt_workload(pkg, workload=None):
@@ -399,6 +403,15 @@ def run_ours(args, rank, world, local_rank):
         c5["scaling"] = "strong"
         c5["spp"] = int(c5["iterations"] * c5["spi"])
 
+    # ---- the reference's own published benchmark scene, at its published sample count (N = 1 only: 1 G samples last ~1 s)
+    office = None
+    if args.office_spp > 0 and world == 1:
+        _, _, _, _, o_spi = load_pt_workload(pkg, "office-fisheye")
+        office = bench_path_tracer(pkg, local_rank, rank, world, max(1, args.office_spp // o_spi), 2, "office-fisheye")
+        office["spp"] = int(office["iterations"] * office["spi"])
+        office["published"] = OFFICE_PUBLISHED
+        office["vs_published"] = office["e2e_value"] / OFFICE_PUBLISHED["value"]
+
     if rank == 0:
         # ---- algorithmic bytes per ray: visit counts from a counting pass over a 2 Mi-ray sample (untimed) ----
         sdev = pkg.Device(local_rank, acquire_stats=True)
@@ -442,6 +455,9 @@ def run_ours(args, rank, world, local_rank):
             pt["cpu_baseline"] = oracle_samples_per_s(pkg) if world == 1 else None
             line["path_tracer"] = pt
             line["gpu_launches"] += pt["gpu_launches"]
+        if office is not None:
+            line["path_tracer_office"] = office
+            line["gpu_launches"] += office["gpu_launches"]
         if c5 is not None:
             c5["cpu_baseline"] = oracle_samples_per_s(pkg, 8.0, "c5-many-point-lights") if world == 1 else None
             line["path_tracer_c5"] = c5
@@ -462,6 +478,8 @@ def main():
                     help="path-traced iterations per GPU; 64 x spi 4 = the 256 spp of BASELINE.json configs[3] (0 disables the leg)")
     ap.add_argument("--c5-spp", type=int, default=1024,
                     help="samples per pixel of the many_point_lights leg (BASELINE.json configs[4]: 1024), split across ranks; 0 disables")
+    ap.add_argument("--office-spp", type=int, default=16384,
+                    help="samples per pixel of the office_scene.json leg (the reference's published run: 16384); 0 disables")
     ap.add_argument("--variant-steps", type=int, default=10,
                     help="timed steps of the any-hit and flattened-mesh variants of the C3 batch (0 disables)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])

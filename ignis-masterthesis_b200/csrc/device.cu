@@ -569,7 +569,7 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
     }
     for (uint64_t i = 0; i < sh->bsdf_count; ++i) {
         const igb200_bsdf& b = sh->bsdfs[i];
-        if (b.type > IGB200_BSDF_BUMPMAP) return fail(IGB200_E_UNSUPPORTED, "bsdf %llu: unknown type %u", (unsigned long long)i, b.type);
+        if (b.type > IGB200_BSDF_THIN_DIELECTRIC) return fail(IGB200_E_UNSUPPORTED, "bsdf %llu: unknown type %u", (unsigned long long)i, b.type);
         if (b.type == IGB200_BSDF_DIFFUSE && b.q[0].u > sh->texture_count)
             return fail(IGB200_E_INVALID, "bsdf %llu: texture %u out of range", (unsigned long long)i, b.q[0].u - 1);
         if (b.type == IGB200_BSDF_BUMPMAP &&
@@ -607,6 +607,7 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
                 return fail(IGB200_E_INVALID, "area light %llu: entity %d out of range", (unsigned long long)i, ls[i].entity);
         }
     }
+    if (sh->camera.type > IGB200_CAMERA_FISHLENS) return fail(IGB200_E_UNSUPPORTED, "unknown camera type %u", sh->camera.type);
     if (sh->technique.type > IGB200_TECH_INFOBUFFER) return fail(IGB200_E_UNSUPPORTED, "unknown technique %u", sh->technique.type);
     if (sh->technique.max_depth > 254) // the stream keeps the depth in 8 bits (reference default: 64, PathTechnique.cpp)
         return fail(IGB200_E_UNSUPPORTED, "technique.max_depth %d exceeds 254", sh->technique.max_depth);

@@ -244,6 +244,18 @@ struct Bsdf {
                 out = BsdfSample{ reflect(out_dir, n), 1.0f, kd(), 1.0f };
             return true;
         }
+        case IGB200_BSDF_THIN_DIELECTRIC: { // make_thin_dielectric_bsdf, bsdf/dielectric.art:30-45
+            const float k     = __fdiv_rn(d.p[0], d.p[1]); // always from outside to inside
+            const float cos_o = fabsf(dot3(out_dir, n));
+            float       cos_t = 0.0f, fterm = 1.0f;
+            if (!fresnel(k, cos_o, cos_t, fterm)) fterm = 1.0f; // math::fresnel_dielectric, core/math.art:120-123
+            const float F = fterm + __fdiv_rn((1.0f - fterm) * fterm, fterm + 1.0f);
+            if (rnd.next_f32() > F)
+                out = BsdfSample{ vneg(out_dir), 1.0f, Color{ d.color2[0], d.color2[1], d.color2[2] }, 1.0f };
+            else
+                out = BsdfSample{ vnormalize(reflect(out_dir, n)), 1.0f, kd(), 1.0f };
+            return true;
+        }
         case IGB200_BSDF_MIRROR: // bsdf/conductor.art:5-7
             out = BsdfSample{ reflect(out_dir, n), 1.0f, kd(), 1.0f };
             return true;

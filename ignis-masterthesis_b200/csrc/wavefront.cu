@@ -201,7 +201,16 @@ __global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __rest
             const float nx = __fdiv_rn(2.0f * ((float)x + rx), (float)set.width) - 1.0f;
             const float ny = 1.0f - __fdiv_rn(2.0f * ((float)y + ry), (float)set.height);
             org   = eye;
-            dir   = vnormalize(mat3_mul(view, Vec3{ sc.cam.scale[0] * nx, sc.cam.scale[1] * ny, 1.0f }));
+            if (sc.cam.type == IGB200_CAMERA_FISHLENS) { // make_fishlens_camera::compute_d, camera/fishlens.art:38-50 (fov = pi)
+                const float fx = nx * sc.cam.scale[0], fy = ny * sc.cam.scale[1];
+                const float r     = __fsqrt_rn(fx * fx + fy * fy);
+                const float theta = __fdiv_rn(r * flt_pi, 2.0f);
+                const float sT = sinf(theta), cT = cosf(theta);
+                const float sP = r < flt_eps ? 0.0f : __fdiv_rn(fy, r), cP = r < flt_eps ? 0.0f : __fdiv_rn(fx, r);
+                dir = vnormalize(mat3_mul(view, Vec3{ sT * cP, sT * sP, cT }));
+            } else {
+                dir = vnormalize(mat3_mul(view, Vec3{ sc.cam.scale[0] * nx, sc.cam.scale[1] * ny, 1.0f }));
+            }
             tmin  = sc.cam.tmin;
             tmax  = sc.cam.tmax;
             flags = kRayCamera;

@@ -71,7 +71,8 @@ def load_fixture(path):
                          [z["leaves0"].view(LEAF_DTYPE), z["leaves1"].view(LEAF_DTYPE)], z["bbox"],
                          int(z["material_count"]), list(z["entity_per_material"]))
     sh = S.Shading()
-    sh.camera = S.Camera.from_buffer_copy(z["camera"].tobytes())
+    cam = z["camera"].tobytes()  # fixtures written before ABI v5 hold the 52-byte camera without `type` (= perspective)
+    sh.camera = S.Camera.from_buffer_copy(cam.ljust(C.sizeof(S.Camera), b"\0"))
     sh.technique = S.Technique.from_buffer_copy(z["technique"].tobytes())
     sh.bsdfs = _untable(S.Bsdf, z["bsdfs"])
     sh.materials = _untable(S.Material, z["materials"])

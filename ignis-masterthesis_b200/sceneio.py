@@ -45,15 +45,64 @@ def _rot(axis, deg):
     return m
 
 
+class _Pairs(dict):
+    """A JSON object that remembers repeated keys (rapidjson keeps every member; a transform may hold two "qrotate" ops)."""
+
+    def __init__(self, pairs):
+        super().__init__(pairs)
+        self.pairs = list(pairs)
+
+
+def _strip_json_comments(text):
+    """rapidjson's kParseCommentsFlag | kParseTrailingCommasFlag (Parser.cpp:546): // and /* */ outside strings, `,]` `,}`."""
+    out, i, n, in_str = [], 0, len(text), False
+    while i < n:
+        c = text[i]
+        if in_str:
+            out.append(c)
+            if c == "\\" and i + 1 < n:
+                out.append(text[i + 1])
+                i += 1
+            elif c == '"':
+                in_str = False
+        elif c == '"':
+            in_str = True
+            out.append(c)
+        elif text.startswith("//", i):
+            while i < n and text[i] != "\n":
+                i += 1
+            continue
+        elif text.startswith("/*", i):
+            i = text.find("*/", i + 2)
+            i = n if i < 0 else i + 2
+            continue
+        else:
+            out.append(c)
+        i += 1
+    import re
+    return re.sub(r",(\s*[\]}])", r"\1", "".join(out))
+
+
+def load_json(path_or_text, is_text=False):
+    """Scene JSON the way the reference's parser reads it: comments, trailing commas, repeated keys in transform objects."""
+    if not is_text:
+        with open(path_or_text) as fh:
+            path_or_text = fh.read()
+    def hook(pairs):
+        keys = [k for k, _ in pairs]
+        return _Pairs(pairs) if len(set(keys)) != len(keys) else dict(pairs)
+    return json.loads(_strip_json_comments(path_or_text), object_pairs_hook=hook)
+
+
 def parse_transform(t):
     if t is None:
         return np.eye(4)
-    if isinstance(t, dict):  # a single object of ops, e.g. {"scale": 0.5} (Parser.cpp: ops applied in key order)
+    if isinstance(t, (dict, _Pairs)):  # a single object of ops, e.g. {"scale": 0.5} (Parser.cpp: ops applied in member order)
         t = [t]
-    if isinstance(t, list) and t and isinstance(t[0], dict):
+    if isinstance(t, list) and t and isinstance(t[0], (dict, _Pairs)):
         m = np.eye(4)
         for op in t:
-            for k, v in op.items():
+            for k, v in (op.pairs if isinstance(op, _Pairs) else op.items()):
                 if k == "translate":
                     o = np.eye(4); o[:3, 3] = v
                 elif k == "scale":
@@ -61,6 +110,12 @@ def parse_transform(t):
                     o[0, 0], o[1, 1], o[2, 2] = (v, v, v) if np.isscalar(v) else v
                 elif k == "rotate":
                     o = _rot(0, v[0]) @ _rot(1, v[1]) @ _rot(2, v[2])
+                elif k == "qrotate":  # Eigen::Quaternionf(w, x, y, z), Parser.cpp:96-105,192-193
+                    qw, qx, qy, qz = [float(c) for c in v]
+                    o = np.eye(4)
+                    o[:3, :3] = [[1 - 2 * (qy * qy + qz * qz), 2 * (qx * qy - qz * qw), 2 * (qx * qz + qy * qw)],
+                                 [2 * (qx * qy + qz * qw), 1 - 2 * (qx * qx + qz * qz), 2 * (qy * qz - qx * qw)],
+                                 [2 * (qx * qz - qy * qw), 2 * (qy * qz + qx * qw), 1 - 2 * (qx * qx + qy * qy)]]
                 elif k == "lookat":
                     origin = v.get("origin", [0, 0, 0])
                     target = np.asarray(v["direction"], float) + np.asarray(origin, float) if "direction" in v \
@@ -445,8 +500,7 @@ def load_ply(path):
 def _merge_externals(scene, base):
     for ext in scene.get("externals", []):
         path = os.path.join(base, ext["filename"])
-        with open(path) as fh:
-            sub = json.load(fh)
+        sub = load_json(path)
         sub = _merge_externals(sub, os.path.dirname(path))
         for k, v in sub.items():
             if isinstance(v, list):
@@ -835,8 +889,7 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
     """scene: dict or path. Returns (SceneTables, Shading, width, height, info)."""
     if isinstance(scene, str):
         base = os.path.dirname(os.path.abspath(scene))
-        with open(scene) as fh:
-            scene = json.load(fh)
+        scene = load_json(scene)
     scene = _merge_externals(dict(scene), base)
     film = scene.get("film", {}).get("size", [1000, 1000])
     width, height = width or int(film[0]), height or int(film[1])
@@ -876,7 +929,7 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
         elif ty in ("dielectric", "glass"):
             bsdf_ids[e["name"]] = sh.add_dielectric(e.get("int_ior", 1.5046), e.get("ext_ior", 1.0),
                                                     _color(e.get("specular_reflectance"), 1.0),
-                                                    _color(e.get("specular_transmittance"), 1.0))
+                                                    _color(e.get("specular_transmittance"), 1.0), bool(e.get("thin", False)))
         elif ty == "mirror":
             bsdf_ids[e["name"]] = sh.add_mirror(_color(e.get("specular_reflectance"), 1.0))
         elif ty == "conductor":  # runtime/bsdf/ConductorBSDF.cpp:13-36, BSDF.cpp:53-99
@@ -1013,8 +1066,12 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
     cam = scene.get("camera", {})
     vertical = "vfov" in cam
     fov = cam.get("vfov", cam.get("hfov", cam.get("fov", 60.0)))
-    sh.set_perspective_from_transform(parse_transform(cam.get("transform")), fov, width, height,
-                                      cam.get("near_clip", 0.0), cam.get("far_clip", float(np.finfo(np.float32).max)), vertical)
+    if cam.get("type", "perspective") in ("fishlens", "fisheye"):  # Camera.cpp registry; FishLensCamera.cpp: mode is always Circular
+        sh.set_fishlens_from_transform(parse_transform(cam.get("transform")), width, height,
+                                       cam.get("near_clip", 0.0), cam.get("far_clip", float(np.finfo(np.float32).max)))
+    else:
+        sh.set_perspective_from_transform(parse_transform(cam.get("transform")), fov, width, height,
+                                          cam.get("near_clip", 0.0), cam.get("far_clip", float(np.finfo(np.float32).max)), vertical)
     tech = scene.get("technique", {"type": "path"})
     if tech.get("type", "path") == "path":
         sh.set_path(tech.get("max_depth", 64), tech.get("min_depth", 2), tech.get("clamp", 0.0), tech.get("nee", True),

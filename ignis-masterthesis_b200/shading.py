@@ -11,7 +11,8 @@ import math
 
 import numpy as np
 
-BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_MIRROR, BSDF_CONDUCTOR, BSDF_BUMPMAP = 0, 1, 2, 3, 4
+BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_MIRROR, BSDF_CONDUCTOR, BSDF_BUMPMAP, BSDF_THIN_DIELECTRIC = 0, 1, 2, 3, 4, 5
+CAMERA_PERSPECTIVE, CAMERA_FISHLENS = 0, 1
 LIGHT_POINT, LIGHT_ENV, LIGHT_AREA_SHAPE, LIGHT_AREA_PLANE, LIGHT_SPOT, LIGHT_DIRECTIONAL, LIGHT_ENV_TEXTURED = 0, 1, 2, 3, 4, 5, 6
 LIGHT_AREA_SPHERE = 7
 TEX_CHECKERBOARD, TEX_IMAGE = 0, 1
@@ -29,7 +30,7 @@ LIGHTFLAG_SCALED_NEE = 1
 
 class Camera(C.Structure):
     _fields_ = [("eye", C.c_float * 3), ("dir", C.c_float * 3), ("up", C.c_float * 3), ("scale", C.c_float * 2),
-                ("tmin", C.c_float), ("tmax", C.c_float)]
+                ("tmin", C.c_float), ("tmax", C.c_float), ("type", C.c_uint32)]
 
 
 class Word(C.Union):
@@ -87,7 +88,7 @@ class RenderStats(C.Structure):
                 ("rounds", C.c_uint64), ("kernel_launches", C.c_uint64), ("device_ms", C.c_float), ("_pad", C.c_float)]
 
 
-assert C.sizeof(Bsdf) == 48 and C.sizeof(Light) == 96 and C.sizeof(Camera) == 52 and C.sizeof(Technique) == 32
+assert C.sizeof(Bsdf) == 48 and C.sizeof(Light) == 96 and C.sizeof(Camera) == 56 and C.sizeof(Technique) == 32
 assert C.sizeof(Texture) == 120
 
 
@@ -160,6 +161,30 @@ class Shading:
         if far < near:
             near, far = far, near
         self.camera.tmin, self.camera.tmax = float(near), float(far)
+        self.camera.type = CAMERA_PERSPECTIVE
+        return self
+
+    def set_fishlens_from_transform(self, m, width, height, near=0.0, far=float(np.finfo(np.float32).max), mode="circular"):
+        """make_fishlens_camera (camera/fishlens.art:8-36): scale = (xasp, yasp) of the aspect mode; orientation as for the
+        perspective camera (FishLensCamera.cpp:59-66)."""
+        m = np.asarray(m, np.float64).reshape(-1, 4)
+        _f3(self.camera.eye, m[:3, 3])
+        _f3(self.camera.dir, m[:3, 2])
+        _f3(self.camera.up, m[:3, 1])
+        asp = np.float32(width) / np.float32(height)
+        one = np.float32(1)
+        if mode == "circular":
+            xasp, yasp = (one if asp < 1 else asp), (one if asp > 1 else asp)
+        elif mode == "cropped":
+            xasp, yasp = (one / asp if asp < 1 else one), (one / asp if asp > 1 else one)
+        else:  # full
+            f = np.float32(np.sqrt(asp * asp + one) * np.float32(height)) / np.float32(min(width, height))
+            xasp, yasp = (f if asp < 1 else f / asp), (f if asp > 1 else f * asp)
+        self.camera.scale[0], self.camera.scale[1] = float(xasp), float(yasp)
+        if far < near:
+            near, far = far, near
+        self.camera.tmin, self.camera.tmax = float(near), float(far)
+        self.camera.type = CAMERA_FISHLENS
         return self
 
     def set_perspective_from_transform(self, m, fov_deg, width, height, near=0.01, far=100.0, vertical=False):
@@ -202,9 +227,10 @@ class Shading:
             self.bsdfs[i].q[0].u = texture + 1
         return i
 
-    def add_dielectric(self, int_ior=1.5046, ext_ior=1.0, specular_reflectance=(1, 1, 1), specular_transmittance=(1, 1, 1)):
-        # n1 = ext_ior (default vacuum), n2 = int_ior (default bk7): runtime/bsdf/DielectricBSDF.cpp:14-35, BSDF.cpp:8-9
-        return self._bsdf(BSDF_DIELECTRIC, specular_reflectance, specular_transmittance, (ext_ior, int_ior))
+    def add_dielectric(self, int_ior=1.5046, ext_ior=1.0, specular_reflectance=(1, 1, 1), specular_transmittance=(1, 1, 1), thin=False):
+        # n1 = ext_ior (default vacuum), n2 = int_ior (default bk7): runtime/bsdf/DielectricBSDF.cpp:14-35, BSDF.cpp:8-9;
+        # "thin": make_thin_dielectric_bsdf (bsdf/dielectric.art:27-47)
+        return self._bsdf(BSDF_THIN_DIELECTRIC if thin else BSDF_DIELECTRIC, specular_reflectance, specular_transmittance, (ext_ior, int_ior))
 
     def add_mirror(self, specular_reflectance=(1, 1, 1)):
         return self._bsdf(BSDF_MIRROR, specular_reflectance)

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define IGB200_ABI_VERSION 4
+#define IGB200_ABI_VERSION 5
 
 enum {
     IGB200_OK            = 0,
@@ -165,13 +165,18 @@ int igb200_get_bvh_info(igb200_device* dev, uint64_t* node_bytes, uint64_t* tri_
 /* make_perspective_camera(eye, dir, up, scale, w, h, tmin, tmax) (src/artic/camera/perspective.art:29-41);
  * scale = compute_scale_from_hfov / _vfov (perspective.art:1-11), chosen by the loader
  * (src/runtime/camera/PerspectiveCamera.cpp:40-54). */
+#define IGB200_CAMERA_PERSPECTIVE 0u
+#define IGB200_CAMERA_FISHLENS    1u /* make_fishlens_camera(eye, dir, up, w, h, mode, tmin, tmax) (src/artic/camera/fishlens.art:8-70):
+                                        180-degree equidistant fisheye; scale = (xasp, yasp) of the aspect mode the loader picked
+                                        (fishlens.art:14-36; runtime/camera/FishLensCamera.cpp uses Circular) */
 typedef struct igb200_camera {
-    float eye[3];
-    float dir[3];
-    float up[3];
-    float scale[2];
-    float tmin; /* near clip */
-    float tmax; /* far clip */
+    float    eye[3];
+    float    dir[3];
+    float    up[3];
+    float    scale[2];
+    float    tmin; /* near clip */
+    float    tmax; /* far clip */
+    uint32_t type; /* IGB200_CAMERA_* (ABI v5) */
 } igb200_camera;
 
 #define IGB200_BSDF_DIFFUSE    0u /* make_lambertian_bsdf(surf, kd = color)           bsdf/diffuse.art:2-11 */
@@ -186,6 +191,9 @@ typedef struct igb200_camera {
 #define IGB200_BSDF_BUMPMAP    4u /* make_bumpmap(ctx, inner = bsdfs[q[1].u - 1], texture_dx(map).r, texture_dy(map).r,
                                      strength = p[0]) with map = textures[q[0].u - 1]
                                      bsdf/map.art:64-68, texture/common.art:28-38, runtime/bsdf/MapBSDF.cpp */
+#define IGB200_BSDF_THIN_DIELECTRIC 5u /* make_thin_dielectric_bsdf(surf, n1 = p[0], n2 = p[1], ks = color, kt = color2): the
+                                     dielectric with "thin": true -- straight-through transmission, Fresnel term with the
+                                     interreflection series              bsdf/dielectric.art:27-47,178-184 */
 typedef union igb200_word {
     float    f;
     uint32_t u;

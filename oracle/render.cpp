@@ -611,6 +611,15 @@ struct Bsdf {
             }
             return BsdfSample{ true, reflect(out_dir, n), 1.0f, kd(), 1.0f };
         }
+        case IGB200_BSDF_THIN_DIELECTRIC: { // make_thin_dielectric_bsdf, bsdf/dielectric.art:30-45
+            const float k     = d->p[0] / d->p[1]; // always from outside to inside
+            const float cos_o = fabsf(dot(out_dir, n));
+            float       cos_t = 0, fterm = 1;
+            if (!fresnel(k, cos_o, cos_t, fterm)) fterm = 1; // math::fresnel_dielectric, core/math.art:120-123
+            const float F = fterm + (1 - fterm) * fterm / (fterm + 1);
+            if (rnd.next_f32() > F) return BsdfSample{ true, neg(out_dir), 1.0f, color(d->color2[0], d->color2[1], d->color2[2]), 1.0f };
+            return BsdfSample{ true, normalize(reflect(out_dir, n)), 1.0f, kd(), 1.0f };
+        }
         case IGB200_BSDF_MIRROR: // bsdf/conductor.art:5-7
             return BsdfSample{ true, reflect(out_dir, n), 1.0f, kd(), 1.0f };
         case IGB200_BSDF_CONDUCTOR: {
@@ -1278,6 +1287,17 @@ extern "C" int igo_texture_eval(const igb200_shading* sh, uint32_t id, const flo
 }
 
 // One render iteration (Device::render, src/runtime/device/Device.cpp:1588-1612 -> cpu_trace).
+// make_fishlens_camera::compute_d, camera/fishlens.art:38-50 (fov = pi)
+static V3 fishlens_dir(const Mat3& view, float xasp, float yasp, float x, float y)
+{
+    const float nx = x * xasp, ny = y * yasp;
+    const float r     = sqrtf(nx * nx + ny * ny);
+    const float theta = r * flt_pi / 2;
+    const float sT = sinf(theta), cT = cosf(theta);
+    const float sP = r < flt_eps ? 0.0f : ny / r, cP = r < flt_eps ? 0.0f : nx / r;
+    return normalize(mat3_mul(view, v3(sT * cP, sT * sP, cT)));
+}
+
 // film: w*h*3 floats, accumulated into (the caller keeps the iteration count).  stats3 = camera / bounce / shadow rays.
 extern "C" int igo_render(const igo_scene* scene, const igb200_shading* sh, const igb200_render_settings* rs, float* film,
                           uint64_t* stats3, int threads)
@@ -1351,7 +1371,8 @@ extern "C" int igo_render_aov(const igo_scene* scene, const igb200_shading* sh, 
                             // make_pixelcoord_from_xy, driver/camera.art:21-29
                             const float nx = 2 * ((float)x + rx) / (float)w - 1;
                             const float ny = 1 - 2 * ((float)y + ry) / (float)h;
-                            const V3    d  = normalize(mat3_mul(view, v3(cam.scale[0] * nx, cam.scale[1] * ny, 1)));
+                            const V3    d  = cam.type == IGB200_CAMERA_FISHLENS ? fishlens_dir(view, cam.scale[0], cam.scale[1], nx, ny)
+                                                                                : normalize(mat3_mul(view, v3(cam.scale[0] * nx, cam.scale[1] * ny, 1)));
                             ray            = make_ray(eye, d, cam.tmin, cam.tmax, ray_flag_camera);
                         }
                         st.camera++;

@@ -36,6 +36,8 @@ JOBS = [  # (fixture, scene file, reference image, width, height)
     ("sphere-light-ico", "evaluation/sphere-light-ico.json", "ref-sphere-light-4096.exr", None, None),  # mesh area light
     ("sphere-light-pure", "evaluation/sphere-light-pure.json", "ref-sphere-light-4096.exr", None, None),  # analytic sphere emitter
     ("two-planes-mirror", "evaluation/two-planes-mirror.json", "ref-two-planes-mirror-rad.exr", None, None),  # sphere light + mirror, Radiance reference
+    # the scene of the reference's only published timings (scenes/radiance/office/benchmark.txt): fishlens camera, thin dielectric
+    ("office", "radiance/office/office_scene.json", None, None, None),
     ("multilight-simple", "evaluation/multilight-simple.json", "ref-multilight-4096.exr", None, None),  # CDF ("simple") selector
     ("many-point-lights", "many_point_lights.json", None, 3840, 2160),  # BASELINE.json configs[4]
     # textured environment + 2-D CDF.  The shipped Mitsuba image (ref-env-4096.exr) is kept for the record but is NOT a

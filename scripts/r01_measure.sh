@@ -8,9 +8,9 @@ mkdir -p gpurun_out
 if [ "$what" = all ]; then
 python bench.py > gpurun_out/${tag}_bench_n1.json 2> gpurun_out/${tag}_bench_n1.err || exit 1
 fi
-python bench.py --steps 2 --warmup 3 --pt-iterations 4 --c5-spp 64 > gpurun_out/${tag}_bench_short.json 2>/dev/null || exit 1
+python bench.py --steps 2 --warmup 3 --pt-iterations 4 --c5-spp 64 --office-spp 256 > gpurun_out/${tag}_bench_short.json 2>/dev/null || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${tag}_launches.csv \
-    python bench.py --steps 2 --warmup 3 --pt-iterations 4 --c5-spp 64 > gpurun_out/${tag}_ncu_launch.log 2>&1
+    python bench.py --steps 2 --warmup 3 --pt-iterations 4 --c5-spp 64 --office-spp 256 > gpurun_out/${tag}_ncu_launch.log 2>&1
 python scripts/ncu_trace_target.py 2 > /dev/null || exit 1
 ncu --set full --clock-control none --import-source on -k regex:trace_kernel -o gpurun_out/${tag}_trace_c3 -f \
     python scripts/ncu_trace_target.py 2 > gpurun_out/${tag}_ncu_trace.log 2>&1

@@ -76,7 +76,7 @@ def test_features_scene_matches_oracle(ig, oracle, dev, selector):
 @pytest.mark.parametrize("name,w,h", [("diamond", 240, 135), ("cbox-d6", 128, 128), ("emissive-plane", 96, 96),
                                       ("primitives", 192, 192), ("multilight-hierarchy", 128, 128),
                                       ("multilight-simple", 128, 128), ("sphere-light-pure", 128, 128),
-                                      ("two-planes-mirror", 128, 128), ("room", 128, 128)])
+                                      ("two-planes-mirror", 128, 128), ("room", 128, 128), ("office", 128, 128)])
 def test_reference_scenes_match_oracle(ig, oracle, dev, name, w, h):
     tables, sh, _, _, _ = load_golden(ig, name)
     film, stats = _render(dev, tables, sh, w, h, 4, 2, seed=11)
