@@ -14,7 +14,7 @@ __device__ __forceinline__ bool light_delta(uint32_t type)
 }
 __device__ __forceinline__ bool light_infinite(uint32_t type)
 {
-    return type == IGB200_LIGHT_ENV || type == IGB200_LIGHT_DIRECTIONAL || type == IGB200_LIGHT_ENV_TEXTURED;
+    return type == IGB200_LIGHT_ENV || type == IGB200_LIGHT_DIRECTIONAL || type == IGB200_LIGHT_ENV_TEXTURED || type == IGB200_LIGHT_ENV_FUNCTION;
 }
 __device__ __forceinline__ Color light_color(const igb200_light& l) { return Color{ l.color[0], l.color[1], l.color[2] }; }
 
@@ -167,9 +167,45 @@ static __device__ __noinline__ Color env_tex_emission(const igb200_texture* text
     map_env_uv(switch_env_up(mat3_mul(light_transform(*l), dir)), u, v);
     return cmul(light_color(*l), tex_eval(textures, blob, l->tex, u, v));
 }
+// cie_wmean + make_cie_sky_light / make_cie_sunny_light, light/cie.art:1-42; `dir` in the light's own frame (Y up)
+static __device__ __noinline__ Color sky_function(const uint8_t* blob, const igb200_light* lp, Vec3 dir)
+{
+    const igb200_light& l = *lp;
+    const float* p = reinterpret_cast<const float*>(blob) + l.cdf;
+    const bool   variant = l.flags & IGB200_SKYFLAG_VARIANT, has_ground = l.flags & IGB200_SKYFLAG_HAS_GROUND;
+    const Color  scale{ __ldg(p + 0), __ldg(p + 1), __ldg(p + 2) }, zenith{ __ldg(p + 3), __ldg(p + 4), __ldg(p + 5) },
+        ground{ __ldg(p + 6), __ldg(p + 7), __ldg(p + 8) };
+    const float cos_theta = dir.y;
+    if (!has_ground && cos_theta < 0.0f) return Color{ 0.0f, 0.0f, 0.0f };
+    const float a  = powf(cos_theta + 1.01f, 10.0f);
+    const float f1 = __fdiv_rn(a * a, a * a + 1.0f), f2 = __fdiv_rn(1.0f, a * a + 1.0f);
+    if (l.tex == IGB200_SKY_CIE) {
+        const float c1 = variant ? __fdiv_rn(1.0f + 2.0f * cos_theta, 3.0f) : 1.0f, c2 = variant ? 0.777777777f : 1.0f;
+        return cadd(cmulf(cmulf(zenith, c1), f1), cmulf(cmulf(ground, __ldg(p + 10) * c2), f2));
+    }
+    const Vec3  sun{ __ldg(p + 12), __ldg(p + 13), __ldg(p + 14) };
+    const float cos_gamma = dot3(dir, sun);
+    const float gamma     = acosf(clampf(cos_gamma, -1.0f, 1.0f));
+    float       c1;
+    if (variant) {
+        c1 = (0.91f + 10.0f * expf(-3.0f * gamma) + 0.45f * cos_gamma * cos_gamma)
+             * (cos_theta >= 0.01f ? 1.0f - expf(__fdiv_rn(-0.32f, cos_theta)) : 1.0f);
+    } else {
+        const float theta = acosf(clampf(cos_theta, -1.0f, 1.0f)), stheta = acosf(clampf(sun.y, -1.0f, 1.0f));
+        c1 = __fdiv_rn((1.35f * sinf(5.631f - 3.59f * theta) + 3.12f) * sinf(4.396f - 2.6f * stheta) + 6.37f - theta, 2.326f)
+             * expf(gamma * (-0.563f) * ((2.629f - theta) * (1.562f - stheta) + 0.812f));
+    }
+    return cmul(scale, cadd(cmulf(cmulf(zenith, __ldg(p + 9) * c1), f1), cmulf(cmulf(ground, __ldg(p + 10) * __ldg(p + 11)), f2)));
+}
+__device__ __forceinline__ bool sky_is_hemi(const igb200_light& l) { return !(l.flags & IGB200_SKYFLAG_HAS_GROUND); } // light/env.art:104-108
 template <bool EXT>
 __device__ __forceinline__ Color env_emission(const ShadeScene& sc, const igb200_light& l, Vec3 dir)
 {
+    if (EXT && l.type == IGB200_LIGHT_ENV_FUNCTION) { // light/env.art:49-57 (hemi), :94 (spherical)
+        const Vec3 local = mat3_mul(light_transform(l), dir);
+        if (sky_is_hemi(l) && !(local.y > flt_eps)) return Color{ 0.0f, 0.0f, 0.0f };
+        return sky_function(sc.blob, &l, local);
+    }
     return EXT && l.type == IGB200_LIGHT_ENV_TEXTURED ? env_tex_emission(sc.textures, sc.blob, &l, dir) : light_color(l);
 }
 __device__ __forceinline__ Cdf2 load_cdf2(const uint8_t* blob, uint32_t off4)
@@ -194,6 +230,10 @@ static __device__ __noinline__ float env_tex_pdf(const uint8_t* blob, const igb2
 template <bool EXT>
 __device__ __forceinline__ float env_pdf(const ShadeScene& sc, const igb200_light& l, Vec3 dir)
 {
+    if (EXT && l.type == IGB200_LIGHT_ENV_FUNCTION && sky_is_hemi(l)) { // light/env.art:58-61: cosine_hemisphere_pdf
+        const float y = mat3_mul(light_transform(l), dir).y;
+        return y > flt_eps ? __fdiv_rn(y, flt_pi) : 0.0f;
+    }
     if (!EXT || l.type != IGB200_LIGHT_ENV_TEXTURED || l.cdf == IGB200_NO_CDF) return __fdiv_rn(1.0f, 4.0f * flt_pi);
     return env_tex_pdf(sc.blob, &l, dir);
 }
@@ -273,6 +313,23 @@ __device__ __forceinline__ DirectSample light_sample_direct(const ShadeScene& sc
         const float pdf = __fdiv_rn(1.0f, 4.0f * flt_pi);
         return DirectSample{ vadd(from.point, vmulf(d, sc.scene_radius)), d, cmulf(light_color(l), __fdiv_rn(1.0f, pdf)), Pdf{ pdf, 0 },
                              1.0f, sc.scene_radius };
+    }
+    case IGB200_LIGHT_ENV_FUNCTION: {
+        if (!EXT) break;
+        const Mat3  tr = light_transform(l);
+        const float u  = rnd.next_f32();
+        const float v  = rnd.next_f32();
+        if (sky_is_hemi(l)) { // make_environment_light_function_hemi::sample_direct, light/env.art:32-38
+            float       pdf;
+            const Vec3  dir = switch_env_up(sample_cosine_hemisphere(u, v, pdf));
+            const Color in  = cmulf(sky_function(sc.blob, &l, dir), __fdiv_rn(1.0f, pdf));
+            const Vec3  gd  = mat3_left_mul(tr, dir);
+            return DirectSample{ vadd(from.point, vmulf(gd, sc.scene_radius)), gd, in, Pdf{ pdf, 0 }, 1.0f, sc.scene_radius };
+        }
+        const Vec3  d   = equal_area_square_to_sphere(u, v); // _spherical::sample_direct, light/env.art:82-86
+        const float pdf = __fdiv_rn(1.0f, 4.0f * flt_pi);
+        return DirectSample{ vadd(from.point, vmulf(d, sc.scene_radius)), d, cmulf(sky_function(sc.blob, &l, mat3_mul(tr, d)), __fdiv_rn(1.0f, pdf)),
+                             Pdf{ pdf, 0 }, 1.0f, sc.scene_radius };
     }
     case IGB200_LIGHT_ENV_TEXTURED: {
         if (!EXT) break;

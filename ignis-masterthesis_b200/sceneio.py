@@ -728,6 +728,52 @@ def ea_from_direction_yup(d):  # ElevationAzimuth::fromDirectionYUp
     return np.float32(math.pi / 2 - math.acos(d[1])), np.float32(phi + 2 * math.pi if phi < 0 else phi)
 
 
+def light_ea(light):
+    """LoaderUtils::getEA (loader/LoaderUtils.cpp:140-151): direction, sun_direction, elevation / azimuth, or time and place."""
+    F = np.float32
+    if "direction" in light or "sun_direction" in light:
+        return ea_from_direction_yup(light.get("direction", light.get("sun_direction")))
+    if "elevation" in light or "azimuth" in light:
+        return F(light.get("elevation", 0)), F(light.get("azimuth", 0))
+    return compute_sun_ea(*[light.get(k, d) for k, d in (("year", 2020), ("month", 5), ("day", 6), ("hour", 12), ("minute", 0),
+                                                         ("seconds", 0.0), ("longitude", -6.9965744), ("latitude", 49.235422),
+                                                         ("timezone", -2.0))])
+
+
+def cie_sky_parameters(light, kind):
+    """CIELight::serialize (runtime/light/CIELight.cpp:41-110): the arguments of make_cie_sky_light / make_cie_sunny_light."""
+    F = np.float32
+    el, az = light_ea(light)
+    sun = np.array([math.cos(el) * math.sin(az), math.sin(el), -math.cos(el) * math.cos(az)], np.float32)  # toDirectionYUp
+    out = dict(scale=_color(light.get("scale"), 1.0), zenith=_color(light.get("zenith"), 1.0), ground=_color(light.get("ground"), 1.0),
+               ground_brightness=F(light.get("ground_brightness", 0.2)), has_ground=bool(light.get("has_ground", True)), sun_dir=sun)
+    if kind in ("cieuniform", "ciecloudy"):
+        return out
+    PI = F(3.14159265358979323846)
+    el = F(min(float(el), float(F(87) * PI / F(180))))  # "Sun too close to zenith"
+    clear = kind == "cieclear"
+    turbidity = F(light.get("turbidity", 2.45))
+    zb = (F(1.376) * turbidity - F(1.81)) * F(math.tan(el)) + F(0.38)
+    if not clear:
+        zb = (zb + F(8.6) * sun[1] + F(0.123)) / F(2)
+    zb = max(F(0), F(zb * F(1000) / F(203)))
+    half_pi = PI / F(2)
+    if clear:
+        factor = F(0.274) * (F(0.91) + F(10) * F(math.exp(-3 * float(half_pi - el))) + F(0.45) * sun[1] * sun[1])
+    else:
+        factor = (F(2.739) + F(0.9891) * F(math.sin(0.3119 + 2.6 * float(el)))) * F(math.exp(-float(half_pi - el) * (0.4441 + 1.48 * float(el))))
+    arr = (2.766521, 0.547665, -0.369832, 0.009237, 0.059229) if clear else (3.5556, -2.7152, -1.3081, 1.0660, 0.60227)
+    x = (float(el) - float(PI) / 4) / (float(PI) / 4)  # skylight_normalization_factor
+    f = arr[4]
+    for i in range(3, -1, -1):
+        f = f * x + arr[i]
+    norm_factor = F(f) / PI / factor
+    solar = F(1.5e9) / F(208) * (F(1.147) - F(0.147) / max(sun[1], F(0.16)))
+    additive = F(6e-5) / PI * solar * sun[1] * (F(1) if clear else F(0.15))
+    out.update(zenith_brightness=F(zb / factor), c2=F(zb * norm_factor + additive), clear=clear)
+    return out
+
+
 def bake_sky(light, hosek_lib):
     """SkyModel::SkyModel (src/runtime/skysun/SkyModel.cpp:9-55) at RES_AZ x RES_EL = 512 x 256 over the reference's own
     ArHosekSkyModel (compiled from the reference tree into oracle/_ref/libhosek.so), followed by the EXR round trip of
@@ -740,14 +786,7 @@ def bake_sky(light, hosek_lib):
     init.restype, init.argtypes = C.c_void_p, [C.c_double] * 3
     rad = getattr(lib, "_Z33arhosek_tristim_skymodel_radianceP20ArHosekSkyModelStateddi")
     rad.restype, rad.argtypes = C.c_double, [C.c_void_p, C.c_double, C.c_double, C.c_int]
-    if "direction" in light or "sun_direction" in light:
-        el, az = ea_from_direction_yup(light.get("direction", light.get("sun_direction")))
-    elif "elevation" in light or "azimuth" in light:
-        el, az = F(light.get("elevation", 0)), F(light.get("azimuth", 0))
-    else:
-        el, az = compute_sun_ea(*[light.get(k, d) for k, d in (("year", 2020), ("month", 5), ("day", 6), ("hour", 12), ("minute", 0),
-                                                               ("seconds", 0.0), ("longitude", -6.9965744), ("latitude", 49.235422),
-                                                               ("timezone", -2.0))])
+    el, az = light_ea(light)
     ground = _color(light.get("ground"), 0.8)
     turbidity = F(light.get("turbidity", 3.0))
     PI = F(3.14159265358979323846)
@@ -1021,6 +1060,13 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
             marginal, cond = compute_cdf2d(img, True, False)
             m3 = parse_transform(l.get("transform"))[:3, :3]
             sh.add_env_textured(tex, _color(l.get("scale"), 1.0), sh.add_cdf2d(marginal, cond), np.linalg.inv(m3.T))
+        elif ty in ("cieuniform", "ciecloudy", "cieclear", "cieintermediate"):  # LoaderLight.cpp registry -> CIELight
+            q = cie_sky_parameters(l, ty)
+            m3 = parse_transform(l.get("transform"))[:3, :3]
+            sunny = ty in ("cieclear", "cieintermediate")
+            sh.add_sky_function(1 if sunny else 0, q.get("clear", False) if sunny else ty == "ciecloudy", q["has_ground"], q["scale"], q["zenith"],
+                                q["ground"], q.get("zenith_brightness", 1.0), q["ground_brightness"], q.get("c2", 1.0), q["sun_dir"],
+                                np.linalg.inv(m3.T))
         elif ty == "area":
             name = l["entity"]
             ent = next(e for e in scene["entities"] if e["name"] == name)

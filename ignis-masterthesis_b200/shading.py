@@ -14,7 +14,9 @@ import numpy as np
 BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_MIRROR, BSDF_CONDUCTOR, BSDF_BUMPMAP, BSDF_THIN_DIELECTRIC = 0, 1, 2, 3, 4, 5
 CAMERA_PERSPECTIVE, CAMERA_FISHLENS = 0, 1
 LIGHT_POINT, LIGHT_ENV, LIGHT_AREA_SHAPE, LIGHT_AREA_PLANE, LIGHT_SPOT, LIGHT_DIRECTIONAL, LIGHT_ENV_TEXTURED = 0, 1, 2, 3, 4, 5, 6
-LIGHT_AREA_SPHERE = 7
+LIGHT_AREA_SPHERE, LIGHT_ENV_FUNCTION = 7, 8
+SKY_CIE, SKY_CIE_SUNNY = 0, 1
+SKYFLAG_VARIANT, SKYFLAG_HAS_GROUND = 1, 2
 TEX_CHECKERBOARD, TEX_IMAGE = 0, 1
 FILTER_NEAREST, FILTER_BILINEAR, FILTER_BICUBIC = 0, 1, 2
 WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = 0, 1, 2
@@ -369,6 +371,21 @@ class Shading:
         self.infinite[i].tex = texture
         self.infinite[i].cdf = NO_CDF if cdf is None else cdf
         self.infinite[i].flags = LIGHTFLAG_SCALED_NEE if scaled_nee else 0
+        return i
+
+    def add_sky_function(self, kind, variant, has_ground, scale=(1, 1, 1), zenith=(1, 1, 1), ground=(1, 1, 1), zenith_brightness=1.0,
+                         ground_brightness=0.2, c2=1.0, sun_dir=(0, 1, 0), transform=None):
+        """make_cie_sky_light (kind SKY_CIE, variant = cloudy) / make_cie_sunny_light (kind SKY_CIE_SUNNY, variant = is_clear),
+        light/cie.art:9-42, sampled by make_environment_light_function (hemisphere when there is no ground, light/env.art:24-108)."""
+        m = np.eye(3, dtype=np.float32) if transform is None else np.asarray(transform, np.float32).reshape(3, 3)
+        params = np.zeros(16, np.float32)
+        params[0:3], params[3:6], params[6:9] = scale, zenith, ground
+        params[9], params[10], params[11] = zenith_brightness, ground_brightness, c2
+        params[12:15] = sun_dir
+        i = self._light(self.infinite, LIGHT_ENV_FUNCTION, (1, 1, 1), tuple(m.T.reshape(-1)))
+        self.infinite[i].tex = kind
+        self.infinite[i].cdf = self._blob_append(params.tobytes()) // 4
+        self.infinite[i].flags = (SKYFLAG_VARIANT if variant else 0) | (SKYFLAG_HAS_GROUND if has_ground else 0)
         return i
 
     def add_sphere_area_light(self, entity, radiance, origin, radius):

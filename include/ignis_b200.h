@@ -255,6 +255,17 @@ typedef struct igb200_material {
 #define IGB200_LIGHT_AREA_SPHERE 7u /* make_area_light(make_sphere_area_emitter(entity, Sphere{origin v[0..2], radius v[3]}),
                                       radiance = color): analytic sphere entity as emitter, sampled on the side facing the
                                       shading point          light/area.art:241-296, runtime/light/AreaLight.cpp:73-82,153-160 */
+#define IGB200_LIGHT_ENV_FUNCTION 8u /* make_environment_light_function(scene_bbox, func, transform = v[0..8], half = !has_ground)
+                                      (light/env.art:24-107): an analytic sky.  tex = IGB200_SKY_* selects func, cdf = offset in
+                                      blob (units of 4 bytes) of its 16 float parameters, flags = IGB200_SKYFLAG_*.
+                                      Parameters: [0..2] scale, [3..5] zenith, [6..8] ground, [9] zenith brightness,
+                                      [10] ground brightness, [11] c2, [12..14] sun direction (Y up), [15] 0 -- the arguments
+                                      runtime/light/CIELight.cpp:41-110 passes to make_cie_sky_light / make_cie_sunny_light
+                                      (light/cie.art:9-42) */
+#define IGB200_SKY_CIE       0u /* cieuniform / ciecloudy (flag VARIANT = cloudy)          light/cie.art:10-19 */
+#define IGB200_SKY_CIE_SUNNY 1u /* cieclear (flag VARIANT = is_clear) / cieintermediate    light/cie.art:22-42 */
+#define IGB200_SKYFLAG_VARIANT    0x1u
+#define IGB200_SKYFLAG_HAS_GROUND 0x2u
 #define IGB200_NO_CDF 0xFFFFFFFFu
 /* make_environment_light_textured::sample_direct returns the UNSCALED texture radiance (light/env.art:138-139 uses
  * `intensity` where emission, :150, uses scale * tex), so next event estimation under-weights a scaled environment map;

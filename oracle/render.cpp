@@ -688,7 +688,8 @@ static inline bool light_delta(const igb200_light& l)
 }
 static inline bool light_infinite(const igb200_light& l)
 {
-    return l.type == IGB200_LIGHT_ENV || l.type == IGB200_LIGHT_DIRECTIONAL || l.type == IGB200_LIGHT_ENV_TEXTURED;
+    return l.type == IGB200_LIGHT_ENV || l.type == IGB200_LIGHT_DIRECTIONAL || l.type == IGB200_LIGHT_ENV_TEXTURED ||
+           l.type == IGB200_LIGHT_ENV_FUNCTION;
 }
 static inline Color light_color(const igb200_light& l) { return color(l.color[0], l.color[1], l.color[2]); }
 
@@ -841,8 +842,45 @@ static inline void map_env_uv(V3 dir, float& u, float& v)
 static inline Mat3 light_transform(const igb200_light& l) { return Mat3{ v3(l.v[0], l.v[1], l.v[2]), v3(l.v[3], l.v[4], l.v[5]), v3(l.v[6], l.v[7], l.v[8]) }; }
 
 // Light::emission of an infinite light along `dir` (light/env.art:93,146-151,163-166)
+// cie_wmean + make_cie_sky_light / make_cie_sunny_light, light/cie.art:1-42; `dir` in the light's own frame (Y up)
+static Color sky_function(const igb200_shading& sh, const igb200_light& l, V3 dir)
+{
+    const float* p = reinterpret_cast<const float*>(sh.blob) + l.cdf;
+    const bool   variant = l.flags & IGB200_SKYFLAG_VARIANT, has_ground = l.flags & IGB200_SKYFLAG_HAS_GROUND;
+    const Color  scale = color(p[0], p[1], p[2]), zenith = color(p[3], p[4], p[5]), ground = color(p[6], p[7], p[8]);
+    const float  cos_theta = dir.y;
+    if (!has_ground && cos_theta < 0) return black;
+    auto wmean = [&](Color c1, Color c2) {
+        const float a  = powf(cos_theta + 1.01f, 10);
+        const float f1 = a * a / (a * a + 1), f2 = 1 / (a * a + 1);
+        return cadd(cmulf(c1, f1), cmulf(c2, f2));
+    };
+    if (l.tex == IGB200_SKY_CIE) {
+        const float c1 = variant ? (1 + 2 * cos_theta) / 3 : 1.0f, c2 = variant ? 0.777777777f : 1.0f;
+        return wmean(cmulf(zenith, c1), cmulf(ground, p[10] * c2));
+    }
+    const V3    sun = v3(p[12], p[13], p[14]);
+    const float cos_gamma = dot(dir, sun);
+    const float gamma     = acosf(clampf(cos_gamma, -1, 1));
+    float       c1;
+    if (variant) {
+        c1 = (0.91f + 10 * expf(-3 * gamma) + 0.45f * cos_gamma * cos_gamma) * (cos_theta >= 0.01f ? 1 - expf(-0.32f / cos_theta) : 1.0f);
+    } else {
+        const float theta = acosf(clampf(cos_theta, -1, 1)), stheta = acosf(clampf(sun.y, -1, 1));
+        c1 = ((1.35f * sinf(5.631f - 3.59f * theta) + 3.12f) * sinf(4.396f - 2.6f * stheta) + 6.37f - theta) / 2.326f
+             * expf(gamma * (-0.563f) * ((2.629f - theta) * (1.562f - stheta) + 0.812f));
+    }
+    return cmul(scale, wmean(cmulf(zenith, p[9] * c1), cmulf(ground, p[10] * p[11])));
+}
+static bool sky_is_hemi(const igb200_light& l) { return !(l.flags & IGB200_SKYFLAG_HAS_GROUND); } // light/env.art:104-108
+
 static Color env_emission(const igb200_shading& sh, const igb200_light& l, V3 dir)
 {
+    if (l.type == IGB200_LIGHT_ENV_FUNCTION) { // light/env.art:49-57 (hemi), :94 (spherical)
+        const V3 local = mat3_mul(light_transform(l), dir);
+        if (sky_is_hemi(l) && !(local.y > flt_eps)) return black;
+        return sky_function(sh, l, local);
+    }
     if (l.type != IGB200_LIGHT_ENV_TEXTURED) return light_color(l);
     float u, v;
     map_env_uv(switch_env_up(mat3_mul(light_transform(l), dir)), u, v);
@@ -851,6 +889,10 @@ static Color env_emission(const igb200_shading& sh, const igb200_light& l, V3 di
 // Light::pdf_direct of an infinite light, solid angle (light/env.art:96,121-127,152)
 static float env_pdf(const igb200_shading& sh, const igb200_light& l, V3 dir)
 {
+    if (l.type == IGB200_LIGHT_ENV_FUNCTION && sky_is_hemi(l)) { // light/env.art:58-61
+        const float y = mat3_mul(light_transform(l), dir).y;
+        return y > flt_eps ? y / flt_pi : 0.0f; // cosine_hemisphere_pdf
+    }
     if (l.type != IGB200_LIGHT_ENV_TEXTURED || l.cdf == IGB200_NO_CDF) return 1 / (4 * flt_pi);
     const V3    ldir     = switch_env_up(mat3_mul(light_transform(l), dir));
     const float sinTheta = safe_sqrt(1 - ldir.z * ldir.z);
@@ -903,6 +945,22 @@ static DirectSample light_sample_direct(const Ctx& c, const igb200_light& l, Rnd
         const V3    d = equal_area_square_to_sphere(u, v);
         const float pdf = 1 / (4 * flt_pi);
         return DirectSample{ add(from.point, mulf(d, c.scene_radius)), d, cmulf(light_color(l), 1 / pdf), solid_pdf(pdf), 1.0f, c.scene_radius };
+    }
+    case IGB200_LIGHT_ENV_FUNCTION: {
+        const Mat3  tr = light_transform(l);
+        const float u  = rnd.next_f32();
+        const float v  = rnd.next_f32();
+        if (sky_is_hemi(l)) { // make_environment_light_function_hemi::sample_direct, light/env.art:32-38
+            const DirSample sm  = sample_cosine_hemisphere(u, v);
+            const V3        dir = switch_env_up(sm.dir);
+            const Color     in  = cmulf(sky_function(*c.sh, l, dir), 1 / sm.pdf);
+            const V3        gd  = mat3_left_mul(tr, dir);
+            return DirectSample{ add(from.point, mulf(gd, c.scene_radius)), gd, in, solid_pdf(sm.pdf), 1.0f, c.scene_radius };
+        }
+        const V3    d   = equal_area_square_to_sphere(u, v); // _spherical::sample_direct, light/env.art:82-86
+        const float pdf = 1 / (4 * flt_pi);
+        return DirectSample{ add(from.point, mulf(d, c.scene_radius)), d, cmulf(sky_function(*c.sh, l, mat3_mul(tr, d)), 1 / pdf), solid_pdf(pdf),
+                             1.0f, c.scene_radius };
     }
     case IGB200_LIGHT_ENV_TEXTURED: {
         const Mat3 tr = light_transform(l);

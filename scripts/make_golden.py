@@ -38,6 +38,11 @@ JOBS = [  # (fixture, scene file, reference image, width, height)
     ("two-planes-mirror", "evaluation/two-planes-mirror.json", "ref-two-planes-mirror-rad.exr", None, None),  # sphere light + mirror, Radiance reference
     # the scene of the reference's only published timings (scenes/radiance/office/benchmark.txt): fishlens camera, thin dielectric
     ("office", "radiance/office/office_scene.json", None, None, None),
+    # analytic CIE skies through the fishlens camera, against the Radiance (gensky) references
+    ("sky-uniform", "evaluation/sky-uniform.json", "ref-sky-uniform-rad.exr", None, None),
+    ("sky-cloudy", "evaluation/sky-cloudy.json", "ref-sky-cloudy-rad.exr", None, None),
+    ("sky-clear", "evaluation/sky-clear.json", "ref-sky-clear-rad.exr", None, None),
+    ("sky-intermediate", "evaluation/sky-intermediate.json", "ref-sky-intermediate-rad.exr", None, None),
     ("multilight-simple", "evaluation/multilight-simple.json", "ref-multilight-4096.exr", None, None),  # CDF ("simple") selector
     ("many-point-lights", "many_point_lights.json", None, 3840, 2160),  # BASELINE.json configs[4]
     # textured environment + 2-D CDF.  The shipped Mitsuba image (ref-env-4096.exr) is kept for the record but is NOT a

@@ -112,3 +112,25 @@ def test_loader_reads_the_office_scene_dialect(ig, tmp_path):
     r = ry @ rx
     assert np.allclose(sh.camera.eye, [1, 2, 3]) and np.allclose(sh.camera.dir, -r[:, 2], atol=1e-6) and np.allclose(sh.camera.up, r[:, 1], atol=1e-6)
     assert json.loads(sio._strip_json_comments('{"a": "// not a comment", "b": [1, 2,], }')) == {"a": "// not a comment", "b": [1, 2]}
+
+
+@pytest.mark.parametrize("kind,variant,has_ground", [(0, True, True), (1, True, True), (1, False, False), (0, False, False)])
+def test_sky_function_sampling_is_consistent_with_its_emission(ig, oracle, kind, variant, has_ground):
+    """make_environment_light_function (light/env.art:24-108): next event estimation (sample_direct + pdf_direct, sphere or
+    cosine-hemisphere sampling) and pure BSDF sampling (emission on miss) must estimate the same image."""
+    from render_common import flat_scene
+    tables, sh = flat_scene(ig, "none", 48, one_sided=True, depth=2)  # |cos| + sphere NEE lights the back side too (DESIGN 4.1 note 2)
+    sun = np.array([0.3, 0.5, -0.8])
+    sh.add_sky_function(kind, variant, has_ground, scale=(1, 1, 1), zenith=(1.0, 0.9, 0.8), ground=(0.3, 0.4, 0.2), zenith_brightness=1.7,
+                        ground_brightness=0.2, c2=0.9, sun_dir=sun / np.linalg.norm(sun),
+                        transform=np.array([[1, 0, 0], [0, 0, -1], [0, 1, 0]], float))   # tilt the sky: its up axis is world -z
+    assert sh.infinite[0].type == ig.shading.LIGHT_ENV_FUNCTION
+    osc = oracle.OracleScene(tables)
+    means = []
+    for nee in (True, False):
+        sh.technique.enable_nee = int(nee)
+        film = osc.render(sh, 48, 48, spi=64, iterations=4, seed=4) / 4
+        assert np.all(np.isfinite(film)) and film.min() >= 0
+        means.append(film.reshape(-1, 3).mean(axis=0))
+    assert means[0].max() > 0.05
+    assert np.allclose(means[0], means[1], rtol=2e-2)

@@ -82,6 +82,10 @@ def test_spot_light_against_quadrature(ig, oracle):
     ("sphere-light-ico", False, 1024, 2e-3),      # icosphere mesh as area light; predef_eps "sphere-light-ico"
     ("sphere-light-pure", False, 256, 3e-3),      # make_sphere_area_emitter; predef_eps "sphere-light-pure"
     ("two-planes-mirror", False, 256, 1e-3),      # sphere emitter + mirror against the Radiance reference
+    ("sky-uniform", False, 16, 1e-3),             # make_cie_sky_light through the fishlens camera vs gensky -u
+    ("sky-cloudy", False, 16, 1e-3),              # ... -c
+    ("sky-clear", False, 16, 1e-3),               # make_cie_sunny_light, sun position from date / time / place vs gensky +s
+    ("sky-intermediate", False, 16, 1e-3),        # ... +i
 ])
 def test_golden_images(ig, oracle, name, one_sided, spp, threshold):
     tables, sh, w, h, ref = load_golden(ig, name)
