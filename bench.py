@@ -265,7 +265,7 @@ def run_reference(args, rank, world):
         c5 = oracle_samples_per_s(pkg, 8.0, "c5-many-point-lights")
         line["path_tracer_c5"] = {"workload": "c5-many-point-lights", "metric": "path-traced samples/s", "unit": "Msamples/s",
                                   "value": c5["value"], "e2e_value": c5["value"], "cpu_baseline": c5}
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
 
 
 def run_ours(args, rank, world, local_rank):
@@ -274,9 +274,6 @@ def run_ours(args, rank, world, local_rank):
 
     torch.cuda.set_device(local_rank)
     if world > 1:
-        # NCCL prints its version banner to STDOUT at NCCL_DEBUG=VERSION; stdout carries exactly one JSON line
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     pkg = load_pkg()
     W = pkg.workloads
@@ -462,12 +459,31 @@ def run_ours(args, rank, world, local_rank):
             c5["cpu_baseline"] = oracle_samples_per_s(pkg, 8.0, "c5-many-point-lights") if world == 1 else None
             line["path_tracer_c5"] = c5
             line["gpu_launches"] += c5["gpu_launches"]
-        print(json.dumps(line), flush=True)
+        emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def reserve_stdout():
+    """stdout carries exactly ONE JSON line: libraries that chat on fd 1 (NCCL prints its version banner there when the
+    first communicator is created) are sent to stderr for the whole run; emit() writes to the real stdout."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(line + "\n")
+    out.flush()
+
+
 def main():
+    reserve_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
