@@ -592,7 +592,7 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
             const bool inf = ls[i].type == IGB200_LIGHT_ENV || ls[i].type == IGB200_LIGHT_DIRECTIONAL || ls[i].type == IGB200_LIGHT_ENV_TEXTURED ||
                              ls[i].type == IGB200_LIGHT_ENV_FUNCTION;
             if (ls[i].type == IGB200_LIGHT_ENV_FUNCTION &&
-                (ls[i].tex > IGB200_SKY_CIE_SUNNY || (uint64_t)ls[i].cdf * 4 + 64 > sh->blob_bytes))
+                (ls[i].tex > IGB200_SKY_PEREZ || (uint64_t)ls[i].cdf * 4 + 64 > sh->blob_bytes))
                 return fail(IGB200_E_INVALID, "sky light %llu: unknown function or parameters outside the blob", (unsigned long long)i);
             if (ls[i].type == IGB200_LIGHT_ENV_TEXTURED) {
                 if (ls[i].tex >= sh->texture_count) return fail(IGB200_E_INVALID, "environment light %llu: texture out of range", (unsigned long long)i);

@@ -184,6 +184,14 @@ static __device__ __noinline__ Color sky_function(const uint8_t* blob, const igb
         return cadd(cmulf(cmulf(zenith, c1), f1), cmulf(cmulf(ground, __ldg(p + 10) * c2), f2));
     }
     const Vec3  sun{ __ldg(p + 12), __ldg(p + 13), __ldg(p + 14) };
+    if (l.tex == IGB200_SKY_PEREZ) { // calc_perez + make_perez_light, light/cie.art:45-57 (zenith slot = lum)
+        const float a = __ldg(p + 9), b = __ldg(p + 10), c_ = __ldg(p + 11), d = __ldg(p + 15), e = __ldg(p + 0);
+        const float sun_c = clampf(dot3(dir, sun), -1.0f, 1.0f);
+        const float sun_a = acosf(sun_c);
+        const float A = 1.0f + a * expf(__fdiv_rn(b, fmaxf(0.01f, cos_theta)));
+        const float B = 1.0f + c_ * expf(d * sun_a) + e * sun_c * sun_c;
+        return cadd(cmulf(cmulf(zenith, A * B), f1), cmulf(ground, f2));
+    }
     const float cos_gamma = dot3(dir, sun);
     const float gamma     = acosf(clampf(cos_gamma, -1.0f, 1.0f));
     float       c1;
@@ -197,7 +205,8 @@ static __device__ __noinline__ Color sky_function(const uint8_t* blob, const igb
     }
     return cmul(scale, cadd(cmulf(cmulf(zenith, __ldg(p + 9) * c1), f1), cmulf(cmulf(ground, __ldg(p + 10) * __ldg(p + 11)), f2)));
 }
-__device__ __forceinline__ bool sky_is_hemi(const igb200_light& l) { return !(l.flags & IGB200_SKYFLAG_HAS_GROUND); } // light/env.art:104-108
+// half = !has_ground for the CIE skies (light/cie.art:19,42), always false for the Perez sky (:57); light/env.art:104-108
+__device__ __forceinline__ bool sky_is_hemi(const igb200_light& l) { return !(l.flags & IGB200_SKYFLAG_HAS_GROUND) && l.tex != IGB200_SKY_PEREZ; }
 template <bool EXT>
 __device__ __forceinline__ Color env_emission(const ShadeScene& sc, const igb200_light& l, Vec3 dir)
 {

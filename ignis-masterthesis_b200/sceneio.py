@@ -774,6 +774,94 @@ def cie_sky_parameters(light, kind):
     return out
 
 
+# ---- Perez all-weather sky: runtime/skysun/PerezModel.cpp (coefficients of Perez, Seals, Michalsky 1993) ----
+_PEREZ_RANGES = (1.000, 1.065, 1.230, 1.500, 1.950, 2.800, 4.500, 6.200, float("inf"))
+_PEREZ = {
+    "a": (1.3525, -0.2576, -0.2690, -1.4366, -1.2219, -0.7730, 1.4148, 1.1016, -1.1000, -0.2515, 0.8952, 0.0156, -0.5484, -0.6654, -0.2672, 0.7117,
+          -0.6000, -0.3566, -2.5000, 2.3250, -1.0156, -0.3670, 1.0078, 1.4051, -1.0000, 0.0211, 0.5025, -0.5119, -1.0500, 0.0289, 0.4260, 0.3590),
+    "b": (-0.7670, 0.0007, 1.2734, -0.1233, -0.2054, 0.0367, -3.9128, 0.9156, 0.2782, -0.1812, -4.5000, 1.1766, 0.7234, -0.6219, -5.6812, 2.6297,
+          0.2937, 0.0496, -5.6812, 1.8415, 0.2875, -0.5328, -3.8500, 3.3750, -0.3000, 0.1922, 0.7023, -1.6317, -0.3250, 0.1156, 0.7781, 0.0025),
+    "c": (2.8000, 0.6004, 1.2375, 1.0000, 6.9750, 0.1774, 6.4477, -0.1239, 24.7219, -13.0812, -37.7000, 34.8438, 33.3389, -18.3000, -62.2500, 52.0781,
+          21.0000, -4.7656, -21.5906, 7.2492, 14.0000, -0.9999, -7.1406, 7.5469, 19.0000, -5.0000, 1.2438, -1.9094, 31.0625, -14.5000, -46.1148, 55.3750),
+    "d": (1.8734, 0.6297, 0.9738, 0.2809, -1.5798, -0.5081, -1.7812, 0.1080, -5.0000, 1.5218, 3.9229, -2.6204, -3.5000, 0.0016, 1.1477, 0.1062,
+          -3.5000, -0.1554, 1.4062, 0.3988, -3.4000, -0.1078, -1.0750, 1.5702, -4.0000, 0.0250, 0.3844, 0.2656, -7.2312, 0.4050, 13.3500, 0.6234),
+    "e": (0.0356, -0.1246, -0.5718, 0.9938, 0.2624, 0.0672, -0.2190, -0.4285, -0.0156, 0.1597, 0.4199, -0.5562, 0.4659, -0.3296, -0.0876, -0.0329,
+          0.0032, 0.0766, -0.0656, -0.1294, -0.0672, 0.4016, 0.3017, -0.4844, 1.0468, -0.3788, -2.4517, 1.4656, 1.5000, -0.6426, 1.8564, 0.5636),
+}
+_SOLAR_E, _SOLAR_L = 1367.0, 127500.0  # skysun/Illuminance.h
+
+
+def _perez_air_mass(z):  # computeAirMass, PerezModel.cpp:184-188
+    zd = min(math.degrees(z), 90.0)
+    return 1 / (math.cos(math.radians(zd)) + 0.15 * math.exp(math.log(93.885 - zd) * -1.253))
+
+
+def _perez_eccentricity(day):  # computeEccentricity :190-194
+    a = 2 * math.pi * min(max(day / 365.0, 0.0), 1.0)
+    return 1.00011 + 0.034221 * math.cos(a) + 0.00128 * math.sin(a) + 0.000719 * math.cos(2 * a) + 0.000077 * math.sin(2 * a)
+
+
+def perez_from_sky(brightness, clearness, z):  # PerezModel::fromSky :146-182
+    if 1.065 < clearness < 2.8 and brightness < 0.2:
+        brightness = 0.2
+    brightness = min(max(brightness, 0.01), 0.6)
+    bin_ = next((k for k in range(8) if _PEREZ_RANGES[k] <= clearness < _PEREZ_RANGES[k + 1]), 8)
+    if bin_ >= 8:  # clearness below 1: the reference reads past its tables; refuse instead
+        raise ValueError("perez: sky clearness outside [1, inf)")
+    lin = lambda x: x[0] + x[1] * z + brightness * (x[2] + x[3] * z)
+    row = lambda k: _PEREZ[k][4 * bin_:4 * bin_ + 4]
+    sc, sd = _PEREZ["c"], _PEREZ["d"]
+    c = lin(row("c")) if bin_ > 0 else math.exp(math.pow(brightness * (sc[0] + sc[1] * z), sc[2])) - sc[3]
+    d = lin(row("d")) if bin_ > 0 else -math.exp(brightness * (sd[0] + sd[1] * z)) + sd[2] + brightness * sd[3]
+    return lin(row("a")), lin(row("b")), c, d, lin(row("e"))
+
+
+def perez_eval(p, cos_sun, cos_theta):  # PerezModel::eval :66-72
+    a, b, c, d, e = p
+    return (1 + a * math.exp(b / max(0.01, cos_theta))) * (1 + c * math.exp(d * math.acos(cos_sun)) + e * cos_sun * cos_sun)
+
+
+def perez_integrate(p, z):  # PerezModel::integrate :74-118: Radiance's 145-patch base
+    rows = ((84, 30), (72, 30), (60, 24), (48, 24), (36, 18), (24, 12), (12, 6), (0, 1))
+    cs, ss, total = math.cos(z), math.sin(z), 0.0
+    for theta, n in rows:
+        ct, st = math.cos(math.radians(theta)), math.sin(math.radians(theta))
+        for k in range(n):
+            cp = math.cos(math.radians(360.0 / n * k))
+            total += perez_eval(p, min(1.0, cs * ct + ss * st * cp), ct) * ct
+    return 2 * math.pi * total / 145
+
+
+def perez_sky_parameters(light):
+    """PerezLight::serialize / getModel (runtime/light/PerezLight.cpp:25-110): sun direction, (a..e), luminance colour, ground."""
+    import datetime
+    el, az = light_ea(light)
+    sun = np.array([math.cos(el) * math.sin(az), math.sin(el), -math.cos(el) * math.cos(az)], np.float32)
+    z = math.acos(min(1.0, max(-1.0, float(sun[1]))))
+    day = datetime.date(int(light.get("year", 2020)), int(light.get("month", 5)), int(light.get("day", 6))).timetuple().tm_yday - 1  # tm_yday
+    if "clearness" in light or "brightness" in light:
+        br = light.get("brightness", 0.2)
+        model = perez_from_sky(br, light.get("clearness", 1.0), z)
+        diff = br * _SOLAR_E * _perez_eccentricity(day) / _perez_air_mass(z)
+    elif "direct_irradiance" in light or "diffuse_irradiance" in light or "direct_illuminance" in light or "diffuse_illuminance" in light:
+        if "direct_irradiance" in light or "diffuse_irradiance" in light:
+            dif, dirr = light.get("diffuse_irradiance", 1.0), light.get("direct_irradiance", 1.0)
+        else:
+            dif, dirr = (light.get(k, 1.0) * _SOLAR_E / _SOLAR_L for k in ("diffuse_illuminance", "direct_illuminance"))
+        a3 = 1.041 * z ** 3
+        model = perez_from_sky(dif * _perez_air_mass(z) / (_SOLAR_E * _perez_eccentricity(day)), ((dif + dirr) / dif + a3) / (1 + a3), z)
+        diff = dif
+    else:
+        model, diff = tuple(light.get(k, 1.0) for k in "abcde"), 1.0
+    diffnorm = diff / perez_integrate(model, z)
+    if "luminance" in light:
+        lum = _color(light.get("luminance"), 1.0) * np.float32(diffnorm)
+    else:
+        sin_el = min(1.0, max(-1.0, -float(sun[1])))
+        lum = _color(light.get("zenith"), 1.0) * np.float32(perez_eval(model, sin_el, 1.0) * diffnorm)  # calc_perez(sin_elevation, 1, ...)
+    return sun, model, lum, _color(light.get("ground"), 1.0), bool(light.get("has_ground", True))
+
+
 def bake_sky(light, hosek_lib):
     """SkyModel::SkyModel (src/runtime/skysun/SkyModel.cpp:9-55) at RES_AZ x RES_EL = 512 x 256 over the reference's own
     ArHosekSkyModel (compiled from the reference tree into oracle/_ref/libhosek.so), followed by the EXR round trip of
@@ -1067,6 +1155,10 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
             sh.add_sky_function(1 if sunny else 0, q.get("clear", False) if sunny else ty == "ciecloudy", q["has_ground"], q["scale"], q["zenith"],
                                 q["ground"], q.get("zenith_brightness", 1.0), q["ground_brightness"], q.get("c2", 1.0), q["sun_dir"],
                                 np.linalg.inv(m3.T))
+        elif ty == "perez":
+            sun, model, lum, ground, has_ground = perez_sky_parameters(l)
+            m3 = parse_transform(l.get("transform"))[:3, :3]
+            sh.add_perez_sky(sun, lum, ground, model, has_ground, np.linalg.inv(m3.T))
         elif ty == "area":
             name = l["entity"]
             ent = next(e for e in scene["entities"] if e["name"] == name)

@@ -15,7 +15,7 @@ BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_MIRROR, BSDF_CONDUCTOR, BSDF_BUMPMAP, BSDF_T
 CAMERA_PERSPECTIVE, CAMERA_FISHLENS = 0, 1
 LIGHT_POINT, LIGHT_ENV, LIGHT_AREA_SHAPE, LIGHT_AREA_PLANE, LIGHT_SPOT, LIGHT_DIRECTIONAL, LIGHT_ENV_TEXTURED = 0, 1, 2, 3, 4, 5, 6
 LIGHT_AREA_SPHERE, LIGHT_ENV_FUNCTION = 7, 8
-SKY_CIE, SKY_CIE_SUNNY = 0, 1
+SKY_CIE, SKY_CIE_SUNNY, SKY_PEREZ = 0, 1, 2
 SKYFLAG_VARIANT, SKYFLAG_HAS_GROUND = 1, 2
 TEX_CHECKERBOARD, TEX_IMAGE = 0, 1
 FILTER_NEAREST, FILTER_BILINEAR, FILTER_BICUBIC = 0, 1, 2
@@ -386,6 +386,19 @@ class Shading:
         self.infinite[i].tex = kind
         self.infinite[i].cdf = self._blob_append(params.tobytes()) // 4
         self.infinite[i].flags = (SKYFLAG_VARIANT if variant else 0) | (SKYFLAG_HAS_GROUND if has_ground else 0)
+        return i
+
+    def add_perez_sky(self, sun_dir, lum, ground, abcde, has_ground=True, transform=None):
+        """make_perez_light (light/cie.art:52-57); make_environment_light_function is called with half = false there."""
+        a, b, c, d, e = [float(x) for x in abcde]
+        i = self.add_sky_function(SKY_PEREZ, False, True, scale=(e, 0, 0), zenith=lum, ground=ground, zenith_brightness=a, ground_brightness=b,
+                                  c2=c, sun_dir=sun_dir, transform=transform)
+        blob = np.frombuffer(self.blob, np.float32)  # writable view on the bytearray
+        blob[self.infinite[i].cdf + 15] = d
+        if has_ground:
+            self.infinite[i].flags |= SKYFLAG_HAS_GROUND
+        else:
+            self.infinite[i].flags &= ~SKYFLAG_HAS_GROUND
         return i
 
     def add_sphere_area_light(self, entity, radiance, origin, radius):

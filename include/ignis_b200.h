@@ -264,6 +264,8 @@ typedef struct igb200_material {
                                       (light/cie.art:9-42) */
 #define IGB200_SKY_CIE       0u /* cieuniform / ciecloudy (flag VARIANT = cloudy)          light/cie.art:10-19 */
 #define IGB200_SKY_CIE_SUNNY 1u /* cieclear (flag VARIANT = is_clear) / cieintermediate    light/cie.art:22-42 */
+#define IGB200_SKY_PEREZ     2u /* make_perez_light(sun_dir = [12..14], lum = [3..5], ground = [6..8], a b c d e = [9], [10], [11],
+                                   [15], [0])                                        light/cie.art:45-57, runtime/light/PerezLight.cpp:58-110 */
 #define IGB200_SKYFLAG_VARIANT    0x1u
 #define IGB200_SKYFLAG_HAS_GROUND 0x2u
 #define IGB200_NO_CDF 0xFFFFFFFFu

@@ -860,6 +860,14 @@ static Color sky_function(const igb200_shading& sh, const igb200_light& l, V3 di
         return wmean(cmulf(zenith, c1), cmulf(ground, p[10] * c2));
     }
     const V3    sun = v3(p[12], p[13], p[14]);
+    if (l.tex == IGB200_SKY_PEREZ) { // calc_perez + make_perez_light, light/cie.art:45-57 (zenith slot = lum)
+        const float a = p[9], b = p[10], c_ = p[11], d = p[15], e = p[0];
+        const float sun_c = clampf(dot(dir, sun), -1, 1);
+        const float sun_a = acosf(sun_c);
+        const float A = 1 + a * expf(b / fmaxf(0.01f, cos_theta));
+        const float B = 1 + c_ * expf(d * sun_a) + e * sun_c * sun_c;
+        return wmean(cmulf(zenith, A * B), ground);
+    }
     const float cos_gamma = dot(dir, sun);
     const float gamma     = acosf(clampf(cos_gamma, -1, 1));
     float       c1;
@@ -872,7 +880,8 @@ static Color sky_function(const igb200_shading& sh, const igb200_light& l, V3 di
     }
     return cmul(scale, wmean(cmulf(zenith, p[9] * c1), cmulf(ground, p[10] * p[11])));
 }
-static bool sky_is_hemi(const igb200_light& l) { return !(l.flags & IGB200_SKYFLAG_HAS_GROUND); } // light/env.art:104-108
+// half = !has_ground for the CIE skies (light/cie.art:19,42), always false for the Perez sky (:57); light/env.art:104-108
+static bool sky_is_hemi(const igb200_light& l) { return !(l.flags & IGB200_SKYFLAG_HAS_GROUND) && l.tex != IGB200_SKY_PEREZ; }
 
 static Color env_emission(const igb200_shading& sh, const igb200_light& l, V3 dir)
 {

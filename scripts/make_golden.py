@@ -43,6 +43,7 @@ JOBS = [  # (fixture, scene file, reference image, width, height)
     ("sky-cloudy", "evaluation/sky-cloudy.json", "ref-sky-cloudy-rad.exr", None, None),
     ("sky-clear", "evaluation/sky-clear.json", "ref-sky-clear-rad.exr", None, None),
     ("sky-intermediate", "evaluation/sky-intermediate.json", "ref-sky-intermediate-rad.exr", None, None),
+    ("sky-perez1", "evaluation/sky-perez1.json", "ref-sky-perez1-rad.exr", None, None),  # Perez all-weather sky vs gendaylit
     ("multilight-simple", "evaluation/multilight-simple.json", "ref-multilight-4096.exr", None, None),  # CDF ("simple") selector
     ("many-point-lights", "many_point_lights.json", None, 3840, 2160),  # BASELINE.json configs[4]
     # textured environment + 2-D CDF.  The shipped Mitsuba image (ref-env-4096.exr) is kept for the record but is NOT a

@@ -114,16 +114,20 @@ def test_loader_reads_the_office_scene_dialect(ig, tmp_path):
     assert json.loads(sio._strip_json_comments('{"a": "// not a comment", "b": [1, 2,], }')) == {"a": "// not a comment", "b": [1, 2]}
 
 
-@pytest.mark.parametrize("kind,variant,has_ground", [(0, True, True), (1, True, True), (1, False, False), (0, False, False)])
+@pytest.mark.parametrize("kind,variant,has_ground", [(0, True, True), (1, True, True), (1, False, False), (0, False, False), (2, False, True), (2, False, False)])
 def test_sky_function_sampling_is_consistent_with_its_emission(ig, oracle, kind, variant, has_ground):
     """make_environment_light_function (light/env.art:24-108): next event estimation (sample_direct + pdf_direct, sphere or
     cosine-hemisphere sampling) and pure BSDF sampling (emission on miss) must estimate the same image."""
     from render_common import flat_scene
     tables, sh = flat_scene(ig, "none", 48, one_sided=True, depth=2)  # |cos| + sphere NEE lights the back side too (DESIGN 4.1 note 2)
     sun = np.array([0.3, 0.5, -0.8])
-    sh.add_sky_function(kind, variant, has_ground, scale=(1, 1, 1), zenith=(1.0, 0.9, 0.8), ground=(0.3, 0.4, 0.2), zenith_brightness=1.7,
-                        ground_brightness=0.2, c2=0.9, sun_dir=sun / np.linalg.norm(sun),
-                        transform=np.array([[1, 0, 0], [0, 0, -1], [0, 1, 0]], float))   # tilt the sky: its up axis is world -z
+    tilt = np.array([[1, 0, 0], [0, 0, -1], [0, 1, 0]], float)                       # tilt the sky: its up axis is world -z
+    if kind == 2:  # Perez: always sphere sampling, black below the horizon without ground
+        sh.add_perez_sky(sun / np.linalg.norm(sun), (1.0, 0.9, 0.8), (0.3, 0.4, 0.2), (-1.0, -0.32, 6.0, -3.0, 0.3), has_ground, tilt)
+        assert bool(sh.infinite[0].flags & ig.shading.SKYFLAG_HAS_GROUND) == has_ground and sh.infinite[0].tex == ig.shading.SKY_PEREZ
+    else:
+        sh.add_sky_function(kind, variant, has_ground, scale=(1, 1, 1), zenith=(1.0, 0.9, 0.8), ground=(0.3, 0.4, 0.2), zenith_brightness=1.7,
+                            ground_brightness=0.2, c2=0.9, sun_dir=sun / np.linalg.norm(sun), transform=tilt)
     assert sh.infinite[0].type == ig.shading.LIGHT_ENV_FUNCTION
     osc = oracle.OracleScene(tables)
     means = []

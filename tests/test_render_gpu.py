@@ -134,6 +134,7 @@ def test_flat_scene_closed_forms_full_size(ig, dev, light, one_sided, expected, 
     ("sky-cloudy", False, 64, 1e-3),
     ("sky-clear", False, 64, 1e-3),
     ("sky-intermediate", False, 64, 1e-3),
+    ("sky-perez1", False, 64, 1e-3),                # make_perez_light, coefficients from irradiances (PerezModel.cpp) vs gendaylit
 ])
 def test_golden_images(ig, dev, name, one_sided, spp, threshold):
     tables, sh, w, h, ref = load_golden(ig, name)
@@ -312,13 +313,17 @@ def test_errors(ig, dev):
         fresh.close()
 
 
-@pytest.mark.parametrize("kind,variant,has_ground", [(0, True, True), (1, True, True), (1, False, False)])
+@pytest.mark.parametrize("kind,variant,has_ground", [(0, True, True), (1, True, True), (1, False, False), (2, False, True)])
 def test_sky_function_lights_match_oracle(ig, oracle, dev, kind, variant, has_ground):
     # make_cie_sky_light / make_cie_sunny_light over make_environment_light_function (sphere and hemisphere sampling)
     tables, sh = room_scene(ig, 96, depth=4)
     sun = np.array([0.3, 0.5, -0.8])
-    sh.add_sky_function(kind, variant, has_ground, zenith=(1.0, 0.9, 0.8), ground=(0.3, 0.4, 0.2), zenith_brightness=1.7, c2=0.9,
-                        sun_dir=sun / np.linalg.norm(sun), transform=np.array([[1, 0, 0], [0, 0, -1], [0, 1, 0]], float))
+    tilt = np.array([[1, 0, 0], [0, 0, -1], [0, 1, 0]], float)
+    if kind == 2:
+        sh.add_perez_sky(sun / np.linalg.norm(sun), (1.0, 0.9, 0.8), (0.3, 0.4, 0.2), (-1.0, -0.32, 6.0, -3.0, 0.3), has_ground, tilt)
+    else:
+        sh.add_sky_function(kind, variant, has_ground, zenith=(1.0, 0.9, 0.8), ground=(0.3, 0.4, 0.2), zenith_brightness=1.7, c2=0.9,
+                            sun_dir=sun / np.linalg.norm(sun), transform=tilt)
     film, stats = _render(dev, tables, sh, 96, 96, 4, 2, seed=13)
     osc = oracle.OracleScene(tables)
     ref = osc.render(sh, 96, 96, spi=4, iterations=2, seed=13)

@@ -86,6 +86,7 @@ def test_spot_light_against_quadrature(ig, oracle):
     ("sky-cloudy", False, 16, 1e-3),              # ... -c
     ("sky-clear", False, 16, 1e-3),               # make_cie_sunny_light, sun position from date / time / place vs gensky +s
     ("sky-intermediate", False, 16, 1e-3),        # ... +i
+    ("sky-perez1", False, 16, 1e-3),                # make_perez_light, coefficients from irradiances (PerezModel.cpp) vs gendaylit
 ])
 def test_golden_images(ig, oracle, name, one_sided, spp, threshold):
     tables, sh, w, h, ref = load_golden(ig, name)
