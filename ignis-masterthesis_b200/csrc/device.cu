@@ -590,7 +590,7 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
         const uint64_t      n  = t ? sh->finite_light_count : sh->infinite_light_count;
         for (uint64_t i = 0; i < n; ++i) {
             const bool inf = ls[i].type == IGB200_LIGHT_ENV || ls[i].type == IGB200_LIGHT_DIRECTIONAL || ls[i].type == IGB200_LIGHT_ENV_TEXTURED ||
-                             ls[i].type == IGB200_LIGHT_ENV_FUNCTION;
+                             ls[i].type == IGB200_LIGHT_ENV_FUNCTION || ls[i].type == IGB200_LIGHT_SUN;
             if (ls[i].type == IGB200_LIGHT_ENV_FUNCTION &&
                 (ls[i].tex > IGB200_SKY_PEREZ || (uint64_t)ls[i].cdf * 4 + 64 > sh->blob_bytes))
                 return fail(IGB200_E_INVALID, "sky light %llu: unknown function or parameters outside the blob", (unsigned long long)i);
@@ -604,7 +604,7 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
                         return fail(IGB200_E_INVALID, "environment light %llu: CDF exceeds the blob", (unsigned long long)i);
                 }
             }
-            if (ls[i].type > IGB200_LIGHT_ENV_FUNCTION || inf != (t == 0))
+            if (ls[i].type > IGB200_LIGHT_SUN || inf != (t == 0))
                 return fail(IGB200_E_INVALID, "%s light %llu has type %u", t ? "finite" : "infinite", (unsigned long long)i, ls[i].type);
             if ((ls[i].type == IGB200_LIGHT_AREA_SHAPE || ls[i].type == IGB200_LIGHT_AREA_PLANE || ls[i].type == IGB200_LIGHT_AREA_SPHERE) &&
                 (ls[i].entity < 0 || (uint64_t)ls[i].entity >= dev->entity_count))
@@ -651,7 +651,9 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
             s.extended = 1;
     }
     for (uint64_t i = 0; i < sh->infinite_light_count; ++i)
-        if (sh->infinite_lights[i].type == IGB200_LIGHT_ENV_TEXTURED || sh->infinite_lights[i].type == IGB200_LIGHT_ENV_FUNCTION) s.extended = 1;
+        if (sh->infinite_lights[i].type == IGB200_LIGHT_ENV_TEXTURED || sh->infinite_lights[i].type == IGB200_LIGHT_ENV_FUNCTION ||
+            sh->infinite_lights[i].type == IGB200_LIGHT_SUN)
+            s.extended = 1;
     for (uint64_t i = 0; i < sh->finite_light_count; ++i)
         if (sh->finite_lights[i].type == IGB200_LIGHT_AREA_SPHERE) s.extended = 1; // the sphere emitter lives in the extended kernel
     {

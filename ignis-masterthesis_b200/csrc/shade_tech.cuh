@@ -10,11 +10,12 @@ struct DirectSample { Vec3 pos, dir; Color intensity; Pdf pdf; float cos, dist; 
 
 __device__ __forceinline__ bool light_delta(uint32_t type)
 {
-    return type == IGB200_LIGHT_POINT || type == IGB200_LIGHT_SPOT || type == IGB200_LIGHT_DIRECTIONAL;
+    return type == IGB200_LIGHT_POINT || type == IGB200_LIGHT_SPOT || type == IGB200_LIGHT_DIRECTIONAL || type == IGB200_LIGHT_SUN;
 }
 __device__ __forceinline__ bool light_infinite(uint32_t type)
 {
-    return type == IGB200_LIGHT_ENV || type == IGB200_LIGHT_DIRECTIONAL || type == IGB200_LIGHT_ENV_TEXTURED || type == IGB200_LIGHT_ENV_FUNCTION;
+    return type == IGB200_LIGHT_ENV || type == IGB200_LIGHT_DIRECTIONAL || type == IGB200_LIGHT_ENV_TEXTURED || type == IGB200_LIGHT_ENV_FUNCTION ||
+           type == IGB200_LIGHT_SUN;
 }
 __device__ __forceinline__ Color light_color(const igb200_light& l) { return Color{ l.color[0], l.color[1], l.color[2] }; }
 
@@ -314,6 +315,28 @@ __device__ __forceinline__ DirectSample light_sample_direct(const ShadeScene& sc
         const Vec3 dir{ l.v[0], l.v[1], l.v[2] };
         return DirectSample{ vadd(from.point, vmulf(dir, -sc.scene_radius)), vneg(dir), light_color(l), Pdf{ 1.0f, 0 }, 1.0f,
                              sc.scene_radius };
+    }
+    case IGB200_LIGHT_SUN: { // make_sun_light::sample_direct, light/sun.art:11-15 (sample_uniform_cone, core/sampling.art:106-116)
+        if (!EXT) break;
+        const Vec3  dir{ l.v[0], l.v[1], l.v[2] };
+        const float cos_angle  = l.v[3];
+        const float sun_radius = __fdiv_rn(__fsqrt_rn(1.0f - cos_angle * cos_angle), cos_angle), sun_area = flt_pi * sun_radius * sun_radius;
+        const float u = rnd.next_f32();
+        const float v = rnd.next_f32();
+        float       px, py; // square_to_concentric_disk, core/warp.art:2-22
+        {
+            const float a = 2.0f * u - 1.0f, b = 2.0f * v - 1.0f;
+            if (a == 0.0f && b == 0.0f) { px = 0.0f; py = 0.0f; }
+            else if (a * a > b * b) { const float phi = __fdiv_rn(flt_pi, 4.0f) * safe_div(b, a); px = cosf(phi) * a; py = sinf(phi) * a; }
+            else { const float phi = __fdiv_rn(flt_pi, 2.0f) - __fdiv_rn(flt_pi, 4.0f) * safe_div(a, b); px = cosf(phi) * b; py = sinf(phi) * b; }
+        }
+        const float c1 = 1.0f - cos_angle, n2 = px * px + py * py;
+        const float z  = cos_angle + c1 * (1.0f - n2), sc = safe_sqrt(c1 * (2.0f - c1 * n2));
+        const float den = 2.0f * flt_pi * (1.0f - cos_angle);
+        const float pdf = fabsf(den) <= flt_eps ? 1.0f : __fdiv_rn(1.0f, den); // uniform_cone_pdf: safe_div_one
+        const Vec3  ndir = mat3_mul(make_orthonormal(dir), Vec3{ px * sc, py * sc, z });
+        return DirectSample{ Vec3{ 0.0f, 0.0f, 0.0f }, vneg(ndir), cmulf(light_color(l), __fdiv_rn(1.0f, sun_area * pdf)), Pdf{ 1.0f, 0 }, z,
+                             __int_as_float(0x7f800000) };
     }
     case IGB200_LIGHT_ENV: { // make_environment_light_function_spherical::sample_direct, light/env.art:82-86
         const float u   = rnd.next_f32();

@@ -1121,6 +1121,10 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
             f = 2 * math.pi * (1 - 0.5 * math.cos(math.radians(falloff)) - 0.5 * math.cos(math.radians(cutoff)))
             d = np.asarray(l.get("direction", (0, 0, 1)), np.float64)
             hier.append((l.get("position", (0, 0, 0)), d / np.linalg.norm(d), float(np.mean(c) * f)))
+        elif ty == "sun":  # SunLight.cpp:8-46: direction through LoaderUtils::getDirection (EA round trip), angle 11.4 degrees unless `radius`
+            el, az = light_ea(l)
+            d = (math.cos(el) * math.sin(az), math.sin(el), -math.cos(el) * math.cos(az))
+            sh.add_sun_light(d, _color(l.get("irradiance"), 1.0), l.get("angle", 11.4), l.get("radius"))
         elif ty in ("directional", "direction", "distant"):
             sh.add_directional_light(l.get("direction", (0, 0, 1)), _color(l.get("irradiance"), 1.0))
         elif ty in ("env", "envmap", "uniform", "constant"):

@@ -14,7 +14,7 @@ import numpy as np
 BSDF_DIFFUSE, BSDF_DIELECTRIC, BSDF_MIRROR, BSDF_CONDUCTOR, BSDF_BUMPMAP, BSDF_THIN_DIELECTRIC = 0, 1, 2, 3, 4, 5
 CAMERA_PERSPECTIVE, CAMERA_FISHLENS = 0, 1
 LIGHT_POINT, LIGHT_ENV, LIGHT_AREA_SHAPE, LIGHT_AREA_PLANE, LIGHT_SPOT, LIGHT_DIRECTIONAL, LIGHT_ENV_TEXTURED = 0, 1, 2, 3, 4, 5, 6
-LIGHT_AREA_SPHERE, LIGHT_ENV_FUNCTION = 7, 8
+LIGHT_AREA_SPHERE, LIGHT_ENV_FUNCTION, LIGHT_SUN = 7, 8, 9
 SKY_CIE, SKY_CIE_SUNNY, SKY_PEREZ = 0, 1, 2
 SKYFLAG_VARIANT, SKYFLAG_HAS_GROUND = 1, 2
 TEX_CHECKERBOARD, TEX_IMAGE = 0, 1
@@ -356,6 +356,13 @@ class Shading:
         d = np.asarray(direction, np.float64)
         d = (d / np.linalg.norm(d)).astype(np.float32)
         return self._light(self.infinite, LIGHT_DIRECTIONAL, irradiance, tuple(d))
+
+    def add_sun_light(self, direction, irradiance=(1, 1, 1), angle_deg=11.4, radius=None):
+        """make_sun_light (light/sun.art:4-28); cos_sun_angle as SunLight.cpp:37-40 derives it from `angle` or `radius`."""
+        d = np.asarray(direction, np.float64)
+        d = (d / np.linalg.norm(d)).astype(np.float32)
+        cos_angle = np.float32(1 / math.sqrt(radius * radius + 1)) if radius is not None else np.float32(math.cos(math.radians(np.float32(angle_deg) / 2)))
+        return self._light(self.infinite, LIGHT_SUN, irradiance, list(d) + [cos_angle])
 
     def add_env_light(self, radiance=(1, 1, 1), scale=(1, 1, 1)):
         r = np.asarray(radiance, np.float32).reshape(-1)

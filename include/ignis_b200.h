@@ -262,6 +262,9 @@ typedef struct igb200_material {
                                       [10] ground brightness, [11] c2, [12..14] sun direction (Y up), [15] 0 -- the arguments
                                       runtime/light/CIELight.cpp:41-110 passes to make_cie_sky_light / make_cie_sunny_light
                                       (light/cie.art:9-42) */
+#define IGB200_LIGHT_SUN 9u /* make_sun_light(dir = v[0..2], scene_bbox, cos_sun_angle = v[3], color) (light/sun.art:4-28): a delta-treated
+                              infinite light sampled uniformly over the sun's cone; the loader gives cos(angle / 2) or
+                              sun_cos_angle_from_radius(radius) (runtime/light/SunLight.cpp:24-46) */
 #define IGB200_SKY_CIE       0u /* cieuniform / ciecloudy (flag VARIANT = cloudy)          light/cie.art:10-19 */
 #define IGB200_SKY_CIE_SUNNY 1u /* cieclear (flag VARIANT = is_clear) / cieintermediate    light/cie.art:22-42 */
 #define IGB200_SKY_PEREZ     2u /* make_perez_light(sun_dir = [12..14], lum = [3..5], ground = [6..8], a b c d e = [9], [10], [11],

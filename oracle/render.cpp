@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <limits>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -684,12 +685,12 @@ struct Ctx { // the slice of the render state lights and the technique need
 
 static inline bool light_delta(const igb200_light& l)
 {
-    return l.type == IGB200_LIGHT_POINT || l.type == IGB200_LIGHT_SPOT || l.type == IGB200_LIGHT_DIRECTIONAL;
+    return l.type == IGB200_LIGHT_POINT || l.type == IGB200_LIGHT_SPOT || l.type == IGB200_LIGHT_DIRECTIONAL || l.type == IGB200_LIGHT_SUN;
 }
 static inline bool light_infinite(const igb200_light& l)
 {
     return l.type == IGB200_LIGHT_ENV || l.type == IGB200_LIGHT_DIRECTIONAL || l.type == IGB200_LIGHT_ENV_TEXTURED ||
-           l.type == IGB200_LIGHT_ENV_FUNCTION;
+           l.type == IGB200_LIGHT_ENV_FUNCTION || l.type == IGB200_LIGHT_SUN;
 }
 static inline Color light_color(const igb200_light& l) { return color(l.color[0], l.color[1], l.color[2]); }
 
@@ -947,6 +948,26 @@ static DirectSample light_sample_direct(const Ctx& c, const igb200_light& l, Rnd
     case IGB200_LIGHT_DIRECTIONAL: { // light/directional.art:6
         const V3 dir = v3(l.v[0], l.v[1], l.v[2]);
         return DirectSample{ add(from.point, mulf(dir, -c.scene_radius)), neg(dir), light_color(l), delta_pdf(), 1.0f, c.scene_radius };
+    }
+    case IGB200_LIGHT_SUN: { // make_sun_light::sample_direct, light/sun.art:11-15 (sample_uniform_cone, core/sampling.art:106-116)
+        const V3    dir = v3(l.v[0], l.v[1], l.v[2]);
+        const float cos_angle = l.v[3];
+        const float sun_radius = sqrtf(1 - cos_angle * cos_angle) / cos_angle, sun_area = flt_pi * sun_radius * sun_radius;
+        const float u = rnd.next_f32();
+        const float v = rnd.next_f32();
+        float       px, py; // square_to_concentric_disk, core/warp.art:2-22
+        {
+            const float a = 2 * u - 1, b = 2 * v - 1;
+            if (a == 0 && b == 0) { px = 0; py = 0; }
+            else if (a * a > b * b) { const float phi = (flt_pi / 4) * safe_div(b, a); px = cosf(phi) * a; py = sinf(phi) * a; }
+            else { const float phi = (flt_pi / 2) - (flt_pi / 4) * safe_div(a, b); px = cosf(phi) * b; py = sinf(phi) * b; }
+        }
+        const float c1 = 1 - cos_angle, n2 = px * px + py * py;
+        const float z  = cos_angle + c1 * (1 - n2), sc = safe_sqrt(c1 * (2 - c1 * n2));
+        const float den = 2 * flt_pi * (1 - cos_angle);
+        const float pdf = fabsf(den) <= flt_eps ? 1.0f : 1 / den; // uniform_cone_pdf: safe_div_one
+        const V3    ndir = mat3_mul(make_orthonormal(dir), v3(px * sc, py * sc, z));
+        return DirectSample{ v3(0, 0, 0), neg(ndir), cmulf(light_color(l), 1 / (sun_area * pdf)), delta_pdf(), z, std::numeric_limits<float>::infinity() };
     }
     case IGB200_LIGHT_ENV: { // make_environment_light_function_spherical::sample_direct, light/env.art:82-86
         const float u = rnd.next_f32();

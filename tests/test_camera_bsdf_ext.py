@@ -138,3 +138,26 @@ def test_sky_function_sampling_is_consistent_with_its_emission(ig, oracle, kind,
         means.append(film.reshape(-1, 3).mean(axis=0))
     assert means[0].max() > 0.05
     assert np.allclose(means[0], means[1], rtol=2e-2)
+
+
+def test_sun_light_closed_form_and_directional_limit(ig, oracle):
+    """make_sun_light (light/sun.art:4-28) over the flat scene of the reference's light tests: a white plane lit head-on.
+    Each sample carries color / (sun_area * pdf) = 2 (1 - c) / tan^2(A) and the plane's cosine is the sampled z, so the mean
+    radiance is (1 / pi) * 2 (1 - c) / tan^2 A * E[z] with E[z] = (1 + c) / 2 for a uniform cone: (1 - c^2) / (pi tan^2 A)
+    = cos^2(A) / pi.  As the cone closes this tends to the directional light's 1 / pi."""
+    from render_common import flat_scene
+    tables, sh = flat_scene(ig, "none", 24, one_sided=False, depth=2)
+    osc = oracle.OracleScene(tables)
+    for angle in (60.0, 11.4, 0.5):
+        sh.infinite.clear()
+        sh.add_sun_light((0, 0, 1), (1, 1, 1), angle)
+        assert sh.infinite[0].type == ig.shading.LIGHT_SUN and sh.infinite[0].v[3] == pytest.approx(np.cos(np.radians(angle / 2)), rel=1e-6)
+        film = osc.render(sh, 24, 24, spi=256, iterations=1, seed=2)
+        want = np.cos(np.radians(angle / 2)) ** 2 / np.pi
+        assert film.mean() == pytest.approx(want, rel=5e-3)
+    sh.infinite.clear()
+    sh.add_directional_light((0, 0, 1), (1, 1, 1))
+    assert osc.render(sh, 24, 24, spi=16, iterations=1, seed=2).mean() == pytest.approx(1 / np.pi, rel=1e-4)
+    sh.infinite.clear()
+    sh.add_sun_light((0, 0, 1), (1, 1, 1), radius=0.1)   # sun_cos_angle_from_radius
+    assert sh.infinite[0].v[3] == pytest.approx(1 / np.sqrt(1.01), rel=1e-6)

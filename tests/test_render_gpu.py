@@ -313,13 +313,15 @@ def test_errors(ig, dev):
         fresh.close()
 
 
-@pytest.mark.parametrize("kind,variant,has_ground", [(0, True, True), (1, True, True), (1, False, False), (2, False, True)])
+@pytest.mark.parametrize("kind,variant,has_ground", [(0, True, True), (1, True, True), (1, False, False), (2, False, True), (3, False, True)])
 def test_sky_function_lights_match_oracle(ig, oracle, dev, kind, variant, has_ground):
     # make_cie_sky_light / make_cie_sunny_light over make_environment_light_function (sphere and hemisphere sampling)
     tables, sh = room_scene(ig, 96, depth=4)
     sun = np.array([0.3, 0.5, -0.8])
     tilt = np.array([[1, 0, 0], [0, 0, -1], [0, 1, 0]], float)
-    if kind == 2:
+    if kind == 3:    # make_sun_light next to the room's own emitters
+        sh.add_sun_light((0.2, -1.0, 0.3), (3.0, 2.5, 2.0), 11.4)
+    elif kind == 2:
         sh.add_perez_sky(sun / np.linalg.norm(sun), (1.0, 0.9, 0.8), (0.3, 0.4, 0.2), (-1.0, -0.32, 6.0, -3.0, 0.3), has_ground, tilt)
     else:
         sh.add_sky_function(kind, variant, has_ground, zenith=(1.0, 0.9, 0.8), ground=(0.3, 0.4, 0.2), zenith_brightness=1.7, c2=0.9,
