@@ -210,3 +210,63 @@ def test_device_resident_call_matches_host_call(ig, dev):
     same = (d_ent.cpu().numpy() == ent) & (d_prim.cpu().numpy() == prim)
     assert same.mean() > 0.9999
     np.testing.assert_allclose(d_t.cpu().numpy()[same], t[same], rtol=1e-5)
+
+
+def test_hostile_rays_and_degenerate_triangles(ig, oracle, dev):
+    """Inputs a production ray list will contain sooner or later: axis-aligned and zero directions, empty and inverted
+    ranges, NaN / infinite components, huge and denormal values, and a mesh with zero-area triangles.  The kernel must
+    terminate, agree with the oracle wherever the reference's arithmetic defines an answer, and report a miss for
+    rays whose components are not finite."""
+    rng = np.random.default_rng(77)
+    W = ig.workloads
+    v, f, n = W.uv_sphere(12, 24)
+    # zero-area triangles: repeated vertex, collinear vertices
+    v = np.concatenate([v, [[0, 0, 2], [0, 0, 2], [1, 0, 2], [2, 0, 2]]]).astype(np.float32)
+    nv = v.shape[0]
+    f = np.concatenate([f, [[nv - 4, nv - 3, nv - 2], [nv - 4, nv - 2, nv - 1]]]).astype(np.uint32)
+    n = np.concatenate([n, np.tile([[0, 0, 1]], (4, 1))]).astype(np.float32)
+    b = ig.SceneBuilder()
+    shape = b.add_trimesh(v, f, n)
+    b.add_entity(shape)
+    m = np.eye(4)
+    m[:3, 3] = [3, 0, 0]
+    b.add_entity(shape, m)
+    tables = b.finish()
+    dev.assign_scene(tables)
+    osc = oracle.OracleScene(tables)
+
+    # ---- defined cases: must equal the oracle exactly
+    org = rng.uniform(-4, 6, (4000, 3)).astype(np.float32)
+    d = rng.normal(size=(4000, 3)).astype(np.float32)
+    d[:1000, 0] = 0                      # axis-aligned in one, two ...
+    d[1000:2000, 0:2] = 0
+    d[1000:2000, 2] = np.where(rng.random(1000) < 0.5, 1, -1)
+    org[1000:1500, 0:2] = 0              # ... straight through the poles / the sphere centre
+    d[2000:2100] *= 1e-20                # tiny but non-zero directions (normalised on upload)
+    d[2100:2200] *= 1e18
+    rays = ig.make_rays(org, d, 0.0, FLT_MAX)
+    rays["tmin"][2200:2400] = 5.0        # window that may start behind the first hit
+    rays["tmax"][2400:2600] = 0.5        # window that may end before the first hit
+    rays["tmin"][2600:2700], rays["tmax"][2600:2700] = 3.0, 1.0    # inverted: nothing can be hit
+    got, want = dev.trace(rays), osc.trace(rays)
+    same = (got[0] == want[0]) & (got[1] == want[1])
+    assert same.mean() > 0.999
+    hit = same & (got[1] >= 0)
+    assert hit.any() and np.array_equal(got[2][hit], want[2][hit])
+    assert np.all(got[1][2600:2700] == -1)
+    agot, awant = dev.trace(rays, any_hit=True), osc.trace(rays)
+    assert np.array_equal(agot[1] >= 0, awant[1] >= 0)
+
+    # ---- undefined cases: non-finite components and the zero direction terminate as misses (zero: norm -> 1, dir stays 0)
+    bad = ig.make_rays(np.zeros((8, 3)), np.tile([[0, 0, 1]], (8, 1)), 0.0, FLT_MAX)
+    bad["org"][0, 0] = np.nan
+    bad["dir"][1, 2] = np.nan
+    bad["org"][2, 1] = np.inf
+    bad["dir"][3] = [np.inf, 0, 0]
+    bad["dir"][4] = [0, 0, 0]
+    bad["tmin"][5] = np.nan
+    bad["tmax"][6] = np.nan
+    bad["org"][7] = [1e30, -1e30, 1e30]
+    for any_hit in (False, True):
+        ent, prim, t, _, _ = dev.trace(bad, any_hit=any_hit)
+        assert np.all(prim[[0, 1, 2, 3, 4, 7]] == -1) and np.all(ent[[0, 1, 2, 3, 4, 7]] == -1)
