@@ -250,7 +250,18 @@ def test_hostile_rays_and_degenerate_triangles(ig, oracle, dev):
     rays["tmin"][2600:2700], rays["tmax"][2600:2700] = 3.0, 1.0    # inverted: nothing can be hit
     got, want = dev.trace(rays), osc.trace(rays)
     same = (got[0] == want[0]) & (got[1] == want[1])
-    assert same.mean() > 0.999
+    groups = {"one zero component": slice(0, 1000), "through the poles": slice(1000, 1500), "axis-aligned": slice(1500, 2000),
+              "tiny directions": slice(2000, 2100), "huge directions": slice(2100, 2200), "late tmin": slice(2200, 2400),
+              "early tmax": slice(2400, 2600), "inverted range": slice(2600, 2700), "plain": slice(2700, 4000)}
+    report = {k: int(np.count_nonzero(~same[g])) for k, g in groups.items()}
+    # rays through a pole hit the vertex shared by a whole fan of triangles: an exact-t tie, resolved by primitive id here and by
+    # leaf order in the reference -- there the ids may differ, hit / miss and t may not
+    pole = groups["through the poles"]
+    assert np.array_equal(got[1][pole] >= 0, want[1][pole] >= 0), report
+    assert np.array_equal(got[2][pole], want[2][pole]), report
+    others = np.ones(rays.size, bool)
+    others[pole] = False
+    assert np.count_nonzero(~same & others) <= 2, report
     hit = same & (got[1] >= 0)
     assert hit.any() and np.array_equal(got[2][hit], want[2][hit])
     assert np.all(got[1][2600:2700] == -1)
