@@ -259,14 +259,23 @@ def test_hostile_rays_and_degenerate_triangles(ig, oracle, dev):
     pole = groups["through the poles"]
     assert np.array_equal(got[1][pole] >= 0, want[1][pole] >= 0), report
     assert np.array_equal(got[2][pole], want[2][pole]), report
+    # directions whose NORM is below flt_eps are not normalised on upload (Device.cpp:588-592), and safe_rcp (core/common.art:95-98)
+    # then treats every component (< 1e-8) as zero: the reference's BVH traversal -- and the oracle with it -- misses what its own
+    # triangle test would hit.  The kernel's box test keeps working down to |d| ~ 2^-80, so for this degenerate group it is
+    # held to the BVH-free brute-force intersector (same Moeller-Trumbore arithmetic) instead.
+    tiny = groups["tiny directions"]
+    brute = osc.brute(rays[tiny])
+    assert np.array_equal(got[0][tiny], brute[0]) and np.array_equal(got[1][tiny], brute[1]) and np.array_equal(got[2][tiny], brute[2]), report
+    assert np.count_nonzero(brute[1] >= 0) > 0 and np.all(want[1][tiny] == -1)
     others = np.ones(rays.size, bool)
     others[pole] = False
-    assert np.count_nonzero(~same & others) <= 2, report
+    others[tiny] = False
+    assert np.count_nonzero(~same & others) == 0, report
     hit = same & (got[1] >= 0)
     assert hit.any() and np.array_equal(got[2][hit], want[2][hit])
     assert np.all(got[1][2600:2700] == -1)
     agot, awant = dev.trace(rays, any_hit=True), osc.trace(rays)
-    assert np.array_equal(agot[1] >= 0, awant[1] >= 0)
+    assert np.array_equal((agot[1] >= 0)[others | pole], (awant[1] >= 0)[others | pole])
 
     # ---- undefined cases: non-finite components and the zero direction terminate as misses (zero: norm -> 1, dir stays 0)
     bad = ig.make_rays(np.zeros((8, 3)), np.tile([[0, 0, 1]], (8, 1)), 0.0, FLT_MAX)
