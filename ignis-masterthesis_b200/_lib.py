@@ -128,6 +128,27 @@ def load():
     return lib
 
 
+HOST_LIB_PATH = os.path.join(_HERE, "lib", "libig_runtime_b200.so")
+_host = None
+
+
+def load_host():
+    """Load libig_runtime_b200.so, the C++ host side above the C ABI (loader pieces: sky bake, scene reader)."""
+    global _host
+    if _host is None:
+        load()  # dependency, resolved through the rpath as well
+        if not os.path.exists(HOST_LIB_PATH):
+            raise RuntimeError(f"{HOST_LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+        h = C.CDLL(HOST_LIB_PATH)
+        fp = C.POINTER(C.c_float)
+        h.ig_b200_bake_sky.argtypes = [fp, C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_uint32, fp]
+        h.ig_b200_bake_sky.restype = C.c_int
+        h.ig_b200_hosek_radiance.argtypes = [C.c_int] + [C.c_double] * 5
+        h.ig_b200_hosek_radiance.restype = C.c_double
+        _host = h
+    return _host
+
+
 class BackendError(RuntimeError):
     def __init__(self, code, message):
         super().__init__(f"ignis_b200 error {code}: {message}")

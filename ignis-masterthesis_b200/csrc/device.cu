@@ -373,6 +373,7 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
     dev->view.spheres    = dev->spheres.ptr;
     dev->view.tlas_nodes = (uint32_t)tlas.nodes.size();
     dev->view.leaf_count = (uint32_t)ordered.size();
+    dev->view.byte_bias  = 0x47000000u;
     dev->node_bytes      = all_nodes.size() * sizeof(Node8);
     dev->tri_bytes       = all_tris.size() * sizeof(float4);
     dev->leaf_bytes      = ordered.size() * sizeof(igb200_entity_leaf);

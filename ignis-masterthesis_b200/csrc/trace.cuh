@@ -22,6 +22,10 @@ struct DeviceScene {
     const float4*   spheres; // origin xyz, radius
     uint32_t        tlas_nodes; // number of TLAS nodes (staged in shared memory when small)
     uint32_t        leaf_count;
+    // 0x47000000, set by the host.  It is a kernel PARAMETER on purpose: ptxas folds any in-code constant into the
+    // immediate slot of PRMT and then has to move the byte selector into a register before each of the 48 PRMTs of a
+    // node step; a constant-bank operand leaves the immediate slot to the selector (trace_core.cuh, biased_byte_to_float).
+    uint32_t        byte_bias;
 };
 
 struct TraceOutputs {

@@ -83,9 +83,19 @@ __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x)
 #define IGB_TLAS_SMEM 0 // number of top-level nodes staged in shared memory (0 = off)
 #endif
 constexpr float kByteBias = 32768.0f;
-__device__ __forceinline__ float biased_byte_to_float(uint32_t w, int j)
+// `bias` must hold 0x47000000 in a REGISTER (see byte_bias_reg): PRMT takes either its selector or its third operand as
+// an immediate, and with the constant as the immediate nvcc moves the selector into a register before every one of the
+// 48 PRMTs of a node step (IMAD.U32 R, RZ, RZ, UR: ~18 % of the node step's instructions in the round-1 SASS).
+__device__ __forceinline__ float biased_byte_to_float(uint32_t w, int j, uint32_t bias)
 {
-    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7604u | ((uint32_t)j << 4)));
+    uint32_t r;
+    switch (j) { // selector as an immediate: byte 3 = bias.3 (0x47), byte 2 = bias.2 (0), byte 1 = w.j, byte 0 = bias.0 (0)
+    case 0: asm("prmt.b32 %0, %1, %2, 0x7604;" : "=r"(r) : "r"(w), "r"(bias)); break;
+    case 1: asm("prmt.b32 %0, %1, %2, 0x7614;" : "=r"(r) : "r"(w), "r"(bias)); break;
+    case 2: asm("prmt.b32 %0, %1, %2, 0x7624;" : "=r"(r) : "r"(w), "r"(bias)); break;
+    default: asm("prmt.b32 %0, %1, %2, 0x7634;" : "=r"(r) : "r"(w), "r"(bias)); break;
+    }
+    return __uint_as_float(r);
 }
 __device__ __forceinline__ uint32_t extract_byte(uint32_t w, int j) { return (w >> (8 * j)) & 0xFFu; }
 
@@ -105,7 +115,8 @@ __device__ __forceinline__ void setup_trav_ray(TravRay& r)
 // Tests the 8 quantised child boxes of one node; returns the (octant-ordered) hit mask:
 // bits 31..24 inner children, bits 23..0 primitives of leaf children.
 __device__ __forceinline__ uint32_t intersect_children(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
-                                                       const uint4 n4, const TravRay& r, float tmin, float tmax)
+                                                       const uint4 n4, const TravRay& r, float tmin, float tmax,
+                                                       const uint32_t bias)
 {
     const uint32_t e  = n0.w;
     const float    sx = __uint_as_float((e & 0xFFu) << 23) * r.idir.x;
@@ -138,12 +149,12 @@ __device__ __forceinline__ uint32_t intersect_children(const uint4 n0, const uin
         const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const float t0x = __fmaf_rn(biased_byte_to_float(nearx, j), sx, o0x);
-            const float t0y = __fmaf_rn(biased_byte_to_float(neary, j), sy, o0y);
-            const float t0z = __fmaf_rn(biased_byte_to_float(nearz, j), sz, o0z);
-            const float t1x = __fmaf_rn(biased_byte_to_float(farx, j), sx, o1x);
-            const float t1y = __fmaf_rn(biased_byte_to_float(fary, j), sy, o1y);
-            const float t1z = __fmaf_rn(biased_byte_to_float(farz, j), sz, o1z);
+            const float t0x = __fmaf_rn(biased_byte_to_float(nearx, j, bias), sx, o0x);
+            const float t0y = __fmaf_rn(biased_byte_to_float(neary, j, bias), sy, o0y);
+            const float t0z = __fmaf_rn(biased_byte_to_float(nearz, j, bias), sz, o0z);
+            const float t1x = __fmaf_rn(biased_byte_to_float(farx, j, bias), sx, o1x);
+            const float t1y = __fmaf_rn(biased_byte_to_float(fary, j, bias), sy, o1y);
+            const float t1z = __fmaf_rn(biased_byte_to_float(farz, j, bias), sz, o1z);
             const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
             // slack on the exit distance: the box test must never reject what the triangle test accepts
             const float cmax = fminf(fminf(fminf(t1x, t1y), t1z) * kBoxSlack, tmax);
@@ -339,7 +350,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
             const uint4    n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
 #endif
             if (STATS) c_nodes++;
-            const uint32_t hitmask = intersect_children(n0, n1, n2, n3, n4, ray, tmin, hit.t);
+            const uint32_t hitmask = intersect_children(n0, n1, n2, n3, n4, ray, tmin, hit.t, sc.byte_bias);
             ngroup                 = make_uint2(n1.x, (hitmask & 0xFF000000u) | (n0.w >> 24));
             tgroup                 = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
         }

@@ -862,41 +862,23 @@ def perez_sky_parameters(light):
     return sun, model, lum, _color(light.get("ground"), 1.0), bool(light.get("has_ground", True))
 
 
-def bake_sky(light, hosek_lib):
-    """SkyModel::SkyModel (src/runtime/skysun/SkyModel.cpp:9-55) at RES_AZ x RES_EL = 512 x 256 over the reference's own
-    ArHosekSkyModel (compiled from the reference tree into oracle/_ref/libhosek.so), followed by the EXR round trip of
-    SkyLight.cpp:33-50: float32 on disk, flipped vertically when loaded (Image.cpp:559-560), alpha 1.
-    Returns the (256, 512, 4) float32 image as the device sees it."""
+def bake_sky(light, width=512, height=256):
+    """SkyLight.cpp:33-50 + SkyModel::SkyModel (src/runtime/skysun/SkyModel.cpp:9-55) at RES_AZ x RES_EL = 512 x 256: the
+    product's own Hosek-Wilkie bake (host/SkyModel.cpp in libig_runtime_b200.so), followed by the EXR round trip of the
+    reference (float32 on disk, flipped vertically when loaded, Image.cpp:559-560, alpha 1).
+    Returns the (height, width, 4) float32 image as the device sees it."""
     import ctypes as C
-    F = np.float32
-    lib = C.CDLL(hosek_lib)
-    init = getattr(lib, "_Z36arhosek_rgb_skymodelstate_alloc_initddd")
-    init.restype, init.argtypes = C.c_void_p, [C.c_double] * 3
-    rad = getattr(lib, "_Z33arhosek_tristim_skymodel_radianceP20ArHosekSkyModelStateddi")
-    rad.restype, rad.argtypes = C.c_double, [C.c_void_p, C.c_double, C.c_double, C.c_int]
+    from . import _lib
+    host = _lib.load_host()
     el, az = light_ea(light)
-    ground = _color(light.get("ground"), 0.8)
-    turbidity = F(light.get("turbidity", 3.0))
-    PI = F(3.14159265358979323846)
-    solar_elevation = F(PI / 2) - el  # (sic) SkyModel.cpp:13
-    sun_se, sun_ce = F(math.sin(solar_elevation)), F(math.cos(solar_elevation))
-    states = [init(float(turbidity), float(ground[k]), float(solar_elevation)) for k in range(3)]
-    H, Wd = 256, 512
-    data = np.zeros((H, Wd, 4), F)
-    for y in range(H):
-        theta = F(PI / 2) * F(y) / F(H)
-        st, ct = F(math.sin(theta)), F(math.cos(theta))
-        for x in range(Wd):
-            azimuth = F(2 * PI) * F(x) / F(Wd) - F(PI / 4)
-            if azimuth < 0:
-                azimuth += F(2) * PI
-            cos_gamma = ct * sun_ce + st * sun_se * F(math.cos(azimuth - az))
-            gamma = F(math.acos(min(1.0, max(-1.0, float(cos_gamma)))))
-            for k in range(3):
-                data[y, x, k] = max(0.0, F(rad(states[k], float(theta), float(gamma), k)) / F(106.856980))
-    img = data[::-1].copy()
-    img[:, :, 3] = 1
-    return np.ascontiguousarray(img)
+    ground = np.ascontiguousarray(_color(light.get("ground"), 0.8), np.float32)
+    H, Wd = height, width
+    img = np.empty((H, Wd, 4), np.float32)
+    rc = host.ig_b200_bake_sky(ground.ctypes.data_as(C.POINTER(C.c_float)), float(el), float(az), float(light.get("turbidity", 3.0)),
+                               Wd, H, img.ctypes.data_as(C.POINTER(C.c_float)))
+    if rc != 0:
+        raise RuntimeError("ig_b200_bake_sky failed")
+    return img
 
 
 def bake_image_texture(px, opaque, filt, wrap, width, height):
@@ -1012,7 +994,7 @@ def build_light_hierarchy(entries):
     return codes, nodes
 
 
-def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
+def load_scene(scene, base=".", width=None, height=None):
     """scene: dict or path. Returns (SceneTables, Shading, width, height, info)."""
     if isinstance(scene, str):
         base = os.path.dirname(os.path.abspath(scene))
@@ -1145,9 +1127,7 @@ def load_scene(scene, base=".", width=None, height=None, hosek_lib=None):
             else:
                 sh.add_env_light(_color(l.get("radiance"), 1.0), _color(l.get("scale"), 1.0))
         elif ty == "sky":  # runtime/light/SkyLight.cpp:52-77
-            if hosek_lib is None:
-                raise ValueError("sky lights need the reference's Hosek model (oracle/_ref/libhosek.so, build container only)")
-            img = bake_sky(l, hosek_lib)
+            img = bake_sky(l)
             tex = sh.add_image_texture(img, 1, (0, 0))  # make_repeat_border(), make_bilinear_filter()
             marginal, cond = compute_cdf2d(img, True, False)
             m3 = parse_transform(l.get("transform"))[:3, :3]

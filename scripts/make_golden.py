@@ -50,12 +50,11 @@ JOBS = [  # (fixture, scene file, reference image, width, height)
     # pin: it is 2.16x below the analytic irradiance of the one lit texel (note 5).
     ("env", "evaluation/env.json", "ref-env-4096.exr", None, None),
 ]
-HOSEK = os.path.join(ROOT, "oracle", "_ref", "libhosek.so")  # `make -C oracle ref`
 only = set(sys.argv[1:])
 for name, scene, ref, w, h in JOBS:
     if only and name not in only:
         continue
-    tables, sh, w, h, info = sceneio.load_scene(f"{REF}/{scene}", width=w, height=h, hosek_lib=HOSEK if os.path.exists(HOSEK) else None)
+    tables, sh, w, h, info = sceneio.load_scene(f"{REF}/{scene}", width=w, height=h)
     fixtures.save_fixture(os.path.join(OUT, name + ".npz"), tables, sh, w, h, exr(ref) if ref else None,
                           meta=f"{scene}; reference image {ref}")
     print(name, w, h, "entities", tables.entity_count, "materials", tables.material_count, os.path.getsize(os.path.join(OUT, name + ".npz")))
