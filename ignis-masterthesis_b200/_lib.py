@@ -31,6 +31,27 @@ ABI_SYMBOLS = [
     "igb200_resize",
     "igb200_set_framebuffer",
     "igb200_get_render_stats",
+    # ABI v6: multi-GPU
+    "igb200_partition_share",
+    "igb200_render_partition",
+    "igb200_set_iteration_count",
+    "igb200_device_ordinal",
+    "igb200_comm_unique_id",
+    "igb200_comm_create",
+    "igb200_comm_destroy",
+    "igb200_comm_render",
+    "igb200_comm_reduce_film",
+    "igb200_group_create",
+    "igb200_group_destroy",
+    "igb200_group_size",
+    "igb200_group_device",
+    "igb200_group_assign_scene",
+    "igb200_group_assign_shading",
+    "igb200_group_resize",
+    "igb200_group_clear_framebuffer",
+    "igb200_group_render",
+    "igb200_group_trace_rays",
+    "igb200_group_get_render_stats",
 ]
 
 
@@ -124,6 +145,31 @@ def load():
     lib.igb200_resize.argtypes = [vp, u32, u32]
     lib.igb200_set_framebuffer.argtypes = [vp, vp, u64, u64]
     lib.igb200_get_render_stats.argtypes = [vp, vp]
+    pu32 = C.POINTER(u32)
+    lib.igb200_partition_share.argtypes = [u32, u32, u32, u32, pu32, pu32, pu32, pu32]
+    lib.igb200_render_partition.argtypes = [vp, vp, u32, u32, u32, u32]
+    lib.igb200_set_iteration_count.argtypes = [vp, C.c_char_p, u64]
+    lib.igb200_device_ordinal.argtypes = [vp]
+    lib.igb200_comm_unique_id.argtypes = [vp]
+    lib.igb200_comm_create.argtypes = [vp, vp, u32, u32, C.POINTER(vp)]
+    lib.igb200_comm_destroy.argtypes = [vp]
+    lib.igb200_comm_destroy.restype = None
+    lib.igb200_comm_render.argtypes = [vp, vp, u32, u32]
+    lib.igb200_comm_reduce_film.argtypes = [vp, u32, u32, u32, i32, C.POINTER(C.c_float)]
+    lib.igb200_group_create.argtypes = [C.POINTER(C.c_int32), u32, i32, C.POINTER(vp)]
+    lib.igb200_group_destroy.argtypes = [vp]
+    lib.igb200_group_destroy.restype = None
+    lib.igb200_group_size.argtypes = [vp]
+    lib.igb200_group_size.restype = u32
+    lib.igb200_group_device.argtypes = [vp, u32]
+    lib.igb200_group_device.restype = vp
+    lib.igb200_group_assign_scene.argtypes = [vp, C.POINTER(Scene)]
+    lib.igb200_group_assign_shading.argtypes = [vp, vp]
+    lib.igb200_group_resize.argtypes = [vp, u32, u32]
+    lib.igb200_group_clear_framebuffer.argtypes = [vp]
+    lib.igb200_group_render.argtypes = [vp, vp, u32, u32]
+    lib.igb200_group_trace_rays.argtypes = [vp, vp, u64, u32, i32, vp, vp, vp, vp, vp]
+    lib.igb200_group_get_render_stats.argtypes = [vp, vp, C.POINTER(C.c_float)]
     _lib = lib
     return lib
 

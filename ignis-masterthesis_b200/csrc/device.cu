@@ -336,6 +336,14 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
     static_assert(sizeof(Node8) == 5 * sizeof(uint4), "node size");
     IGB_CUDA(dev->nodes.upload(reinterpret_cast<const uint4*>(all_nodes.data()), all_nodes.size() * 5, dev->stream));
     IGB_CUDA(dev->tris.upload(all_tris.data(), all_tris.size(), dev->stream));
+    // The device copy of a leaf carries its shape's BVH root and primitive type where the reference keeps the offset of
+    // the shape's prim-BVH blob (user1 / user2, SceneBVHAdapter.h:73-105; that blob is not consumed here): the entity step
+    // of the traversal then needs ONE dependent fetch instead of leaf -> shape record.
+    for (igb200_entity_leaf& l : ordered) {
+        const ShapeRef& r = shape_refs[l.shape_id];
+        l.user1 = (int32_t)r.root_node;
+        l.user2 = (int32_t)(r.type | (r.sphere << 8));
+    }
     IGB_CUDA(dev->leaves.upload(reinterpret_cast<const float4*>(ordered.data()), ordered.size() * 6, dev->stream));
     IGB_CUDA(dev->shapes.upload(shape_refs.data(), shape_refs.size(), dev->stream));
     IGB_CUDA(dev->spheres.upload(all_spheres.data(), all_spheres.size(), dev->stream));
@@ -739,7 +747,15 @@ static int ensure_wave(igb200_device* dev)
     return IGB200_OK;
 }
 
-static int render_batch(igb200_device* dev, const igb200_render_settings* rs, uint32_t count)
+// rows of the film that tile-row partition `rank` of `parts` owns (16-pixel tile rows rank, rank + parts, ...)
+static uint32_t owned_rows(uint32_t h, uint32_t rank, uint32_t parts)
+{
+    uint32_t rows = 0;
+    for (uint32_t t = rank; t * igb::kTileSize < h; t += parts) rows += std::min(igb::kTileSize, h - t * igb::kTileSize);
+    return rows;
+}
+
+static int render_batch(igb200_device* dev, const igb200_render_settings* rs, uint32_t count, uint32_t tile_rank = 0, uint32_t tile_count = 1)
 {
     if (!dev || !rs) return fail(IGB200_E_INVALID, "igb200_render: NULL argument");
     if (count == 0) return IGB200_OK;
@@ -748,18 +764,20 @@ static int render_batch(igb200_device* dev, const igb200_render_settings* rs, ui
     const uint64_t w = list ? rs->ray_count : rs->width, h = list ? 1 : rs->height;
     if (w == 0 || h == 0 || rs->spi == 0) return fail(IGB200_E_INVALID, "igb200_render: empty film or spi == 0");
     if (w * h * rs->spi >= 0x7FFF0000ull) return fail(IGB200_E_UNSUPPORTED, "igb200_render: more than 2^31 samples per iteration");
-    const uint64_t per_iter = w * h * rs->spi;
+    if (list || tile_count <= 1) { tile_rank = 0; tile_count = 1; }
+    const uint64_t rows     = tile_count > 1 ? owned_rows((uint32_t)h, tile_rank, tile_count) : h;
+    const uint64_t per_iter = w * rows * rs->spi; // ray ids per iteration on THIS device
     {
         // one wavefront may span several iterations (its queue regenerates across them); split the request so
         // that a batch has fewer than 2^31 ray ids and fewer than 2^24 iterations
-        const uint64_t max_count = std::max<uint64_t>(1, std::min<uint64_t>(0x7FFF0000ull / per_iter, 1u << 23));
+        const uint64_t max_count = std::max<uint64_t>(1, std::min<uint64_t>(0x7FFF0000ull / std::max<uint64_t>(per_iter, 1), 1u << 23));
         if (count > max_count) {
             igb200_render_settings part = *rs;
             igb200_render_stats    sum{};
             for (uint32_t done = 0; done < count;) {
                 const uint32_t c = (uint32_t)std::min<uint64_t>(max_count, count - done);
                 part.iteration   = rs->iteration + done;
-                if (int rc = render_batch(dev, &part, c)) return rc;
+                if (int rc = render_batch(dev, &part, c, tile_rank, tile_count)) return rc;
                 done += c;
                 // the counters describe the whole call, not its last batch
                 sum.camera_rays += dev->render_stats.camera_rays;
@@ -777,6 +795,12 @@ static int render_batch(igb200_device* dev, const igb200_render_settings* rs, ui
     if (int rc = ensure_wave(dev)) return rc;
     if (int rc = ensure_film(dev, (uint32_t)w, (uint32_t)h)) return rc;
     cudaStream_t st = dev->stream;
+    if (per_iter == 0) { // more partitions than tile rows: this device owns nothing, but its (zero) film takes part in the reduce
+        dev->render_stats = igb200_render_stats{};
+        if (dev->shade.tech.type != IGB200_TECH_INFOBUFFER) dev->iterations += count;
+        dev->film_mapped = false;
+        return IGB200_OK;
+    }
 
     igb::WaveSettings set{};
     set.spi = rs->spi; set.width = (uint32_t)w; set.height = (uint32_t)h;
@@ -784,6 +808,7 @@ static int render_batch(igb200_device* dev, const igb200_render_settings* rs, ui
     set.per_iter = (uint32_t)per_iter;
     set.inv_spi  = 1.0f / (float)rs->spi;
     set.capacity = dev->wave_capacity;
+    set.tile_rank = tile_rank; set.tile_count = tile_count;
     if (list) {
         // Interface::loadRayList (Device.cpp:573-611): upload + normalise
         IGB_CUDA(dev->d_list_rays.ensure(2 * rs->ray_count));
@@ -868,6 +893,72 @@ int igb200_render(igb200_device* dev, const igb200_render_settings* rs) { return
 int igb200_render_iterations(igb200_device* dev, const igb200_render_settings* rs, uint32_t count)
 {
     return render_batch(dev, rs, count);
+}
+
+int igb200_partition_share(uint32_t total_iterations, uint32_t part, uint32_t parts, uint32_t mode, uint32_t* first, uint32_t* count,
+                           uint32_t* tile_rank, uint32_t* tile_count)
+{
+    if (parts == 0 || part >= parts || !first || !count || !tile_rank || !tile_count)
+        return fail(IGB200_E_INVALID, "igb200_partition_share: partition %u of %u", part, parts);
+    if (mode == IGB200_PARTITION_AUTO) mode = total_iterations >= parts ? IGB200_PARTITION_ITERATIONS : IGB200_PARTITION_TILE_ROWS;
+    if (mode == IGB200_PARTITION_ITERATIONS) {
+        // balanced contiguous blocks of the iteration range: the RNG seed hashes the iteration index
+        // (src/artic/core/random.art:34-43), so the union over the partitions is exactly the single-device sample set
+        const uint32_t base = total_iterations / parts, rem = total_iterations % parts;
+        *first      = part * base + std::min(part, rem);
+        *count      = base + (part < rem ? 1u : 0u);
+        *tile_rank  = 0;
+        *tile_count = 1;
+    } else if (mode == IGB200_PARTITION_TILE_ROWS) {
+        *first      = 0;
+        *count      = total_iterations;
+        *tile_rank  = part;
+        *tile_count = parts;
+    } else {
+        return fail(IGB200_E_INVALID, "igb200_partition_share: unknown mode %u", mode);
+    }
+    return IGB200_OK;
+}
+
+int igb200_render_partition(igb200_device* dev, const igb200_render_settings* rs, uint32_t total_iterations, uint32_t part,
+                            uint32_t parts, uint32_t mode)
+{
+    if (!dev || !rs) return fail(IGB200_E_INVALID, "igb200_render_partition: NULL argument");
+    uint32_t first = 0, count = 0, tr = 0, tc = 1;
+    if (int rc = igb200_partition_share(total_iterations, part, parts, rs->rays ? IGB200_PARTITION_ITERATIONS : mode, &first, &count, &tr, &tc))
+        return rc;
+    dev->render_stats = igb200_render_stats{};
+    if (count == 0) return IGB200_OK;
+    igb200_render_settings mine = *rs;
+    mine.iteration += first;
+    return render_batch(dev, &mine, count, tr, tc);
+}
+
+int igb200_set_iteration_count(igb200_device* dev, const char* name, uint64_t iterations)
+{
+    if (!dev) return fail(IGB200_E_INVALID, "igb200_set_iteration_count: NULL device");
+    const int img = find_image(name);
+    if (img == -2 || (img >= 0 && !dev->aov[img].d.ptr)) return fail(IGB200_E_INVALID, "igb200_set_iteration_count: unknown AOV '%s'", name);
+    if (img < 0) {
+        dev->iterations  = iterations;
+        dev->film_mapped = false;
+    } else {
+        dev->aov[img].iterations = iterations;
+        dev->aov[img].mapped     = false;
+    }
+    return IGB200_OK;
+}
+
+int igb200_device_ordinal(const igb200_device* dev) { return dev ? dev->ordinal : -1; }
+
+// hooks for multi_gpu.cpp (not part of the public header): error channel and film size
+int igb200_internal_fail(int code, const char* message) { return fail(code, "%s", message ? message : ""); }
+int igb200_internal_film_size(igb200_device* dev, uint32_t* w, uint32_t* h)
+{
+    if (!dev) return IGB200_E_INVALID;
+    if (w) *w = dev->d_film.ptr ? dev->film_w : 0;
+    if (h) *h = dev->d_film.ptr ? dev->film_h : 0;
+    return IGB200_OK;
 }
 
 int igb200_framebuffer(igb200_device* dev, const char* name, int device, float** data, uint64_t* iterations)

@@ -26,7 +26,10 @@ constexpr float    kFltEps   = 1.1920928955078125e-7f;
 constexpr float    kFltMax   = 3.402823466e+38f;
 constexpr uint32_t kSentinel = 0xFFFFFFFFu;
 constexpr int      kBlock       = 128;
-constexpr int      kBlocksPerSM = 8;
+#ifndef IGB_BLOCKS_PER_SM
+#define IGB_BLOCKS_PER_SM 8
+#endif
+constexpr int      kBlocksPerSM = IGB_BLOCKS_PER_SM;
 constexpr int      kChunk       = 64; // rays a warp claims per atomic on the global work counter
 #ifndef IGB_VOTE_TRI
 #define IGB_VOTE_TRI 4
@@ -42,6 +45,15 @@ constexpr int      kVoteEnt     = IGB_VOTE_ENT; // same for the entity-leaf phas
 constexpr int      kVoteRefill  = IGB_VOTE_REFILL; // idle lanes that must wait before the warp fetches new rays
 #ifndef IGB_PARK_PRIMS
 #define IGB_PARK_PRIMS 0 // 1: park triangle groups, 2: entity-leaf groups too (measured: see DESIGN.md section 7)
+#endif
+#ifndef IGB_TRI_LOAD2
+#define IGB_TRI_LOAD2 0
+#endif
+#ifndef IGB_ENT_ONE_WAIT
+#define IGB_ENT_ONE_WAIT 1
+#endif
+#ifndef IGB_NODE_REPS
+#define IGB_NODE_REPS 1 // node steps per loop trip (lanes that can take another one do; the other phases run once per trip)
 #endif
 #ifndef IGB_TRI_PER_TRIP
 #define IGB_TRI_PER_TRIP 2
@@ -332,6 +344,18 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
         }
 #endif
         // ---- node phase: lanes with inner children pending and no primitives waiting
+#if IGB_NODE_REPS > 1
+#pragma unroll 1
+        for (int rep = 0; rep < IGB_NODE_REPS; ++rep) {
+        if (rep > 0 && active && tgroup.y == 0u && ngroup.y <= 0x00FFFFFFu && sp > 0) {
+            // quick pop between node steps: only a plain inner group (sentinels / parked primitive groups wait for the pop phase)
+            const uint2 e = stack[sp - 1];
+            if (e.x != kSentinel && e.y > 0x00FFFFFFu) {
+                ngroup = e;
+                --sp;
+            }
+        }
+#endif
         if (active && tgroup.y == 0u && ngroup.y > 0x00FFFFFFu) {
             const uint32_t hits            = ngroup.y;
             const uint32_t imask           = ngroup.y & 0xFFu;
@@ -354,6 +378,9 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
             ngroup                 = make_uint2(n1.x, (hitmask & 0xFF000000u) | (n0.w >> 24));
             tgroup                 = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
         }
+#if IGB_NODE_REPS > 1
+        }
+#endif
 
         // ---- primitive phases.  Triangle tests and entity-leaf steps are rare next to node steps (C3: 0.9 and 0.8 per
         // ray against 5 node steps), so run immediately they execute with ~2 and ~5 live lanes.  A lane with primitives
@@ -365,6 +392,21 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
         const uint32_t free_v = __ballot_sync(0xFFFFFFFFu, active && tgroup.y == 0u);
         if (tri_v != 0u && (__popc(tri_v) >= kVoteTri || free_v == 0u)) {
             if (want_p && in_blas) {
+#if IGB_TRI_LOAD2
+                // two triangles per phase, both records in flight before the first test: one memory wait instead of two
+                const uint32_t i0 = 31u - (uint32_t)__clz(tgroup.y);
+                tgroup.y &= ~(1u << i0);
+                const bool     two = tgroup.y != 0u;
+                const uint32_t i1  = two ? 31u - (uint32_t)__clz(tgroup.y) : i0;
+                tgroup.y &= ~(1u << i1);
+                const float4* tp0 = sc.tris + 3 * (size_t)(tgroup.x + i0);
+                const float4* tp1 = sc.tris + 3 * (size_t)(tgroup.x + i1);
+                const float4  a0 = __ldg(tp0 + 0), b0 = __ldg(tp0 + 1), c0 = __ldg(tp0 + 2);
+                const float4  a1 = __ldg(tp1 + 0), b1 = __ldg(tp1 + 1), c1 = __ldg(tp1 + 2);
+                if (STATS) c_tris += two ? 2u : 1u;
+                intersect_triangle(a0, b0, c0, ray, tmin, cur_ent, hit);
+                if (two && !(ANY_HIT && hit.prim >= 0)) intersect_triangle(a1, b1, c1, ray, tmin, cur_ent, hit);
+#else
                 int budget = kTriPerTrip > 0 ? kTriPerTrip : 32;
                 while (tgroup.y != 0u && budget-- > 0) {
                     const uint32_t idx = 31u - (uint32_t)__clz(tgroup.y);
@@ -375,6 +417,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                     intersect_triangle(a, b, c, ray, tmin, cur_ent, hit);
                     if (ANY_HIT && hit.prim >= 0) break;
                 }
+#endif
             }
         }
         if (ent_v != 0u && (__popc(ent_v) >= kVoteEnt || free_v == 0u)) {
@@ -385,6 +428,9 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                     // Entity leaf step: gpu_traverse_scene::scene_handle (traversal/mapping_gpu.art:196-222)
                     const float4*  lp = sc.leaves + 6 * (size_t)(tgroup.x + idx);
                     const float4   l0 = __ldg(lp + 0), l1 = __ldg(lp + 1), l5 = __ldg(lp + 5);
+#if IGB_ENT_ONE_WAIT
+                    const float4   l2 = __ldg(lp + 2), l3 = __ldg(lp + 3), l4 = __ldg(lp + 4); // whole leaf in flight at once
+#endif
                     const uint32_t leaf_flags = __float_as_uint(l5.x);
                     // check_ray_visibility (traversal/ray.art:51)
                     if ((ray_flags & 0xFu) != ((ray_flags & leaf_flags) & 0xFu)) continue;
@@ -396,10 +442,16 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                     const float exit_ = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z)) * kBoxSlack;
                     if (!(entry <= fminf(exit_, hit.t))) continue;
 
+#if !IGB_ENT_ONE_WAIT
                     const float4 l2 = __ldg(lp + 2), l3 = __ldg(lp + 3), l4 = __ldg(lp + 4);
+#endif
                     if (STATS) c_ents++;
                     cur_ent              = __float_as_int(l0.w) & 0x7FFFFFFF;
-                    const ShapeRef shape = sc.shapes[__float_as_int(l1.w)];
+                    // the device leaf carries its shape's BVH root / type / sphere index in user1, user2 (device.cu)
+                    ShapeRef shape;
+                    shape.root_node = __float_as_uint(l5.z);
+                    shape.type      = __float_as_uint(l5.w) & 0xFFu;
+                    shape.sphere    = __float_as_uint(l5.w) >> 8;
                     // transform_ray (traversal/ray.art:56-59): matrix columns l2.xyz | l2.w l3.xy | l3.zw l4.x | l4.yzw
                     TravRay local;
                     local.org = Vec3{ dot4(l2.x, l2.w, l3.z, l4.y, ray.org.x, ray.org.y, ray.org.z, 1.0f),

@@ -181,8 +181,14 @@ __global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __rest
         const uint32_t gid    = first + k;                 // id within the batch of iterations
         const uint32_t it     = gid / set.per_iter;        // iteration offset: the batch regenerates across iterations
         const uint32_t id     = gid - it * set.per_iter;   // ray id = (y * w + x) * spi + sample (mapping_gpu.art:655)
-        const uint32_t sample = id % set.spi, pixel = id / set.spi;
-        const uint32_t y = pixel / set.width, x = pixel - y * set.width;
+        const uint32_t sample = id % set.spi;
+        uint32_t       pixel  = id / set.spi;
+        uint32_t       y = pixel / set.width;
+        const uint32_t x = pixel - y * set.width;
+        if (set.tile_count > 1u) { // local row -> film row: owned tile rows are tile_rank, tile_rank + tile_count, ...
+            y     = ((y / kTileSize) * set.tile_count + set.tile_rank) * kTileSize + (y % kTileSize);
+            pixel = y * set.width + x;
+        }
         Rnd            rnd{ create_random_seed(sample, set.iter + it, set.frame, x, y, set.seed), 1u };
         Vec3           org, dir;
         float          tmin, tmax;

@@ -57,7 +57,12 @@ struct WaveSettings {
     float*        film;      // w * h * 3, RGB sums
     float*        aov[3];    // technique AOVs, same layout, or nullptr: path + aov_mis: Direct Weights, NEE Weights;
                              // infobuffer: Normals, Albedo, Depth
+    // Multi-GPU tile split (igb200_render_partition): this device renders the rows of the 16-pixel tile rows
+    // t with t % tile_count == tile_rank (the reference's CPU driver walks the same 16 x 16 tiles,
+    // mapping_cpu.art:694-706).  tile_count <= 1: the whole film.  per_iter counts the rays of the OWNED rows only.
+    uint32_t      tile_rank, tile_count;
 };
+constexpr uint32_t kTileSize = 16; // rows per tile row of the multi-GPU split
 
 // Device-resident control block of one render() call.
 struct WaveControl {

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define IGB200_ABI_VERSION 5
+#define IGB200_ABI_VERSION 6
 
 enum {
     IGB200_OK            = 0,
@@ -421,6 +421,71 @@ int igb200_tonemap(igb200_device* dev, const igb200_tonemap_settings* settings, 
 int igb200_set_framebuffer(igb200_device* dev, const float* d_src, uint64_t count, uint64_t iterations);
 
 int igb200_get_render_stats(igb200_device* dev, igb200_render_stats* out);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Multi-GPU (ABI v6).  north_star: "work is partitioned by image tile and sample index, with the scene replicated per
+ * GPU and accumulation buffers combined via NCCL reduce over NVLink".  The reference is single-device
+ * (src/runtime/device/Device.cpp:232-243); its own partitioning analogue is the CPU driver's loop over 16 x 16 tiles
+ * on TBB workers (src/artic/driver/mapping_cpu.art:694-706, src/artic/core/cpu_common.art:101-125).
+ *
+ * Partitioning of a request of `total_iterations` iterations (settings->iteration ... + total - 1):
+ *   ITERATIONS  partition p renders a contiguous block of the iteration range.  The RNG seed hashes the iteration
+ *               index (src/artic/core/random.art:34-43), so the union is EXACTLY the single-device sample set.
+ *   TILE_ROWS   every partition renders all iterations of the 16-pixel tile rows t with t % parts == p (seeds hash
+ *               the pixel, so again the same samples).  For spp < parts * spi, where there are not enough iterations.
+ *   AUTO        ITERATIONS when total_iterations >= parts, else TILE_ROWS.
+ * Either way the sum of the per-device films is the single-device film up to the order of the f32 additions.
+ * ------------------------------------------------------------------------------------------------------------- */
+enum { IGB200_PARTITION_AUTO = 0, IGB200_PARTITION_ITERATIONS = 1, IGB200_PARTITION_TILE_ROWS = 2 };
+
+/* The share of partition `part` of `parts`: iterations [first, first + count) relative to settings->iteration and the
+ * tile-row ownership (tile_rank of tile_count; tile_count == 1: whole film).  Pure host arithmetic, no device needed. */
+int igb200_partition_share(uint32_t total_iterations, uint32_t part, uint32_t parts, uint32_t mode, uint32_t* first,
+                           uint32_t* count, uint32_t* tile_rank, uint32_t* tile_count);
+/* Renders this device's share in one wavefront (as igb200_render_iterations).  The device's film then holds a PARTIAL
+ * sum; combine with igb200_comm_reduce_film / igb200_group_render.  Ray-list mode always splits by iteration. */
+int igb200_render_partition(igb200_device* dev, const igb200_render_settings* settings, uint32_t total_iterations,
+                            uint32_t part, uint32_t parts, uint32_t mode);
+/* IterationCount of the film (name NULL / "" / "Color") or of an AOV, e.g. after a reduce (Device.cpp:1460-1472). */
+int igb200_set_iteration_count(igb200_device* dev, const char* name, uint64_t iterations);
+int igb200_device_ordinal(const igb200_device* dev);
+
+/* ---- one process per GPU (torchrun / MPI launchers): an NCCL communicator next to a device handle ----
+ * Rank 0 calls igb200_comm_unique_id and hands the 128 bytes to the other ranks by any means (the launcher's store, a
+ * file, MPI_Bcast); then every rank calls igb200_comm_create.  NCCL is loaded at run time (libnccl.so.2). */
+#define IGB200_COMM_ID_BYTES 128
+typedef struct igb200_comm igb200_comm;
+int  igb200_comm_unique_id(uint8_t id[IGB200_COMM_ID_BYTES]);
+int  igb200_comm_create(igb200_device* dev, const uint8_t id[IGB200_COMM_ID_BYTES], uint32_t nranks, uint32_t rank, igb200_comm** out);
+void igb200_comm_destroy(igb200_comm* comm);
+/* This rank's share of the request (igb200_render_partition with part = rank, parts = nranks). */
+int  igb200_comm_render(igb200_comm* comm, const igb200_render_settings* settings, uint32_t total_iterations, uint32_t mode);
+/* ONE ncclReduce(sum, f32) per image (film + every AOV in use) onto `root` over NVLink / NVSwitch, timed with CUDA
+ * events on the communicator's stream (*reduce_ms, may be NULL).  Afterwards root's images hold the sums and the
+ * iteration counts of the whole request (`total_iterations` as passed to the matching igb200_comm_render, added to what
+ * root held before); the other ranks' images are cleared so the next request starts from zero there.
+ * warm != 0: additionally runs one untimed reduce of a scratch buffer of the film's size first (communicator
+ * first-use cost: channel setup and buffer registration happen on the first large collective). */
+int  igb200_comm_reduce_film(igb200_comm* comm, uint32_t root, uint32_t total_iterations, uint32_t mode, int warm, float* reduce_ms);
+
+/* ---- one process, N devices (ncclCommInitAll): what igcli --gpus N and IG::Runtime use ----
+ * Scene and shading are replicated; member 0 is the root that holds the combined film. */
+typedef struct igb200_group igb200_group;
+int            igb200_group_create(const int32_t* devices, uint32_t count, int acquire_stats, igb200_group** out);
+void           igb200_group_destroy(igb200_group* group);
+uint32_t       igb200_group_size(const igb200_group* group);
+igb200_device* igb200_group_device(igb200_group* group, uint32_t index);
+int            igb200_group_assign_scene(igb200_group* group, const igb200_scene* scene);
+int            igb200_group_assign_shading(igb200_group* group, const igb200_shading* shading);
+int            igb200_group_resize(igb200_group* group, uint32_t width, uint32_t height);
+int            igb200_group_clear_framebuffer(igb200_group* group);
+/* Partition, render on all members concurrently (one host thread and one stream per device), reduce onto member 0. */
+int            igb200_group_render(igb200_group* group, const igb200_render_settings* settings, uint32_t total_iterations, uint32_t mode);
+/* igtrace batches: contiguous ray ranges per member, results gathered by the D2H copies -- no collective. */
+int            igb200_group_trace_rays(igb200_group* group, const igb200_ray* rays, uint64_t n, uint32_t ray_flags, int any_hit,
+                                       int32_t* ent_id, int32_t* prim_id, float* t, float* u, float* v);
+/* Sum of the members' ray counters of the last igb200_group_render, max of their device times, and the reduce time. */
+int            igb200_group_get_render_stats(igb200_group* group, igb200_render_stats* out, float* reduce_ms);
 
 /* Host-only test hook (no GPU needed): builds the compressed BVH8 over `n` boxes (min xyz, max xyz) and
  * checks its invariants -- every primitive referenced exactly once, every dequantised child box contains

@@ -6,5 +6,5 @@ name=$1; shift
 mkdir -p build/variants
 C=ignis-masterthesis_b200/csrc
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=false -Xcompiler -fPIC -shared "$@" \
-  -o build/variants/lib$name.so $C/bvh8_build.cpp $C/debug_api.cpp $C/trace.cu $C/wavefront.cu $C/tonemap.cu $C/device.cu 2>&1 | grep -i "error" || true
+  -o build/variants/lib$name.so $C/bvh8_build.cpp $C/debug_api.cpp $C/trace.cu $C/wavefront.cu $C/tonemap.cu $C/device.cu $C/multi_gpu.cpp -ldl 2>&1 | grep -i "error" || true
 ls -la build/variants/lib$name.so

@@ -7,14 +7,14 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
 def eval_error(img, ref):
-    """scripts/RunEvaluations.py:79-86 of the reference: mean over pixels of the relative squared error
-    (absolute where ref == 0), channel mean, clipped at its 99th percentile."""
+    """error_image() of the reference, scripts/RunEvaluations.py:79-86, literally: per ELEMENT (pixel and channel) the
+    relative squared error, absolute where ref == 0; clipped at the 99th percentile over all elements; mean."""
     img, ref = np.asarray(img, np.float64), np.asarray(ref, np.float64)
     mask = ref != 0
-    e = np.square(img - ref)
-    e[mask] /= np.square(ref[mask])
-    e = e.mean(axis=2)
-    return float(np.clip(e, 0, np.percentile(e, 99)).mean())
+    err = np.zeros_like(ref)
+    err[mask] = np.square((img[mask] - ref[mask]) / ref[mask])
+    err[~mask] = np.square(img[~mask])
+    return float(np.average(np.clip(err, 0, np.percentile(err, 99))))
 
 
 def flat_scene(ig, light, res, one_sided=False, depth=2):

@@ -165,6 +165,28 @@ def test_c2_primitives_full_size(ig, oracle, dev):
     assert eval_error(small / 8, ref / 8) < 5e-3
 
 
+def test_c2_primitives_full_size_per_pixel_parity(ig, oracle, dev):
+    # BASELINE.json configs[1] as stated -- 1024 x 1024, 64 spp = 8 iterations of spi 8, seed 42 -- per pixel against the
+    # oracle's render of the SAME configuration (67 M samples on the host cores), standard tolerance.
+    tables, sh, w, h, _ = load_golden(ig, "primitives")
+    film, stats = _render(dev, tables, sh, w, h, 8, 8, seed=42)
+    osc = oracle.OracleScene(tables)
+    ref = osc.render(sh, w, h, spi=8, iterations=8, seed=42)
+    _assert_parity(film, ref, stats, osc.ray_stats.astype(np.int64))
+
+
+def test_c4_diamond_full_resolution_per_pixel_parity(ig, oracle, dev):
+    # BASELINE.json configs[3] at its resolution, 1920 x 1080, one iteration of spi 4 (recommendSPI), seed 42, depth 64:
+    # per pixel against the oracle.  Glass paths are chaotic (a last-bit difference flips a refract / reflect decision), so
+    # like the 240 x 135 case a small fraction of the pixels takes another path; the bars are those of _assert_parity.
+    tables, sh, w, h, _ = load_golden(ig, "diamond")
+    assert (w, h) == (1920, 1080)
+    film, stats = _render(dev, tables, sh, w, h, 4, 1, seed=42)
+    osc = oracle.OracleScene(tables)
+    ref = osc.render(sh, w, h, spi=4, iterations=1, seed=42)
+    _assert_parity(film, ref, stats, osc.ray_stats.astype(np.int64))
+
+
 @pytest.mark.parametrize("max_depth,far_limit,count_tol", [(2, 5e-3, 0.0), (64, 4e-2, 1.5e-2)])
 def test_c5_many_point_lights_matches_oracle(ig, oracle, dev, max_depth, far_limit, count_tol):
     # Up to depth 2 (every ABI v3 feature evaluated once per path) the standard tolerance holds.  Deeper paths bounce

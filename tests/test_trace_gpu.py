@@ -27,13 +27,22 @@ def _compare(ig, oracle, dev, tables, rays, max_degenerate=1e-4):
     oent, oprim, ot, ou, ov = osc.trace(rays)
     same = (ent == oent) & (prim == oprim)
     bad = np.flatnonzero(~same)
+    degenerate = 0
     if bad.size:
         assert bad.size <= max(4, max_degenerate * rays.size), f"{bad.size} id mismatches"
-        # classify every mismatch with the BVH-free intersector: it must be a near-tie
+        # Classify every mismatch with the BVH-free intersector.  Accepted only if
+        #  (a) the ray is a tie / near-tie (second-best t within 1e-6 relative: degenerate by the contract), or
+        #  (b) the GPU result IS the brute-force result (ids and t bit-exact) -- then it is the oracle's BVH that culled a
+        #      hit its own triangle test accepts (box-test rounding), not the GPU that is wrong.
         bent, bprim, bt, _, _, tie, second = osc.brute(rays[bad])
         gap = np.abs(second - bt) <= 1e-6 * np.abs(bt)
-        borderline = tie | gap | (bprim != oprim[bad]) | (bent != oent[bad])  # last two: oracle's own box cull
-        assert np.all(borderline), "GPU differs from the oracle on a non-degenerate ray"
+        gpu_is_brute = (ent[bad] == bent) & (prim[bad] == bprim) & ((t[bad] == bt) | (bprim < 0))
+        assert np.all(tie | gap | gpu_is_brute), "GPU differs from the oracle AND from brute force on a non-degenerate ray"
+        # a (near-)tie must still be a hit on one of the tied primitives: same t to 1e-6
+        near = (tie | gap) & ~gpu_is_brute
+        assert np.all(np.abs(t[bad][near] - bt[near]) <= 1e-6 * np.abs(bt[near])), "tie resolved to a different distance"
+        degenerate = int(np.count_nonzero(tie | gap))
+    _compare.last = dict(mismatches=int(bad.size), degenerate=degenerate, rays=int(rays.size))
     hit = same & (prim >= 0)
     assert np.array_equal(t[hit], ot[hit]), "t not bit-identical for the same triangle"
     assert np.array_equal(u[hit], ou[hit]) and np.array_equal(v[hit], ov[hit])
@@ -64,6 +73,23 @@ def test_c3_full_scene_2m_rays(ig, oracle, dev):
     assert frac > 0.9999
     st = dev.trace_stats()
     assert st["rays"] == rays.size and st["nodes_visited"] > rays.size and st["tris_tested"] > 0
+
+
+def test_c3_benchmark_batch_itself_16m_rays(ig, oracle, dev, capsys):
+    """The batch bench.py times (BASELINE.json configs[2]: 16 777 216 rays, seed 0xB200, generation order) against the
+    oracle, closest-hit and any-hit.  Prints the mismatch / degenerate counts DESIGN.md section 4 quotes."""
+    tables = ig.workloads.c3_scene()
+    rays = ig.workloads.c3_rays(tables)
+    assert rays.size == 1 << 24
+    frac, hits = _compare(ig, oracle, dev, tables, rays)
+    info = dict(_compare.last, hits=int(hits))
+    aprim = dev.trace(rays, any_hit=True)[1]
+    oprim = oracle.OracleScene(tables).trace(rays, any_hit=True)[1]
+    occl = int(np.count_nonzero((aprim >= 0) != (oprim >= 0)))
+    info["any_hit_occlusion_mismatches"] = occl
+    with capsys.disabled():
+        print(f"\nC3 16Mi parity: {info}")
+    assert frac > 0.99999 and occl <= 4    # a grazing ray may be occluded by one side of a tie only
 
 
 def test_c3_full_size_instanced_equals_flattened(ig, dev):
