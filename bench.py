@@ -141,67 +141,86 @@ def load_pt_workload(pkg, workload=None):
     return tables, sh, w, h, spi
 
 
-def bench_path_tracer(pkg, local_rank, rank, world, iterations, warmup, workload=None, first=None):
-    """Path-traced samples/s (igcli's definition: spi * w * h / iteration seconds, src/frontend/cli/main.cpp:135).
-    N GPUs: rank r renders the block of iterations [r*K, (r+1)*K) in one wavefront (the seed hashes the iteration
-    index, so the union is the single-GPU sample set), then the films are summed onto rank 0 with one NCCL reduce
-    over NVLink."""
+_COMM = {}
+
+
+def product_comm(pkg, dev, rank, world):
+    """The product's per-process communicator (igb200_comm_*: NCCL next to the device handle).  torch.distributed is only
+    the launcher-side plumbing that hands rank 0's 128-byte id to the other ranks."""
+    import torch
+    import torch.distributed as dist
+    uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        uid = torch.frombuffer(bytearray(pkg.Comm.unique_id()), dtype=torch.uint8).cuda()
+    dist.broadcast(uid, src=0)
+    return pkg.Comm(dev, bytes(uid.cpu().numpy().tobytes()), world, rank)
+
+
+def bench_path_tracer(pkg, local_rank, rank, world, total_iterations, warmup, workload=None, mode=None):
+    """Path-traced samples/s (igcli's definition: spi * w * h * iterations / seconds, src/frontend/cli/main.cpp:135) of ONE
+    request of `total_iterations` iterations over all ranks, through the product's multi-GPU entries: igb200_comm_render
+    (the request partitioned by iteration index or by tile rows inside the library, scene replicated) and
+    igb200_comm_reduce_film (one ncclReduce of the film onto rank 0 over NVLink, communicator warmed beforehand).
+    `value` stops after the reduce (film resident on rank 0's device); `e2e_value` adds the D2H read of the presented
+    film through igb200_framebuffer into the device's pinned mirror (no further host copy)."""
     import torch
     import torch.distributed as dist
     workload = workload or PT_WORKLOAD
     tables, sh, w, h, spi = load_pt_workload(pkg, workload)
     dev = pkg.Device(local_rank)
+    t_build = time.perf_counter()
     dev.assign_scene(tables)
+    build_s = time.perf_counter() - t_build
     dev.assign_shading(sh)
     dev.resize(w, h)
+    comm = product_comm(pkg, dev, rank, world) if world > 1 else None
+    mode = pkg.device.PARTITION_AUTO if mode is None else mode
     for it in range(warmup):
         dev.render(w, h, spi=spi, iteration=1_000_000 + it)
+    if comm is not None:  # warm the communicator on a film-sized buffer outside the timed region (first-use cost)
+        comm.reduce_film(warmup, root=0, mode=pkg.device.PARTITION_ITERATIONS, warm=True)
     dev.clear_framebuffer()
-    its = torch.tensor([float(iterations)], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(its, op=dist.ReduceOp.SUM)
-    total_iterations = int(its.item())
+    dev.framebuffer(copy=False)  # pinned mirror allocated and touched before timing
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
-    dev.render(w, h, spi=spi, iteration=rank * iterations if first is None else first, iterations=iterations)
+    if comm is not None:
+        comm.render(w, h, spi, total_iterations, mode=mode)
+    else:
+        dev.render(w, h, spi=spi, iteration=0, iterations=total_iterations)
     st = dev.render_stats()
-    ms = [st["device_ms"] / iterations]
+    ms_iter = st["device_ms"]
     rays = st["camera_rays"] + st["bounce_rays"] + st["shadow_rays"]
-    launches = st["kernel_launches"]
-    rounds = st["rounds"]
-    ptr, n_it = dev.framebuffer_device()
-    film = torch.as_tensor(_DevArray(ptr, w * h * 3), device=f"cuda:{local_rank}")
-    reduce_ms = 0.0
-    if world > 1:
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)
-        e1.record()
-        torch.cuda.synchronize()
-        reduce_ms = e0.elapsed_time(e1)
-        if rank == 0:
-            dev.set_framebuffer(ptr, w * h * 3, total_iterations)
+    launches, rounds = st["kernel_launches"], st["rounds"]
+    reduce_ms = comm.reduce_film(total_iterations, root=0, mode=mode, warm=False) if comm is not None else 0.0
     total_s = time.perf_counter() - t0
-    host_film, n_total = dev.framebuffer()  # D2H of the presented frame: the e2e read
+    host_film, n_total = dev.framebuffer(copy=False)  # D2H of the presented frame into the pinned mirror: the e2e read
     e2e_s = time.perf_counter() - t0
-    stats = torch.tensor([total_s, e2e_s, float(rays), float(np.sum(ms)), float(launches)], device="cuda", dtype=torch.float64)
+    film_mean = float(host_film.mean() / max(1, n_total)) if rank == 0 else 0.0
+    stats = torch.tensor([total_s, e2e_s, float(rays), float(ms_iter), float(launches), float(reduce_ms)], device="cuda", dtype=torch.float64)
     if world > 1:
         mx = stats.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = stats.clone()
         dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        total_s, e2e_s, rays, launches = float(mx[0]), float(mx[1]), float(sm[2]), float(sm[4])
+        total_s, e2e_s, rays, launches, reduce_ms, ms_iter = float(mx[0]), float(mx[1]), float(sm[2]), float(sm[4]), float(mx[5]), float(mx[3])
     samples = float(spi) * w * h * total_iterations
+    first, count, tr, tc = pkg.partition_share(total_iterations, rank, world, mode)
     out = {
-        "workload": workload, "width": w, "height": h, "spi": spi, "iterations": total_iterations,
+        "workload": workload, "width": w, "height": h, "spi": spi, "iterations": int(total_iterations),
         "max_depth": int(sh.technique.max_depth), "metric": "path-traced samples/s", "unit": "Msamples/s",
         "value": samples / total_s / 1e6, "e2e_value": samples / e2e_s / 1e6,
-        "ms_per_iteration_median": float(np.median(ms)), "mrays_per_s": rays / total_s / 1e6,
-        "rays_per_sample": rays / samples, "film_reduce_ms": reduce_ms, "d2h_bytes": w * h * 3 * 4,
-        "gpu_launches": int(launches), "rounds_rank0": int(rounds), "film_mean": float(host_film.mean() / max(1, n_total)),
+        "device_ms_max_rank": ms_iter, "mrays_per_s": rays / total_s / 1e6,
+        "rays_per_sample": rays / samples, "film_reduce_ms": reduce_ms,
+        "film_reduce_wire_ms_at_450GBs": (w * h * 3 * 4) / 450e9 * 1e3 if world > 1 else 0.0,
+        "d2h_bytes": w * h * 3 * 4, "partition": "tile rows" if tc > 1 else "iteration blocks",
+        "api": "igb200_comm_render + igb200_comm_reduce_film" if world > 1 else "igb200_render_iterations",
+        "gpu_launches": int(launches), "rounds_rank0": int(rounds), "iterations_on_root_film": int(n_total), "film_mean": film_mean,
+        "bvh_build_s": build_s,
     }
+    if comm is not None:
+        comm.close()
     dev.close()
     return out
 
@@ -233,7 +252,7 @@ def run_reference(args, rank, world):
         return
     pkg = load_pkg()
     tables = pkg.workloads.c3_scene()
-    n = min(args.rays, 2_000_000)
+    n = args.rays  # the SAME batch as the GPU arm (16 777 216 rays, seed 0xB200): ~0.3 s per step on 16 cores
     rays = pkg.workloads.c3_rays(tables, n=n)
     oracle = load_oracle()
     osc = oracle.OracleScene(tables)
@@ -253,7 +272,7 @@ def run_reference(args, rank, world):
         "config": {"workload": "c3-instanced", "triangles": 1032192, "entities": 64, "rays_per_step": n,
                    "ray_order": "generation order (incoherent)"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{n} rays per step of the c3-instanced batch (bounded sample of 16 777 216)"},
+                         "sample": f"all {n} rays of the c3-instanced batch per step"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -283,8 +302,10 @@ def run_ours(args, rank, world, local_rank):
     rays = W.c3_rays(tables, n=n, seed=0xB200 + rank)
 
     dev = pkg.Device(local_rank)
+    t_build = time.perf_counter()
     dev.assign_scene(tables)
     info = dev.bvh_info()
+    info["build_s"] = time.perf_counter() - t_build  # host BVH8 build + upload (igb200_assign_scene), one host thread
 
     d_rays = torch.from_numpy(rays.view(np.float32).reshape(-1, 8)).cuda()
     d_ent = torch.empty(n, dtype=torch.int32, device="cuda")
@@ -328,9 +349,10 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- BASELINE.json configs[2] also names any-hit on the same batch, and SURVEY 8(d) a flattened variant of the
     # same triangles (one 1 M-triangle BVH, ~75 MB of nodes + triangles: L2- instead of L1-resident) ----
-    def timed_variant(device, any_hit, steps):
+    def timed_variant(device, any_hit, steps, src=None):
+        src = d_rays if src is None else src
         def one():
-            device.trace_device(d_rays.data_ptr(), n, d_ent.data_ptr(), d_prim.data_ptr(), d_t.data_ptr(), d_u.data_ptr(),
+            device.trace_device(src.data_ptr(), n, d_ent.data_ptr(), d_prim.data_ptr(), d_t.data_ptr(), d_u.data_ptr(),
                                 d_v.data_ptr(), any_hit=any_hit, stream=stream.cuda_stream)
         for _ in range(3):
             one()
@@ -354,10 +376,34 @@ def run_ours(args, rank, world, local_rank):
         variants = {"c3-instanced any-hit": timed_variant(dev, True, args.variant_steps)}
         fdev = pkg.Device(local_rank)
         ftables = W.c3_scene(flat=True)
+        t_build = time.perf_counter()
         fdev.assign_scene(ftables)
+        flat_build_s = time.perf_counter() - t_build
         variants["c3-flat closest-hit"] = timed_variant(fdev, False, args.variant_steps)
         variants["c3-flat any-hit"] = timed_variant(fdev, True, args.variant_steps)
-        variants["c3-flat bvh"] = fdev.bvh_info()
+        variants["c3-flat bvh"] = dict(fdev.bvh_info(), build_s=flat_build_s)
+        # c3-dense: the same two scenes under rays that (nearly) all hit -- aimed at a random sphere each, so they cross
+        # the grid and are occluded on the way (workloads.c3_dense_rays): deep traversal instead of C3's 18 % hit rate.
+        dense = W.c3_dense_rays(tables, n=n, seed=0xDE5E + rank)
+        d_dense = torch.from_numpy(dense.view(np.float32).reshape(-1, 8)).cuda()
+        peak_v, _ = measured_peak()
+        for name, device, scene_tables in (("c3-dense", dev, tables), ("c3-dense-flat", fdev, ftables)):
+            for any_hit in (False, True):
+                r = timed_variant(device, any_hit, args.variant_steps, d_dense)
+                if rank == 0:  # visit counts of the same kernel (STATS instantiation) on a 2 Mi-ray sample, untimed
+                    sdev = pkg.Device(local_rank, acquire_stats=True)
+                    sdev.assign_scene(scene_tables)
+                    m = min(n, 1 << 21)
+                    sdev.trace(dense[:m], any_hit=any_hit)
+                    st = sdev.trace_stats()
+                    sdev.close()
+                    pr = {"nodes": st["nodes_visited"] / m, "tris": st["tris_tested"] / m, "entities": st["entities_entered"] / m}
+                    bpr = 32 + (4 if any_hit else 20) + 80 * pr["nodes"] + 48 * pr["tris"] + 96 * pr["entities"]
+                    ach = bpr * n / (r["ms_per_step"] * 1e-3) / 1e9
+                    r.update(per_ray=pr, bytes_per_ray=bpr, roofline={"bound": "hbm", "achieved": ach, "peak": peak_v, "unit": "GB/s",
+                                                                      "frac": ach / peak_v})
+                variants[name + (" any-hit" if any_hit else " closest-hit")] = r
+        del d_dense, dense
         fdev.close()
         del ftables
 
@@ -382,21 +428,34 @@ def run_ours(args, rank, world, local_rank):
         e2e_s = float(tm.item())
     e2e_val = world * n * e2e_steps / e2e_s / 1e6
     assert int((outs[1] >= 0).sum()) > 0
+    # the same call asking for the columns igtrace's debug modes 15 / 17 / 13 need (ids + t): 12 B instead of 20 B per ray back
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        dev.trace_into(h_rays_np, outs[0], outs[1], outs[2], None, None)
+    barrier()
+    e2e_ids_s = time.perf_counter() - t0
+    if world > 1:
+        tm = torch.tensor([e2e_ids_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        e2e_ids_s = float(tm.item())
+    e2e_ids_val = world * n * e2e_steps / e2e_ids_s / 1e6
     dev.close()
     del d_rays, d_ent, d_prim, d_t, d_u, d_v
 
     # ---- second headline metric: path-traced samples/s (all ranks take part) ----
-    pt = bench_path_tracer(pkg, local_rank, rank, world, args.pt_iterations, 2) if args.pt_iterations > 0 else None
+    # (weak scaling: the request grows with the number of ranks, pt_iterations per GPU)
+    pt = bench_path_tracer(pkg, local_rank, rank, world, args.pt_iterations * world, 2) if args.pt_iterations > 0 else None
+    if pt is not None:
+        pt["scaling"] = "weak"
 
     # ---- BASELINE.json configs[4]: many_point_lights at 3840x2160, a FIXED number of samples per pixel split across
-    # the ranks by iteration index (strong scaling); rank r renders iterations [r*K, (r+1)*K) (+ the remainder on the last)
+    # the ranks inside the library (strong scaling: igb200_partition_share, iteration blocks; tile rows when spp < ranks * spi)
     c5 = None
     if args.c5_spp > 0:
         _, _, _, _, c5_spi = load_pt_workload(pkg, "c5-many-point-lights")
-        total_it = max(world, args.c5_spp // c5_spi)
-        per = total_it // world
-        mine = per + (total_it - per * world if rank == world - 1 else 0)
-        c5 = bench_path_tracer(pkg, local_rank, rank, world, mine, 2, "c5-many-point-lights", first=rank * per)
+        total_it = max(1, args.c5_spp // c5_spi)
+        c5 = bench_path_tracer(pkg, local_rank, rank, world, total_it, 2, "c5-many-point-lights")
         c5["scaling"] = "strong"
         c5["spp"] = int(c5["iterations"] * c5["spi"])
 
@@ -436,7 +495,8 @@ def run_ours(args, rank, world, local_rank):
                        "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (n * 52 / 1e6),
                        "bvh": info},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 20,
-                    "steps": e2e_steps},
+                    "steps": e2e_steps,
+                    "ids_and_t_only": {"value": e2e_ids_val, "unit": UNIT, "d2h_bytes_per_step": n * 12}},
             "gpu_launches": args.steps,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -447,7 +507,7 @@ def run_ours(args, rank, world, local_rank):
         }
         if variants is not None:
             line["trace_variants"] = variants
-            line["gpu_launches"] += 3 * (args.variant_steps + 3)
+            line["gpu_launches"] += 7 * (args.variant_steps + 3) + 4
         if pt is not None:
             pt["cpu_baseline"] = oracle_samples_per_s(pkg) if world == 1 else None
             line["path_tracer"] = pt

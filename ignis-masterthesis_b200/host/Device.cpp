@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 namespace IG {
 // reference: `static Interface* sInterface` + IG_ASSERT(sInterface == nullptr, ...) (Device.cpp:1540,1564)
@@ -25,14 +26,17 @@ Device::Device(const SetupSettings& settings)
         std::fprintf(stderr, "[FATAL] Device: Only a single instance allowed!\n");
         std::abort();
     }
-    igb200_setup setup{ (int32_t)settings.target.device(), settings.AcquireStats ? 1 : 0, settings.DebugTrace ? 1 : 0, 0 };
-    if (igb200_create(&setup, &mHandle) != IGB200_OK) fatal("Device");
+    if (mSetup.DeviceCount == 0) mSetup.DeviceCount = 1;
+    std::vector<int32_t> ordinals(mSetup.DeviceCount);
+    for (size_t i = 0; i < ordinals.size(); ++i) ordinals[i] = (int32_t)(settings.target.device() + i);
+    if (igb200_group_create(ordinals.data(), (uint32_t)ordinals.size(), settings.AcquireStats ? 1 : 0, &mGroup) != IGB200_OK) fatal("Device");
+    mHandle   = igb200_group_device(mGroup, 0);
     sInstance = this;
 }
 
 Device::~Device()
 {
-    igb200_destroy(mHandle);
+    igb200_group_destroy(mGroup);
     sInstance = nullptr;
 }
 
@@ -62,12 +66,12 @@ void Device::assignScene(const SceneSettings& settings)
     std::memcpy(sc.scene_bbox + 0, db.SceneBBox.min.data(), 12);
     std::memcpy(sc.scene_bbox + 3, db.SceneBBox.max.data(), 12);
     sc.material_count = (uint32_t)db.MaterialCount;
-    if (igb200_assign_scene(mHandle, &sc) != IGB200_OK) fatal("Device::assignScene");
+    if (igb200_group_assign_scene(mGroup, &sc) != IGB200_OK) fatal("Device::assignScene");
 }
 
 void Device::assignShading(const igb200_shading& shading)
 {
-    if (igb200_assign_shading(mHandle, &shading) != IGB200_OK) fatal("Device::assignShading");
+    if (igb200_group_assign_shading(mGroup, &shading) != IGB200_OK) fatal("Device::assignShading");
 }
 
 static igb200_render_settings to_abi(const Device::RenderSettings& rs)
@@ -96,12 +100,14 @@ void Device::renderIterations(const RenderSettings& settings, size_t count)
         mWidth  = settings.width;
         mHeight = 1;
     }
-    if (igb200_render_iterations(mHandle, &s, (uint32_t)count) != IGB200_OK) fatal("Device::render");
+    // one member: plain igb200_render_iterations on it; several: partition (AUTO: by iteration when there are enough of them,
+    // else by tile rows), render concurrently, ncclReduce onto member 0
+    if (igb200_group_render(mGroup, &s, (uint32_t)count, IGB200_PARTITION_AUTO) != IGB200_OK) fatal("Device::render");
 }
 
 void Device::resize(size_t width, size_t height)
 {
-    if (igb200_resize(mHandle, (uint32_t)width, (uint32_t)height) != IGB200_OK) fatal("Device::resize");
+    if (igb200_group_resize(mGroup, (uint32_t)width, (uint32_t)height) != IGB200_OK) fatal("Device::resize");
     mWidth  = width;
     mHeight = height;
 }
@@ -134,14 +140,22 @@ void Device::clearFramebuffer(const std::string& name)
 }
 void Device::clearAllFramebuffer()
 {
-    if (igb200_clear_framebuffer(mHandle) != IGB200_OK) error("Device::clearAllFramebuffer");
+    if (igb200_group_clear_framebuffer(mGroup) != IGB200_OK) error("Device::clearAllFramebuffer");
 }
 
 igb200_render_stats Device::renderStats() const
 {
     igb200_render_stats st{};
-    igb200_get_render_stats(mHandle, &st);
+    igb200_group_get_render_stats(mGroup, &st, nullptr); // summed over the members
     return st;
+}
+
+float Device::lastFilmReduceMs() const
+{
+    igb200_render_stats st{};
+    float               ms = 0.0f;
+    igb200_group_get_render_stats(mGroup, &st, &ms);
+    return ms;
 }
 
 void Device::tonemap(uint32_t* out, const TonemapSettings& s)

@@ -24,6 +24,10 @@ public:
         bool   AcquireStats  = false;
         bool   DebugTrace    = false;
         bool   IsInteractive = false;
+        // B200 extension (no reference counterpart: the reference is single-device, Device.cpp:232-243): number of GPUs of
+        // this box to render on, target.device() .. + DeviceCount - 1.  Scene replicated, requests partitioned by iteration
+        // index or by interleaved tile rows, films combined with one ncclReduce onto the first device (igb200_group_*).
+        size_t DeviceCount   = 1;
     };
     struct SceneSettings { // Device.h:25-30; borrowed pointers, read during assignScene only (the backend copies to HBM)
         SceneDatabase*                  database            = nullptr;
@@ -78,10 +82,14 @@ public:
     // path run with EnableTonemapping = false (cli/main.cpp:62, trace/main.cpp:77) and never call them.
 
     [[nodiscard]] igb200_device* handle() const { return mHandle; }
+    [[nodiscard]] igb200_group*  group() const { return mGroup; }
+    [[nodiscard]] size_t deviceCount() const { return mSetup.DeviceCount; }
+    [[nodiscard]] float  lastFilmReduceMs() const;
 
 private:
     SetupSettings  mSetup;
-    igb200_device* mHandle = nullptr;
+    igb200_group*  mGroup  = nullptr; // owns the device handles (one member when DeviceCount == 1: no NCCL involved)
+    igb200_device* mHandle = nullptr; // member 0: holds the combined film
     size_t         mWidth = 0, mHeight = 0;
 };
 } // namespace IG

@@ -14,7 +14,7 @@ struct ProgramOptions {
     std::string           InputScene, InputRay, Output;
     std::optional<size_t> SPP, SPI, Width, Height;
     size_t                Seed   = 0;
-    int                   Device = 0, DebugMode = 0;
+    int                   Device = 0, DebugMode = 0, Gpus = 1;
     std::string           Technique;
     bool                  Quiet = false, ShouldExit = false, Stats = false;
     int                   ExitCode = EXIT_SUCCESS;
@@ -35,7 +35,7 @@ struct ProgramOptions {
             if (a == "-h" || a == "--help") {
                 std::cout << title << "\nusage: " << argv[0] << " scene.igdb "
                           << (tracer ? "[-i rays.txt] " : "") << "[-o output] [--spp N] [--spi N] [--seed N] [--technique path|debug|infobuffer]"
-                          << " [--debug-mode N] [--width W --height H] [--device N] [--stats] [-q]" << std::endl;
+                          << " [--debug-mode N] [--width W --height H] [--device N] [--gpus N] [--stats] [-q]" << std::endl;
                 ShouldExit = true;
             } else if (a == "-o" || a == "--output") Output = value(i);
             else if (tracer && (a == "-i" || a == "--input")) InputRay = value(i);
@@ -45,6 +45,7 @@ struct ProgramOptions {
             else if (a == "--width") Width = (size_t)std::strtoull(value(i), nullptr, 10);
             else if (a == "--height") Height = (size_t)std::strtoull(value(i), nullptr, 10);
             else if (a == "--device") Device = std::atoi(value(i));
+            else if (a == "--gpus") Gpus = std::atoi(value(i));
             else if (a == "--technique") Technique = value(i);
             else if (a == "--debug-mode") DebugMode = std::atoi(value(i));
             else if (a == "--stats") Stats = true;
@@ -60,6 +61,7 @@ struct ProgramOptions {
     void populate(RuntimeOptions& opts) const
     {
         opts.DeviceOrdinal     = Device;
+        opts.DeviceCount       = Gpus;
         opts.Seed              = Seed;
         opts.SPI               = SPI.value_or(0);
         opts.OverrideTechnique = Technique;

@@ -21,6 +21,7 @@ Runtime::Runtime(const RuntimeOptions& opts)
     Device::SetupSettings setup;
     setup.target       = Target(opts.DeviceOrdinal);
     setup.AcquireStats = opts.AcquireStats;
+    setup.DeviceCount  = (size_t)std::max(1, opts.DeviceCount);
     mDevice            = std::make_unique<Device>(setup);
 }
 

@@ -11,6 +11,7 @@
 namespace IG {
 struct RuntimeOptions { // src/runtime/RuntimeSettings.h (the fields these frontends set)
     int    DeviceOrdinal = 0;
+    int    DeviceCount   = 1;     // --gpus N: GPUs DeviceOrdinal .. + N - 1 (B200 extension, see Device::SetupSettings)
     bool   IsTracer      = false; // igtrace: list emitter, film = N x 1
     bool   AcquireStats  = false;
     size_t Seed          = 0;

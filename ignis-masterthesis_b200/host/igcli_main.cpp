@@ -74,6 +74,8 @@ int main(int argc, char** argv)
         const igb200_render_stats st = runtime.device().renderStats();
         std::cout << "  Iterations: " << runtime.currentIterationCount() << "\n  SPP: " << runtime.currentSampleCount() << "\n  SPI: " << SPI
                   << "\n  Render>  " << render_s * 1e3 << " ms\n  Total>   " << std::chrono::duration<double>(clock::now() - t_all).count() * 1e3 << " ms" << std::endl;
+        if (runtime.device().deviceCount() > 1)
+            std::cout << "  GPUs: " << runtime.device().deviceCount() << "\n  Film reduce (last call)> " << runtime.device().lastFilmReduceMs() << " ms" << std::endl;
         if (cmd.Stats)
             std::cout << "  Rays (last call)> camera " << st.camera_rays << " bounce " << st.bounce_rays << " shadow " << st.shadow_rays << std::endl;
         std::sort(samples_sec.begin(), samples_sec.end());

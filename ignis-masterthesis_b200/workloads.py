@@ -136,3 +136,36 @@ def c3_rays(tables, n=16_777_216, seed=0xB200, chunk=1 << 20):
     rays["tmin"] = 1e-4
     rays["tmax"] = np.finfo(np.float32).max
     return rays
+
+
+def c3_dense_rays(tables, n=16_777_216, seed=0xDE5E, grid=4, chunk=1 << 20):
+    """The high-hit-rate companion of c3_rays on the same scene: origins uniform in the scene box
+    scaled x1.25 as before, but every ray is aimed at a point inside a randomly chosen sphere (centre + 0.9 r * uniform
+    ball), so it hits that sphere or an occluder in front of it: hit rate ~1, long paths through the grid, rays still
+    in generation order (incoherent: consecutive rays share neither origin nor target)."""
+    lo, hi = tables.bbox[:3].astype(np.float64), tables.bbox[3:].astype(np.float64)
+    c, h = (lo + hi) / 2, (hi - lo) / 2 * 1.25
+    diag = 2.0 * np.sqrt(3.0)                       # bbox diagonal of the unit sphere (uv_sphere, radius 1)
+    spacing = 2.5 * diag / np.sqrt(3.0)
+    rays = np.zeros(n, RAY_DTYPE)
+    for start in range(0, n, chunk):
+        m = min(chunk, n - start)
+        u = uniform01(seed, 8 * start, 8 * m).reshape(m, 8).astype(np.float64)
+        org = c + (u[:, :3] * 2 - 1) * h
+        cell = np.minimum((u[:, 3:6] * grid).astype(np.int64), grid - 1)
+        centre = (cell - (grid - 1) / 2.0) * spacing
+        # uniform point in the ball of radius 0.9 from three of the remaining numbers (direction from 6, 7; radius from the
+        # fractional part of u3 * grid, which is independent of the cell index)
+        z = 1 - 2 * u[:, 6]
+        r = np.sqrt(np.maximum(0.0, 1 - z * z))
+        phi = 2 * np.pi * u[:, 7]
+        rad = 0.9 * np.cbrt(u[:, 3] * grid - cell[:, 0])
+        tgt = centre + rad[:, None] * np.stack([r * np.cos(phi), r * np.sin(phi), z], axis=1)
+        d = tgt - org
+        d /= np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-30)
+        sl = rays[start:start + m]
+        sl["org"] = org.astype(np.float32)
+        sl["dir"] = d.astype(np.float32)
+    rays["tmin"] = 1e-4
+    rays["tmax"] = np.finfo(np.float32).max
+    return rays

@@ -122,3 +122,26 @@ def test_igcli_image_matches_the_binding(ig, host_bin, tmp_path, name, size, bat
     assert iters == 2 and img.shape == (sh_, sw, 3) and img.mean() > 0.01
     # the same samples; only the order of the f32 atomic additions into the film differs
     np.testing.assert_allclose(img, film / 2, rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("batch", [False, True])
+def test_igcli_gpus_2_image_equals_one_gpu_image(ig, host_bin, tmp_path, batch):
+    """`igcli --gpus 2` (IG::Device over igb200_group_*): per-iteration steps split by tile rows (1 iteration < 2 GPUs), the
+    --batch form by iteration index; either way the EXR equals the one-GPU EXR up to f32 summation order."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    import cv2
+    tables, sh, w, h, _ = load_golden(ig, "cbox-d6")
+    scene = str(tmp_path / "scene.igdb")
+    ig.fixtures.save_igdb(scene, tables, sh, w, h)
+    imgs = []
+    for gpus in (1, 2):
+        out = str(tmp_path / f"out{gpus}.exr")
+        cmd = [os.path.join(host_bin, "igcli"), scene, "-o", out, "--spp", "16", "--spi", "4", "--seed", "7", "--width", "160", "--height", "120",
+               "--gpus", str(gpus)] + (["--batch"] if batch else [])
+        r = _run(*cmd)
+        assert "Iterations: 4" in r.stdout and ("GPUs: 2" in r.stdout) == (gpus == 2)
+        imgs.append(cv2.imread(out, cv2.IMREAD_UNCHANGED))
+    np.testing.assert_allclose(imgs[1], imgs[0], rtol=1e-4, atol=1e-6)

@@ -92,6 +92,21 @@ def test_c3_benchmark_batch_itself_16m_rays(ig, oracle, dev, capsys):
     assert frac > 0.99999 and occl <= 4    # a grazing ray may be occluded by one side of a tie only
 
 
+@pytest.mark.parametrize("flat", [False, True])
+def test_c3_dense_2m_rays(ig, oracle, dev, flat):
+    """bench.py's c3-dense variants: rays aimed at the spheres (hit rate ~1, deep traversal) against the oracle, closest-hit
+    ids / t / u / v and any-hit occlusion, instanced and flattened scene."""
+    tables = ig.workloads.c3_scene(flat=flat)
+    rays = ig.workloads.c3_dense_rays(tables, n=1 << 21)
+    frac, hits = _compare(ig, oracle, dev, tables, rays)
+    assert frac > 0.9999 and hits > 0.99 * rays.size
+    st = dev.trace_stats()
+    assert st["nodes_visited"] > 8 * rays.size     # several times deeper than C3's 5 node steps per ray
+    aprim = dev.trace(rays, any_hit=True)[1]
+    oprim = oracle.OracleScene(tables).trace(rays, any_hit=True)[1]
+    assert np.count_nonzero((aprim >= 0) != (oprim >= 0)) <= 2
+
+
 def test_c3_full_size_instanced_equals_flattened(ig, dev):
     """Size-independent property at BASELINE.json's full scene size: the 64-instance scene and the same 1 032 192
     triangles baked to world space (SURVEY 8(d) 'C3-flat') are one geometry, so entity e / primitive p of the
