@@ -31,6 +31,7 @@ ABI_SYMBOLS = [
     "igb200_resize",
     "igb200_set_framebuffer",
     "igb200_get_render_stats",
+    "igb200_get_section_stats",
     # ABI v6: multi-GPU
     "igb200_partition_share",
     "igb200_render_partition",
@@ -97,6 +98,11 @@ class Setup(C.Structure):
     _fields_ = [("device", C.c_int32), ("acquire_stats", C.c_int32), ("debug_trace", C.c_int32), ("_pad", C.c_int32)]
 
 
+class SectionStats(C.Structure):
+    _fields_ = [("kernel_ms", C.c_float * 6), ("launches", C.c_uint64 * 6), ("framebuffer_host_update_ms", C.c_float),
+                ("framebuffer_host_updates", C.c_uint32)]
+
+
 class TraceStats(C.Structure):
     _fields_ = [
         ("rays", C.c_uint64),
@@ -145,6 +151,7 @@ def load():
     lib.igb200_resize.argtypes = [vp, u32, u32]
     lib.igb200_set_framebuffer.argtypes = [vp, vp, u64, u64]
     lib.igb200_get_render_stats.argtypes = [vp, vp]
+    lib.igb200_get_section_stats.argtypes = [vp, vp, i32]
     pu32 = C.POINTER(u32)
     lib.igb200_partition_share.argtypes = [u32, u32, u32, u32, pu32, pu32, pu32, pu32]
     lib.igb200_render_partition.argtypes = [vp, vp, u32, u32, u32, u32]

@@ -134,6 +134,8 @@ struct igb200_device {
     uint64_t                      iterations = 0;
     bool                          film_mapped = false; // host copy is current
     igb200_render_stats           render_stats{};
+    igb200_section_stats          section{};   // accumulated since create / igb200_reset_section_stats (stats mode only)
+    cudaEvent_t                   sec_ev[igb::kWaveLaunchesPerRound + 1] = {};
 
     // Named AOV images next to the film (Interface::aovs, Device.cpp:95-100,1300-1307): allocated at film size the first
     // time a technique that enables them renders, each with its own iteration count (markAOVAsUsed / present,
@@ -212,6 +214,8 @@ void igb200_destroy(igb200_device* dev)
         if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : dev->round_ev)
         if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : dev->sec_ev)
+        if (e) cudaEventDestroy(e);
     if (dev->round_graph) cudaGraphExecDestroy(dev->round_graph);
     if (dev->h_done) cudaFreeHost(dev->h_done);
     if (dev->h_film) cudaFreeHost(dev->h_film);
@@ -241,6 +245,16 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
                             (unsigned long long)sc->shape_count);
             if (sc->shape_lookups[l.shape_id].type_id != (uint32_t)k)
                 return fail(IGB200_E_INVALID, "entity %d: shape %d is not of primitive type %d", l.entity_id, l.shape_id, k);
+            // the shading kernels index ent_mat[], entities[36 * ent] and the shape tables with the hit's entity id unguarded
+            if (sc->entities) {
+                if (l.entity_id < 0 || (uint64_t)l.entity_id >= sc->entity_count)
+                    return fail(IGB200_E_INVALID, "leaf %llu of type %d: entity id %d of %llu", (unsigned long long)i, k, l.entity_id,
+                                (unsigned long long)sc->entity_count);
+                int32_t row_shape;
+                std::memcpy(&row_shape, sc->entities + 36 * (size_t)l.entity_id + 33, 4);
+                if (row_shape != l.shape_id)
+                    return fail(IGB200_E_INVALID, "entity %d: leaf says shape %d, entity row says shape %d", l.entity_id, l.shape_id, row_shape);
+            }
             in_leaves.push_back(l);
         }
     }
@@ -284,8 +298,13 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
             if (avail < 48) return fail(IGB200_E_INVALID, "shape %llu: truncated mesh header", (unsigned long long)s);
             uint32_t hdr[4];
             std::memcpy(hdr, data, 16);
-            const uint64_t nf = hdr[0], nv = hdr[1], nn = hdr[2];
-            if (avail < 4 * (12 + nv * 4 + nn * 4 + nf * 4))
+            const uint64_t nf = hdr[0], nv = hdr[1], nn = hdr[2], nt = hdr[3];
+            // TriMesh::normal(idx) and tex_base()[idx] (shade_lib.cuh) are indexed by VERTEX index: one normal and one
+            // texture coordinate per vertex, and the texcoord block inside the table (TriMeshProvider.cpp:577-598)
+            if (nn < nv || nt < nv)
+                return fail(IGB200_E_INVALID, "shape %llu: %llu normals / %llu texcoords for %llu vertices", (unsigned long long)s,
+                            (unsigned long long)nn, (unsigned long long)nt, (unsigned long long)nv);
+            if (avail < 4 * (12 + nv * 4 + nn * 4 + nf * 4) + 8 * nt)
                 return fail(IGB200_E_INVALID, "shape %llu: truncated mesh data", (unsigned long long)s);
             const float*    verts = reinterpret_cast<const float*>(data) + 12;
             const uint32_t* idx   = reinterpret_cast<const uint32_t*>(data) + 12 + nv * 4 + nn * 4;
@@ -382,6 +401,8 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
     dev->view.tlas_nodes = (uint32_t)tlas.nodes.size();
     dev->view.leaf_count = (uint32_t)ordered.size();
     dev->view.byte_bias  = 0x47000000u;
+    dev->view.node_count = (uint32_t)all_nodes.size();
+    dev->view.tri_count  = (uint32_t)(all_tris.size() / 3);
     dev->node_bytes      = all_nodes.size() * sizeof(Node8);
     dev->tri_bytes       = all_tris.size() * sizeof(float4);
     dev->leaf_bytes      = ordered.size() * sizeof(igb200_entity_leaf);
@@ -856,6 +877,24 @@ static int render_batch(igb200_device* dev, const igb200_render_settings* rs, ui
         cudaGraphDestroy(g);
         if (e4 != cudaSuccess) return fail(IGB200_E_CUDA, "igb200_render: cudaGraphInstantiate failed: %s", cudaGetErrorString(e4));
     }
+    if (dev->stats) {
+        // --stats (Device::SetupSettings::AcquireStats): rounds are launched one by one with an event between the kernels
+        // and a host sync per pair, so that the time of every kernel kind is known (Statistics.h:9-63 names on the host side).
+        if (!dev->sec_ev[0])
+            for (cudaEvent_t& e : dev->sec_ev) IGB_CUDA(cudaEventCreate(&e));
+        for (; pairs < max_pairs; ++pairs) {
+            for (int parity = 0; parity < 2; ++parity) {
+                IGB_CUDA(igb::launch_wave_round(dev->view, dev->shade, dev->wave, parity, dev->wave_sort, dev->sm_count, st, dev->sec_ev));
+                IGB_CUDA(cudaStreamSynchronize(st));
+                for (int k = 0; k < igb::kWaveLaunchesPerRound; ++k) {
+                    float ms = 0.0f;
+                    if (cudaEventElapsedTime(&ms, dev->sec_ev[k], dev->sec_ev[k + 1]) == cudaSuccess) dev->section.kernel_ms[k] += ms;
+                    dev->section.launches[k] += (k == 3 && !dev->wave_sort) ? 0 : 1;
+                }
+            }
+            if (*reinterpret_cast<volatile uint32_t*>(dev->h_done)) { ++pairs; break; }
+        }
+    } else
     for (; pairs < max_pairs; ++pairs) {
         IGB_CUDA(cudaGraphLaunch(dev->round_graph, st));
         IGB_CUDA(cudaEventRecord(dev->round_ev[pairs % 4], st));
@@ -994,9 +1033,17 @@ int igb200_framebuffer(igb200_device* dev, const char* name, int device, float**
         return IGB200_OK;
     }
     if (!dev->film_mapped) { // lazy D2H once per iteration (the `Mapped` flag, Device.cpp:1330-1363)
+        if (dev->stats) IGB_CUDA(cudaEventRecord(dev->ev0, dev->stream));
         IGB_CUDA(cudaMemcpyAsync(dev->h_film, dev->d_film.ptr, (size_t)dev->film_w * dev->film_h * 3 * sizeof(float),
                                  cudaMemcpyDeviceToHost, dev->stream));
+        if (dev->stats) IGB_CUDA(cudaEventRecord(dev->ev1, dev->stream));
         IGB_CUDA(cudaStreamSynchronize(dev->stream));
+        if (dev->stats) { // SectionType::FramebufferHostUpdate (Statistics.h:50)
+            float ms = 0.0f;
+            cudaEventElapsedTime(&ms, dev->ev0, dev->ev1);
+            dev->section.framebuffer_host_update_ms += ms;
+            dev->section.framebuffer_host_updates += 1;
+        }
         dev->film_mapped = true;
     }
     *data = dev->h_film;
@@ -1082,6 +1129,14 @@ int igb200_set_framebuffer(igb200_device* dev, const float* d_src, uint64_t coun
     IGB_CUDA(cudaStreamSynchronize(dev->stream));
     dev->iterations  = iterations;
     dev->film_mapped = false;
+    return IGB200_OK;
+}
+
+int igb200_get_section_stats(igb200_device* dev, igb200_section_stats* out, int reset)
+{
+    if (!dev || !out) return fail(IGB200_E_INVALID, "igb200_get_section_stats: NULL argument");
+    *out = dev->section;
+    if (reset) dev->section = igb200_section_stats{};
     return IGB200_OK;
 }
 

@@ -17,6 +17,8 @@
 #pragma once
 #include "trace.cuh"
 
+#include <cstdio>
+
 #include "../../include/ignis_b200.h"
 
 namespace igb {
@@ -52,6 +54,28 @@ constexpr int      kVoteRefill  = IGB_VOTE_REFILL; // idle lanes that must wait 
 #ifndef IGB_ENT_ONE_WAIT
 #define IGB_ENT_ONE_WAIT 1
 #endif
+// Debug build (scripts/build_variant.sh dbg -DIGB_DEBUG_CHECKS=1): device-side bounds checks on every stack push and
+// on every node / triangle / leaf index the traversal dereferences; a violation prints once and traps.  This is the
+// stand-in for compute-sanitizer memcheck, which is closed on this GPU pool (profiles/r02_sanitizer_closed.txt).
+#ifndef IGB_DEBUG_CHECKS
+#define IGB_DEBUG_CHECKS 0
+#endif
+#if IGB_DEBUG_CHECKS
+#define IGB_CHECK(cond, what)                                                                              \
+    do {                                                                                                   \
+        if (!(cond)) {                                                                                     \
+            printf("IGB_CHECK failed: %s (%s:%d, block %u thread %u)\n", what, __FILE__, __LINE__, blockIdx.x, threadIdx.x); \
+            __trap();                                                                                      \
+        }                                                                                                  \
+    } while (0)
+#else
+#define IGB_CHECK(cond, what) ((void)0)
+#endif
+#define IGB_PUSH(v)                                        \
+    do {                                                   \
+        IGB_CHECK(sp < kStackSize, "traversal stack overflow"); \
+        stack[sp++] = (v);                                 \
+    } while (0)
 #ifndef IGB_NODE_REPS
 #define IGB_NODE_REPS 1 // node steps per loop trip (lanes that can take another one do; the other phases run once per trip)
 #endif
@@ -339,7 +363,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
         // Experiment: a lane with both inner children and primitives pending parks the primitive group on the stack and
         // keeps descending (it is tested when popped) instead of waiting for the primitive vote.
         if (active && tgroup.y != 0u && ngroup.y > 0x00FFFFFFu && (IGB_PARK_PRIMS == 2 || in_blas)) {
-            stack[sp++] = tgroup;
+            IGB_PUSH(tgroup);
             tgroup      = make_uint2(0u, 0u);
         }
 #endif
@@ -361,7 +385,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
             const uint32_t imask           = ngroup.y & 0xFFu;
             const uint32_t child_bit_index = 31u - (uint32_t)__clz(hits);
             ngroup.y &= ~(1u << child_bit_index);
-            if (ngroup.y > 0x00FFFFFFu) stack[sp++] = ngroup;
+            if (ngroup.y > 0x00FFFFFFu) IGB_PUSH(ngroup);
 
             const uint32_t slot_index     = (child_bit_index - 24u) ^ (ray.octinv4 & 0xFFu);
             const uint32_t relative_index = __popc(imask & ~(0xFFFFFFFFu << slot_index));
@@ -370,6 +394,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
             const uint4*   np             = ni < n_top ? s_top + 5 * ni : sc.nodes + 5 * (size_t)ni; // generic loads
             const uint4    n0 = np[0], n1 = np[1], n2 = np[2], n3 = np[3], n4 = np[4];
 #else
+            IGB_CHECK(ngroup.x + relative_index < sc.node_count, "node index out of range");
             const uint4*   np             = sc.nodes + 5 * (size_t)(ngroup.x + relative_index);
             const uint4    n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
 #endif
@@ -399,6 +424,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                 const bool     two = tgroup.y != 0u;
                 const uint32_t i1  = two ? 31u - (uint32_t)__clz(tgroup.y) : i0;
                 tgroup.y &= ~(1u << i1);
+                IGB_CHECK(tgroup.x + i0 < sc.tri_count, "triangle index out of range");
                 const float4* tp0 = sc.tris + 3 * (size_t)(tgroup.x + i0);
                 const float4* tp1 = sc.tris + 3 * (size_t)(tgroup.x + i1);
                 const float4  a0 = __ldg(tp0 + 0), b0 = __ldg(tp0 + 1), c0 = __ldg(tp0 + 2);
@@ -411,6 +437,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                 while (tgroup.y != 0u && budget-- > 0) {
                     const uint32_t idx = 31u - (uint32_t)__clz(tgroup.y);
                     tgroup.y &= ~(1u << idx);
+                    IGB_CHECK(tgroup.x + idx < sc.tri_count, "triangle index out of range");
                     const float4* tp = sc.tris + 3 * (size_t)(tgroup.x + idx);
                     const float4  a = __ldg(tp + 0), b = __ldg(tp + 1), c = __ldg(tp + 2);
                     if (STATS) c_tris++;
@@ -426,6 +453,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                     const uint32_t idx = 31u - (uint32_t)__clz(tgroup.y);
                     tgroup.y &= ~(1u << idx);
                     // Entity leaf step: gpu_traverse_scene::scene_handle (traversal/mapping_gpu.art:196-222)
+                    IGB_CHECK(tgroup.x + idx < sc.leaf_count, "entity leaf index out of range");
                     const float4*  lp = sc.leaves + 6 * (size_t)(tgroup.x + idx);
                     const float4   l0 = __ldg(lp + 0), l1 = __ldg(lp + 1), l5 = __ldg(lp + 5);
 #if IGB_ENT_ONE_WAIT
@@ -466,15 +494,15 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                         continue;
                     }
                     // Enter the shape's BVH: park the entity-level state and the world ray under a sentinel.
-                    if (ngroup.y > 0x00FFFFFFu) stack[sp++] = ngroup;
-                    if (tgroup.y != 0u) stack[sp++] = tgroup;
-                    stack[sp++] = make_uint2(__float_as_uint(ray.org.x), __float_as_uint(ray.org.y));
-                    stack[sp++] = make_uint2(__float_as_uint(ray.org.z), __float_as_uint(ray.dir.x));
-                    stack[sp++] = make_uint2(__float_as_uint(ray.dir.y), __float_as_uint(ray.dir.z));
+                    if (ngroup.y > 0x00FFFFFFu) IGB_PUSH(ngroup);
+                    if (tgroup.y != 0u) IGB_PUSH(tgroup);
+                    IGB_PUSH(make_uint2(__float_as_uint(ray.org.x), __float_as_uint(ray.org.y)));
+                    IGB_PUSH(make_uint2(__float_as_uint(ray.org.z), __float_as_uint(ray.dir.x)));
+                    IGB_PUSH(make_uint2(__float_as_uint(ray.dir.y), __float_as_uint(ray.dir.z)));
                     // the world ray's box-test reciprocals and octant travel too: leaving the shape costs loads, not three MUFUs
-                    stack[sp++] = make_uint2(__float_as_uint(ray.idir.x), __float_as_uint(ray.idir.y));
-                    stack[sp++] = make_uint2(__float_as_uint(ray.idir.z), ray.octinv4);
-                    stack[sp++] = make_uint2(kSentinel, 0u);
+                    IGB_PUSH(make_uint2(__float_as_uint(ray.idir.x), __float_as_uint(ray.idir.y)));
+                    IGB_PUSH(make_uint2(__float_as_uint(ray.idir.z), ray.octinv4));
+                    IGB_PUSH(make_uint2(kSentinel, 0u));
                     ray         = local;
                     setup_trav_ray(ray);
                     in_blas = true;
@@ -493,6 +521,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                     finished = true;
                 } else {
                     uint2 e = stack[--sp];
+                    IGB_CHECK(e.x != kSentinel || sp >= 5, "sentinel without a parked world ray");
                     if (e.x == kSentinel) {
                         // Leave the shape: back to world space.
                         const uint2 i1 = stack[--sp], i0 = stack[--sp], c = stack[--sp], b = stack[--sp], a = stack[--sp];
@@ -517,6 +546,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                 }
             }
             if (finished) {
+                IGB_CHECK(ray_id < n, "ray id out of range at store");
                 io.store(ray_id, hit, s_bins);
                 active = false;
             }

@@ -586,19 +586,25 @@ cudaError_t launch_wave_reset(const WaveBuffers& buf, const WaveSettings& set, u
 }
 
 cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene& sh, const WaveBuffers& buf, int parity,
-                              int sort, int sm_count, cudaStream_t stream)
+                              int sort, int sm_count, cudaStream_t stream, cudaEvent_t* ev)
 {
+#define IGB_EV(k) do { if (ev) cudaEventRecord(ev[k], stream); } while (0)
     const PathStream& cur = buf.stream[parity & 1];
     const PathStream& nxt = buf.stream[(parity + 1) & 1];
     const uint32_t    n_bins = (uint32_t)sh.n_mat + 1u;
     if (n_bins > kWaveMaxBins) return cudaErrorInvalidValue;
     const int wide = sm_count * 8; // grid-stride kernels: a whole number of waves
 
+    IGB_EV(0);
     begin_round_kernel<<<1, 256, 0, stream>>>(buf.ctl, n_bins, buf.host_done);
+    IGB_EV(1);
     generate_kernel<<<wide, 256, 0, stream>>>(buf.ctl, cur, sh);
+    IGB_EV(2);
     const PrimaryIO pio{ cur, buf.keys, buf.ent_mat, buf.ctl, n_bins };
     trace_kernel<PrimaryIO, false, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, pio, nullptr, buf.ctl->work_primary);
+    IGB_EV(3);
     if (sort) scatter_kernel<<<wide / 2, 256, 0, stream>>>(buf.ctl, buf.keys, buf.sorted, n_bins, sort == 2 && n_bins <= kMaxSmemBins);
+    IGB_EV(4);
     // four instantiations: {lean, extended material set} x {path / debug, infobuffer}, picked per scene and technique
 #define SHADE_LAUNCH(EXT)                                                                                                           \
     do {                                                                                                                            \
@@ -612,8 +618,11 @@ cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene&
     else
         SHADE_LAUNCH(false);
 #undef SHADE_LAUNCH
+    IGB_EV(5);
     const ShadowIO sio{ buf.shadow, buf.ctl };
     trace_kernel<ShadowIO, true, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, sio, nullptr, buf.ctl->work_shadow);
+    IGB_EV(6);
+#undef IGB_EV
     return cudaGetLastError();
 }
 

@@ -100,7 +100,9 @@ namespace shade { struct ShadeScene; }
 // Enqueues ONE wavefront round (parity selects which stream buffer is current) on `stream`:
 // begin_round, generate, trace_primary(+histogram+scan), scatter, shade, trace_shadow(+splat).
 cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene& sh, const WaveBuffers& buf, int parity,
-                              int sort, int sm_count, cudaStream_t stream); // sort: 0 off, 1 global, 2 tile-local
+                              int sort, int sm_count, cudaStream_t stream, // sort: 0 off, 1 global, 2 tile-local
+                              cudaEvent_t* events = nullptr); // stats mode: kWaveLaunchesPerRound + 1 events, one before each
+                                                              // kernel and one after the last (not capturable into a graph)
 
 // Resets the control block for a new call (total = spi * w * h * iterations) and stores its settings.
 cudaError_t launch_wave_reset(const WaveBuffers& buf, const WaveSettings& set, uint32_t total, cudaStream_t stream);

@@ -167,6 +167,16 @@ class Device:
                 "rounds": st.rounds, "kernel_launches": st.kernel_launches, "device_ms": st.device_ms,
                 "film": getattr(self, "_film", (0, 0))}
 
+    SECTION_NAMES = ("begin_round", "generate", "trace_primary", "scatter", "shade", "trace_shadow")
+
+    def section_stats(self, reset=False):
+        """igb200_get_section_stats: per-kernel-kind device ms and launch counts (devices created with acquire_stats)."""
+        st = _lib.SectionStats()
+        _lib.check(self._lib.igb200_get_section_stats(self._h, C.addressof(st), 1 if reset else 0))
+        out = {n: {"ms": st.kernel_ms[i], "launches": st.launches[i]} for i, n in enumerate(self.SECTION_NAMES)}
+        out["framebuffer_host_update"] = {"ms": st.framebuffer_host_update_ms, "launches": st.framebuffer_host_updates}
+        return out
+
     def bvh_info(self):
         nb, tb, lb, d = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_uint32()
         _lib.check(self._lib.igb200_get_bvh_info(self._h, C.byref(nb), C.byref(tb), C.byref(lb), C.byref(d)))

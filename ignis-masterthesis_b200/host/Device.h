@@ -12,6 +12,7 @@
 #include "technique/TechniqueVariant.h"
 #else
 #include "IgTypes.h"
+#include "Statistics.h"
 #endif
 
 #include <ignis_b200.h>
@@ -74,12 +75,19 @@ public:
     void clearFramebuffer(const std::string& name);
     void clearAllFramebuffer();
 
-    [[nodiscard]] const Statistics* getStatistics() { return nullptr; } // ray counters: renderStats()
+    // Device.h:68 -- per-kernel times (device created with AcquireStats) and ray counters under the reference's names
+    [[nodiscard]] const Statistics* getStatistics();
     [[nodiscard]] igb200_render_stats renderStats() const;
 
     void tonemap(uint32_t* out, const TonemapSettings& settings);
-    // evaluateGlare / imageinfo / bake: out of scope (SURVEY.md 8(b) "Utility"); the reference's frontends on this
-    // path run with EnableTonemapping = false (cli/main.cpp:62, trace/main.cpp:77) and never call them.
+    // Device.h:71-73.  Off the hot path (SURVEY.md 8(b) "Utility"; the frontends on this path run with EnableTonemapping =
+    // false, cli/main.cpp:62, trace/main.cpp:77) but present, so that IG::Runtime links (Runtime.cpp:447,649,663):
+    //   imageinfo     luminance statistics of the film or an AOV (entrypoints/imageinfo.art), computed from the host copy
+    //   evaluateGlare not available in this backend: logs once, returns a zeroed GlareOutput
+    //   bake          texture baking runs through the JIT'd shader the reference hands in; there is none here: zero-fills
+    [[nodiscard]] GlareOutput     evaluateGlare(uint32_t* out, const GlareSettings& settings);
+    [[nodiscard]] ImageInfoOutput imageinfo(const ImageInfoSettings& settings);
+    void bake(const ShaderOutput<void*>& shader, const std::vector<std::string>* resource_map, float* output);
 
     [[nodiscard]] igb200_device* handle() const { return mHandle; }
     [[nodiscard]] igb200_group*  group() const { return mGroup; }
@@ -91,5 +99,9 @@ private:
     igb200_group*  mGroup  = nullptr; // owns the device handles (one member when DeviceCount == 1: no NCCL involved)
     igb200_device* mHandle = nullptr; // member 0: holds the combined film
     size_t         mWidth = 0, mHeight = 0;
+    uint64_t       mRays[3] = { 0, 0, 0 }; // camera, bounce, shadow since creation
+#ifndef IG_B200_IN_REFERENCE_TREE
+    Statistics     mStats;
+#endif
 };
 } // namespace IG

@@ -123,6 +123,43 @@ struct TechniqueVariantShaderSet {};
 struct ParameterSet {};
 class Statistics;
 
+// RuntimeStructs.h:15-54 -- utility entry points of the device (out of the hot path; Device.h:70-73)
+struct GlareSettings {
+    const char* AOV                 = nullptr;
+    float       Scale               = 1;
+    float       LuminanceMax        = 0;
+    float       LuminanceAverage    = 0;
+    float       LuminanceMultiplier = 0;
+    float       VerticalIlluminance = 0;
+};
+struct GlareOutput {
+    float DGP                 = 0;
+    float VerticalIlluminance = 0;
+    int   NumPixels           = 0;
+    float AvgLum              = 0;
+    float AvgOmega            = 0;
+};
+struct ImageInfoSettings {
+    const char* AOV   = nullptr;
+    float       Scale = 1;
+    size_t      Bins  = 0;
+    int*        HistogramR = nullptr;
+    int*        HistogramG = nullptr;
+    int*        HistogramB = nullptr;
+    int*        HistogramL = nullptr;
+    bool        AcquireErrorStats = false;
+    bool        AcquireHistogram  = false;
+};
+struct ImageInfoOutput {
+    float Min = 0, Max = 0, Average = 0, SoftMin = 0, SoftMax = 0, Median = 0;
+    int   InfCount = 0, NaNCount = 0, NegCount = 0;
+};
+// device/ShaderOutput.h: the JIT'd entry point of a shader; this backend never executes it
+template <typename T>
+struct ShaderOutput {
+    T Exec{};
+};
+
 // Target.h: only the device ordinal matters to this backend.
 class Target {
 public:

@@ -77,6 +77,9 @@ int main(int argc, char** argv)
         if (runtime.device().deviceCount() > 1)
             std::cout << "  GPUs: " << runtime.device().deviceCount() << "\n  Film reduce (last call)> " << runtime.device().lastFilmReduceMs() << " ms" << std::endl;
         if (cmd.Stats)
+            if (const Statistics* stats = runtime.device().getStatistics()) // cli/main.cpp:155-166
+                std::cout << stats->dump((size_t)(render_s * 1e3), runtime.currentIterationCount(), false);
+        if (cmd.Stats)
             std::cout << "  Rays (last call)> camera " << st.camera_rays << " bounce " << st.bounce_rays << " shadow " << st.shadow_rays << std::endl;
         std::sort(samples_sec.begin(), samples_sec.end());
         std::cout << "# " << samples_sec.front() * 1e-6 << "/" << samples_sec[samples_sec.size() / 2] * 1e-6 << "/" << samples_sec.back() * 1e-6

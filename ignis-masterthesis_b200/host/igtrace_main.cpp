@@ -7,40 +7,49 @@
 #include "Options.h"
 
 #include <cmath>
+#include <cstdio>
 #include <fstream>
-#include <iterator>
 #include <limits>
-#include <sstream>
 
 using namespace IG;
 
-static std::vector<Ray> read_input(std::istream& is)
+// Text contract only (the format is the reference's, this parser is not): numbers separated by blanks, parsed with strtof
+// until the first token that is not a number; six or more make a ray, fewer drop the line; an empty line ends the list.
+static bool parseRayLine(const char* text, Ray& ray)
 {
-    std::vector<Ray> rays;
-    std::string      line;
-    while (std::getline(is, line) && !line.empty()) {
-        std::vector<float> data;
-        std::stringstream  stream(line);
-        std::copy(std::istream_iterator<float>(stream), std::istream_iterator<float>(), std::back_inserter(data));
-        if (data.size() < 6) continue;
-        Ray ray;
-        for (int k = 0; k < 3; ++k) {
-            ray.Origin(k)    = data[k];
-            ray.Direction(k) = data[3 + k];
-        }
-        ray.Range(0) = data.size() > 6 ? data[6] : 0;
-        ray.Range(1) = data.size() > 7 ? data[7] : 0;
-        if (ray.Range(1) <= ray.Range(0)) ray.Range(1) = std::numeric_limits<float>::max();
-        rays.push_back(ray);
+    float       v[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    int         n    = 0;
+    const char* p    = text;
+    while (n < 8) {
+        char*       end = nullptr;
+        const float x   = std::strtof(p, &end);
+        if (end == p) break;
+        v[n++] = x;
+        p      = end;
     }
-    return rays;
+    if (n < 6) return false;
+    ray.Origin    = { v[0], v[1], v[2] };
+    ray.Direction = { v[3], v[4], v[5] };
+    const float tmin = v[6], tmax = v[7];
+    ray.Range = { tmin, tmax > tmin ? tmax : std::numeric_limits<float>::max() }; // open range unless a valid one is given
+    return true;
 }
 
-static void write_output(std::ostream& os, const float* data, size_t count, size_t iterations)
+static std::vector<Ray> loadRayList(std::istream& in)
 {
-    for (size_t i = 0; i < count; ++i)
-        os << std::scientific << data[3 * i + 0] / iterations << "\t" << data[3 * i + 1] / iterations << "\t" << data[3 * i + 2] / iterations << "\n";
-    os.flush();
+    std::vector<Ray> list;
+    Ray              ray;
+    for (std::string text; std::getline(in, text) && !text.empty();)
+        if (parseRayLine(text.c_str(), ray)) list.push_back(ray);
+    return list;
+}
+
+// film sums -> `r<TAB>g<TAB>b` per ray in %e (what std::scientific prints), divided by the number of iterations
+static void saveContributions(std::FILE* out, const std::vector<float>& rgb, size_t iterations)
+{
+    const float inv = 1.0f / (float)iterations;
+    for (size_t i = 0; i + 2 < rgb.size(); i += 3) std::fprintf(out, "%e\t%e\t%e\n", rgb[i] * inv, rgb[i + 1] * inv, rgb[i + 2] * inv);
+    std::fflush(out);
 }
 
 int main(int argc, char** argv)
@@ -56,13 +65,9 @@ int main(int argc, char** argv)
     opts.SPI      = 1; // "Fix samples per iteration to 1"
     opts.IsTracer = true;
 
-    std::vector<Ray> rays;
-    if (cmd.InputRay.empty()) {
-        rays = read_input(std::cin);
-    } else {
-        std::ifstream stream(cmd.InputRay);
-        rays = read_input(stream);
-    }
+    std::ifstream    file;
+    if (!cmd.InputRay.empty()) file.open(cmd.InputRay);
+    std::vector<Ray> rays = loadRayList(cmd.InputRay.empty() ? static_cast<std::istream&>(std::cin) : file);
     if (rays.empty()) {
         std::cerr << "[ERROR] No rays given" << std::endl;
         return EXIT_FAILURE;
@@ -77,20 +82,20 @@ int main(int argc, char** argv)
     const size_t SPI          = runtime.samplesPerIteration();
     const size_t desired_iter = std::max<size_t>(1, (size_t)std::ceil(cmd.SPP.value_or(1) / (float)SPI));
 
-    std::vector<float> accum_data, iter_data;
-    for (size_t iter = 0; iter < desired_iter; ++iter) {
-        runtime.trace(rays, iter_data); // the film accumulates on the device: the last read is the sum
-        accum_data = iter_data;
-    }
-    if (accum_data.size() != rays.size() * 3) {
-        std::cerr << "[FATAL] Got trace output size " << accum_data.size() << " but expected " << rays.size() * 3 << std::endl;
+    // every iteration traces the same rays into the same N x 1 film, which accumulates on the device: the read after the
+    // last iteration is the sum over all of them
+    std::vector<float> film;
+    for (size_t it = 0; it < desired_iter; ++it) runtime.trace(rays, film);
+    if (film.size() != rays.size() * 3) {
+        std::cerr << "[FATAL] film holds " << film.size() << " values for " << rays.size() << " rays" << std::endl;
         return EXIT_FAILURE;
     }
-    if (cmd.Output.empty()) {
-        write_output(std::cout, accum_data.data(), rays.size(), runtime.currentIterationCount());
-    } else {
-        std::ofstream stream(cmd.Output);
-        write_output(stream, accum_data.data(), rays.size(), runtime.currentIterationCount());
+    std::FILE* out = cmd.Output.empty() ? stdout : std::fopen(cmd.Output.c_str(), "w");
+    if (!out) {
+        std::cerr << "[ERROR] Could not open " << cmd.Output << std::endl;
+        return EXIT_FAILURE;
     }
+    saveContributions(out, film, runtime.currentIterationCount());
+    if (out != stdout) std::fclose(out);
     return EXIT_SUCCESS;
 }

@@ -422,6 +422,22 @@ int igb200_set_framebuffer(igb200_device* dev, const float* d_src, uint64_t coun
 
 int igb200_get_render_stats(igb200_device* dev, igb200_render_stats* out);
 
+/* Per-kernel-kind device times, only gathered when the device was created with acquire_stats (Device::SetupSettings::
+ * AcquireStats, `--stats`): the wavefront rounds then run un-graphed with a CUDA event between the kernels.  This is what
+ * the reference's Statistics (src/runtime/Statistics.h:9-63, begin/endShaderLaunch + the GPUSort / GPUCompact sections
+ * of src/artic/core/stats.art) reports; host/Statistics.h maps the slots onto its ShaderType / SectionType names:
+ *   0 begin_round  -> ShaderType::Device            3 scatter (index sort) -> SectionType::GPUSortPrimary (+Sort)
+ *   1 generate     -> ShaderType::RayGeneration     4 shade (+compaction)  -> ShaderType::Hit (Miss and GPUCompactPrimary are fused into it)
+ *   2 primary traversal (+ sort histogram, scan) -> ShaderType::PrimaryTraversal (+ GPUSortPrimaryCount / Scan)
+ *   5 shadow traversal (+ film splat)            -> ShaderType::SecondaryTraversal */
+typedef struct igb200_section_stats {
+    float    kernel_ms[6];
+    uint64_t launches[6];
+    float    framebuffer_host_update_ms; /* lazy D2H of the film, SectionType::FramebufferHostUpdate */
+    uint32_t framebuffer_host_updates;
+} igb200_section_stats;
+int igb200_get_section_stats(igb200_device* dev, igb200_section_stats* out, int reset);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * Multi-GPU (ABI v6).  north_star: "work is partitioned by image tile and sample index, with the scene replicated per
  * GPU and accumulation buffers combined via NCCL reduce over NVLink".  The reference is single-device

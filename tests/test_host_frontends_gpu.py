@@ -145,3 +145,21 @@ def test_igcli_gpus_2_image_equals_one_gpu_image(ig, host_bin, tmp_path, batch):
         assert "Iterations: 4" in r.stdout and ("GPUs: 2" in r.stdout) == (gpus == 2)
         imgs.append(cv2.imread(out, cv2.IMREAD_UNCHANGED))
     np.testing.assert_allclose(imgs[1], imgs[0], rtol=1e-4, atol=1e-6)
+
+
+def test_igcli_stats_reports_the_reference_categories(ig, host_bin, tmp_path):
+    """`--stats`: Device::getStatistics with the reference's ShaderType / SectionType / Quantity names (Statistics.h:9-63),
+    filled from CUDA events between the kernels of the wavefront rounds (igb200_get_section_stats)."""
+    tables, sh, w, h, _ = load_golden(ig, "cbox-d6")
+    scene, out = str(tmp_path / "scene.igdb"), str(tmp_path / "out.exr")
+    ig.fixtures.save_igdb(scene, tables, sh, w, h)
+    r = _run(os.path.join(host_bin, "igcli"), scene, "-o", out, "--spp", "8", "--spi", "4", "--width", "96", "--height", "96", "--stats")
+    for name in ("PrimaryTraversal", "SecondaryTraversal", "RayGeneration", "Hit", "GPUSortPrimary", "FramebufferHostUpdate"):
+        assert name in r.stdout, r.stdout
+    assert f"CameraRays> {96 * 96 * 8}" in r.stdout
+    # the stats mode renders the same image as the graph mode
+    out2 = str(tmp_path / "out2.exr")
+    _run(os.path.join(host_bin, "igcli"), scene, "-o", out2, "--spp", "8", "--spi", "4", "--width", "96", "--height", "96")
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    import cv2
+    np.testing.assert_allclose(cv2.imread(out, cv2.IMREAD_UNCHANGED), cv2.imread(out2, cv2.IMREAD_UNCHANGED), rtol=1e-4, atol=1e-6)

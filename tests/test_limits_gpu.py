@@ -102,3 +102,30 @@ def test_a_request_beyond_2_31_samples_is_split_and_the_counters_cover_all_of_it
     assert n2 == 2
     assert film.mean() / count == pytest.approx(two.mean() / 2, rel=2e-3)
     assert np.all(np.isfinite(film))
+
+
+def test_scene_tables_are_validated(ig, dev):
+    """Malformed SceneDatabase blobs (a corrupt .igdb, a buggy ABI caller) come back as IGB200_E_INVALID instead of
+    out-of-bounds device reads in the shading kernels (ent_mat[], entities[36 * ent], normals / texcoords by vertex index)."""
+    def refused(mutate, needle):
+        tables, _ = flat_scene(ig, "point", 8)
+        tables.shape_data = tables.shape_data.copy()   # the builder hands out read-only views
+        tables.entities = tables.entities.copy()
+        tables.leaves = [l.copy() for l in tables.leaves]
+        mutate(tables)
+        with pytest.raises(ig._lib.BackendError) as e:
+            dev.assign_scene(tables)
+        assert e.value.code == E_INVALID and needle in str(e.value), str(e.value)
+
+    def hdr(t):
+        return t.shape_data[int(t.lookups["offset"][0]):].view(np.uint32)
+
+    refused(lambda t: t.leaves[0].__setitem__("entity_id", 5), "entity id")                       # leaf -> entity out of range
+    refused(lambda t: t.entities.view(np.int32).__setitem__(33, 3), "entity row says shape")       # entity row disagrees / out of range
+    refused(lambda t: hdr(t).__setitem__(2, 1), "normals")                                         # fewer normals than vertices
+    refused(lambda t: hdr(t).__setitem__(3, 0), "texcoords")                                       # no texcoord block
+    refused(lambda t: hdr(t).__setitem__(3, 1 << 20), "truncated")                                 # texcoord block past the table
+    tables, sh = flat_scene(ig, "point", 8)      # and the untouched tables still load and render
+    dev.assign_scene(tables)
+    dev.assign_shading(sh)
+    dev.render(8, 8, spi=1)
