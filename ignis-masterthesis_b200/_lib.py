@@ -53,6 +53,7 @@ ABI_SYMBOLS = [
     "igb200_group_render",
     "igb200_group_trace_rays",
     "igb200_group_get_render_stats",
+    "igb200_trace_rays_noalloc",
 ]
 
 
@@ -137,6 +138,7 @@ def load():
     lib.igb200_destroy.restype = None
     lib.igb200_assign_scene.argtypes = [vp, C.POINTER(Scene)]
     lib.igb200_trace_rays.argtypes = [vp, vp, u64, u32, i32, vp, vp, vp, vp, vp]
+    lib.igb200_trace_rays_noalloc.argtypes = [vp, vp, u64, u32, i32, vp, vp, vp, vp, vp]
     lib.igb200_trace_rays_device.argtypes = [vp, vp, u64, u32, i32, vp, vp, vp, vp, vp, vp]
     lib.igb200_get_trace_stats.argtypes = [vp, C.POINTER(TraceStats)]
     lib.igb200_get_bvh_info.argtypes = [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(u32)]

@@ -14,6 +14,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1148,3 +1149,85 @@ int igb200_get_render_stats(igb200_device* dev, igb200_render_stats* out)
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// igb200_trace_rays_noalloc -- no counterpart in the reference.
+//
+// The host-buffer trace (igb200_trace_rays above) stages rays and hit columns in cudaMalloc'd buffers and uses
+// cudaMalloc'd work counters.  Callers that may not allocate (code under CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc) get this variant: the same traversal kernel with ALL of its scratch -- work counters,
+// ray staging, the five hit columns -- in one file-scope device array of fixed size.  Every GPU that loads the library
+// holds the array (kNoAllocBytes, ~3.25 MiB) until the process exits.
+//
+// `g_noalloc_scratch` below is a HOST-SIDE STAND-IN in host code, not a device address; the device address is resolved
+// once per device with cudaGetSymbolAddress (that device current) and only that pointer is handed to kernels / memcpys.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+struct NoAllocScratch {
+    uint32_t work[2];                 // persistent-kernel work counter + retired-block counter: must be 0 at launch
+    uint32_t _pad[62];                // keeps the staging areas 256-byte aligned
+    float4   rays[2 * IGB200_NOALLOC_MAX_RAYS];
+    int32_t  ent[IGB200_NOALLOC_MAX_RAYS];
+    int32_t  prim[IGB200_NOALLOC_MAX_RAYS];
+    float    t[IGB200_NOALLOC_MAX_RAYS];
+    float    u[IGB200_NOALLOC_MAX_RAYS];
+    float    v[IGB200_NOALLOC_MAX_RAYS];
+};
+constexpr size_t kNoAllocBytes = sizeof(NoAllocScratch);
+static_assert(kNoAllocBytes == 256 + (size_t)IGB200_NOALLOC_MAX_RAYS * 52, "scratch layout");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+constexpr int   kNoAllocMaxDevices = 64;
+NoAllocScratch* g_noalloc_ptr[kNoAllocMaxDevices] = {}; // device address of the array on each GPU, resolved on first use
+std::mutex      g_noalloc_mutex;
+
+// Device address of the scratch array on `ordinal`; that device must be current.  No allocation: the array is part of
+// the loaded module.
+int noalloc_scratch(int ordinal, NoAllocScratch** out)
+{
+    if (ordinal < 0 || ordinal >= kNoAllocMaxDevices) return fail(IGB200_E_UNSUPPORTED, "igb200_trace_rays_noalloc: device ordinal %d", ordinal);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[ordinal]) {
+        void*             p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(IGB200_E_CUDA, "igb200_trace_rays_noalloc: cudaGetSymbolAddress failed on device %d: %s", ordinal, cudaGetErrorString(e));
+        g_noalloc_ptr[ordinal] = static_cast<NoAllocScratch*>(p);
+    }
+    *out = g_noalloc_ptr[ordinal];
+    return IGB200_OK;
+}
+} // namespace
+
+extern "C" int igb200_trace_rays_noalloc(igb200_device* dev, const igb200_ray* rays, uint64_t n, uint32_t ray_flags, int any_hit,
+                                         int32_t* ent_id, int32_t* prim_id, float* t, float* u, float* v)
+{
+    if (!dev) return fail(IGB200_E_INVALID, "igb200_trace_rays_noalloc: NULL device");
+    if (!dev->has_scene) return fail(IGB200_E_STATE, "igb200_trace_rays_noalloc: no scene assigned");
+    if (n > IGB200_NOALLOC_MAX_RAYS)
+        return fail(IGB200_E_UNSUPPORTED, "igb200_trace_rays_noalloc: %llu rays exceed the static scratch of %u rays; split the batch or use igb200_trace_rays",
+                    (unsigned long long)n, (unsigned)IGB200_NOALLOC_MAX_RAYS);
+    if (n == 0) return IGB200_OK;
+    if (!rays) return fail(IGB200_E_INVALID, "igb200_trace_rays_noalloc: rays is NULL");
+    IGB_CUDA(cudaSetDevice(dev->ordinal));
+    NoAllocScratch* s = nullptr;
+    if (int rc = noalloc_scratch(dev->ordinal, &s)) return rc;
+    cudaStream_t st = dev->stream;
+    // The array keeps the previous call's contents.  What must start at zero is cleared here (the kernel rewinds its
+    // counters itself, but a call that faulted half way would leave them behind); the staging areas are overwritten for
+    // [0, n) before they are read, and nothing beyond n is ever read back.
+    IGB_CUDA(cudaMemsetAsync(s->work, 0, sizeof(s->work), st));
+    IGB_CUDA(cudaMemcpyAsync(s->rays, rays, n * sizeof(igb200_ray), cudaMemcpyHostToDevice, st));
+    const igb::TraceOutputs out{ ent_id ? s->ent : nullptr, prim_id ? s->prim : nullptr, t ? s->t : nullptr, u ? s->u : nullptr,
+                                 v ? s->v : nullptr };
+    // same kernel and same in-kernel direction normalisation as igb200_trace_rays (Interface::loadRayList, Device.cpp:588-592)
+    IGB_CUDA(igb::launch_trace(dev->view, s->rays, n, ray_flags, any_hit, out, nullptr, s->work, dev->sm_count, st, true));
+    if (ent_id) IGB_CUDA(cudaMemcpyAsync(ent_id, s->ent, n * 4, cudaMemcpyDeviceToHost, st));
+    if (prim_id) IGB_CUDA(cudaMemcpyAsync(prim_id, s->prim, n * 4, cudaMemcpyDeviceToHost, st));
+    if (t) IGB_CUDA(cudaMemcpyAsync(t, s->t, n * 4, cudaMemcpyDeviceToHost, st));
+    if (u) IGB_CUDA(cudaMemcpyAsync(u, s->u, n * 4, cudaMemcpyDeviceToHost, st));
+    if (v) IGB_CUDA(cudaMemcpyAsync(v, s->v, n * 4, cudaMemcpyDeviceToHost, st));
+    IGB_CUDA(cudaStreamSynchronize(st));
+    return IGB200_OK;
+}

@@ -79,6 +79,16 @@ class Device:
         _lib.check(self._lib.igb200_trace_rays(self._h, rays.ctypes.data, n, ray_flags, 1 if any_hit else 0,
                                                p(ent), p(prim), p(t), p(u), p(v)))
 
+    NOALLOC_MAX_RAYS = 65536  # IGB200_NOALLOC_MAX_RAYS
+
+    # igb200_trace_rays_noalloc: same results, scratch in a static device array (no cudaMalloc on the call)
+    def trace_noalloc_into(self, rays, ent, prim, t, u, v, ray_flags=0, any_hit=False):
+        n = rays.size
+        assert rays.dtype == RAY_DTYPE and rays.flags.c_contiguous
+        p = lambda a: None if a is None else a.ctypes.data
+        _lib.check(self._lib.igb200_trace_rays_noalloc(self._h, rays.ctypes.data if n else None, n, ray_flags, 1 if any_hit else 0,
+                                                       p(ent), p(prim), p(t), p(u), p(v)))
+
     # Same call on device-resident buffers (raw device pointers, e.g. torch tensors' data_ptr()).
     def trace_device(self, d_rays, n, d_ent, d_prim, d_t, d_u, d_v, ray_flags=0, any_hit=False, stream=0):
         _lib.check(self._lib.igb200_trace_rays_device(self._h, d_rays, n, ray_flags, 1 if any_hit else 0,

@@ -509,6 +509,22 @@ int            igb200_group_get_render_stats(igb200_group* group, igb200_render_
  * out5 = {node_count, max_depth, violations, primitives_not_seen_exactly_once, leaf_count}. */
 int igb200_debug_check_bvh8(const float* boxes, uint32_t n, uint32_t max_leaf, uint64_t* out5);
 
+/* No counterpart in the reference.
+ * igb200_trace_rays for callers that may not allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc): same kernel, same host buffers in, same five host hit columns out (NULL = column not
+ * wanted), same results -- but every byte of scratch (work counters, ray staging, hit columns) lives in ONE static device
+ * array inside the library, so the call performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ * Limits and caveats:
+ *   - n <= IGB200_NOALLOC_MAX_RAYS, otherwise IGB200_E_UNSUPPORTED (split the batch or use igb200_trace_rays);
+ *   - every GPU that loads the library holds the array (256 B + 52 B per ray = 3.25 MiB) until the process exits;
+ *   - the array is shared by EVERY call and every device handle on that GPU and keeps the last call's contents: the
+ *     entry clears what must start at zero and is synchronous, but calls that overlap on the GPU (two host threads, two
+ *     handles on one GPU, two processes do NOT share it) race on it -- serialise them;
+ *   - no traversal statistics are gathered (igb200_get_trace_stats is unaffected by this call). */
+#define IGB200_NOALLOC_MAX_RAYS 65536u
+int igb200_trace_rays_noalloc(igb200_device* dev, const igb200_ray* rays, uint64_t n, uint32_t ray_flags, int any_hit,
+                              int32_t* ent_id, int32_t* prim_id, float* t, float* u, float* v);
+
 #ifdef __cplusplus
 }
 #endif
