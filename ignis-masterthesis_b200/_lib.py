@@ -21,6 +21,7 @@ ABI_SYMBOLS = [
     "igb200_get_trace_stats",
     "igb200_get_bvh_info",
     "igb200_debug_check_bvh8",
+    "igb200_debug_bvh8_quality",
     "igb200_assign_shading",
     "igb200_render",
     "igb200_render_iterations",
@@ -143,6 +144,7 @@ def load():
     lib.igb200_get_trace_stats.argtypes = [vp, C.POINTER(TraceStats)]
     lib.igb200_get_bvh_info.argtypes = [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(u32)]
     lib.igb200_debug_check_bvh8.argtypes = [vp, u32, u32, vp]
+    lib.igb200_debug_bvh8_quality.argtypes = [vp, u32, u32, vp]
     lib.igb200_assign_shading.argtypes = [vp, vp]
     lib.igb200_render.argtypes = [vp, vp]
     lib.igb200_render_iterations.argtypes = [vp, vp, u32]

@@ -41,6 +41,9 @@ struct Bvh8 {
     std::vector<Node8>    nodes;        // nodes[0] is the root
     std::vector<uint32_t> prim_indices; // primitive records in leaf-contiguous order (indices into the input)
     uint32_t              max_depth = 0;
+    // SAH cost of the wide tree, split in its two sums (areas relative to the root's): sum over wide nodes of A_n and
+    // sum over leaf children of A_l * N_l.  cost = c_node * node_term + c_prim * prim_term.
+    double                sah_node_term = 0.0, sah_prim_term = 0.0;
 };
 
 // boxes: n x {min xyz, max xyz}. max_leaf in 1..3 (the meta encoding holds at most 3 per leaf).

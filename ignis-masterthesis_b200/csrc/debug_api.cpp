@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <cfloat>
+#include <chrono>
 #include <cstring>
 #include <vector>
 
@@ -70,4 +71,19 @@ extern "C" int igb200_debug_check_bvh8(const float* boxes, uint32_t n, uint32_t 
         out5[4] = c.leaves;
     }
     return (c.violations == 0 && missing == 0) ? IGB200_OK : IGB200_E_INVALID;
+}
+
+extern "C" int igb200_debug_bvh8_quality(const float* boxes, uint32_t n, uint32_t max_leaf, double* out4)
+{
+    igb::Bvh8 bvh;
+    const auto t0 = std::chrono::steady_clock::now();
+    igb::build_bvh8(boxes, n, max_leaf, bvh);
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    if (out4) {
+        out4[0] = bvh.sah_node_term;
+        out4[1] = bvh.sah_prim_term;
+        out4[2] = (double)bvh.nodes.size();
+        out4[3] = ms;
+    }
+    return IGB200_OK;
 }

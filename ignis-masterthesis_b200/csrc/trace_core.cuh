@@ -37,7 +37,7 @@ constexpr int      kChunk       = 64; // rays a warp claims per atomic on the gl
 #define IGB_VOTE_TRI 4
 #endif
 #ifndef IGB_VOTE_ENT
-#define IGB_VOTE_ENT 4
+#define IGB_VOTE_ENT 6 // swept separately from VOTE_TRI in round 2 (profiles/r02_ab_vote_tri_ent_separately.txt): 6 is best
 #endif
 constexpr int      kVoteTri     = IGB_VOTE_TRI; // lanes that must wait for a triangle phase before it runs
 constexpr int      kVoteEnt     = IGB_VOTE_ENT; // same for the entity-leaf phase

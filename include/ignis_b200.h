@@ -508,6 +508,12 @@ int            igb200_group_get_render_stats(igb200_group* group, igb200_render_
  * the exact bounds of its subtree, meta/imask encoding consistent.
  * out5 = {node_count, max_depth, violations, primitives_not_seen_exactly_once, leaf_count}. */
 int igb200_debug_check_bvh8(const float* boxes, uint32_t n, uint32_t max_leaf, uint64_t* out5);
+/* Host-only: builds the BVH8 and reports its quality and cost (row a25: the reference builds with madmann91/bvh's SBVH +
+ * reinsertion, src/runtime/bvh/TriBVHAdapter.h:163-202, and collapses by area, NArityBvh.h:65-116).
+ * out4 = {sum over wide nodes of A_n / A_root, sum over leaf children of A_l * N_l / A_root, node count, build ms}.
+ * Builder switches (environment, read per build): IGB200_BVH_COLLAPSE = dp | greedy, IGB200_BVH_CNODE, IGB200_BVH_CPRIM,
+ * IGB200_BVH_THREADS. */
+int igb200_debug_bvh8_quality(const float* boxes, uint32_t n, uint32_t max_leaf, double* out4);
 
 /* No counterpart in the reference.
  * igb200_trace_rays for callers that may not allocate device memory (code under CUDA graph capture, tight serving loops,

@@ -76,3 +76,33 @@ def test_bvh8_c3_mesh(ig):
     tri = v[f]
     rc, st = _check(ig, np.concatenate([tri.min(axis=1), tri.max(axis=1)], axis=1))
     assert rc == 0 and st["depth"] <= 16, st
+
+
+@pytest.mark.parametrize("collapse", ["dp", "greedy"])
+@pytest.mark.parametrize("threads", ["1", "8"])
+def test_bvh8_builder_variants_keep_the_invariants(ig, monkeypatch, collapse, threads):
+    """Both wide collapses (SAH-optimal dynamic programming, greedy by area) and the parallel binary build: every primitive
+    once, conservative quantised boxes, consistent meta / imask -- on a mesh large enough for the parallel path (> 64 Ki)."""
+    monkeypatch.setenv("IGB200_BVH_COLLAPSE", collapse)
+    monkeypatch.setenv("IGB200_BVH_THREADS", threads)
+    v, f, _ = ig.workloads.uv_sphere(192, 192)      # 72 960 triangles
+    tri = v[f]
+    boxes = np.concatenate([tri.min(axis=1), tri.max(axis=1)], axis=1)
+    rc, st = _check(ig, boxes)
+    assert rc == 0 and st["violations"] == 0 and st["missing"] == 0 and st["depth"] <= 20, st
+    for n in (1, 2, 3, 4, 9, 700):                  # small inputs incl. the "whole scene is one leaf" case
+        rc, st = _check(ig, boxes[:n])
+        assert rc == 0, (n, st)
+
+
+def test_bvh8_dp_collapse_lowers_the_sah_cost(ig, monkeypatch):
+    v, f, _ = ig.workloads.uv_sphere(64, 128)
+    tri = v[f]
+    boxes = np.ascontiguousarray(np.concatenate([tri.min(axis=1), tri.max(axis=1)], axis=1), np.float32)
+    cost = {}
+    for collapse in ("greedy", "dp"):
+        monkeypatch.setenv("IGB200_BVH_COLLAPSE", collapse)
+        out = np.zeros(4, np.float64)
+        assert ig._lib.load().igb200_debug_bvh8_quality(boxes.ctypes.data, boxes.shape[0], 3, out.ctypes.data) == 0
+        cost[collapse] = 1.0 * out[0] + 0.7 * out[1]     # c_node = 1, c_prim = 0.7: the DP default constants
+    assert cost["dp"] <= cost["greedy"] * 1.0001, cost
