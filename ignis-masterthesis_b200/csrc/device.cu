@@ -402,6 +402,7 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
     dev->view.tlas_nodes = (uint32_t)tlas.nodes.size();
     dev->view.leaf_count = (uint32_t)ordered.size();
     dev->view.byte_bias  = 0x47000000u;
+    dev->view.half_bias  = 0x64006400u;
     dev->view.node_count = (uint32_t)all_nodes.size();
     dev->view.tri_count  = (uint32_t)(all_tris.size() / 3);
     dev->node_bytes      = all_nodes.size() * sizeof(Node8);

@@ -23,10 +23,14 @@ struct ListIO {
     __device__ __forceinline__ uint32_t bin_count() const { return 0u; }
     __device__ __forceinline__ uint32_t* global_bins() const { return nullptr; }
     __device__ __forceinline__ void finalize_last_block() const {}
+    __device__ __forceinline__ void prefetch(uint32_t first, uint32_t count, uint32_t lane) const
+    {
+        if (2u * lane < count) prefetch_line(rays + 2 * (size_t)(first + 2u * lane)); // 64 B = two rays per lane
+    }
     __device__ __forceinline__ bool load(uint32_t i, Vec3& org, Vec3& dir, float& tmin, float& tmax, uint32_t& flags) const
     {
-        const float4 r0 = __ldg(rays + 2 * (size_t)i);
-        const float4 r1 = __ldg(rays + 2 * (size_t)i + 1);
+        const float4 r0 = stream_load(rays + 2 * (size_t)i, true);
+        const float4 r1 = stream_load(rays + 2 * (size_t)i + 1, true);
         org   = Vec3{ r0.x, r0.y, r0.z };
         dir   = Vec3{ r0.w, r1.x, r1.y };
         if (NORMALIZE) { // same arithmetic as normalize_rays_kernel below
@@ -41,11 +45,11 @@ struct ListIO {
     }
     __device__ __forceinline__ void store(uint32_t i, const HitRec& hit, uint32_t*) const
     {
-        if (out.ent_id) out.ent_id[i] = hit.ent;
-        if (out.prim_id) out.prim_id[i] = hit.prim;
-        if (out.t) out.t[i] = hit.t;
-        if (out.u) out.u[i] = hit.u;
-        if (out.v) out.v[i] = hit.v;
+        if (out.ent_id) stream_store(out.ent_id + i, hit.ent);
+        if (out.prim_id) stream_store(out.prim_id + i, hit.prim);
+        if (out.t) stream_store(out.t + i, hit.t);
+        if (out.u) stream_store(out.u + i, hit.u);
+        if (out.v) stream_store(out.v + i, hit.v);
     }
 };
 
@@ -89,7 +93,8 @@ cudaError_t launch_trace(const DeviceScene& scene, const float4* d_rays, uint64_
                          cudaStream_t stream, bool normalize)
 {
     if (n == 0) return cudaSuccess;
-    if (n > 0xFFFF0000ull) return cudaErrorInvalidValue;
+    // every warp of the grid overshoots the work counter by up to two chunks: keep it well clear of the 32-bit wrap
+    if (n > 0xFF000000ull) return cudaErrorInvalidValue;
     // persistent grid: one wave of resident CTAs (a multiple of the SM count), fewer for tiny batches
     const uint64_t want = (n + kChunk - 1) / kChunk; // warps that can get at least one chunk
     const uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)sm_count * kBlocksPerSM, (want + 3) / 4));

@@ -26,6 +26,7 @@ struct DeviceScene {
     // immediate slot of PRMT and then has to move the byte selector into a register before each of the 48 PRMTs of a
     // node step; a constant-bank operand leaves the immediate slot to the selector (trace_core.cuh, biased_byte_to_float).
     uint32_t        byte_bias;
+    uint32_t        half_bias; // 0x64006400 (half2 {1024, 1024}), a parameter for the same reason
     uint32_t        node_count, tri_count; // array sizes (debug bounds checks, IGB_DEBUG_CHECKS)
 };
 

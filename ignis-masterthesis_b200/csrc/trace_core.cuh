@@ -18,6 +18,7 @@
 #include "trace.cuh"
 
 #include <cstdio>
+#include <cuda_fp16.h>
 
 #include "../../include/ignis_b200.h"
 
@@ -135,6 +136,45 @@ __device__ __forceinline__ float biased_byte_to_float(uint32_t w, int j, uint32_
 }
 __device__ __forceinline__ uint32_t extract_byte(uint32_t w, int j) { return (w >> (8 * j)) & 0xFFu; }
 
+// Ray records and hit columns are touched once per launch; the BVH is what should stay in L1.
+//   IGB_STREAM_IO 1: ld.global.cs / st.global.cs (evict-first) for ray input and hit output, 2: L1::no_allocate loads.
+#ifndef IGB_STREAM_IO
+#define IGB_STREAM_IO 0
+#endif
+//   IGB_RAY_PREFETCH 1: a warp claims its ray chunks one ahead and prefetches the records into L2, 2: into L1.
+#ifndef IGB_RAY_PREFETCH
+#define IGB_RAY_PREFETCH 0
+#endif
+__device__ __forceinline__ void prefetch_line(const void* p)
+{
+#if IGB_RAY_PREFETCH == 2
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#else
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#endif
+}
+__device__ __forceinline__ float4 stream_load(const float4* p, bool read_only)
+{
+#if IGB_STREAM_IO == 1
+    return __ldcs(p);
+#elif IGB_STREAM_IO == 2
+    float4 v;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+#else
+    return read_only ? __ldg(p) : *p;
+#endif
+}
+template <typename T>
+__device__ __forceinline__ void stream_store(T* p, T v)
+{
+#if IGB_STREAM_IO
+    __stcs(p, v);
+#else
+    *p = v;
+#endif
+}
+
 struct TravRay {
     Vec3     org, dir;    // current space (world or object); dir un-normalised in object space
     Vec3     idir;        // box-test reciprocals
@@ -148,12 +188,73 @@ __device__ __forceinline__ void setup_trav_ray(TravRay& r)
     r.octinv4          = (7u - oct) * 0x01010101u;
 }
 
+// ---- node-step instruction mix (round 2).  scripts/pipe_probe.cu measures the issue rates on B200: PRMT, FMNMX/FMNMX3,
+// LOP3, SHF and FSETP share the ALU pipe, FFMA/FMUL/FADD/HADD2/IMAD the FMA pipe, and a scheduler can start one
+// instruction per pipe every other cycle -- so a node step with 16 ALU-pipe and 7 FMA-pipe instructions per child is bound
+// by the ALU pipe, not by issue slots.  The switches below move work across:
+//   IGB_CVT_HALF   1: every byte -> float conversion goes through a half2 pair {1024 + b_j, 1024 + b_k} built by ONE PRMT and
+//                     two HADD2.F32 (FMA pipe) instead of one PRMT per byte; 2: far planes only.
+//   IGB_FFMA2      1: the plane distances of two children are computed by one packed fma.rn.f32x2.
+//   IGB_SLACK_FOLD 1: the exit-distance slack is folded into the far-plane coefficients (6 FMUL per node instead of 8).
+// Measured on B200 (profiles/r02_ab_node_step_mix.txt): C3 7021 -> 7125 (half) / 7130 (f32x2) / 7203 (both) Mrays/s,
+// C4 1117 -> 1127 Msamples/s; the slack fold changes nothing.  Both are on.
+#ifndef IGB_CVT_HALF
+#define IGB_CVT_HALF 1
+#endif
+#ifndef IGB_FFMA2
+#define IGB_FFMA2 1
+#endif
+#ifndef IGB_SLACK_FOLD
+#define IGB_SLACK_FOLD 0
+#endif
+constexpr float kHalfBias = 1024.0f; // half 0x6400: the byte lands in mantissa bits 0..7
+
+// bias + byte j of w for j = 0..3.  HALF: two PRMTs build the half2 pairs, four HADD2.F32 widen them.
+template <bool HALF>
+__device__ __forceinline__ void unpack4(uint32_t w, uint32_t bias, uint32_t hbias, float (&q)[4])
+{
+    if (HALF) {
+        uint32_t h01, h23; // bytes {w.0, 0x64, w.1, 0x64} and {w.2, 0x64, w.3, 0x64}; hbias = 0x64006400 in a register
+        asm("prmt.b32 %0, %1, %2, 0x7150;" : "=r"(h01) : "r"(w), "r"(hbias));
+        asm("prmt.b32 %0, %1, %2, 0x7352;" : "=r"(h23) : "r"(w), "r"(hbias));
+        const __half2 a = *reinterpret_cast<const __half2*>(&h01), b = *reinterpret_cast<const __half2*>(&h23);
+        q[0] = __low2float(a);
+        q[1] = __high2float(a);
+        q[2] = __low2float(b);
+        q[3] = __high2float(b);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) q[j] = biased_byte_to_float(w, j, bias);
+    }
+}
+
+// t[j] = q[j] * s + o for four children
+__device__ __forceinline__ void planes4(const float (&q)[4], float s, float o, float (&t)[4])
+{
+#if IGB_FFMA2
+    unsigned long long q01, q23, ss, oo, t01, t23;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(q01) : "f"(q[0]), "f"(q[1]));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(q23) : "f"(q[2]), "f"(q[3]));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(ss) : "f"(s));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(oo) : "f"(o));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(t01) : "l"(q01), "l"(ss), "l"(oo));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(t23) : "l"(q23), "l"(ss), "l"(oo));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(t[0]), "=f"(t[1]) : "l"(t01));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(t[2]), "=f"(t[3]) : "l"(t23));
+#else
+#pragma unroll
+    for (int j = 0; j < 4; ++j) t[j] = __fmaf_rn(q[j], s, o);
+#endif
+}
+
 // Tests the 8 quantised child boxes of one node; returns the (octant-ordered) hit mask:
 // bits 31..24 inner children, bits 23..0 primitives of leaf children.
 __device__ __forceinline__ uint32_t intersect_children(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3,
                                                        const uint4 n4, const TravRay& r, float tmin, float tmax,
-                                                       const uint32_t bias)
+                                                       const uint32_t bias, const uint32_t hbias)
 {
+    constexpr bool  kHalfNear = IGB_CVT_HALF == 1, kHalfFar = IGB_CVT_HALF >= 1;
+    constexpr float kBiasNear = kHalfNear ? kHalfBias : kByteBias, kBiasFar = kHalfFar ? kHalfBias : kByteBias;
     const uint32_t e  = n0.w;
     const float    sx = __uint_as_float((e & 0xFFu) << 23) * r.idir.x;
     const float    sy = __uint_as_float(((e >> 8) & 0xFFu) << 23) * r.idir.y;
@@ -161,12 +262,18 @@ __device__ __forceinline__ uint32_t intersect_children(const uint4 n0, const uin
     const float    ox = (__uint_as_float(n0.x) - r.org.x) * r.idir.x;
     const float    oy = (__uint_as_float(n0.y) - r.org.y) * r.idir.y;
     const float    oz = (__uint_as_float(n0.z) - r.org.z) * r.idir.z;
-    // plane distance = q * s + o = (32768 + q) * s + (o - 32768 s).  Folding the bias costs one rounding of
+    // plane distance = q * s + o = (bias + q) * s + (o - bias s).  Folding the bias costs one rounding of
     // magnitude <= |s| / 512 (s = one quantisation step in t), so entry planes move 1/256 step out, exit planes in.
-    const float ax = __fmaf_rn(-kByteBias, sx, ox), dx = fabsf(sx) * 0.00390625f;
-    const float ay = __fmaf_rn(-kByteBias, sy, oy), dy = fabsf(sy) * 0.00390625f;
-    const float az = __fmaf_rn(-kByteBias, sz, oz), dz = fabsf(sz) * 0.00390625f;
-    const float o0x = ax - dx, o1x = ax + dx, o0y = ay - dy, o1y = ay + dy, o0z = az - dz, o1z = az + dz;
+    const float dx = fabsf(sx) * 0.00390625f, dy = fabsf(sy) * 0.00390625f, dz = fabsf(sz) * 0.00390625f;
+    const float o0x = __fmaf_rn(-kBiasNear, sx, ox) - dx, o0y = __fmaf_rn(-kBiasNear, sy, oy) - dy, o0z = __fmaf_rn(-kBiasNear, sz, oz) - dz;
+    float       o1x = __fmaf_rn(-kBiasFar, sx, ox) + dx, o1y = __fmaf_rn(-kBiasFar, sy, oy) + dy, o1z = __fmaf_rn(-kBiasFar, sz, oz) + dz;
+#if IGB_SLACK_FOLD
+    // min(t1x, t1y, t1z) * slack == min(t1x * slack, ...): the slack moves into the coefficients of the far planes
+    const float fx = sx * kBoxSlack, fy = sy * kBoxSlack, fz = sz * kBoxSlack;
+    o1x *= kBoxSlack, o1y *= kBoxSlack, o1z *= kBoxSlack;
+#else
+    const float fx = sx, fy = sy, fz = sz;
+#endif
     const bool     nx = r.dir.x < 0.0f, ny = r.dir.y < 0.0f, nz = r.dir.z < 0.0f;
 
     uint32_t hitmask = 0;
@@ -183,17 +290,22 @@ __device__ __forceinline__ uint32_t intersect_children(const uint4 n0, const uin
         const uint32_t nearx = nx ? qhix : qlox, farx = nx ? qlox : qhix;
         const uint32_t neary = ny ? qhiy : qloy, fary = ny ? qloy : qhiy;
         const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
+        float q[4], t0x[4], t0y[4], t0z[4], t1x[4], t1y[4], t1z[4];
+        unpack4<kHalfNear>(nearx, bias, hbias, q), planes4(q, sx, o0x, t0x);
+        unpack4<kHalfNear>(neary, bias, hbias, q), planes4(q, sy, o0y, t0y);
+        unpack4<kHalfNear>(nearz, bias, hbias, q), planes4(q, sz, o0z, t0z);
+        unpack4<kHalfFar>(farx, bias, hbias, q), planes4(q, fx, o1x, t1x);
+        unpack4<kHalfFar>(fary, bias, hbias, q), planes4(q, fy, o1y, t1y);
+        unpack4<kHalfFar>(farz, bias, hbias, q), planes4(q, fz, o1z, t1z);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const float t0x = __fmaf_rn(biased_byte_to_float(nearx, j, bias), sx, o0x);
-            const float t0y = __fmaf_rn(biased_byte_to_float(neary, j, bias), sy, o0y);
-            const float t0z = __fmaf_rn(biased_byte_to_float(nearz, j, bias), sz, o0z);
-            const float t1x = __fmaf_rn(biased_byte_to_float(farx, j, bias), sx, o1x);
-            const float t1y = __fmaf_rn(biased_byte_to_float(fary, j, bias), sy, o1y);
-            const float t1z = __fmaf_rn(biased_byte_to_float(farz, j, bias), sz, o1z);
-            const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
+            const float cmin = fmaxf(fmaxf(t0x[j], t0y[j]), fmaxf(t0z[j], tmin));
             // slack on the exit distance: the box test must never reject what the triangle test accepts
-            const float cmax = fminf(fminf(fminf(t1x, t1y), t1z) * kBoxSlack, tmax);
+#if IGB_SLACK_FOLD
+            const float cmax = fminf(fminf(fminf(t1x[j], t1y[j]), t1z[j]), tmax);
+#else
+            const float cmax = fminf(fminf(fminf(t1x[j], t1y[j]), t1z[j]) * kBoxSlack, tmax);
+#endif
             if (cmin <= cmax) hitmask |= extract_byte(child_bits4, j) << extract_byte(bit_index4, j);
         }
     }
@@ -281,6 +393,7 @@ __device__ __forceinline__ void intersect_sphere(const float4 sph, const TravRay
 // IO policy (how rays come in and results go out):
 //   uint32_t count() const                                         number of rays (may read device memory)
 //   bool     load(i, org, dir, tmin, tmax, flags) const            false = slot holds no ray
+//   void     prefetch(first, count, lane) const                    the warp will load rays [first, first + count) soon
 //   void     store(i, hit, s_bins)                                 ray i finished (hit.prim < 0: miss, hit.t = tmax)
 //   static constexpr bool kBins                                    block-level key histogram in shared memory
 //   uint32_t bin_count() const; uint32_t* global_bins() const; void finalize_last_block() const   (only when kBins)
@@ -309,6 +422,10 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
     uint32_t       c_nodes = 0, c_tris = 0, c_ents = 0;
 
     uint32_t pool_next = 0, pool_end = 0; // warp-uniform
+#if IGB_RAY_PREFETCH
+    constexpr uint32_t kNoChunk = 0xFFFFFFFFu;
+    uint32_t           ahead    = kNoChunk; // warp-uniform: base of the chunk claimed one step ahead
+#endif
     bool     exhausted = false;           // warp-uniform
     bool     active    = false;
 
@@ -328,9 +445,23 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
         if (idle != 0u && (kVoteRefill <= 1 || exhausted || __popc(idle) >= kVoteRefill)) {
             if (!exhausted) {
                 if (pool_next == pool_end) {
+#if IGB_RAY_PREFETCH
+                    // One chunk ahead: the chunk this warp works on next was claimed (and its ray records prefetched)
+                    // when the previous one was opened, so a refilled lane's first use of its ray does not stall the
+                    // other 31 lanes of the warp for a DRAM round trip.
+                    uint32_t base = ahead, next = 0;
+                    if (lane == 0) {
+                        if (base == kNoChunk) base = atomicAdd(work, (uint32_t)kChunk);
+                        next = base < n ? atomicAdd(work, (uint32_t)kChunk) : base;
+                    }
+                    base  = __shfl_sync(0xFFFFFFFFu, base, 0);
+                    ahead = __shfl_sync(0xFFFFFFFFu, next, 0);
+                    if (ahead < n) io.prefetch(ahead, min((uint32_t)kChunk, n - ahead), lane);
+#else
                     uint32_t base = 0;
                     if (lane == 0) base = atomicAdd(work, (uint32_t)kChunk);
                     base = __shfl_sync(0xFFFFFFFFu, base, 0);
+#endif
                     if (base >= n) {
                         exhausted = true;
                     } else {
@@ -399,7 +530,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
             const uint4    n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
 #endif
             if (STATS) c_nodes++;
-            const uint32_t hitmask = intersect_children(n0, n1, n2, n3, n4, ray, tmin, hit.t, sc.byte_bias);
+            const uint32_t hitmask = intersect_children(n0, n1, n2, n3, n4, ray, tmin, hit.t, sc.byte_bias, sc.half_bias);
             ngroup                 = make_uint2(n1.x, (hitmask & 0xFF000000u) | (n0.w >> 24));
             tgroup                 = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
         }

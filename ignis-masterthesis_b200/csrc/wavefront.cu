@@ -31,10 +31,14 @@ struct PrimaryIO {
     __device__ __forceinline__ uint32_t  count() const { return ctl->n_cur; }
     __device__ __forceinline__ uint32_t  bin_count() const { return n_bins; }
     __device__ __forceinline__ uint32_t* global_bins() const { return ctl->bins; }
+    __device__ __forceinline__ void prefetch(uint32_t first, uint32_t count, uint32_t lane) const
+    {
+        for (uint32_t k = lane; k < count; k += 32u) prefetch_line(s.rec + kRecVec * (size_t)(first + k)); // the ray sector of each record
+    }
     __device__ __forceinline__ bool load(uint32_t i, Vec3& org, Vec3& dir, float& tmin, float& tmax, uint32_t& flags) const
     {
         const float4* r = s.rec + kRecVec * (size_t)i;
-        const float4  o = r[0], d = r[1];
+        const float4  o = stream_load(r, false), d = stream_load(r + 1, false);
         org   = Vec3{ o.x, o.y, o.z };
         dir   = Vec3{ d.x, d.y, d.z };
         tmin  = o.w;
@@ -45,8 +49,8 @@ struct PrimaryIO {
     __device__ __forceinline__ void store(uint32_t i, const HitRec& hit, uint32_t* s_bins) const
     {
         float4* r = s.rec + kRecVec * (size_t)i; // the whole third sector: no partial-sector write
-        r[4] = make_float4(__int_as_float(hit.ent), __int_as_float(hit.prim), hit.t, hit.u);
-        r[5] = make_float4(hit.v, 0.0f, 0.0f, 0.0f);
+        stream_store(r + 4, make_float4(__int_as_float(hit.ent), __int_as_float(hit.prim), hit.t, hit.u));
+        stream_store(r + 5, make_float4(hit.v, 0.0f, 0.0f, 0.0f));
         const uint32_t key = hit.prim >= 0 ? (uint32_t)__ldg(ent_mat + hit.ent) : n_bins - 1u;
         keys[i]            = key;
         if (n_bins <= (uint32_t)kMaxSmemBins)
@@ -89,9 +93,16 @@ struct ShadowIO {
     __device__ __forceinline__ uint32_t  bin_count() const { return 0u; }
     __device__ __forceinline__ uint32_t* global_bins() const { return nullptr; }
     __device__ __forceinline__ void      finalize_last_block() const {}
+    __device__ __forceinline__ void prefetch(uint32_t first, uint32_t count, uint32_t lane) const
+    {
+        if (2u * lane < count) { // 32 B = two rays per lane and column
+            prefetch_line(s.org_tmin + first + 2u * lane);
+            prefetch_line(s.dir_tmax + first + 2u * lane);
+        }
+    }
     __device__ __forceinline__ bool load(uint32_t i, Vec3& org, Vec3& dir, float& tmin, float& tmax, uint32_t& flags) const
     {
-        const float4 o = s.org_tmin[i], d = s.dir_tmax[i];
+        const float4 o = stream_load(s.org_tmin + i, false), d = stream_load(s.dir_tmax + i, false);
         org   = Vec3{ o.x, o.y, o.z };
         dir   = Vec3{ d.x, d.y, d.z };
         tmin  = o.w;
