@@ -12,7 +12,10 @@ namespace {
 using namespace core;
 
 // Ray list in (32 B StreamRay, two 128-bit loads), five hit columns out (src/artic/driver/streams.art:80-100).
-template <bool NORMALIZE> // host-buffer path: Interface::loadRayList's normalisation (Device.cpp:588-592) fused into the load
+// NORMALIZE: host-buffer path, Interface::loadRayList's normalisation (Device.cpp:588-592) fused into the load.
+// ALL_OUT: all five columns requested (the usual case): no per-column null checks in the store (the checked store is ~40
+// instructions per finished ray at ~7 live lanes, 5 % of the kernel's issue slots on C3).
+template <bool NORMALIZE, bool ALL_OUT>
 struct ListIO {
     static constexpr bool kBins = false;
     const float4* rays;
@@ -45,11 +48,11 @@ struct ListIO {
     }
     __device__ __forceinline__ void store(uint32_t i, const HitRec& hit, uint32_t*) const
     {
-        if (out.ent_id) stream_store(out.ent_id + i, hit.ent);
-        if (out.prim_id) stream_store(out.prim_id + i, hit.prim);
-        if (out.t) stream_store(out.t + i, hit.t);
-        if (out.u) stream_store(out.u + i, hit.u);
-        if (out.v) stream_store(out.v + i, hit.v);
+        if (ALL_OUT || out.ent_id) stream_store(out.ent_id + i, hit.ent);
+        if (ALL_OUT || out.prim_id) stream_store(out.prim_id + i, hit.prim);
+        if (ALL_OUT || out.t) stream_store(out.t + i, hit.t);
+        if (ALL_OUT || out.u) stream_store(out.u + i, hit.u);
+        if (ALL_OUT || out.v) stream_store(out.v + i, hit.v);
     }
 };
 
@@ -69,20 +72,19 @@ __global__ void normalize_rays_kernel(float4* rays, uint64_t n)
     rays[2 * i + 1] = r1;
 }
 
-template <bool NORMALIZE>
-void launch_list(const DeviceScene& scene, const ListIO<NORMALIZE>& io, int any_hit, TraceCounters* d_counters, uint32_t* d_work,
-                 uint32_t grid, cudaStream_t stream)
+template <typename IO>
+void launch_list(const DeviceScene& scene, const IO& io, int any_hit, TraceCounters* d_counters, uint32_t* d_work, uint32_t grid, cudaStream_t stream)
 {
     if (d_counters) {
         if (any_hit)
-            trace_kernel<ListIO<NORMALIZE>, true, true><<<grid, kBlock, 0, stream>>>(scene, io, d_counters, d_work);
+            trace_kernel<IO, true, true><<<grid, kBlock, 0, stream>>>(scene, io, d_counters, d_work);
         else
-            trace_kernel<ListIO<NORMALIZE>, false, true><<<grid, kBlock, 0, stream>>>(scene, io, d_counters, d_work);
+            trace_kernel<IO, false, true><<<grid, kBlock, 0, stream>>>(scene, io, d_counters, d_work);
     } else {
         if (any_hit)
-            trace_kernel<ListIO<NORMALIZE>, true, false><<<grid, kBlock, 0, stream>>>(scene, io, nullptr, d_work);
+            trace_kernel<IO, true, false><<<grid, kBlock, 0, stream>>>(scene, io, nullptr, d_work);
         else
-            trace_kernel<ListIO<NORMALIZE>, false, false><<<grid, kBlock, 0, stream>>>(scene, io, nullptr, d_work);
+            trace_kernel<IO, false, false><<<grid, kBlock, 0, stream>>>(scene, io, nullptr, d_work);
     }
 }
 
@@ -98,10 +100,18 @@ cudaError_t launch_trace(const DeviceScene& scene, const float4* d_rays, uint64_
     // persistent grid: one wave of resident CTAs (a multiple of the SM count), fewer for tiny batches
     const uint64_t want = (n + kChunk - 1) / kChunk; // warps that can get at least one chunk
     const uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)sm_count * kBlocksPerSM, (want + 3) / 4));
-    if (normalize)
-        launch_list<true>(scene, ListIO<true>{ d_rays, (uint32_t)n, ray_flags, out }, any_hit, d_counters, d_work, grid, stream);
-    else
-        launch_list<false>(scene, ListIO<false>{ d_rays, (uint32_t)n, ray_flags, out }, any_hit, d_counters, d_work, grid, stream);
+    const bool     all  = out.ent_id && out.prim_id && out.t && out.u && out.v;
+    if (normalize) {
+        if (all)
+            launch_list(scene, ListIO<true, true>{ d_rays, (uint32_t)n, ray_flags, out }, any_hit, d_counters, d_work, grid, stream);
+        else
+            launch_list(scene, ListIO<true, false>{ d_rays, (uint32_t)n, ray_flags, out }, any_hit, d_counters, d_work, grid, stream);
+    } else {
+        if (all)
+            launch_list(scene, ListIO<false, true>{ d_rays, (uint32_t)n, ray_flags, out }, any_hit, d_counters, d_work, grid, stream);
+        else
+            launch_list(scene, ListIO<false, false>{ d_rays, (uint32_t)n, ray_flags, out }, any_hit, d_counters, d_work, grid, stream);
+    }
     return cudaGetLastError();
 }
 

@@ -55,6 +55,9 @@ constexpr int      kVoteRefill  = IGB_VOTE_REFILL; // idle lanes that must wait 
 #ifndef IGB_ENT_ONE_WAIT
 #define IGB_ENT_ONE_WAIT 1
 #endif
+#ifndef IGB_ENT_BOX
+#define IGB_ENT_BOX 1 // 0: skip the exact entity-box test of the leaf step (the quantised box of the TLAS node was tested already)
+#endif
 // Debug build (scripts/build_variant.sh dbg -DIGB_DEBUG_CHECKS=1): device-side bounds checks on every stack push and
 // on every node / triangle / leaf index the traversal dereferences; a violation prints once and traps.  This is the
 // stand-in for compute-sanitizer memcheck, which is closed on this GPU pool (profiles/r02_sanitizer_closed.txt).
@@ -138,8 +141,9 @@ __device__ __forceinline__ uint32_t extract_byte(uint32_t w, int j) { return (w 
 
 // Ray records and hit columns are touched once per launch; the BVH is what should stay in L1.
 //   IGB_STREAM_IO 1: ld.global.cs / st.global.cs (evict-first) for ray input and hit output, 2: L1::no_allocate loads.
+// Measured (profiles/r02_ab_stream_io_prefetch.txt): 7200 -> 7260 Mrays/s on C3, 1128 -> 1135 Msamples/s on C4 with 1; on.
 #ifndef IGB_STREAM_IO
-#define IGB_STREAM_IO 0
+#define IGB_STREAM_IO 1
 #endif
 //   IGB_RAY_PREFETCH 1: a warp claims its ray chunks one ahead and prefetches the records into L2, 2: into L1.
 #ifndef IGB_RAY_PREFETCH
@@ -427,9 +431,10 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
     uint32_t           ahead    = kNoChunk; // warp-uniform: base of the chunk claimed one step ahead
 #endif
     bool     exhausted = false;           // warp-uniform
-    bool     active    = false;
-
-    uint32_t ray_id = 0;
+    // a lane is active while it owns a ray: ray_id != kNoRay (one register less than a separate flag, which spilled)
+    constexpr uint32_t kNoRay = 0xFFFFFFFFu;
+    uint32_t ray_id = kNoRay;
+#define IGB_ACTIVE (ray_id != kNoRay)
     float    tmin   = 0.0f;
     TravRay  ray;
     HitRec   hit;
@@ -441,7 +446,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
     int32_t  cur_ent = -1;
 
     for (;;) {
-        const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !active);
+        const uint32_t idle = __ballot_sync(0xFFFFFFFFu, !IGB_ACTIVE);
         if (idle != 0u && (kVoteRefill <= 1 || exhausted || __popc(idle) >= kVoteRefill)) {
             if (!exhausted) {
                 if (pool_next == pool_end) {
@@ -471,17 +476,17 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                 }
                 const uint32_t avail = pool_end - pool_next;
                 const uint32_t rank  = __popc(idle & lt_mask);
-                if (!active && rank < avail) {
-                    ray_id     = pool_next + rank;
+                if (!IGB_ACTIVE && rank < avail) {
+                    const uint32_t id = pool_next + rank;
                     float tmax = 0.0f;
-                    if (io.load(ray_id, ray.org, ray.dir, tmin, tmax, ray_flags)) {
+                    if (io.load(id, ray.org, ray.dir, tmin, tmax, ray_flags)) {
+                        ray_id  = id;
                         setup_trav_ray(ray);
                         hit     = HitRec{ tmax, 0.0f, 0.0f, -1, -1 };
                         sp      = 0;
                         ngroup  = make_uint2(0u, 0x80000000u);
                         tgroup  = make_uint2(0u, 0u);
                         in_blas = false;
-                        active  = true;
                     }
                 }
                 pool_next += min(avail, (uint32_t)__popc(idle));
@@ -493,7 +498,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
 #if IGB_PARK_PRIMS
         // Experiment: a lane with both inner children and primitives pending parks the primitive group on the stack and
         // keeps descending (it is tested when popped) instead of waiting for the primitive vote.
-        if (active && tgroup.y != 0u && ngroup.y > 0x00FFFFFFu && (IGB_PARK_PRIMS == 2 || in_blas)) {
+        if (IGB_ACTIVE && tgroup.y != 0u && ngroup.y > 0x00FFFFFFu && (IGB_PARK_PRIMS == 2 || in_blas)) {
             IGB_PUSH(tgroup);
             tgroup      = make_uint2(0u, 0u);
         }
@@ -502,7 +507,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
 #if IGB_NODE_REPS > 1
 #pragma unroll 1
         for (int rep = 0; rep < IGB_NODE_REPS; ++rep) {
-        if (rep > 0 && active && tgroup.y == 0u && ngroup.y <= 0x00FFFFFFu && sp > 0) {
+        if (rep > 0 && IGB_ACTIVE && tgroup.y == 0u && ngroup.y <= 0x00FFFFFFu && sp > 0) {
             // quick pop between node steps: only a plain inner group (sentinels / parked primitive groups wait for the pop phase)
             const uint2 e = stack[sp - 1];
             if (e.x != kSentinel && e.y > 0x00FFFFFFu) {
@@ -511,7 +516,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
             }
         }
 #endif
-        if (active && tgroup.y == 0u && ngroup.y > 0x00FFFFFFu) {
+        if (IGB_ACTIVE && tgroup.y == 0u && ngroup.y > 0x00FFFFFFu) {
             const uint32_t hits            = ngroup.y;
             const uint32_t imask           = ngroup.y & 0xFFu;
             const uint32_t child_bit_index = 31u - (uint32_t)__clz(hits);
@@ -542,10 +547,10 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
         // ray against 5 node steps), so run immediately they execute with ~2 and ~5 live lanes.  A lane with primitives
         // pending waits instead; a phase runs once kVoteTri / kVoteEnt lanes wait for it, or when no lane of the warp
         // can progress otherwise.
-        const bool     want_p = active && tgroup.y != 0u;
+        const bool     want_p = IGB_ACTIVE && tgroup.y != 0u;
         const uint32_t tri_v  = __ballot_sync(0xFFFFFFFFu, want_p && in_blas);
         const uint32_t ent_v  = __ballot_sync(0xFFFFFFFFu, want_p && !in_blas);
-        const uint32_t free_v = __ballot_sync(0xFFFFFFFFu, active && tgroup.y == 0u);
+        const uint32_t free_v = __ballot_sync(0xFFFFFFFFu, IGB_ACTIVE && tgroup.y == 0u);
         if (tri_v != 0u && (__popc(tri_v) >= kVoteTri || free_v == 0u)) {
             if (want_p && in_blas) {
 #if IGB_TRI_LOAD2
@@ -593,6 +598,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                     const uint32_t leaf_flags = __float_as_uint(l5.x);
                     // check_ray_visibility (traversal/ray.art:51)
                     if ((ray_flags & 0xFu) != ((ray_flags & leaf_flags) & 0xFu)) continue;
+#if IGB_ENT_BOX
                     // intersect_ray_box_single_section on the exact leaf box + `tmin <= hit.distance`
                     const float t0x = (l0.x - ray.org.x) * ray.idir.x, t1x = (l1.x - ray.org.x) * ray.idir.x;
                     const float t0y = (l0.y - ray.org.y) * ray.idir.y, t1y = (l1.y - ray.org.y) * ray.idir.y;
@@ -600,6 +606,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                     const float entry = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tmin));
                     const float exit_ = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z)) * kBoxSlack;
                     if (!(entry <= fminf(exit_, hit.t))) continue;
+#endif
 
 #if !IGB_ENT_ONE_WAIT
                     const float4 l2 = __ldg(lp + 2), l3 = __ldg(lp + 3), l4 = __ldg(lp + 4);
@@ -645,7 +652,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
         }
 
         // ---- pop / finish: lanes with nothing pending at the current node
-        if (active) {
+        if (IGB_ACTIVE) {
             bool finished = ANY_HIT && hit.prim >= 0;
             if (!finished && tgroup.y == 0u && ngroup.y <= 0x00FFFFFFu) {
                 if (sp == 0) {
@@ -679,7 +686,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
             if (finished) {
                 IGB_CHECK(ray_id < n, "ray id out of range at store");
                 io.store(ray_id, hit, s_bins);
-                active = false;
+                ray_id = kNoRay;
             }
         }
     }
@@ -724,5 +731,6 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
     }
 }
 
+#undef IGB_ACTIVE
 } // namespace core
 } // namespace igb

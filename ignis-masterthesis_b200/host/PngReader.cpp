@@ -113,7 +113,7 @@ bool loadPng8(const std::string& path, PngImage& out, std::string& error)
         case 2: r = p[0], g = p[1], b = p[2]; break;
         case 3: {
             const size_t k = p[0];
-            if (3 * k + 2 >= palette.size() + 0 && 3 * k + 2 > palette.size() - 1 + 0) {
+            if (3 * k + 2 >= palette.size()) {
                 r = g = b = 0;
             } else {
                 r = palette[3 * k], g = palette[3 * k + 1], b = palette[3 * k + 2];

@@ -1,4 +1,5 @@
 #include "Runtime.h"
+#include "SceneLoader.h"
 
 #include <algorithm>
 #include <cmath>
@@ -30,7 +31,9 @@ Runtime::~Runtime() = default;
 bool Runtime::loadFromFile(const std::string& path)
 {
     std::string err;
-    if (!loadSceneFile(path, mScene, err)) {
+    // scene JSON goes through the loader of this directory (SceneLoader.cpp); `.igdb` is the loader's output, stored
+    const size_t ow = mOptions.OverrideFilmSize ? mOptions.OverrideFilmSize->first : 0, oh = mOptions.OverrideFilmSize ? mOptions.OverrideFilmSize->second : 0;
+    if (!loadAnyScene(path, mScene, err, ow, oh)) {
         std::fprintf(stderr, "[ERROR] %s\n", err.c_str());
         return false;
     }

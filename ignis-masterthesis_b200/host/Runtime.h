@@ -1,6 +1,7 @@
 // Runtime.h -- the slice of `IG::Runtime` (src/runtime/Runtime.h, Runtime.cpp:121-448) that the igcli / igtrace
-// frontends call, over IG::Device.  Scene loading reads an `.igdb` (SceneFile.h) instead of running the reference's
-// JSON loader + shader generators; everything after loading follows the reference's control flow.
+// frontends call, over IG::Device.  Scene loading reads the reference's scene JSON through SceneLoader.cpp (tables instead
+// of generated shader source) or an `.igdb` (SceneFile.h: the loader's output, stored); everything after loading follows the
+// reference's control flow.
 #pragma once
 
 #include "SceneFile.h"

@@ -1,8 +1,10 @@
 // igdbtool -- host-only checks of the frontends' file formats (no device needed):
 //   igdbtool inspect scene.igdb        prints the table sizes the .igdb reader sees, one `key value` per line
 //   igdbtool testimage out.(exr|pfm) W H   writes the image rgb(x, y) = (x, y, x * y + 0.5) through ImageIO
+//   igdbtool json2igdb scene.json out.igdb [W H]   runs the scene loader (SceneLoader.cpp) and stores its tables
 #include "ImageIO.h"
 #include "SceneFile.h"
+#include "SceneLoader.h"
 
 #include <cstdlib>
 #include <iostream>
@@ -45,6 +47,16 @@ int main(int argc, char** argv)
             }
         return saveImageRGB(argv[2], rgb.data(), w, h, 1.0f) ? EXIT_SUCCESS : EXIT_FAILURE;
     }
-    std::cerr << "usage: igdbtool inspect scene.igdb | igdbtool testimage out.(exr|pfm) W H" << std::endl;
+    if (cmd == "json2igdb" && (argc == 4 || argc == 6)) {
+        SceneFile   scene;
+        std::string err;
+        const size_t w = argc == 6 ? std::strtoull(argv[4], nullptr, 10) : 0, h = argc == 6 ? std::strtoull(argv[5], nullptr, 10) : 0;
+        if (!loadSceneJson(argv[2], scene, err, w, h) || !saveSceneFile(argv[3], scene, err)) {
+            std::cerr << "[ERROR] " << err << std::endl;
+            return EXIT_FAILURE;
+        }
+        return EXIT_SUCCESS;
+    }
+    std::cerr << "usage: igdbtool json2igdb scene.json out.igdb [W H] | igdbtool inspect scene.igdb | igdbtool testimage out.(exr|pfm) W H" << std::endl;
     return EXIT_FAILURE;
 }

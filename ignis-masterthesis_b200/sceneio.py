@@ -693,7 +693,9 @@ def compute_sun_ea(year=2020, month=5, day=6, hour=12, minute=0, seconds=0.0, lo
     """computeSunEA (src/runtime/skysun/SunLocation.cpp:17-103) with the defaults of SunLocation.h:8-36.
     Returns (elevation, azimuth west of south) in radians, float32 like ElevationAzimuth."""
     F = np.float32
-    dec_hours = hour + F(timezone) + (minute + F(seconds) / 60.0) / 60.0
+    # double arithmetic like the reference (`Hour + Timezone + (Minute + Seconds / 60.0) / 60.0` promotes to double); numpy float32
+    # SCALARS would keep every following product in float32 and round the Julian day count to 0.25 days
+    dec_hours = float(hour) + float(F(timezone)) + (float(minute) + float(F(seconds)) / 60.0) / 60.0
     aux1 = int((month - 14) / 12)
     aux2 = int((1461 * (year + 4800 + aux1)) / 4) + int((367 * (month - 2 - 12 * aux1)) / 12) - int((3 * int((year + 4900 + aux1) / 100)) / 4) + day - 32075
     elapsed = (float(aux2) - 0.5 + dec_hours / 24.0) - 2451545.0

@@ -163,3 +163,26 @@ def test_igcli_stats_reports_the_reference_categories(ig, host_bin, tmp_path):
     os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
     import cv2
     np.testing.assert_allclose(cv2.imread(out, cv2.IMREAD_UNCHANGED), cv2.imread(out2, cv2.IMREAD_UNCHANGED), rtol=1e-4, atol=1e-6)
+
+
+def test_igcli_renders_a_scene_json_without_python(ig, host_bin, tmp_path):
+    """`igcli scene.json`: the C++ loader (host/SceneLoader.cpp) builds the tables, no .igdb and no Python in the path.  The image
+    equals the one rendered from the tables the C++ loader wrote out (json2igdb -> binding); the demo scene is this repo's own."""
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    import cv2
+    from test_scene_loader_cpp import _write_pyramid
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    scene = str(tmp_path / "loader_demo.json")
+    open(scene, "w").write(open(os.path.join(root, "tests", "scenes", "loader_demo.json")).read())
+    _write_pyramid(str(tmp_path / "loader_demo_pyramid.ply"))
+    out, igdb = str(tmp_path / "out.exr"), str(tmp_path / "demo.igdb")
+    r = _run(os.path.join(host_bin, "igcli"), scene, "-o", out, "--spp", "16", "--spi", "4", "--seed", "3")
+    assert "Iterations: 4" in r.stdout
+    img = cv2.imread(out, cv2.IMREAD_UNCHANGED)[:, :, ::-1]
+    assert img.shape == (120, 160, 3) and np.all(np.isfinite(img)) and img.mean() > 0.02
+    _run(os.path.join(host_bin, "igdbtool"), "json2igdb", scene, igdb)
+    out2 = str(tmp_path / "out2.exr")
+    _run(os.path.join(host_bin, "igcli"), igdb, "-o", out2, "--spp", "16", "--spi", "4", "--seed", "3")
+    np.testing.assert_allclose(img, cv2.imread(out2, cv2.IMREAD_UNCHANGED)[:, :, ::-1], rtol=1e-4, atol=1e-6)
+    # every light type of the scene contributes: the lamp (area), the point and spot lights and the sky
+    assert img[:, :, 2].mean() > 0.01 and img.max() > 1.0
