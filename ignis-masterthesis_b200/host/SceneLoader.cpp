@@ -1086,10 +1086,8 @@ int addSkyFunction(ShadingBuilder& sb, const SkyFunction& q, const std::array<fl
 } // namespace
 
 // ------------------------------------------------------------------------------------------------ the loader
-static void loadSceneImpl(const std::string& path, SceneFile& out, size_t width_override, size_t height_override)
+static void loadDocumentImpl(const Value& scene, const std::string& base, SceneFile& out, size_t width_override, size_t height_override)
 {
-    const std::string base  = dirName(path);
-    const Value       scene = mergeExternals(json::parse(readText(path)), base);
     auto list = [&](const char* key) -> const std::vector<Value>& {
         static const std::vector<Value> empty;
         const Value* v = scene.find(key);
@@ -1562,10 +1560,22 @@ static void loadSceneImpl(const std::string& path, SceneFile& out, size_t width_
     out.height = height;
 }
 
+bool loadSceneDocument(const json::Value& scene, const std::string& base_dir, SceneFile& out, std::string& error, size_t width, size_t height)
+{
+    try {
+        loadDocumentImpl(scene, base_dir, out, width, height);
+        return true;
+    } catch (const std::exception& e) {
+        error = e.what();
+        return false;
+    }
+}
+
 bool loadSceneJson(const std::string& path, SceneFile& out, std::string& error, size_t width, size_t height)
 {
     try {
-        loadSceneImpl(path, out, width, height);
+        const std::string base = dirName(path);
+        loadDocumentImpl(mergeExternals(json::parse(readText(path)), base), base, out, width, height);
         return true;
     } catch (const std::exception& e) {
         error = e.what();

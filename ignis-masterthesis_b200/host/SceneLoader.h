@@ -15,6 +15,12 @@
 #include "SceneFile.h"
 
 namespace IG {
+namespace json {
+struct Value;
+}
+/// The loader proper, on an already parsed document (host/Json.h) whose externals have been merged; `base_dir` resolves
+/// relative file names.  This is the entry the reference-side bridge (host/ReferenceBridge.cpp) uses.
+bool loadSceneDocument(const json::Value& scene, const std::string& base_dir, SceneFile& out, std::string& error, size_t width = 0, size_t height = 0);
 /// Loads `path` (scene JSON).  width / height override the film size when non-zero (igcli --width / --height).
 bool loadSceneJson(const std::string& path, SceneFile& out, std::string& error, size_t width = 0, size_t height = 0);
 /// Writes the container host/SceneFile.h describes.
