@@ -75,6 +75,11 @@ struct igb200_device {
     bool         stats   = false;
     cudaStream_t stream  = nullptr;
     cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
+    // igb200_trace_rays_device on caller streams: the kernel's work counters belong to the handle, so two launches must not
+    // overlap.  ev_trace marks the end of the last one; a launch on ANOTHER stream waits for it (ordering on the device, no host wait).
+    cudaEvent_t  ev_trace = nullptr;
+    cudaStream_t last_trace_stream = nullptr;
+    bool         trace_pending = false;
     int          sm_count = 0;
     static constexpr int      kPipe      = 3;         // streams of the host-buffer pipeline
     uint64_t                 chunk_rays = 1u << 20;   // rays per bulk chunk of the host-buffer pipeline (32 MiB up, 20 MiB down)
@@ -182,6 +187,7 @@ int igb200_create(const igb200_setup* setup, igb200_device** out)
     dev->sm_count      = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&dev->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&dev->ev0) != cudaSuccess || cudaEventCreate(&dev->ev1) != cudaSuccess ||
+        cudaEventCreateWithFlags(&dev->ev_trace, cudaEventDisableTiming) != cudaSuccess ||
         cudaStreamCreateWithFlags(&dev->pipe[0], cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&dev->pipe[1], cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&dev->pipe[2], cudaStreamNonBlocking) != cudaSuccess) {
@@ -208,6 +214,7 @@ void igb200_destroy(igb200_device* dev)
     cudaDeviceSynchronize();
     if (dev->ev0) cudaEventDestroy(dev->ev0);
     if (dev->ev1) cudaEventDestroy(dev->ev1);
+    if (dev->ev_trace) cudaEventDestroy(dev->ev_trace);
     if (dev->stream) cudaStreamDestroy(dev->stream);
     for (cudaStream_t p : dev->pipe)
         if (p) cudaStreamDestroy(p);
@@ -422,10 +429,14 @@ static int trace_on_stream(igb200_device* dev, const igb200_ray* d_rays, uint64_
         IGB_CUDA(cudaMemsetAsync(dev->d_counters.ptr, 0, sizeof(igb::TraceCounters), stream));
         counters = dev->d_counters.ptr;
     }
+    if (dev->trace_pending && dev->last_trace_stream != stream) IGB_CUDA(cudaStreamWaitEvent(stream, dev->ev_trace, 0));
     if (timed) IGB_CUDA(cudaEventRecord(dev->ev0, stream));
     IGB_CUDA(igb::launch_trace(dev->view, reinterpret_cast<const float4*>(d_rays), n, ray_flags, any_hit, out, counters,
                                dev->d_work.ptr + 2 * igb200_device::kPipe, dev->sm_count, stream));
     if (timed) IGB_CUDA(cudaEventRecord(dev->ev1, stream));
+    IGB_CUDA(cudaEventRecord(dev->ev_trace, stream));
+    dev->last_trace_stream = stream;
+    dev->trace_pending     = true;
     return IGB200_OK;
 }
 

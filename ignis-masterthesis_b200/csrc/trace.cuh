@@ -50,7 +50,7 @@ constexpr int kStackSize = IGB_STACK; // traversal stack entries per ray (uint2 
 // Launches the closest-hit (any_hit = 0) or any-hit traversal of `n` rays on `stream`.
 // counters may be nullptr (then the non-counting kernel variant is used).  d_work: two zero-initialised
 // uint32 (work counter, retired-block counter) owned by the device handle; the kernel rewinds them itself,
-// so only one trace launch per handle may be in flight at a time.
+// so only one trace launch per handle may be in flight at a time (device.cu orders launches on different streams by an event).
 cudaError_t launch_trace(const DeviceScene& scene, const float4* d_rays, uint64_t n, uint32_t ray_flags, int any_hit,
                          const TraceOutputs& out, TraceCounters* d_counters, uint32_t* d_work, int sm_count,
                          cudaStream_t stream, bool normalize = false);

@@ -3,6 +3,8 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <new>
+#include <sys/stat.h>
 
 namespace IG {
 igb200_shading ShadingTables::view() const
@@ -61,10 +63,26 @@ bool loadSceneFile(const std::string& path, SceneFile& out, std::string& error)
         if (std::fread(head, 4, 2, f) != 2 || head[0] != 1u || head[1] > 64u) { error = "unsupported .igdb version"; break; }
         std::vector<TocEntry> toc(head[1]);
         if (std::fread(toc.data(), sizeof(TocEntry), toc.size(), f) != toc.size()) { error = "truncated table of contents"; break; }
+        // the table of contents is untrusted input: every section must lie inside the file before anything is allocated
+        struct stat st {};
+        if (fstat(fileno(f), &st) != 0) { error = "cannot stat " + path; break; }
+        const uint64_t file_size = (uint64_t)st.st_size;
         bool bad = false;
         for (const TocEntry& e : toc) {
-            std::vector<uint8_t> data(e.bytes);
-            if (std::fseek(f, (long)e.offset, SEEK_SET) != 0 || (e.bytes && std::fread(data.data(), 1, e.bytes, f) != e.bytes)) {
+            if (e.offset > file_size || e.bytes > file_size - e.offset) {
+                error = std::string("section ") + std::string(e.name, strnlen(e.name, 24)) + " lies outside the file";
+                bad   = true;
+                break;
+            }
+            std::vector<uint8_t> data;
+            try {
+                data.resize(e.bytes);
+            } catch (const std::bad_alloc&) {
+                error = "out of memory reading " + path;
+                bad   = true;
+                break;
+            }
+            if (fseeko(f, (off_t)e.offset, SEEK_SET) != 0 || (e.bytes && std::fread(data.data(), 1, e.bytes, f) != e.bytes)) {
                 error = std::string("truncated section ") + std::string(e.name, strnlen(e.name, 24));
                 bad   = true;
                 break;
@@ -126,6 +144,8 @@ bool loadSceneFile(const std::string& path, SceneFile& out, std::string& error)
     std::memcpy(two, s_flm->data(), 8);
     out.width  = two[0];
     out.height = two[1];
+    for (const char* name : { "bsdfs", "materials", "infinite", "finite", "textures", "blob" })
+        if (!need(name, 0)) return false; // a missing shading section is an error, not an empty table
     const bool tables_ok = typed(sec["bsdfs"], sh.bsdfs) && typed(sec["materials"], sh.materials) && typed(sec["infinite"], sh.infinite)
                            && typed(sec["finite"], sh.finite) && typed(sec["textures"], sh.textures);
     if (!tables_ok) {

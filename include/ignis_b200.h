@@ -140,7 +140,10 @@ int igb200_trace_rays(igb200_device* dev, const igb200_ray* rays, uint64_t n, ui
 
 /* Device-resident form of the same call: `d_rays` and the outputs are device pointers (e.g. torch
  * tensors' data_ptr) on this device; enqueued on `stream` (a cudaStream_t, 0 = default), not synchronised.
- * Directions must already be normalised. */
+ * Directions must already be normalised.  Calls on DIFFERENT streams of one handle are ordered on the device (each
+ * waits for the previous launch through an event): the traversal kernel's work counters belong to the handle, so two
+ * launches never overlap; use one handle per stream for concurrent traversal.  Calls from different host threads on
+ * one handle must be serialised by the caller, as for every igb200_* function. */
 int igb200_trace_rays_device(igb200_device* dev, const igb200_ray* d_rays, uint64_t n, uint32_t ray_flags,
                              int any_hit, int32_t* d_ent_id, int32_t* d_prim_id, float* d_t, float* d_u,
                              float* d_v, void* stream);

@@ -46,6 +46,25 @@ def test_igdb_reader_rejects_garbage_and_truncation(ig, host_bin, tmp_path):
         r = _run(os.path.join(host_bin, "igdbtool"), "inspect", bad)
         assert r.returncode != 0 and "[ERROR]" in r.stderr, label
     assert _run(os.path.join(host_bin, "igdbtool"), "inspect", str(tmp_path / "missing.igdb")).returncode != 0
+    # a table of contents that points outside the file (a multi-GB `bytes` field) is refused before any allocation
+    import struct
+    evil = bytearray(raw)
+    evil[16 + 24:16 + 32] = struct.pack("<Q", 1 << 40)
+    bad = str(tmp_path / "evil.igdb")
+    open(bad, "wb").write(bytes(evil))
+    r = _run(os.path.join(host_bin, "igdbtool"), "inspect", bad)
+    assert r.returncode != 0 and "outside the file" in r.stderr
+    # a file without its shading sections is an error, not a scene with empty tables
+    n_sec = struct.unpack("<I", raw[12:16])[0]
+    cut = bytearray(raw)
+    for i in range(n_sec):
+        e = 16 + 40 * i
+        if cut[e:e + 24].rstrip(b"\0") == b"bsdfs":
+            cut[e:e + 5] = b"xsdfs"
+    nob = str(tmp_path / "nobsdfs.igdb")
+    open(nob, "wb").write(bytes(cut))
+    r = _run(os.path.join(host_bin, "igdbtool"), "inspect", nob)
+    assert r.returncode != 0 and "bsdfs" in r.stderr
 
 
 def test_exr_and_pfm_writers(host_bin, tmp_path):

@@ -333,3 +333,33 @@ def test_hostile_rays_and_degenerate_triangles(ig, oracle, dev):
     for any_hit in (False, True):
         ent, prim, t, _, _ = dev.trace(bad, any_hit=any_hit)
         assert np.all(prim[[0, 1, 2, 3, 4, 7]] == -1) and np.all(ent[[0, 1, 2, 3, 4, 7]] == -1)
+
+
+def test_device_resident_launches_on_two_streams_are_ordered(ig):
+    """igb200_trace_rays_device from two CUDA streams on ONE handle: the kernel's work counters belong to the handle, so the
+    library orders the launches on the device (VERDICT r1 'weak' 16: silent wrong answers before).  Results of interleaved
+    launches on two streams must equal those of the same launches on one stream."""
+    import torch
+    tables = ig.workloads.c3_scene(grid=2, stacks=16, slices=32)
+    n = 1 << 18
+    batches = [ig.workloads.c3_rays(tables, n=n, seed=s) for s in (1, 2)]
+    with ig.Device(0) as dev:
+        dev.assign_scene(tables)
+        d_rays = [torch.from_numpy(b.view(np.float32).reshape(-1, 8)).cuda() for b in batches]
+        def outs():
+            return [torch.empty(n, dtype=torch.int32, device="cuda") for _ in range(2)] + [torch.empty(n, dtype=torch.float32, device="cuda") for _ in range(3)]
+        ref = [outs(), outs()]
+        s0 = torch.cuda.current_stream()
+        for k in range(2):
+            dev.trace_device(d_rays[k].data_ptr(), n, *[x.data_ptr() for x in ref[k]], stream=s0.cuda_stream)
+        torch.cuda.synchronize()
+        streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+        got = [outs(), outs()]
+        for rep in range(8):  # back-to-back launches alternating between the two streams
+            for k in range(2):
+                dev.trace_device(d_rays[k].data_ptr(), n, *[x.data_ptr() for x in got[k]], stream=streams[k].cuda_stream)
+        torch.cuda.synchronize()
+        for k in range(2):
+            for a, b in zip(ref[k], got[k]):
+                assert torch.equal(a, b)
+        assert int((ref[0][1] >= 0).sum()) > 0
