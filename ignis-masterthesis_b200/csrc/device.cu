@@ -232,6 +232,77 @@ void igb200_destroy(igb200_device* dev)
     delete dev; // DeviceBuffer destructors free the allocations (Device::releaseAll, Device.cpp:948-952)
 }
 
+// Disk cache of large mesh BVHs, the counterpart of setup_bvh's cache (src/runtime/shape/TriMeshProvider.cpp:329-353: meshes
+// above 500 000 faces, keyed by a content hash, one file per mesh in the cache directory).  Opt-in through the environment
+// variable IGB200_CACHE_DIR (the reference's CacheManager can be disabled likewise); a file that does not match the mesh
+// (hash, face count, builder version) or is damaged is ignored and rewritten.  Key = FNV-1a over the triangle boxes the
+// builder consumes, so it is independent of where the mesh sits in the shape table.
+static constexpr uint64_t kBvhCacheMinFaces = 500000;
+static constexpr uint32_t kBvhCacheVersion  = 2; // bump when bvh8_build.cpp changes the tree it produces
+static void build_or_load_blas(const std::vector<float>& boxes, uint32_t nf, igb::Bvh8& blas)
+{
+    using igb::Node8;
+    const char* dir = std::getenv("IGB200_CACHE_DIR");
+    if (!dir || !*dir || nf <= kBvhCacheMinFaces) {
+        igb::build_bvh8(boxes.data(), nf, 3, blas);
+        return;
+    }
+    uint64_t h = 1469598103934665603ull;
+    const uint8_t* bytes = reinterpret_cast<const uint8_t*>(boxes.data());
+    for (size_t i = 0; i < boxes.size() * sizeof(float); ++i) h = (h ^ bytes[i]) * 1099511628211ull;
+    char name[64];
+    std::snprintf(name, sizeof(name), "/_bvh8_%016llx.bin", (unsigned long long)h);
+    const std::string path = std::string(dir) + name;
+    struct Head {
+        char     magic[8];
+        uint32_t version, faces;
+        uint64_t hash, nodes, prims;
+        uint32_t max_depth, pad;
+        double   sah_node, sah_prim;
+    };
+    if (FILE* f = std::fopen(path.c_str(), "rb")) {
+        Head hd{};
+        bool ok = std::fread(&hd, sizeof(hd), 1, f) == 1 && std::memcmp(hd.magic, "IGBVH8\0\0", 8) == 0 && hd.version == kBvhCacheVersion &&
+                  hd.faces == nf && hd.hash == h && hd.prims == nf && hd.nodes >= 1 && hd.nodes <= 2ull * nf + 1;
+        if (ok) {
+            blas.nodes.resize(hd.nodes);
+            blas.prim_indices.resize(hd.prims);
+            ok = std::fread(blas.nodes.data(), sizeof(Node8), hd.nodes, f) == hd.nodes &&
+                 std::fread(blas.prim_indices.data(), sizeof(uint32_t), hd.prims, f) == hd.prims;
+            for (size_t i = 0; ok && i < blas.prim_indices.size(); ++i) ok = blas.prim_indices[i] < nf; // never trust indices from disk
+        }
+        std::fclose(f);
+        if (ok) {
+            blas.max_depth     = hd.max_depth;
+            blas.sah_node_term = hd.sah_node;
+            blas.sah_prim_term = hd.sah_prim;
+            return;
+        }
+        blas = igb::Bvh8{};
+    }
+    igb::build_bvh8(boxes.data(), nf, 3, blas);
+    const std::string tmp = path + ".tmp";
+    if (FILE* f = std::fopen(tmp.c_str(), "wb")) {
+        Head hd{};
+        std::memcpy(hd.magic, "IGBVH8\0\0", 8);
+        hd.version   = kBvhCacheVersion;
+        hd.faces     = nf;
+        hd.hash      = h;
+        hd.nodes     = blas.nodes.size();
+        hd.prims     = blas.prim_indices.size();
+        hd.max_depth = blas.max_depth;
+        hd.sah_node  = blas.sah_node_term;
+        hd.sah_prim  = blas.sah_prim_term;
+        const bool ok = std::fwrite(&hd, sizeof(hd), 1, f) == 1 && std::fwrite(blas.nodes.data(), sizeof(Node8), blas.nodes.size(), f) == blas.nodes.size() &&
+                        std::fwrite(blas.prim_indices.data(), sizeof(uint32_t), blas.prim_indices.size(), f) == blas.prim_indices.size();
+        std::fclose(f);
+        if (ok)
+            std::rename(tmp.c_str(), path.c_str()); // atomic publish: readers never see a half-written file
+        else
+            std::remove(tmp.c_str());
+    }
+}
+
 int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
 {
     using namespace igb;
@@ -329,7 +400,7 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
                 }
             }
             Bvh8 blas;
-            build_bvh8(boxes.data(), (uint32_t)nf, 3, blas);
+            build_or_load_blas(boxes, (uint32_t)nf, blas);
             blas_depth = std::max(blas_depth, blas.max_depth);
             const uint32_t node_base = (uint32_t)all_nodes.size();
             const uint32_t tri_base  = (uint32_t)(all_tris.size() / 3);

@@ -18,6 +18,31 @@ constexpr uint32_t kRayCamera = 0x1u, kRayBounce = 0x4u, kRayShadow = 0x8u; // s
 // Traversal IO policies (trace_core.cuh)
 // ---------------------------------------------------------------------------------------------------------
 
+// The ray streams (hundreds of MB per round) are read and written once per kernel; the mesh, BVH and texture data are what
+// the 126 MB L2 should keep.  IGB_WAVE_STREAM 1: evict-first loads / stores (ld/st.global.cs) for stream records in the
+// generate and shade kernels (the traversal kernels' own switch is IGB_STREAM_IO).
+#ifndef IGB_WAVE_STREAM
+#define IGB_WAVE_STREAM 0
+#endif
+template <typename T>
+__device__ __forceinline__ T ws_load(const T* p)
+{
+#if IGB_WAVE_STREAM
+    return __ldcs(p);
+#else
+    return *p;
+#endif
+}
+template <typename T>
+__device__ __forceinline__ void ws_store(T* p, T v)
+{
+#if IGB_WAVE_STREAM
+    __stcs(p, v);
+#else
+    *p = v;
+#endif
+}
+
 // K2, gpu_traverse_primary (driver/mapping_gpu.art:45-68): closest hit over the current primary stream; the
 // sort key (material id of the hit entity, n_mat for a miss) and its histogram are produced here
 // (replaces the reset + count launches of gpu_sort_primary, mapping_gpu.art:431-446).
@@ -234,10 +259,10 @@ __global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __rest
         }
         const uint32_t slot    = base + k;
         float4*        r       = s.rec + kRecVec * (size_t)slot;
-        r[0]          = make_float4(org.x, org.y, org.z, tmin);
-        r[1]          = make_float4(dir.x, dir.y, dir.z, tmax);
-        r[2]          = make_float4(__uint_as_float(pixel), __uint_as_float(rnd.counter), __uint_as_float(rnd.seed), 1.0f);
-        r[3]          = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+        ws_store(r, make_float4(org.x, org.y, org.z, tmin));
+        ws_store(r + 1, make_float4(dir.x, dir.y, dir.z, tmax));
+        ws_store(r + 2, make_float4(__uint_as_float(pixel), __uint_as_float(rnd.counter), __uint_as_float(rnd.seed), 1.0f));
+        ws_store(r + 3, make_float4(1.0f, 1.0f, 1.0f, 0.0f));
         s.flags[slot] = (uint16_t)(flags | (1u << 8)); // depth 1
     }
 }
@@ -354,7 +379,7 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
 {
     const igb200_technique& tech = sc.tech;
     const float4* rec = cur.rec + kRecVec * (size_t)i;
-    const float4  o4 = rec[0], d4 = rec[1], meta = rec[2], cp = rec[3], h0 = rec[4];
+    const float4  o4 = ws_load(rec), d4 = ws_load(rec + 1), meta = ws_load(rec + 2), cp = ws_load(rec + 3), h0 = ws_load(rec + 4);
     const Vec3   org{ o4.x, o4.y, o4.z }, dir{ d4.x, d4.y, d4.z };
     const int32_t ent = __float_as_int(h0.x), prim = __float_as_int(h0.y);
     const float   t = h0.z, u = h0.w;
@@ -563,10 +588,10 @@ __global__ void __launch_bounds__(128, IGB_SHADE_MIN_BLOCKS) shade_kernel(WaveCo
             if (alive) {
                 const uint32_t slot      = base + __popc(am & lt_mask);
                 float4*        r    = nxt.rec + kRecVec * (size_t)slot;
-                r[0]            = nx.org_tmin;
-                r[1]            = nx.dir_tmax;
-                r[2]            = nx.meta;
-                r[3]            = nx.contrib_invpdf;
+                ws_store(r, nx.org_tmin);
+                ws_store(r + 1, nx.dir_tmax);
+                ws_store(r + 2, nx.meta);
+                ws_store(r + 3, nx.contrib_invpdf);
                 nxt.flags[slot] = nx.flags;
             }
         }
@@ -577,9 +602,9 @@ __global__ void __launch_bounds__(128, IGB_SHADE_MIN_BLOCKS) shade_kernel(WaveCo
             base = __shfl_sync(0xFFFFFFFFu, base, __ffs(sm) - 1);
             if (has_shadow) {
                 const uint32_t slot    = base + __popc(sm & lt_mask);
-                shq.org_tmin[slot]     = sh.org_tmin;
-                shq.dir_tmax[slot]     = sh.dir_tmax;
-                shq.color_pixel[slot]  = sh.color_pixel;
+                ws_store(shq.org_tmin + slot, sh.org_tmin);
+                ws_store(shq.dir_tmax + slot, sh.dir_tmax);
+                ws_store(shq.color_pixel + slot, sh.color_pixel);
             }
         }
     }

@@ -6,6 +6,8 @@ when the brute-force intersector finds a second primitive within 1e-6 relative o
 resolve by tree order in the reference, src/artic/traversal/mapping_cpu.art:469) -- those are counted,
 reported and excluded; they must stay below 1e-4 of the batch.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -363,3 +365,36 @@ def test_device_resident_launches_on_two_streams_are_ordered(ig):
             for a, b in zip(ref[k], got[k]):
                 assert torch.equal(a, b)
         assert int((ref[0][1] >= 0).sum()) > 0
+
+
+def test_bvh_disk_cache_round_trip(ig, tmp_path, monkeypatch):
+    """IGB200_CACHE_DIR: the BVH8 of a mesh above 500 000 faces is stored on the first igb200_assign_scene and loaded on the next
+    (the counterpart of setup_bvh's cache, src/runtime/shape/TriMeshProvider.cpp:329-353).  Loaded and built trees give the same
+    hits; a damaged cache file is ignored and rewritten."""
+    import glob, time
+    tables = ig.workloads.c3_scene(flat=True)  # one mesh of 1 032 192 triangles
+    rays = ig.workloads.c3_rays(tables, n=1 << 18, seed=11)
+    with ig.Device(0) as dev:  # no cache
+        dev.assign_scene(tables)
+        ref = dev.trace(rays)
+    monkeypatch.setenv("IGB200_CACHE_DIR", str(tmp_path))
+    times = []
+    for _ in range(2):
+        with ig.Device(0) as dev:
+            t0 = time.perf_counter()
+            dev.assign_scene(tables)
+            times.append(time.perf_counter() - t0)
+            got = dev.trace(rays)
+        for a, b in zip(ref, got):
+            assert np.array_equal(a, b)
+    files = glob.glob(str(tmp_path / "_bvh8_*.bin"))
+    assert len(files) == 1 and os.path.getsize(files[0]) > 1 << 20
+    print(f"\nBVH cache: build + store {times[0]:.2f} s, load {times[1]:.2f} s")
+    raw = bytearray(open(files[0], "rb").read())
+    raw[len(raw) // 2:] = b"\xff" * (len(raw) - len(raw) // 2)  # prim indices out of range
+    open(files[0], "wb").write(bytes(raw))
+    with ig.Device(0) as dev:
+        dev.assign_scene(tables)
+        got = dev.trace(rays)
+    for a, b in zip(ref, got):
+        assert np.array_equal(a, b)
