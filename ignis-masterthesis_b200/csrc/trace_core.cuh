@@ -55,6 +55,9 @@ constexpr int      kVoteRefill  = IGB_VOTE_REFILL; // idle lanes that must wait 
 #ifndef IGB_ENT_ONE_WAIT
 #define IGB_ENT_ONE_WAIT 1
 #endif
+#ifndef IGB_PARK_SMEM
+#define IGB_PARK_SMEM 0 // 1: the world ray of a lane inside an instance is parked in shared memory instead of on the local-memory stack
+#endif
 #ifndef IGB_ENT_BOX
 #define IGB_ENT_BOX 1 // 0: skip the exact entity-box test of the leaf step (the quantised box of the TLAS node was tested already)
 #endif
@@ -75,11 +78,38 @@ constexpr int      kVoteRefill  = IGB_VOTE_REFILL; // idle lanes that must wait 
 #else
 #define IGB_CHECK(cond, what) ((void)0)
 #endif
+// IGB_STACK_SMEM = N > 0: the first N stack entries of every thread live in shared memory (N x 8 B x 128 threads per CTA,
+// lane-contiguous: conflict-free), deeper ones in local memory.  ncu on C3: the local-memory stack is 41 % of the kernel's
+// L1 sectors and its loads miss L1 a third of the time.
+#ifndef IGB_STACK_SMEM
+#define IGB_STACK_SMEM 0
+#endif
+#if IGB_STACK_SMEM
+#define IGB_STACK_AT(i) (*((i) < IGB_STACK_SMEM ? &s_stack[(i) * kBlock + threadIdx.x] : &stack[(i) - IGB_STACK_SMEM]))
+#define IGB_PUSH(v)                                             \
+    do {                                                        \
+        IGB_CHECK(sp < kStackSize, "traversal stack overflow"); \
+        if (sp < IGB_STACK_SMEM)                                \
+            s_stack[sp * kBlock + threadIdx.x] = (v);           \
+        else                                                    \
+            stack[sp - IGB_STACK_SMEM] = (v);                   \
+        ++sp;                                                   \
+    } while (0)
+__device__ __forceinline__ uint2 stack_read(const uint2* s_stack, const uint2* stack, int i, int block, int tid)
+{
+    return i < IGB_STACK_SMEM ? s_stack[i * block + tid] : stack[i - IGB_STACK_SMEM];
+}
+#define IGB_TOP() stack_read(s_stack, stack, sp - 1, kBlock, threadIdx.x)
+#define IGB_POP() stack_read(s_stack, stack, --sp, kBlock, threadIdx.x)
+#else
 #define IGB_PUSH(v)                                        \
     do {                                                   \
         IGB_CHECK(sp < kStackSize, "traversal stack overflow"); \
         stack[sp++] = (v);                                 \
     } while (0)
+#define IGB_TOP() stack[sp - 1]
+#define IGB_POP() stack[--sp]
+#endif
 #ifndef IGB_NODE_REPS
 #define IGB_NODE_REPS 1 // node steps per loop trip (lanes that can take another one do; the other phases run once per trip)
 #endif
@@ -419,6 +449,9 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
     for (uint32_t i = threadIdx.x; i < n_top * 5u; i += blockDim.x) s_top[i] = sc.nodes[i];
     __syncthreads();
 #endif
+#if IGB_PARK_SMEM
+    __shared__ uint32_t s_park[10 * kBlock];
+#endif
     const uint32_t n = io.count();
     uint32_t       ray_flags = 0;
     const uint32_t lane    = threadIdx.x & 31u;
@@ -438,7 +471,12 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
     float    tmin   = 0.0f;
     TravRay  ray;
     HitRec   hit;
+#if IGB_STACK_SMEM
+    __shared__ uint2 s_stack[IGB_STACK_SMEM * kBlock];
+    uint2            stack[kStackSize - IGB_STACK_SMEM];
+#else
     uint2    stack[kStackSize];
+#endif
     int      sp      = 0;
     uint2    ngroup  = make_uint2(0u, 0u);
     uint2    tgroup  = make_uint2(0u, 0u);
@@ -509,7 +547,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
         for (int rep = 0; rep < IGB_NODE_REPS; ++rep) {
         if (rep > 0 && IGB_ACTIVE && tgroup.y == 0u && ngroup.y <= 0x00FFFFFFu && sp > 0) {
             // quick pop between node steps: only a plain inner group (sentinels / parked primitive groups wait for the pop phase)
-            const uint2 e = stack[sp - 1];
+            const uint2 e = IGB_TOP();
             if (e.x != kSentinel && e.y > 0x00FFFFFFu) {
                 ngroup = e;
                 --sp;
@@ -634,12 +672,28 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                     // Enter the shape's BVH: park the entity-level state and the world ray under a sentinel.
                     if (ngroup.y > 0x00FFFFFFu) IGB_PUSH(ngroup);
                     if (tgroup.y != 0u) IGB_PUSH(tgroup);
+#if IGB_PARK_SMEM
+                    // The scene has ONE level of instancing, so the world ray needs one parking slot per thread, not a
+                    // stack: ten words in shared memory (lane-contiguous columns, conflict-free).  The local-memory stack
+                    // carried 5 of the ~9 entries a C3 ray pushes for this, and its pops missed L1 a third of the time.
+                    s_park[0 * kBlock + threadIdx.x] = __float_as_uint(ray.org.x);
+                    s_park[1 * kBlock + threadIdx.x] = __float_as_uint(ray.org.y);
+                    s_park[2 * kBlock + threadIdx.x] = __float_as_uint(ray.org.z);
+                    s_park[3 * kBlock + threadIdx.x] = __float_as_uint(ray.dir.x);
+                    s_park[4 * kBlock + threadIdx.x] = __float_as_uint(ray.dir.y);
+                    s_park[5 * kBlock + threadIdx.x] = __float_as_uint(ray.dir.z);
+                    s_park[6 * kBlock + threadIdx.x] = __float_as_uint(ray.idir.x);
+                    s_park[7 * kBlock + threadIdx.x] = __float_as_uint(ray.idir.y);
+                    s_park[8 * kBlock + threadIdx.x] = __float_as_uint(ray.idir.z);
+                    s_park[9 * kBlock + threadIdx.x] = ray.octinv4;
+#else
                     IGB_PUSH(make_uint2(__float_as_uint(ray.org.x), __float_as_uint(ray.org.y)));
                     IGB_PUSH(make_uint2(__float_as_uint(ray.org.z), __float_as_uint(ray.dir.x)));
                     IGB_PUSH(make_uint2(__float_as_uint(ray.dir.y), __float_as_uint(ray.dir.z)));
                     // the world ray's box-test reciprocals and octant travel too: leaving the shape costs loads, not three MUFUs
                     IGB_PUSH(make_uint2(__float_as_uint(ray.idir.x), __float_as_uint(ray.idir.y)));
                     IGB_PUSH(make_uint2(__float_as_uint(ray.idir.z), ray.octinv4));
+#endif
                     IGB_PUSH(make_uint2(kSentinel, 0u));
                     ray         = local;
                     setup_trav_ray(ray);
@@ -658,20 +712,30 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                 if (sp == 0) {
                     finished = true;
                 } else {
-                    uint2 e = stack[--sp];
-                    IGB_CHECK(e.x != kSentinel || sp >= 5, "sentinel without a parked world ray");
+                    uint2 e = IGB_POP();
+                    IGB_CHECK(e.x != kSentinel || IGB_PARK_SMEM || sp >= 5, "sentinel without a parked world ray");
                     if (e.x == kSentinel) {
                         // Leave the shape: back to world space.
-                        const uint2 i1 = stack[--sp], i0 = stack[--sp], c = stack[--sp], b = stack[--sp], a = stack[--sp];
+#if IGB_PARK_SMEM
+                        ray.org     = Vec3{ __uint_as_float(s_park[0 * kBlock + threadIdx.x]), __uint_as_float(s_park[1 * kBlock + threadIdx.x]),
+                                            __uint_as_float(s_park[2 * kBlock + threadIdx.x]) };
+                        ray.dir     = Vec3{ __uint_as_float(s_park[3 * kBlock + threadIdx.x]), __uint_as_float(s_park[4 * kBlock + threadIdx.x]),
+                                            __uint_as_float(s_park[5 * kBlock + threadIdx.x]) };
+                        ray.idir    = Vec3{ __uint_as_float(s_park[6 * kBlock + threadIdx.x]), __uint_as_float(s_park[7 * kBlock + threadIdx.x]),
+                                            __uint_as_float(s_park[8 * kBlock + threadIdx.x]) };
+                        ray.octinv4 = s_park[9 * kBlock + threadIdx.x];
+#else
+                        const uint2 i1 = IGB_POP(), i0 = IGB_POP(), c = IGB_POP(), b = IGB_POP(), a = IGB_POP();
                         ray.org     = Vec3{ __uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(b.x) };
                         ray.dir     = Vec3{ __uint_as_float(b.y), __uint_as_float(c.x), __uint_as_float(c.y) };
                         ray.idir    = Vec3{ __uint_as_float(i0.x), __uint_as_float(i0.y), __uint_as_float(i1.x) };
                         ray.octinv4 = i1.y;
+#endif
                         in_blas = false;
                         if (sp == 0)
                             finished = true;
                         else
-                            e = stack[--sp];
+                            e = IGB_POP();
                     }
                     if (!finished) {
                         if (e.y > 0x00FFFFFFu) {

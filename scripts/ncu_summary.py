@@ -5,9 +5,14 @@ instruction, occupancy, registers, local-memory traffic."""
 import csv, io, subprocess, sys
 
 METRICS = [
-    "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "lts__t_bytes.sum",
+    "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "lts__t_bytes.sum", "l1tex__t_bytes.sum",
     "sm__inst_executed.sum", "smsp__thread_inst_executed_per_inst_executed.ratio",
     "sm__inst_issued.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+    "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio",
     "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
     "smsp__inst_executed_op_local_ld.sum", "smsp__inst_executed_op_local_st.sum",
     "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct",
