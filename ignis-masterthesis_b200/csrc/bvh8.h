@@ -48,7 +48,9 @@ struct Bvh8 {
 
 // boxes: n x {min xyz, max xyz}. max_leaf in 1..3 (the meta encoding holds at most 3 per leaf).
 // An empty input yields a single node with no children.
-void build_bvh8(const float* boxes, uint32_t n, uint32_t max_leaf, Bvh8& out);
+// balanced: object-median splits (binary depth <= ceil(log2 n)) instead of binned SAH -- the fallback when the SAH tree of a
+// degenerate mesh is deeper than the traversal stack allows.
+void build_bvh8(const float* boxes, uint32_t n, uint32_t max_leaf, Bvh8& out, bool balanced = false);
 
 // Dequantised box of child `slot` (for the conservative-bounds property test).
 void node8_child_box(const Node8& node, int slot, float* out_min_max6);

@@ -56,6 +56,7 @@ struct BinaryBuilder {
     std::vector<uint32_t> idx;
     std::vector<float>    cent; // 3 per primitive
     std::vector<BNode>    nodes;
+    bool                  median_only = false; // balanced object-median splits instead of binned SAH (depth fallback)
 
     struct Task { uint32_t node, begin, end; };
 
@@ -184,6 +185,25 @@ struct BinaryBuilder {
         out[t.node].count = count;
         auto leaf = [&]() { out[t.node].left = out[t.node].right = 0; };
         if (count == 1) { leaf(); return; }
+        if (median_only) {
+            // Balanced fallback (depth <= ceil(log2 n)): object median along the longest centroid axis.  Used when the SAH tree
+            // of a mesh comes out deeper than the traversal stack allows (slivers, exponentially spaced geometry).
+            int axis = 0;
+            for (int k = 1; k < 3; ++k)
+                if (cb.hi[k] - cb.lo[k] > cb.hi[axis] - cb.lo[axis]) axis = k;
+            const uint32_t half = t.begin + count / 2;
+            if (cb.hi[axis] > cb.lo[axis])
+                std::nth_element(idx.begin() + t.begin, idx.begin() + half, idx.begin() + t.end,
+                                 [&](uint32_t a, uint32_t b) { return cent[3 * (size_t)a + axis] < cent[3 * (size_t)b + axis]; });
+            const uint32_t l = (uint32_t)out.size();
+            out.emplace_back();
+            out.emplace_back();
+            out[t.node].left  = l;
+            out[t.node].right = l + 1;
+            todo.push_back(Task{ l + 1, half, t.end });
+            todo.push_back(Task{ l, t.begin, half });
+            return;
+        }
 
         float scale[3];
         bool  any_axis = false;
@@ -358,7 +378,7 @@ void node8_child_box(const Node8& node, int slot, float* o)
     }
 }
 
-void build_bvh8(const float* boxes, uint32_t n, uint32_t max_leaf, Bvh8& out)
+void build_bvh8(const float* boxes, uint32_t n, uint32_t max_leaf, Bvh8& out, bool balanced)
 {
     out.nodes.clear();
     out.prim_indices.clear();
@@ -388,6 +408,7 @@ void build_bvh8(const float* boxes, uint32_t n, uint32_t max_leaf, Bvh8& out)
         t_last = now;
     };
     BinaryBuilder bb{ boxes, opt.collapse == 1 ? 1u : max_leaf, {}, {}, {} };
+    bb.median_only = balanced || std::getenv("IGB200_BVH_BALANCED") != nullptr;
     bb.run(n, opt.threads);
     lap("binary");
     std::vector<BNode>& bn = bb.nodes;

@@ -353,6 +353,10 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
                 boxes[6 * i + 3 + k] = in_leaves[i].bbox_max[k];
             }
         build_bvh8(boxes.data(), (uint32_t)in_leaves.size(), 1, tlas);
+        if (tlas.max_depth + 9 + 4 > (uint32_t)kStackSize) { // leave room for at least a shallow mesh below it
+            tlas = Bvh8{};
+            build_bvh8(boxes.data(), (uint32_t)in_leaves.size(), 1, tlas, true);
+        }
         all_nodes = tlas.nodes;
     }
     std::vector<igb200_entity_leaf> ordered(in_leaves.size());
@@ -401,6 +405,12 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
             }
             Bvh8 blas;
             build_or_load_blas(boxes, (uint32_t)nf, blas);
+            if (tlas.max_depth + blas.max_depth + 9 > (uint32_t)kStackSize) {
+                // SAH on sorted, sliver or exponentially spaced geometry can go deeper than the traversal stack: rebuild this
+                // mesh with balanced splits (depth <= log2 n) instead of refusing the scene
+                blas = Bvh8{};
+                build_bvh8(boxes.data(), (uint32_t)nf, 3, blas, true);
+            }
             blas_depth = std::max(blas_depth, blas.max_depth);
             const uint32_t node_base = (uint32_t)all_nodes.size();
             const uint32_t tri_base  = (uint32_t)(all_tris.size() / 3);

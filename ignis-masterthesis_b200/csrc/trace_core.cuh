@@ -58,6 +58,9 @@ constexpr int      kVoteRefill  = IGB_VOTE_REFILL; // idle lanes that must wait 
 #ifndef IGB_PARK_SMEM
 #define IGB_PARK_SMEM 0 // 1: the world ray of a lane inside an instance is parked in shared memory instead of on the local-memory stack
 #endif
+#ifndef IGB_TRI_PREFETCH
+#define IGB_TRI_PREFETCH 0
+#endif
 #ifndef IGB_ENT_BOX
 #define IGB_ENT_BOX 1 // 0: skip the exact entity-box test of the leaf step (the quantised box of the TLAS node was tested already)
 #endif
@@ -84,6 +87,9 @@ constexpr int      kVoteRefill  = IGB_VOTE_REFILL; // idle lanes that must wait 
 #ifndef IGB_STACK_SMEM
 #define IGB_STACK_SMEM 0
 #endif
+#ifndef IGB_TOS_CACHE
+#define IGB_TOS_CACHE 0
+#endif
 #if IGB_STACK_SMEM
 #define IGB_STACK_AT(i) (*((i) < IGB_STACK_SMEM ? &s_stack[(i) * kBlock + threadIdx.x] : &stack[(i) - IGB_STACK_SMEM]))
 #define IGB_PUSH(v)                                             \
@@ -101,6 +107,26 @@ __device__ __forceinline__ uint2 stack_read(const uint2* s_stack, const uint2* s
 }
 #define IGB_TOP() stack_read(s_stack, stack, sp - 1, kBlock, threadIdx.x)
 #define IGB_POP() stack_read(s_stack, stack, --sp, kBlock, threadIdx.x)
+#elif IGB_TOS_CACHE
+// The top of the stack lives in two registers (`top`); memory holds entries 0 .. sp - 2.  A pop hands out the registers and
+// starts the load of the next top, which is not needed before the FOLLOWING pop: the local-memory latency (a third of the stack
+// loads miss L1) leaves the critical path.  The reference's stack does the same (src/artic/traversal/stack.art:52-123).
+#define IGB_PUSH(v)                                             \
+    do {                                                        \
+        IGB_CHECK(sp < kStackSize, "traversal stack overflow"); \
+        if (sp > 0) stack[sp - 1] = top;                        \
+        top = (v);                                              \
+        ++sp;                                                   \
+    } while (0)
+#define IGB_TOP() top
+#define IGB_POP() stack_pop(stack, top, sp)
+__device__ __forceinline__ uint2 stack_pop(const uint2* stack, uint2& top, int& sp)
+{
+    const uint2 v = top;
+    --sp;
+    if (sp > 0) top = stack[sp - 1];
+    return v;
+}
 #else
 #define IGB_PUSH(v)                                        \
     do {                                                   \
@@ -112,6 +138,9 @@ __device__ __forceinline__ uint2 stack_read(const uint2* s_stack, const uint2* s
 #endif
 #ifndef IGB_NODE_REPS
 #define IGB_NODE_REPS 1 // node steps per loop trip (lanes that can take another one do; the other phases run once per trip)
+#endif
+#if IGB_TOS_CACHE && (IGB_STACK_SMEM || IGB_NODE_REPS > 1)
+#error "IGB_TOS_CACHE excludes IGB_STACK_SMEM and IGB_NODE_REPS > 1 (the quick pop between node steps reads the stack directly)"
 #endif
 #ifndef IGB_TRI_PER_TRIP
 #define IGB_TRI_PER_TRIP 2
@@ -477,6 +506,9 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
 #else
     uint2    stack[kStackSize];
 #endif
+#if IGB_TOS_CACHE
+    uint2 top = make_uint2(0u, 0u);
+#endif
     int      sp      = 0;
     uint2    ngroup  = make_uint2(0u, 0u);
     uint2    tgroup  = make_uint2(0u, 0u);
@@ -576,6 +608,18 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
             const uint32_t hitmask = intersect_children(n0, n1, n2, n3, n4, ray, tmin, hit.t, sc.byte_bias, sc.half_bias);
             ngroup                 = make_uint2(n1.x, (hitmask & 0xFF000000u) | (n0.w >> 24));
             tgroup                 = make_uint2(n1.y, hitmask & 0x00FFFFFFu);
+#if IGB_TRI_PREFETCH
+            // The triangle phase runs a few trips later (when enough lanes wait for it) and its first use of the record stalls the
+            // whole warp; start the fetch of the first pending record now.  IGB_TRI_PREFETCH 1: into L2, 2: into L1.
+            if (in_blas && tgroup.y != 0u) {
+                const float4* tp = sc.tris + 3 * (size_t)(tgroup.x + (31u - (uint32_t)__clz(tgroup.y)));
+#if IGB_TRI_PREFETCH == 2
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(tp));
+#else
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(tp));
+#endif
+            }
+#endif
         }
 #if IGB_NODE_REPS > 1
         }
