@@ -53,6 +53,30 @@ def measured_traffic(n):
         return None
 
 
+def ncu_counters():
+    """The committed ncu capture of the dominant kernel (profiles/roofline_traffic.json): the denominators that actually bind
+    it.  The kernel's working set lives in L1 / L2, so algorithmic bytes over HBM peak (the contract's `frac`) says little;
+    issue-slot utilisation x SIMT efficiency and the L1 / L2 throughputs say where the time goes."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            t = json.load(f)
+        keys = ("kernel_ms", "issue_slot_pct", "threads_per_inst", "alu_pipe_pct", "fma_pipe_pct", "l1_bytes", "l2_bytes",
+                "l1_hit_pct", "l2_hit_pct", "local_memory_l1_bytes", "dram_bytes_read", "dram_bytes_write", "warp_insts", "source")
+        out = {k: t[k] for k in keys if k in t}
+        if "kernel_ms" in t:
+            sec = t["kernel_ms"] * 1e-3
+            out["dram_gbs"] = (t["dram_bytes_read"] + t["dram_bytes_write"]) / sec / 1e9
+            if "l2_bytes" in t:
+                out["l2_gbs"] = t["l2_bytes"] / sec / 1e9
+            if "l1_bytes" in t:
+                out["l1_gbs"] = t["l1_bytes"] / sec / 1e9
+        if "issue_slot_pct" in t and "threads_per_inst" in t:
+            out["issue_x_simt"] = t["issue_slot_pct"] / 100.0 * t["threads_per_inst"] / 32.0
+        return out
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -502,7 +526,9 @@ def run_ours(args, rank, world, local_rank):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": measured_traffic(n), "peak_kind": peak_kind, "kernel": "trace_kernel<closest>",
                          "kernel_ms": kernel_ms, "bytes_per_ray": bytes_per_ray,
-                         "per_ray": {"nodes": n_node, "tris": n_tri, "entities": n_ent}},
+                         "per_ray": {"nodes": n_node, "tris": n_tri, "entities": n_ent},
+                         "dram_frac": (measured_traffic(n) / (kernel_ms * 1e-3) / 1e9 / peak) if measured_traffic(n) else None,
+                         "ncu": ncu_counters()},
             "cpu_baseline": cpu,
         }
         if variants is not None:

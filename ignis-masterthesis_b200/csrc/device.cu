@@ -232,6 +232,16 @@ void igb200_destroy(igb200_device* dev)
     delete dev; // DeviceBuffer destructors free the allocations (Device::releaseAll, Device.cpp:948-952)
 }
 
+// Levels the traversal stack has room for (kStackSize entries; an instance entry parks 6 + up to 2 of them, hence the + 9 at the
+// call sites).  IGB200_STACK_BUDGET lowers it -- never raises it -- so that the balanced-rebuild path can be exercised on
+// ordinary geometry (tests/test_limits_gpu.py) and deep trees can be avoided on purpose.
+static uint32_t stack_budget()
+{
+    uint32_t budget = (uint32_t)igb::kStackSize;
+    if (const char* e = std::getenv("IGB200_STACK_BUDGET")) budget = std::min<uint32_t>(budget, (uint32_t)std::max(14, std::atoi(e)));
+    return budget;
+}
+
 // Disk cache of large mesh BVHs, the counterpart of setup_bvh's cache (src/runtime/shape/TriMeshProvider.cpp:329-353: meshes
 // above 500 000 faces, keyed by a content hash, one file per mesh in the cache directory).  Opt-in through the environment
 // variable IGB200_CACHE_DIR (the reference's CacheManager can be disabled likewise); a file that does not match the mesh
@@ -353,7 +363,7 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
                 boxes[6 * i + 3 + k] = in_leaves[i].bbox_max[k];
             }
         build_bvh8(boxes.data(), (uint32_t)in_leaves.size(), 1, tlas);
-        if (tlas.max_depth + 9 + 4 > (uint32_t)kStackSize) { // leave room for at least a shallow mesh below it
+        if (tlas.max_depth + 9 + 4 > stack_budget()) { // leave room for at least a shallow mesh below it
             tlas = Bvh8{};
             build_bvh8(boxes.data(), (uint32_t)in_leaves.size(), 1, tlas, true);
         }
@@ -405,7 +415,7 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
             }
             Bvh8 blas;
             build_or_load_blas(boxes, (uint32_t)nf, blas);
-            if (tlas.max_depth + blas.max_depth + 9 > (uint32_t)kStackSize) {
+            if (tlas.max_depth + blas.max_depth + 9 > stack_budget()) {
                 // SAH on sorted, sliver or exponentially spaced geometry can go deeper than the traversal stack: rebuild this
                 // mesh with balanced splits (depth <= log2 n) instead of refusing the scene
                 blas = Bvh8{};
