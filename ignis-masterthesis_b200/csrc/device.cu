@@ -503,6 +503,20 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
     dev->view.half_bias  = 0x64006400u;
     dev->view.node_count = (uint32_t)all_nodes.size();
     dev->view.tri_count  = (uint32_t)(all_tris.size() / 3);
+    {
+        // Triangle records bypass L1 allocation when the NODE array fits L1 (<= 192 KiB; a B200 SM has ~200 KB of L1) and the
+        // triangle array does not (> 256 KiB): the records then only evict nodes that would have stayed.  Measured
+        // (profiles/r02_ab_tri_stream.txt): C3 instanced (138 KB nodes, 774 KB triangles) +1.2 %, its dense variant +1.7 %; with
+        // everything large (C3-flat: 10 MB nodes) caching the records wins 1.5-2.8 % (neighbouring records share lines), and a
+        // scene that fits L1 entirely loses 41-56 % without it (C4, office).  IGB200_TRI_STREAM_BYTES overrides the triangle
+        // threshold (0 = always, huge = never), for A/Bs.
+        uint64_t limit = 256u << 10, node_limit = 192u << 10;
+        if (const char* e = std::getenv("IGB200_TRI_STREAM_BYTES")) {
+            limit      = std::strtoull(e, nullptr, 10);
+            node_limit = ~0ull;
+        }
+        dev->view.tri_stream = (all_tris.size() * sizeof(float4) > limit && all_nodes.size() * sizeof(Node8) <= node_limit) ? 1u : 0u;
+    }
     dev->node_bytes      = all_nodes.size() * sizeof(Node8);
     dev->tri_bytes       = all_tris.size() * sizeof(float4);
     dev->leaf_bytes      = ordered.size() * sizeof(igb200_entity_leaf);

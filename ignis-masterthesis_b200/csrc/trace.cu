@@ -26,10 +26,12 @@ struct ListIO {
     __device__ __forceinline__ uint32_t bin_count() const { return 0u; }
     __device__ __forceinline__ uint32_t* global_bins() const { return nullptr; }
     __device__ __forceinline__ void finalize_last_block() const {}
+#if IGB_RAY_PREFETCH
     __device__ __forceinline__ void prefetch(uint32_t first, uint32_t count, uint32_t lane) const
     {
         if (2u * lane < count) prefetch_line(rays + 2 * (size_t)(first + 2u * lane)); // 64 B = two rays per lane
     }
+#endif
     __device__ __forceinline__ bool load(uint32_t i, Vec3& org, Vec3& dir, float& tmin, float& tmax, uint32_t& flags) const
     {
         const float4 r0 = stream_load(rays + 2 * (size_t)i, true);

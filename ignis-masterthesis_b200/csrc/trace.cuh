@@ -28,6 +28,7 @@ struct DeviceScene {
     uint32_t        byte_bias;
     uint32_t        half_bias; // 0x64006400 (half2 {1024, 1024}), a parameter for the same reason
     uint32_t        node_count, tri_count; // array sizes (debug bounds checks, IGB_DEBUG_CHECKS)
+    uint32_t        tri_stream;            // != 0: triangle records bypass L1 allocation (set when the array dwarfs L1)
 };
 
 struct TraceOutputs {

@@ -238,6 +238,37 @@ __device__ __forceinline__ void stream_store(T* p, T v)
 #endif
 }
 
+// Cache policy of the BVH fetches (L1 is the contended resource: nodes, triangles, ray records and the local-memory stack
+// share it).  IGB_TRI_NOALLOC 1: triangle records bypass L1 allocation; IGB_NODE_EVICT_LAST 1: node fetches ask L1 to evict them last.
+#ifndef IGB_TRI_NOALLOC
+#define IGB_TRI_NOALLOC 0
+#endif
+#ifndef IGB_NODE_EVICT_LAST
+#define IGB_NODE_EVICT_LAST 0
+#endif
+// `stream` is DeviceScene::tri_stream, a launch-uniform flag the host sets when the triangle array is much larger than L1:
+// then a record is rarely reused by the same SM and caching it only evicts nodes and stack lines (C3: +1.2 %), whereas a small
+// triangle set lives in L1 and must be cached (C4's 80 KB scene loses 41 % without).  IGB_TRI_NOALLOC 1 forces it on.
+__device__ __forceinline__ float4 tri_load(const float4* p, bool stream)
+{
+    if (IGB_TRI_NOALLOC || stream) {
+        float4 v;
+        asm("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+        return v;
+    }
+    return __ldg(p);
+}
+__device__ __forceinline__ uint4 node_load(const uint4* p)
+{
+#if IGB_NODE_EVICT_LAST
+    uint4 v;
+    asm("ld.global.nc.L1::evict_last.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
+
 struct TravRay {
     Vec3     org, dir;    // current space (world or object); dir un-normalised in object space
     Vec3     idir;        // box-test reciprocals
@@ -602,7 +633,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
 #else
             IGB_CHECK(ngroup.x + relative_index < sc.node_count, "node index out of range");
             const uint4*   np             = sc.nodes + 5 * (size_t)(ngroup.x + relative_index);
-            const uint4    n0 = __ldg(np + 0), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+            const uint4    n0 = node_load(np + 0), n1 = node_load(np + 1), n2 = node_load(np + 2), n3 = node_load(np + 3), n4 = node_load(np + 4);
 #endif
             if (STATS) c_nodes++;
             const uint32_t hitmask = intersect_children(n0, n1, n2, n3, n4, ray, tmin, hit.t, sc.byte_bias, sc.half_bias);
@@ -657,7 +688,7 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                     tgroup.y &= ~(1u << idx);
                     IGB_CHECK(tgroup.x + idx < sc.tri_count, "triangle index out of range");
                     const float4* tp = sc.tris + 3 * (size_t)(tgroup.x + idx);
-                    const float4  a = __ldg(tp + 0), b = __ldg(tp + 1), c = __ldg(tp + 2);
+                    const float4  a = tri_load(tp + 0, sc.tri_stream != 0u), b = tri_load(tp + 1, sc.tri_stream != 0u), c = tri_load(tp + 2, sc.tri_stream != 0u);
                     if (STATS) c_tris++;
                     intersect_triangle(a, b, c, ray, tmin, cur_ent, hit);
                     if (ANY_HIT && hit.prim >= 0) break;

@@ -56,10 +56,12 @@ struct PrimaryIO {
     __device__ __forceinline__ uint32_t  count() const { return ctl->n_cur; }
     __device__ __forceinline__ uint32_t  bin_count() const { return n_bins; }
     __device__ __forceinline__ uint32_t* global_bins() const { return ctl->bins; }
+#if IGB_RAY_PREFETCH
     __device__ __forceinline__ void prefetch(uint32_t first, uint32_t count, uint32_t lane) const
     {
         for (uint32_t k = lane; k < count; k += 32u) prefetch_line(s.rec + kRecVec * (size_t)(first + k)); // the ray sector of each record
     }
+#endif
     __device__ __forceinline__ bool load(uint32_t i, Vec3& org, Vec3& dir, float& tmin, float& tmax, uint32_t& flags) const
     {
         const float4* r = s.rec + kRecVec * (size_t)i;
@@ -118,6 +120,7 @@ struct ShadowIO {
     __device__ __forceinline__ uint32_t  bin_count() const { return 0u; }
     __device__ __forceinline__ uint32_t* global_bins() const { return nullptr; }
     __device__ __forceinline__ void      finalize_last_block() const {}
+#if IGB_RAY_PREFETCH
     __device__ __forceinline__ void prefetch(uint32_t first, uint32_t count, uint32_t lane) const
     {
         if (2u * lane < count) { // 32 B = two rays per lane and column
@@ -125,6 +128,7 @@ struct ShadowIO {
             prefetch_line(s.dir_tmax + first + 2u * lane);
         }
     }
+#endif
     __device__ __forceinline__ bool load(uint32_t i, Vec3& org, Vec3& dir, float& tmin, float& tmax, uint32_t& flags) const
     {
         const float4 o = stream_load(s.org_tmin + i, false), d = stream_load(s.dir_tmax + i, false);
