@@ -1288,7 +1288,8 @@ static void loadDocumentImpl(const Value& scene, const std::string& base, SceneF
         return Vec3f{ (float)(d[0] / n), (float)(d[1] / n), (float)(d[2] / n) };
     };
     for (const Value& l : lights) {
-        const std::string ty = l.str("type", "");
+        std::string ty = l.str("type", "");
+        if (ty.rfind("cie_", 0) == 0) ty = "cie" + ty.substr(4); // both spellings are registered (LoaderLight.cpp:90-97)
         if (ty == "point") { // PointLight.cpp:16-49
             Vec3f c;
             if (l.has("power")) {

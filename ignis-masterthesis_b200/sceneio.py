@@ -1091,6 +1091,8 @@ def load_scene(scene, base=".", width=None, height=None):
     SR = np.float32(4 * math.pi)
     for l in lights:
         ty = l["type"]
+        if ty.startswith("cie_"):  # both spellings are registered (LoaderLight.cpp:90-97)
+            ty = "cie" + ty[4:]
         if ty == "point":
             c = _color(l.get("power"), 4 * math.pi) / SR if "power" in l else _color(l.get("intensity"), 1.0)
             sh.add_point_light(l.get("position", (0, 0, 0)), c)
