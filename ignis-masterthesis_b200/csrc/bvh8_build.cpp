@@ -310,17 +310,140 @@ struct BinaryBuilder {
     }
 };
 
+// ---- Reinsertion optimisation of the binary tree (Bittner, Hapala, Havran, "Fast Insertion-Based Optimization of Bounding
+// Volume Hierarchies", CGF 2013; the reference runs madmann91/bvh's parallel variant of it after its SBVH build,
+// src/runtime/bvh/TriBVHAdapter.h:163-202).  One pass: every non-root node whose parent is not the root, in order of decreasing
+// surface area, is detached (its sibling takes the parent's place) and re-attached where the induced increase of the tree's
+// surface-area sum is smallest -- a best-first search bounded by the best position found so far.  The original position is
+// among the candidates, so a reinsertion never makes the sum larger.  Serial; meant for per-mesh trees, not for million-node ones.
+#ifndef IGB_BVH_REINSERT_DEFAULT
+#define IGB_BVH_REINSERT_DEFAULT 0
+#endif
+static void reinsertion_pass(std::vector<BNode>& bn, std::vector<uint32_t>& idx, int passes)
+{
+    const uint32_t n = (uint32_t)bn.size();
+    if (n < 8 || passes <= 0) return;
+    std::vector<uint32_t> parent(n, 0);
+    {
+        std::vector<uint32_t> st{ 0 };
+        while (!st.empty()) {
+            const uint32_t i = st.back();
+            st.pop_back();
+            if (!bn[i].leaf()) {
+                parent[bn[i].left] = parent[bn[i].right] = i;
+                st.push_back(bn[i].left);
+                st.push_back(bn[i].right);
+            }
+        }
+    }
+    auto merged_area = [](const Aabb& a, const Aabb& b) {
+        Aabb m = a;
+        m.grow(b);
+        return m.area();
+    };
+    auto refit_up = [&](uint32_t i) { // boxes and primitive counts from i to the root
+        for (;;) {
+            BNode& b = bn[i];
+            b.box    = bn[b.left].box;
+            b.box.grow(bn[b.right].box);
+            b.count = bn[b.left].count + bn[b.right].count;
+            if (i == 0) break;
+            i = parent[i];
+        }
+    };
+    struct Cand { float induced; uint32_t node; };
+    auto worse = [](const Cand& a, const Cand& b) { return a.induced > b.induced; };
+    std::vector<Cand> heap;
+    for (int pass = 0; pass < passes; ++pass) {
+        std::vector<uint32_t> order;
+        order.reserve(n);
+        for (uint32_t i = 1; i < n; ++i)
+            if (parent[i] != 0) order.push_back(i);
+        std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return bn[a].box.area() > bn[b].box.area(); });
+        for (uint32_t l : order) {
+            const uint32_t p = parent[l];
+            if (p == 0) continue; // moved under the root by an earlier reinsertion of this pass
+            const uint32_t g = parent[p];
+            const uint32_t s = bn[p].left == l ? bn[p].right : bn[p].left;
+            // detach l: s takes p's place under g
+            (bn[g].left == p ? bn[g].left : bn[g].right) = s;
+            parent[s]                                     = g;
+            refit_up(g);
+            // best-first search for the cheapest position
+            const Aabb  lb    = bn[l].box;
+            const float la    = lb.area();
+            float       best  = FLT_MAX;
+            uint32_t    where = s;
+            heap.clear();
+            heap.push_back(Cand{ 0.0f, 0u });
+            while (!heap.empty()) {
+                std::pop_heap(heap.begin(), heap.end(), worse);
+                const Cand c = heap.back();
+                heap.pop_back();
+                if (c.induced + la >= best) break; // every remaining candidate is at least this expensive
+                const float direct = merged_area(bn[c.node].box, lb);
+                const float total  = c.induced + direct;
+                if (c.node != 0 && total < best) {
+                    best  = total;
+                    where = c.node;
+                }
+                const float child_induced = total - bn[c.node].box.area();
+                if (!bn[c.node].leaf() && child_induced + la < best) {
+                    heap.push_back(Cand{ child_induced, bn[c.node].left });
+                    std::push_heap(heap.begin(), heap.end(), worse);
+                    heap.push_back(Cand{ child_induced, bn[c.node].right });
+                    std::push_heap(heap.begin(), heap.end(), worse);
+                }
+            }
+            // attach: p becomes the parent of (where, l) in where's place
+            const uint32_t q = parent[where];
+            (bn[q].left == where ? bn[q].left : bn[q].right) = p;
+            parent[p]     = q;
+            bn[p].left    = where;
+            bn[p].right   = l;
+            parent[where] = p;
+            parent[l]     = p;
+            refit_up(p);
+        }
+    }
+    // the primitive ranges of subtrees are no longer contiguous in `idx`: relinearise in depth-first order
+    std::vector<uint32_t> fresh;
+    fresh.reserve(idx.size());
+    struct Frame { uint32_t node; bool done; };
+    std::vector<Frame> st{ Frame{ 0, false } };
+    while (!st.empty()) {
+        Frame f = st.back();
+        st.pop_back();
+        BNode& b = bn[f.node];
+        if (b.leaf()) {
+            const uint32_t first = (uint32_t)fresh.size();
+            for (uint32_t k = 0; k < b.count; ++k) fresh.push_back(idx[b.first + k]);
+            b.first = first;
+        } else if (!f.done) {
+            st.push_back(Frame{ f.node, true });
+            st.push_back(Frame{ b.right, false });
+            st.push_back(Frame{ b.left, false });
+        } else {
+            b.first = bn[b.left].first;
+            b.count = bn[b.left].count + bn[b.right].count;
+        }
+    }
+    idx.swap(fresh);
+}
+
 // Build switches (environment, read per build so that one binary serves the A/Bs of DESIGN.md):
 //   IGB200_BVH_COLLAPSE = dp (default) | greedy      IGB200_BVH_CNODE / IGB200_BVH_CPRIM = SAH constants of the DP
 //   IGB200_BVH_THREADS  = worker threads of the binary build (default: hardware concurrency, at most 16)
-struct BuildOptions { int collapse; float c_node, c_prim; unsigned threads; };
+//   IGB200_BVH_REINSERT = passes of the reinsertion optimisation over the binary tree (0 = off)
+struct BuildOptions { int collapse; float c_node, c_prim; unsigned threads; int reinsert; };
 BuildOptions build_options()
 {
-    BuildOptions o{ 1, 1.0f, 0.7f, std::min(16u, std::max(1u, std::thread::hardware_concurrency())) };
+    BuildOptions o{ 1, 1.0f, 0.7f, std::min(16u, std::max(1u, std::thread::hardware_concurrency())), IGB_BVH_REINSERT_DEFAULT };
     if (const char* e = std::getenv("IGB200_BVH_COLLAPSE")) o.collapse = std::strcmp(e, "greedy") == 0 ? 0 : 1;
     if (const char* e = std::getenv("IGB200_BVH_CNODE")) o.c_node = (float)std::atof(e);
     if (const char* e = std::getenv("IGB200_BVH_CPRIM")) o.c_prim = (float)std::atof(e);
     if (const char* e = std::getenv("IGB200_BVH_THREADS")) o.threads = (unsigned)std::max(1, std::atoi(e));
+    if (const char* e = std::getenv("IGB200_BVH_REINSERT")) o.reinsert = std::max(0, std::atoi(e));
     return o;
 }
 
@@ -412,6 +535,10 @@ void build_bvh8(const float* boxes, uint32_t n, uint32_t max_leaf, Bvh8& out, bo
     bb.run(n, opt.threads);
     lap("binary");
     std::vector<BNode>& bn = bb.nodes;
+    if (opt.reinsert > 0 && !bb.median_only && n <= (1u << 18)) { // per-mesh trees; a serial pass over millions of nodes takes seconds
+        reinsertion_pass(bn, bb.idx, opt.reinsert);
+        lap("reinsert");
+    }
 
     // ---- SAH-optimal collapse to 8-wide nodes by dynamic programming over the binary tree (the formulation of Ylitie,
     // Karras, Laine, "Efficient Incoherent Ray Traversal on GPUs Through Compressed Wide BVHs", HPG 2017, section 4.1; the
