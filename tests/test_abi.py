@@ -106,3 +106,32 @@ def test_bvh8_dp_collapse_lowers_the_sah_cost(ig, monkeypatch):
         assert ig._lib.load().igb200_debug_bvh8_quality(boxes.ctypes.data, boxes.shape[0], 3, out.ctypes.data) == 0
         cost[collapse] = 1.0 * out[0] + 0.7 * out[1]     # c_node = 1, c_prim = 0.7: the DP default constants
     assert cost["dp"] <= cost["greedy"] * 1.0001, cost
+
+
+def test_bvh8_reinsertion_pass_keeps_the_invariants_and_does_not_raise_the_cost(ig, monkeypatch):
+    """IGB200_BVH_REINSERT: the reinsertion optimisation of the binary tree (Bittner et al. 2013; the reference runs madmann91's after
+    its SBVH build, TriBVHAdapter.h:163-202).  Topology changes, so: every primitive still exactly once, boxes conservative, and the
+    SAH cost of the collapsed tree not above the plain build's (random boxes: clearly below)."""
+    rng = np.random.default_rng(7)
+    n = 6000
+    c = rng.uniform(-50, 50, (n, 3)) * rng.choice([0.05, 1.0], (n, 1))   # a dense cluster inside a sparse cloud
+    h = rng.uniform(0.01, 1.5, (n, 3))
+    boxes = np.ascontiguousarray(np.concatenate([c - h, c + h], axis=1), np.float32)
+    v, f, _ = ig.workloads.uv_sphere(64, 128)
+    tri = v[f]
+    sphere = np.ascontiguousarray(np.concatenate([tri.min(axis=1), tri.max(axis=1)], axis=1), np.float32)
+    lib = ig._lib.load()
+    for name, b, slack in (("random", boxes, 0.99), ("sphere", sphere, 1.0001)):
+        cost = {}
+        for passes in ("0", "2"):
+            monkeypatch.setenv("IGB200_BVH_REINSERT", passes)
+            rc, st = _check(ig, b)
+            assert rc == 0 and st["violations"] == 0 and st["missing"] == 0, (name, passes, st)
+            out = np.zeros(4, np.float64)
+            assert lib.igb200_debug_bvh8_quality(b.ctypes.data, b.shape[0], 3, out.ctypes.data) == 0
+            cost[passes] = out[0] + 0.7 * out[1]
+        assert cost["2"] <= cost["0"] * slack, (name, cost)
+    for k in (1, 2, 3, 7, 8, 9):   # below and at the pass's minimum size
+        monkeypatch.setenv("IGB200_BVH_REINSERT", "3")
+        rc, st = _check(ig, boxes[:k])
+        assert rc == 0 and st["missing"] == 0, (k, st)
