@@ -562,6 +562,9 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
     nx.flags          = (uint16_t)(kRayBounce | ((uint32_t)(depth + 1) << 8));
 }
 
+#ifndef IGB_SHADE_PREFETCH
+#define IGB_SHADE_PREFETCH 0
+#endif
 #ifndef IGB_SHADE_MIN_BLOCKS
 #define IGB_SHADE_MIN_BLOCKS 6 // 85 registers, 80 B of spills: +2 % over 4 blocks (112 registers) on B200
 #endif
@@ -578,6 +581,16 @@ __global__ void __launch_bounds__(128, IGB_SHADE_MIN_BLOCKS) shade_kernel(WaveCo
     const uint32_t step    = gridDim.x * blockDim.x;
     for (uint32_t p0 = blockIdx.x * blockDim.x; p0 < n; p0 += step) { // block-uniform trip count
         const uint32_t p = p0 + threadIdx.x;
+#if IGB_SHADE_PREFETCH
+        // the record gather through the sorted index is a random 96-byte read: start the next trip's now (three 32-byte sectors)
+        if (p + step < n) {
+            const uint32_t nxi = sorted ? __ldg(sorted + p + step) : p + step;
+            const float4*  nr  = cur.rec + kRecVec * (size_t)nxi;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(nr));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(nr + 2));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(nr + 4));
+        }
+#endif
         bool        alive = false, has_shadow = false;
         NextState   nx;
         ShadowState sh;
