@@ -83,6 +83,7 @@ struct igb200_device {
     int          sm_count = 0;
     static constexpr int      kPipe      = 3;         // streams of the host-buffer pipeline
     uint64_t                 chunk_rays = 1u << 20;   // rays per bulk chunk of the host-buffer pipeline (32 MiB up, 20 MiB down)
+    int                      pipe_sms   = 0;          // SMs the pipeline's traversal launches occupy (0 = all; IGB200_PIPE_SMS)
     uint64_t                 chunk_min  = 1u << 18;   // first / last chunk of the ramp (IGB200_TRACE_CHUNK / _MIN override both)
     cudaStream_t             pipe[kPipe] = {};
     std::vector<cudaEvent_t> chunk_events;
@@ -201,6 +202,8 @@ int igb200_create(const igb200_setup* setup, igb200_device** out)
     }
     if (const char* e = std::getenv("IGB200_TRACE_CHUNK")) // experiment switch: rays per chunk of the host-buffer pipeline
         dev->chunk_rays = std::max<uint64_t>(1u << 12, std::min<uint64_t>(1u << 26, std::strtoull(e, nullptr, 10)));
+    if (const char* e = std::getenv("IGB200_PIPE_SMS")) // experiment switch: grid of the pipeline's launches = this many SMs x 8 CTAs
+        dev->pipe_sms = std::atoi(e) > 0 ? std::min(dev->sm_count, std::atoi(e)) : 0;
     if (const char* e = std::getenv("IGB200_TRACE_CHUNK_MIN"))
         dev->chunk_min = std::max<uint64_t>(1u << 12, std::min<uint64_t>(1u << 26, std::strtoull(e, nullptr, 10)));
     *out = dev;
@@ -608,34 +611,67 @@ int igb200_trace_rays(igb200_device* dev, const igb200_ray* rays, uint64_t n, ui
         }
     }
     const uint64_t nchunks = sizes.size();
-    if (dev->chunk_events.size() < 3 * nchunks) {
+    // IGB200_PIPE_TIMELINE=1 (diagnostic): two more events per chunk and one at the start; the per-chunk times of upload end,
+    // traversal start / end and download end go to stderr after the call
+    static const bool timeline = std::getenv("IGB200_PIPE_TIMELINE") != nullptr;
+    const size_t      n_events = 3 * nchunks + (timeline ? nchunks + 1 : 0);
+    if (dev->chunk_events.size() < n_events) {
         const size_t old = dev->chunk_events.size();
-        dev->chunk_events.resize(3 * nchunks, nullptr);
+        dev->chunk_events.resize(n_events, nullptr);
         for (size_t i = old; i < dev->chunk_events.size(); ++i) IGB_CUDA(cudaEventCreate(&dev->chunk_events[i]));
     }
     cudaStream_t s_up = dev->pipe[0], s_trace = dev->pipe[1], s_down = dev->pipe[2];
     uint64_t     off  = 0;
-    for (uint64_t c = 0; c < nchunks; off += sizes[c], ++c) {
+    if (timeline) IGB_CUDA(cudaEventRecord(dev->chunk_events[4 * nchunks], s_up));
+    // Download schedule: the hit columns of chunk c-1 are queued behind BOTH its traversal and the upload of chunk c, so that a
+    // download starts at an upload boundary.  Measured (scripts/pcie_chunk_probe.py, profiles/r02_ab_e2e_aligned_download.txt):
+    // a download that starts in the middle of an upload costs the pair ~7 % of the link: 16 Mi rays end to end 1460 -> 1530 Mrays/s.
+    // Exempting the ramp-down chunks changes nothing.  IGB200_PIPE_ALIGN=0 restores the round-1 schedule (download right behind
+    // the traversal).
+    static const bool align = [] { const char* e = std::getenv("IGB200_PIPE_ALIGN"); return !e || std::atoi(e) != 0; }();
+    auto deferred = [&](uint64_t c) { return align && c + 1 < nchunks; }; // all but the last chunk
+    auto download = [&](uint64_t c, uint64_t at, cudaEvent_t boundary) -> cudaError_t {
+        const uint64_t m = sizes[c];
+        cudaError_t    e = cudaStreamWaitEvent(s_down, dev->chunk_events[3 * c + 1], 0);
+        if (e == cudaSuccess && boundary) e = cudaStreamWaitEvent(s_down, boundary, 0);
+        if (e == cudaSuccess && ent_id) e = cudaMemcpyAsync(ent_id + at, dev->d_ent.ptr + at, m * 4, cudaMemcpyDeviceToHost, s_down);
+        if (e == cudaSuccess && prim_id) e = cudaMemcpyAsync(prim_id + at, dev->d_prim.ptr + at, m * 4, cudaMemcpyDeviceToHost, s_down);
+        if (e == cudaSuccess && t) e = cudaMemcpyAsync(t + at, dev->d_t.ptr + at, m * 4, cudaMemcpyDeviceToHost, s_down);
+        if (e == cudaSuccess && u) e = cudaMemcpyAsync(u + at, dev->d_u.ptr + at, m * 4, cudaMemcpyDeviceToHost, s_down);
+        if (e == cudaSuccess && v) e = cudaMemcpyAsync(v + at, dev->d_v.ptr + at, m * 4, cudaMemcpyDeviceToHost, s_down);
+        if (e == cudaSuccess && timeline) e = cudaEventRecord(dev->chunk_events[3 * nchunks + c], s_down);
+        return e;
+    };
+    uint64_t prev_off = 0;
+    for (uint64_t c = 0; c < nchunks; prev_off = off, off += sizes[c], ++c) {
         const uint64_t m  = sizes[c];
         float4*        dr = dev->d_rays.ptr + 2 * off;
         IGB_CUDA(cudaMemcpyAsync(dr, rays + off, m * sizeof(igb200_ray), cudaMemcpyHostToDevice, s_up));
         IGB_CUDA(cudaEventRecord(dev->chunk_events[3 * c + 2], s_up));
+        if (c > 0 && deferred(c - 1)) IGB_CUDA(download(c - 1, prev_off, dev->chunk_events[3 * c + 2]));
         IGB_CUDA(cudaStreamWaitEvent(s_trace, dev->chunk_events[3 * c + 2], 0));
         const igb::TraceOutputs out{ ent_id ? dev->d_ent.ptr + off : nullptr, prim_id ? dev->d_prim.ptr + off : nullptr,
                                      t ? dev->d_t.ptr + off : nullptr, u ? dev->d_u.ptr + off : nullptr,
                                      v ? dev->d_v.ptr + off : nullptr };
         IGB_CUDA(cudaEventRecord(dev->chunk_events[3 * c], s_trace));
         // Interface::loadRayList's direction normalisation (Device.cpp:588-592) happens in the kernel's ray load
-        IGB_CUDA(igb::launch_trace(dev->view, dr, m, ray_flags, any_hit, out, counters, dev->d_work.ptr, dev->sm_count, s_trace, true));
+        IGB_CUDA(igb::launch_trace(dev->view, dr, m, ray_flags, any_hit, out, counters, dev->d_work.ptr,
+                                   dev->pipe_sms ? dev->pipe_sms : dev->sm_count, s_trace, true));
         IGB_CUDA(cudaEventRecord(dev->chunk_events[3 * c + 1], s_trace));
-        IGB_CUDA(cudaStreamWaitEvent(s_down, dev->chunk_events[3 * c + 1], 0));
-        if (ent_id) IGB_CUDA(cudaMemcpyAsync(ent_id + off, out.ent_id, m * 4, cudaMemcpyDeviceToHost, s_down));
-        if (prim_id) IGB_CUDA(cudaMemcpyAsync(prim_id + off, out.prim_id, m * 4, cudaMemcpyDeviceToHost, s_down));
-        if (t) IGB_CUDA(cudaMemcpyAsync(t + off, out.t, m * 4, cudaMemcpyDeviceToHost, s_down));
-        if (u) IGB_CUDA(cudaMemcpyAsync(u + off, out.u, m * 4, cudaMemcpyDeviceToHost, s_down));
-        if (v) IGB_CUDA(cudaMemcpyAsync(v + off, out.v, m * 4, cudaMemcpyDeviceToHost, s_down));
+        if (!deferred(c)) IGB_CUDA(download(c, off, nullptr));
     }
     for (int k = 0; k < igb200_device::kPipe; ++k) IGB_CUDA(cudaStreamSynchronize(dev->pipe[k]));
+    if (timeline) {
+        std::fprintf(stderr, "# igb200_trace_rays timeline, ms since the first upload was queued: chunk rays up_end trace_start trace_end down_end\n");
+        for (uint64_t c = 0; c < nchunks; ++c) {
+            float a = 0, b = 0, d = 0, e = 0;
+            cudaEventElapsedTime(&a, dev->chunk_events[4 * nchunks], dev->chunk_events[3 * c + 2]);
+            cudaEventElapsedTime(&b, dev->chunk_events[4 * nchunks], dev->chunk_events[3 * c]);
+            cudaEventElapsedTime(&d, dev->chunk_events[4 * nchunks], dev->chunk_events[3 * c + 1]);
+            cudaEventElapsedTime(&e, dev->chunk_events[4 * nchunks], dev->chunk_events[3 * nchunks + c]);
+            std::fprintf(stderr, "%3llu %8llu %7.3f %7.3f %7.3f %7.3f\n", (unsigned long long)c, (unsigned long long)sizes[c], a, b, d, e);
+        }
+    }
 
     dev->last_stats      = igb200_trace_stats{};
     dev->last_stats.rays = n;
