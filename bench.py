@@ -223,12 +223,16 @@ def bench_path_tracer(pkg, local_rank, rank, world, total_iterations, warmup, wo
     e2e_s = time.perf_counter() - t0
     film_mean = float(host_film.mean() / max(1, n_total)) if rank == 0 else 0.0
     stats = torch.tensor([total_s, e2e_s, float(rays), float(ms_iter), float(launches), float(reduce_ms)], device="cuda", dtype=torch.float64)
+    reduce_ms_min = reduce_ms
     if world > 1:
         mx = stats.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = stats.clone()
         dist.all_reduce(sm, op=dist.ReduceOp.SUM)
         total_s, e2e_s, rays, launches, reduce_ms, ms_iter = float(mx[0]), float(mx[1]), float(sm[2]), float(sm[4]), float(mx[5]), float(mx[3])
+        mn = stats.clone()  # the rank that arrives last does not wait for anybody: its time is the collective itself
+        dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+        reduce_ms_min = float(mn[5])
     samples = float(spi) * w * h * total_iterations
     first, count, tr, tc = pkg.partition_share(total_iterations, rank, world, mode)
     out = {
@@ -236,7 +240,7 @@ def bench_path_tracer(pkg, local_rank, rank, world, total_iterations, warmup, wo
         "max_depth": int(sh.technique.max_depth), "metric": "path-traced samples/s", "unit": "Msamples/s",
         "value": samples / total_s / 1e6, "e2e_value": samples / e2e_s / 1e6,
         "device_ms_max_rank": ms_iter, "mrays_per_s": rays / total_s / 1e6,
-        "rays_per_sample": rays / samples, "film_reduce_ms": reduce_ms,
+        "rays_per_sample": rays / samples, "film_reduce_ms": reduce_ms, "film_reduce_ms_min_rank": reduce_ms_min,
         "film_reduce_wire_ms_at_450GBs": (w * h * 3 * 4) / 450e9 * 1e3 if world > 1 else 0.0,
         "d2h_bytes": w * h * 3 * 4, "partition": "tile rows" if tc > 1 else "iteration blocks",
         "api": "igb200_comm_render + igb200_comm_reduce_film" if world > 1 else "igb200_render_iterations",
