@@ -83,6 +83,7 @@ struct igb200_device {
     int          sm_count = 0;
     static constexpr int      kPipe      = 3;         // streams of the host-buffer pipeline
     uint64_t                 chunk_rays = 1u << 20;   // rays per bulk chunk of the host-buffer pipeline (32 MiB up, 20 MiB down)
+    bool                     pipe_align = true;       // downloads start at upload boundaries (IGB200_PIPE_ALIGN=0: right behind the traversal)
     int                      pipe_sms   = 0;          // SMs the pipeline's traversal launches occupy (0 = all; IGB200_PIPE_SMS)
     uint64_t                 chunk_min  = 1u << 18;   // first / last chunk of the ramp (IGB200_TRACE_CHUNK / _MIN override both)
     cudaStream_t             pipe[kPipe] = {};
@@ -202,6 +203,7 @@ int igb200_create(const igb200_setup* setup, igb200_device** out)
     }
     if (const char* e = std::getenv("IGB200_TRACE_CHUNK")) // experiment switch: rays per chunk of the host-buffer pipeline
         dev->chunk_rays = std::max<uint64_t>(1u << 12, std::min<uint64_t>(1u << 26, std::strtoull(e, nullptr, 10)));
+    if (const char* e = std::getenv("IGB200_PIPE_ALIGN")) dev->pipe_align = std::atoi(e) != 0;
     if (const char* e = std::getenv("IGB200_PIPE_SMS")) // experiment switch: grid of the pipeline's launches = this many SMs x 8 CTAs
         dev->pipe_sms = std::atoi(e) > 0 ? std::min(dev->sm_count, std::atoi(e)) : 0;
     if (const char* e = std::getenv("IGB200_TRACE_CHUNK_MIN"))
@@ -628,8 +630,7 @@ int igb200_trace_rays(igb200_device* dev, const igb200_ray* rays, uint64_t n, ui
     // a download that starts in the middle of an upload costs the pair ~7 % of the link: 16 Mi rays end to end 1460 -> 1530 Mrays/s.
     // Exempting the ramp-down chunks changes nothing.  IGB200_PIPE_ALIGN=0 restores the round-1 schedule (download right behind
     // the traversal).
-    static const bool align = [] { const char* e = std::getenv("IGB200_PIPE_ALIGN"); return !e || std::atoi(e) != 0; }();
-    auto deferred = [&](uint64_t c) { return align && c + 1 < nchunks; }; // all but the last chunk
+    auto deferred = [&](uint64_t c) { return dev->pipe_align && c + 1 < nchunks; }; // all but the last chunk
     auto download = [&](uint64_t c, uint64_t at, cudaEvent_t boundary) -> cudaError_t {
         const uint64_t m = sizes[c];
         cudaError_t    e = cudaStreamWaitEvent(s_down, dev->chunk_events[3 * c + 1], 0);

@@ -227,6 +227,31 @@ def test_edge_cases_empty_and_ragged(ig, oracle, dev):
     assert np.all(ent == -1) and np.all(prim == -1) and np.all(t == FLT_MAX)
 
 
+def test_chunked_pipeline_schedules_agree(ig, dev, monkeypatch):
+    """igb200_trace_rays with many small chunks and a ramp (IGB200_TRACE_CHUNK / _MIN), with downloads queued at upload
+    boundaries (default) and right behind the traversal (IGB200_PIPE_ALIGN=0), a column subset, a ragged ray count:
+    all identical to the one-chunk call."""
+    tables = ig.workloads.c3_scene(grid=2, stacks=16, slices=32)
+    rays = ig.workloads.c3_rays(tables, n=300_001, seed=0x51)
+    dev.assign_scene(tables)
+    want = dev.trace(rays)  # default chunk size: one chunk
+    assert int((want[1] >= 0).sum()) > 1000
+    monkeypatch.setenv("IGB200_TRACE_CHUNK", "16384")
+    monkeypatch.setenv("IGB200_TRACE_CHUNK_MIN", "4096")
+    for align in ("1", "0"):
+        monkeypatch.setenv("IGB200_PIPE_ALIGN", align)
+        with ig.Device(0) as d:
+            d.assign_scene(tables)
+            for n in (rays.size, 40_000, 4097):
+                got = d.trace(rays[:n])
+                for g, w in zip(got, want):
+                    assert np.array_equal(g, w[:n]), (align, n)
+            ent = np.full(rays.size, 7, np.int32)
+            t = np.full(rays.size, 7, np.float32)
+            d.trace_into(rays, ent, None, t, None, None)  # only two of the five columns
+            assert np.array_equal(ent, want[0]) and np.array_equal(t, want[2])
+
+
 def test_trace_before_scene_is_an_error(ig):
     with ig.Device(0) as d:
         with pytest.raises(ig._lib.BackendError) as e:
