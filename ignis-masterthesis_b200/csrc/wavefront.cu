@@ -568,6 +568,11 @@ __device__ __forceinline__ void shade_one(const ShadeScene& sc, const DeviceScen
 #ifndef IGB_SHADE_MIN_BLOCKS
 #define IGB_SHADE_MIN_BLOCKS 6 // 85 registers, 80 B of spills: +2 % over 4 blocks (112 registers) on B200
 #endif
+// Blocks of the grid-stride launch per SM.  Exactly the resident wave: with 16 per SM (2.67 waves of 6) the last partial wave
+// cost 2-3 % on all three path-tracer workloads (profiles/r02_ab_shade_grid.txt: 6 / 12 / 16 / 18 / 24 per SM).
+#ifndef IGB_SHADE_GRID_PER_SM
+#define IGB_SHADE_GRID_PER_SM IGB_SHADE_MIN_BLOCKS
+#endif
 template <bool EXT, bool IB>
 __global__ void __launch_bounds__(128, IGB_SHADE_MIN_BLOCKS) shade_kernel(WaveControl* __restrict__ ctl, const PathStream cur, const PathStream nxt,
                                                     const ShadowStream shq, const uint32_t* __restrict__ sorted, const ShadeScene sc,
@@ -662,9 +667,9 @@ cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene&
 #define SHADE_LAUNCH(EXT)                                                                                                           \
     do {                                                                                                                            \
         if (sh.tech.type == IGB200_TECH_INFOBUFFER)                                                                                 \
-            shade_kernel<EXT, true><<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene); \
+            shade_kernel<EXT, true><<<sm_count * IGB_SHADE_GRID_PER_SM, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene); \
         else                                                                                                                        \
-            shade_kernel<EXT, false><<<wide * 2, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene); \
+            shade_kernel<EXT, false><<<sm_count * IGB_SHADE_GRID_PER_SM, 128, 0, stream>>>(buf.ctl, cur, nxt, buf.shadow, sort ? buf.sorted : nullptr, sh, scene); \
     } while (0)
     if (sh.extended)
         SHADE_LAUNCH(true);
