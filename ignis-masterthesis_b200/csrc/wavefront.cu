@@ -210,7 +210,13 @@ __global__ void reset_kernel(WaveControl* ctl, const WaveSettings set, uint32_t 
 // K1, gpu_generate_rays (driver/mapping_gpu.art:618-667) with make_camera_emitter / make_list_emitter
 // (driver/emitter.art:6-31), make_perspective_camera (camera/perspective.art:29-41), make_uniform_pixel_sampler
 // (sampler/pixel_sampler.art:4-10) and init_pt_raypayload (technique/pathtracer.art:33-38).
-__global__ void __launch_bounds__(256) generate_kernel(const WaveControl* __restrict__ ctl, const PathStream s, const ShadeScene sc)
+#ifndef IGB_GEN_MIN_BLOCKS
+#define IGB_GEN_MIN_BLOCKS 1
+#endif
+#ifndef IGB_GEN_GRID_PER_SM
+#define IGB_GEN_GRID_PER_SM 8
+#endif
+__global__ void __launch_bounds__(256, IGB_GEN_MIN_BLOCKS) generate_kernel(const WaveControl* __restrict__ ctl, const PathStream s, const ShadeScene sc)
 {
     const WaveSettings set = ctl->set;
     const uint32_t count = ctl->gen_count, base = ctl->gen_base, first = ctl->gen_first;
@@ -656,7 +662,7 @@ cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene&
     IGB_EV(0);
     begin_round_kernel<<<1, 256, 0, stream>>>(buf.ctl, n_bins, buf.host_done);
     IGB_EV(1);
-    generate_kernel<<<wide, 256, 0, stream>>>(buf.ctl, cur, sh);
+    generate_kernel<<<sm_count * IGB_GEN_GRID_PER_SM, 256, 0, stream>>>(buf.ctl, cur, sh);
     IGB_EV(2);
     const PrimaryIO pio{ cur, buf.keys, buf.ent_mat, buf.ctl, n_bins };
     trace_kernel<PrimaryIO, false, false><<<sm_count * kBlocksPerSM, kBlock, 0, stream>>>(scene, pio, nullptr, buf.ctl->work_primary);
