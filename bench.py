@@ -199,8 +199,12 @@ def bench_path_tracer(pkg, local_rank, rank, world, total_iterations, warmup, wo
     dev.resize(w, h)
     comm = product_comm(pkg, dev, rank, world) if world > 1 else None
     mode = pkg.device.PARTITION_AUTO if mode is None else mode
+    # warm-up in the shape of the timed call: enough iterations per call for the library to size its wavefront streams as the
+    # timed request will (they grow on demand up to 32 Mi rays; growing re-allocates and re-captures the round graph)
+    share = max(1, total_iterations // world)
+    warm_iters = max(1, min(share, -(-(1 << 25) // (w * h * spi))))
     for it in range(warmup):
-        dev.render(w, h, spi=spi, iteration=1_000_000 + it)
+        dev.render(w, h, spi=spi, iteration=1_000_000 + it * warm_iters, iterations=warm_iters)
     if comm is not None:  # warm the communicator on a film-sized buffer outside the timed region (first-use cost)
         comm.reduce_film(warmup, root=0, mode=pkg.device.PARTITION_ITERATIONS, warm=True)
     dev.clear_framebuffer()

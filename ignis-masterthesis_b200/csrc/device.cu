@@ -893,12 +893,20 @@ static int find_image(const char* name)
     return -2;
 }
 
-static int ensure_wave(igb200_device* dev)
+// Streams of the wavefront, sized to the request: `want` rays (all iterations of the call), rounded up to a power of two between
+// 1 Mi (the reference's capacity, mapping_gpu.art:1125) and 32 Mi -- 232 B per ray, 7.8 GB at the cap.  Measured on B200
+// (profiles/r02_ab_wave_capacity.txt): every round costs a fixed 6 launches, a 1-CTA kernel and the tails of two persistent
+// traversals, so fuller rounds are cheaper per ray: 4 / 8 / 16 / 32 / 64 Mi = C4 1087 / 1162 / 1196 / 1210 / 1214 Msamples/s.
+// Grows on demand (the captured graph holds the pointers: re-captured then); IGB200_WAVE_CAPACITY pins it.
+static int ensure_wave(igb200_device* dev, uint64_t want)
 {
-    if (dev->wave_capacity) return IGB200_OK;
-    uint32_t cap = 1u << 23; // 8 Mi rays (the reference: 1 Mi, mapping_gpu.art:1125); ~2.1 GB of streams, measured best on B200
-    if (const char* e = std::getenv("IGB200_WAVE_CAPACITY")) cap = (uint32_t)std::max(1024l, std::atol(e));
+    uint64_t cap = 1u << 20;
+    while (cap < want && cap < (1u << 25)) cap <<= 1;
+    if (const char* e = std::getenv("IGB200_WAVE_CAPACITY")) cap = (uint64_t)std::max(1024l, std::atol(e));
     if (const char* e = std::getenv("IGB200_WAVE_SORT")) dev->wave_sort = std::max(0, std::min(2, std::atoi(e)));
+    if (cap <= dev->wave_capacity) return IGB200_OK;
+    if (dev->round_graph) { cudaGraphExecDestroy(dev->round_graph); dev->round_graph = nullptr; }
+    IGB_CUDA(cudaStreamSynchronize(dev->stream));
     for (int b = 0; b < 2; ++b) {
         IGB_CUDA(dev->w_rec[b].ensure((size_t)cap * igb::kRecVec));
         IGB_CUDA(dev->w_flags[b].ensure(cap));
@@ -908,18 +916,20 @@ static int ensure_wave(igb200_device* dev)
     dev->wave.shadow = igb::ShadowStream{ dev->w_sh_f4[0].ptr, dev->w_sh_f4[1].ptr, dev->w_sh_f4[2].ptr };
     IGB_CUDA(dev->w_keys.ensure(cap));
     IGB_CUDA(dev->w_sorted.ensure(cap));
-    IGB_CUDA(dev->w_ctl.ensure(1));
-    IGB_CUDA(cudaMemset(dev->w_ctl.ptr, 0, sizeof(igb::WaveControl)));
-    IGB_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&dev->h_done), sizeof(uint32_t), cudaHostAllocMapped));
-    *dev->h_done = 0;
-    uint32_t* d_alias = nullptr;
-    IGB_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d_alias), dev->h_done, 0));
-    dev->wave.host_done = d_alias;
-    dev->wave.keys      = dev->w_keys.ptr;
-    dev->wave.sorted    = dev->w_sorted.ptr;
-    dev->wave.ctl       = dev->w_ctl.ptr;
-    for (cudaEvent_t& e : dev->round_ev) IGB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    dev->wave_capacity = cap;
+    dev->wave.keys   = dev->w_keys.ptr;
+    dev->wave.sorted = dev->w_sorted.ptr;
+    if (!dev->h_done) {
+        IGB_CUDA(dev->w_ctl.ensure(1));
+        IGB_CUDA(cudaMemset(dev->w_ctl.ptr, 0, sizeof(igb::WaveControl)));
+        IGB_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&dev->h_done), sizeof(uint32_t), cudaHostAllocMapped));
+        *dev->h_done = 0;
+        uint32_t* d_alias = nullptr;
+        IGB_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d_alias), dev->h_done, 0));
+        dev->wave.host_done = d_alias;
+        dev->wave.ctl       = dev->w_ctl.ptr;
+        for (cudaEvent_t& e : dev->round_ev) IGB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    dev->wave_capacity = (uint32_t)cap;
     return IGB200_OK;
 }
 
@@ -968,7 +978,7 @@ static int render_batch(igb200_device* dev, const igb200_render_settings* rs, ui
         }
     }
     IGB_CUDA(cudaSetDevice(dev->ordinal));
-    if (int rc = ensure_wave(dev)) return rc;
+    if (int rc = ensure_wave(dev, (uint64_t)per_iter * count)) return rc;
     if (int rc = ensure_film(dev, (uint32_t)w, (uint32_t)h)) return rc;
     cudaStream_t st = dev->stream;
     if (per_iter == 0) { // more partitions than tile rows: this device owns nothing, but its (zero) film takes part in the reduce

@@ -20,10 +20,10 @@ else:
     resy = res
 with pkg.Device(0) as dev:
     dev.assign_scene(tables); dev.assign_shading(sh)
-    for it in range(int(os.environ.get('WARM','2'))): dev.render(res, resy, spi=spi, iteration=it)
+    batch = int(os.environ.get("BATCH", "1"))
+    for it in range(int(os.environ.get('WARM','2'))): dev.render(res, resy, spi=spi, iteration=1_000_000 + it * batch, iterations=batch)  # same shape as the timed calls
     ms, rays = [], 0
     t0 = time.time()
-    batch = int(os.environ.get("BATCH", "1"))
     for it in range(iters):
         dev.render(res, resy, spi=spi, iteration=2+it*batch, iterations=batch)
         st = dev.render_stats(); ms.append(st["device_ms"]/batch); rays = (st["camera_rays"]+st["bounce_rays"]+st["shadow_rays"])/batch
