@@ -296,6 +296,31 @@ def test_batched_iterations_equal_single_iterations(ig, dev):
     assert tuple(sa) == (st["camera_rays"], st["bounce_rays"], st["shadow_rays"])
 
 
+def test_streams_grow_with_the_request(ig, dev):
+    """The wavefront streams are sized to the request (power of two >= 1 Mi rays) and grow when a later call needs more:
+    a device that first renders 64 x 64 and then 768 x 768 x 4 spp x 3 iterations (7 M rays: re-allocation, round graph
+    re-captured) gives the film and the ray counts of a fresh device."""
+    tables, sh = room_scene(ig, 768, depth=5)
+    dev.assign_scene(tables); dev.assign_shading(sh)
+    dev.resize(64, 64)
+    dev.render(64, 64, spi=1, seed=4)                    # 4096 rays: 1 Mi streams
+    dev.resize(768, 768)
+    dev.clear_framebuffer()
+    dev.render(768, 768, spi=4, iteration=0, seed=4, iterations=3)
+    a, n = dev.framebuffer()
+    sa = dev.render_stats()
+    assert n == 3
+    with ig.Device(0) as fresh:
+        fresh.assign_scene(tables); fresh.assign_shading(sh)
+        fresh.resize(768, 768)
+        fresh.render(768, 768, spi=4, iteration=0, seed=4, iterations=3)
+        b, _ = fresh.framebuffer()
+        sb = fresh.render_stats()
+    np.testing.assert_allclose(a, b, rtol=2e-5, atol=1e-6)
+    assert all(sa[k] == sb[k] for k in ("camera_rays", "bounce_rays", "shadow_rays"))
+    assert sa["rounds"] == sb["rounds"]                   # same stream size in the end: same number of rounds
+
+
 def test_capacity_smaller_than_one_iteration(ig, oracle, monkeypatch):
     # regeneration: 256 x 256 x 8 samples = 512 Ki rays flow through 64 Ki-ray streams
     monkeypatch.setenv("IGB200_WAVE_CAPACITY", "65536")
