@@ -25,6 +25,8 @@ ABI_SYMBOLS = [
     "igb200_assign_shading",
     "igb200_render",
     "igb200_render_iterations",
+    "igb200_render_pipelined",
+    "igb200_flush",
     "igb200_framebuffer",
     "igb200_clear_framebuffer",
     "igb200_clear_aov",
@@ -148,6 +150,8 @@ def load():
     lib.igb200_assign_shading.argtypes = [vp, vp]
     lib.igb200_render.argtypes = [vp, vp]
     lib.igb200_render_iterations.argtypes = [vp, vp, u32]
+    lib.igb200_render_pipelined.argtypes = [vp, vp]
+    lib.igb200_flush.argtypes = [vp]
     lib.igb200_framebuffer.argtypes = [vp, C.c_char_p, i32, C.POINTER(vp), C.POINTER(u64)]
     lib.igb200_clear_framebuffer.argtypes = [vp]
     lib.igb200_clear_aov.argtypes = [vp, C.c_char_p]

@@ -121,7 +121,9 @@ class Runtime:
     def step(self, ignoreDenoiser=False):
         if self._opts.IsTracer:
             raise RuntimeError("Trying to use step() in a trace driver!")
-        self._dev.render(self._w, self._h, spi=self._spi, iteration=self._iteration, frame=self._frame, seed=self._opts.Seed)
+        # pipelined step: returns once the iteration's rays are generated; every framebuffer access completes the film first
+        self._dev.render(self._w, self._h, spi=self._spi, iteration=self._iteration, frame=self._frame, seed=self._opts.Seed,
+                         pipelined=True)
         self._iteration += 1
         if not self._lock_film:
             self._samples += self._spi

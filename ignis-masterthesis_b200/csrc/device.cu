@@ -131,7 +131,9 @@ struct igb200_device {
     DeviceBuffer<uint32_t>        w_keys, w_sorted;
     DeviceBuffer<igb::WaveControl> w_ctl;
     igb::WaveBuffers              wave{};
-    uint32_t*                     h_done = nullptr; // mapped pinned host flag
+    uint32_t*                     h_done = nullptr; // two mapped pinned host flags: [0] wavefront drained, [1] all ids of the call generated
+    bool                          wave_pending = false; // igb200_render_pipelined left paths in flight (survivors in stream 0)
+    igb::WaveSettings             pending_set{};        // settings of the call that left them
     cudaEvent_t                   round_ev[4] = {};
     cudaGraphExec_t               round_graph = nullptr; // one round pair; invalidated by assign_scene / assign_shading
     DeviceBuffer<float4>          d_list_rays;
@@ -161,6 +163,8 @@ struct igb200_device {
 static const char* const kAovNames[igb200_device::kAovCount] = { "Direct Weights", "NEE Weights", "Normals", "Albedo", "Depth" };
 
 extern "C" {
+
+static int flush_wave(igb200_device* dev); // drains the paths left in flight by igb200_render_pipelined
 
 int igb200_abi_version(void) { return IGB200_ABI_VERSION; }
 
@@ -325,6 +329,7 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
     if (sc->shape_count && (!sc->shape_lookups || !sc->shape_data))
         return fail(IGB200_E_INVALID, "igb200_assign_scene: shape table pointers are NULL");
     IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (int rc = flush_wave(dev)) return rc;
     dev->has_scene = false;
 
     // ---- entity leaves (both primitive types share one top-level BVH8) ----
@@ -725,6 +730,8 @@ int igb200_get_bvh_info(igb200_device* dev, uint64_t* node_bytes, uint64_t* tri_
 // ---------------------------------------------------------------------------------------------------------
 int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
 {
+    if (dev)
+        if (int rc = flush_wave(dev)) return rc;
     if (!dev || !sh) return fail(IGB200_E_INVALID, "igb200_assign_shading: NULL argument");
     if (!dev->has_scene) return fail(IGB200_E_STATE, "igb200_assign_shading: no scene assigned");
     if ((sh->bsdf_count && !sh->bsdfs) || (sh->material_count && !sh->materials) || (sh->infinite_light_count && !sh->infinite_lights) ||
@@ -921,8 +928,8 @@ static int ensure_wave(igb200_device* dev, uint64_t want)
     if (!dev->h_done) {
         IGB_CUDA(dev->w_ctl.ensure(1));
         IGB_CUDA(cudaMemset(dev->w_ctl.ptr, 0, sizeof(igb::WaveControl)));
-        IGB_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&dev->h_done), sizeof(uint32_t), cudaHostAllocMapped));
-        *dev->h_done = 0;
+        IGB_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&dev->h_done), 2 * sizeof(uint32_t), cudaHostAllocMapped));
+        dev->h_done[0] = dev->h_done[1] = 0;
         uint32_t* d_alias = nullptr;
         IGB_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d_alias), dev->h_done, 0));
         dev->wave.host_done = d_alias;
@@ -941,7 +948,115 @@ static uint32_t owned_rows(uint32_t h, uint32_t rank, uint32_t parts)
     return rows;
 }
 
-static int render_batch(igb200_device* dev, const igb200_render_settings* rs, uint32_t count, uint32_t tile_rank = 0, uint32_t tile_count = 1)
+// Launches wavefront rounds on dev->stream until the device reports the queue drained (until_generated = false: the host runs
+// ahead by up to kAhead round pairs and polls the mapped flag; rounds enqueued after the drain are no-ops) or until every ray id
+// of the call has been generated (pipelined steps: one host sync per pair, nothing is launched beyond what the ids need).
+static int run_wave(igb200_device* dev, bool until_generated, uint64_t& pairs)
+{
+    cudaStream_t       st        = dev->stream;
+    constexpr int      kAhead    = 3;
+    const uint64_t     max_pairs = 1ull << 24;
+    volatile uint32_t* flags     = dev->h_done;
+    pairs                        = 0;
+    // One round pair (12 launches) is captured once into a CUDA graph; per-call settings live in device memory, so
+    // the graph only depends on the scene / shading tables and the stream buffers (re-captured when they change).
+    if (!dev->round_graph) {
+        cudaGraph_t g = nullptr;
+        IGB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        cudaError_t e1 = igb::launch_wave_round(dev->view, dev->shade, dev->wave, 0, dev->wave_sort, dev->sm_count, st);
+        cudaError_t e2 = igb::launch_wave_round(dev->view, dev->shade, dev->wave, 1, dev->wave_sort, dev->sm_count, st);
+        cudaError_t e3 = cudaStreamEndCapture(st, &g);
+        if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || !g)
+            return fail(IGB200_E_CUDA, "igb200_render: graph capture failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3)));
+        cudaError_t e4 = cudaGraphInstantiate(&dev->round_graph, g, 0);
+        cudaGraphDestroy(g);
+        if (e4 != cudaSuccess) return fail(IGB200_E_CUDA, "igb200_render: cudaGraphInstantiate failed: %s", cudaGetErrorString(e4));
+    }
+    if (dev->stats) {
+        // --stats (Device::SetupSettings::AcquireStats): rounds are launched one by one with an event between the kernels
+        // and a host sync per pair, so that the time of every kernel kind is known (Statistics.h:9-63 names on the host side).
+        if (!dev->sec_ev[0])
+            for (cudaEvent_t& e : dev->sec_ev) IGB_CUDA(cudaEventCreate(&e));
+        for (; pairs < max_pairs; ++pairs) {
+            for (int parity = 0; parity < 2; ++parity) {
+                IGB_CUDA(igb::launch_wave_round(dev->view, dev->shade, dev->wave, parity, dev->wave_sort, dev->sm_count, st, dev->sec_ev));
+                IGB_CUDA(cudaStreamSynchronize(st));
+                for (int k = 0; k < igb::kWaveLaunchesPerRound; ++k) {
+                    float ms = 0.0f;
+                    if (cudaEventElapsedTime(&ms, dev->sec_ev[k], dev->sec_ev[k + 1]) == cudaSuccess) dev->section.kernel_ms[k] += ms;
+                    dev->section.launches[k] += (k == 3 && !dev->wave_sort) ? 0 : 1;
+                }
+            }
+            if (flags[0]) { ++pairs; break; }
+        }
+    } else if (until_generated) {
+        for (; pairs < max_pairs; ++pairs) {
+            IGB_CUDA(cudaGraphLaunch(dev->round_graph, st));
+            IGB_CUDA(cudaEventRecord(dev->round_ev[0], st));
+            IGB_CUDA(cudaEventSynchronize(dev->round_ev[0]));
+            if (flags[0] || flags[1]) { ++pairs; break; }
+        }
+    } else {
+        for (; pairs < max_pairs; ++pairs) {
+            IGB_CUDA(cudaGraphLaunch(dev->round_graph, st));
+            IGB_CUDA(cudaEventRecord(dev->round_ev[pairs % 4], st));
+            if (pairs >= (uint64_t)kAhead) IGB_CUDA(cudaEventSynchronize(dev->round_ev[(pairs - kAhead) % 4]));
+            if (flags[0]) { ++pairs; break; }
+        }
+    }
+    return IGB200_OK;
+}
+
+// Copies the device-side ray counters of the call into (add = false) or onto (add = true) dev->render_stats.
+static int read_wave_stats(igb200_device* dev, uint64_t pairs, bool list, bool add)
+{
+    igb::WaveControl ctl;
+    IGB_CUDA(cudaMemcpy(&ctl, dev->w_ctl.ptr, offsetof(igb::WaveControl, bins), cudaMemcpyDeviceToHost));
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, dev->ev0, dev->ev1);
+    igb200_render_stats s{};
+    s.camera_rays     = ctl.camera_rays;
+    s.bounce_rays     = ctl.bounce_rays;
+    s.shadow_rays     = ctl.shadow_rays;
+    s.rounds          = ctl.rounds;
+    s.kernel_launches = 1 + pairs * 2 * (igb::kWaveLaunchesPerRound - (dev->wave_sort ? 0 : 1)) + (list ? 1 : 0);
+    s.device_ms       = ms;
+    if (add) {
+        s.camera_rays += dev->render_stats.camera_rays;
+        s.bounce_rays += dev->render_stats.bounce_rays;
+        s.shadow_rays += dev->render_stats.shadow_rays;
+        s.rounds += dev->render_stats.rounds;
+        s.kernel_launches += dev->render_stats.kernel_launches;
+        s.device_ms += dev->render_stats.device_ms;
+    }
+    dev->render_stats = s;
+    return IGB200_OK;
+}
+
+// Drains the paths igb200_render_pipelined left in flight (no new ids; same settings).  Every entry that reads, clears or
+// re-allocates the film, or changes the scene, the shading tables or the streams, calls this first.  The rays it traces are
+// added to the counters of the last call.
+static int flush_wave(igb200_device* dev)
+{
+    if (!dev->wave_pending) return IGB200_OK;
+    IGB_CUDA(cudaSetDevice(dev->ordinal));
+    cudaStream_t st = dev->stream;
+    IGB_CUDA(cudaEventRecord(dev->ev0, st));
+    IGB_CUDA(igb::launch_wave_reset(dev->wave, dev->pending_set, 0u, st, true));
+    IGB_CUDA(cudaStreamSynchronize(st));
+    uint64_t pairs = 0;
+    if (int rc = run_wave(dev, false, pairs)) return rc;
+    IGB_CUDA(cudaEventRecord(dev->ev1, st));
+    IGB_CUDA(cudaStreamSynchronize(st));
+    dev->wave_pending = false;
+    if (!dev->h_done[0]) return fail(IGB200_E_CUDA, "igb200_flush: wavefront did not drain");
+    dev->film_mapped = false;
+    for (igb200_device::Aov& a : dev->aov) a.mapped = false;
+    return read_wave_stats(dev, pairs, false, true);
+}
+
+static int render_batch(igb200_device* dev, const igb200_render_settings* rs, uint32_t count, uint32_t tile_rank = 0, uint32_t tile_count = 1,
+                        bool pipelined = false)
 {
     if (!dev || !rs) return fail(IGB200_E_INVALID, "igb200_render: NULL argument");
     if (count == 0) return IGB200_OK;
@@ -978,7 +1093,21 @@ static int render_batch(igb200_device* dev, const igb200_render_settings* rs, ui
         }
     }
     IGB_CUDA(cudaSetDevice(dev->ordinal));
-    if (int rc = ensure_wave(dev, (uint64_t)per_iter * count)) return rc;
+    // Pipelined steps (igb200_render_pipelined): the call returns when its ray ids have been generated; the paths still in flight
+    // stay in the stream and continue in the next call's rounds (or in flush_wave).  Streams four iterations deep, so that the
+    // survivors of earlier steps and a whole new iteration fit one round.
+    const bool pipe = pipelined && !list && !dev->stats;
+    uint64_t   want = (uint64_t)per_iter * count * (pipe ? 4u : 1u);
+    if (dev->wave_pending) {
+        const igb::WaveSettings& p = dev->pending_set;
+        uint64_t cap = 1u << 20;
+        while (cap < want && cap < (1u << 25)) cap <<= 1;
+        const bool same = pipe && p.spi == rs->spi && p.width == w && p.height == h && p.per_iter == per_iter &&
+                          p.tile_rank == tile_rank && p.tile_count == tile_count && cap <= dev->wave_capacity;
+        if (!same)
+            if (int rc = flush_wave(dev)) return rc;
+    }
+    if (int rc = ensure_wave(dev, want)) return rc;
     if (int rc = ensure_film(dev, (uint32_t)w, (uint32_t)h)) return rc;
     cudaStream_t st = dev->stream;
     if (per_iter == 0) { // more partitions than tile rows: this device owns nothing, but its (zero) film takes part in the reduce
@@ -1021,64 +1150,16 @@ static int render_batch(igb200_device* dev, const igb200_render_settings* rs, ui
     dev->wave.ent_mat = dev->d_ent_mat.ptr;
 
     IGB_CUDA(cudaEventRecord(dev->ev0, st));
-    IGB_CUDA(igb::launch_wave_reset(dev->wave, set, (uint32_t)(per_iter * count), st));
-    IGB_CUDA(cudaStreamSynchronize(st)); // the mapped flag is cleared before the host starts polling it
-    // The host runs ahead of the device by up to kAhead round pairs and polls the mapped `done` flag; rounds
-    // enqueued after the queue has drained are no-ops (every kernel reads a zero count).
-    constexpr int kAhead = 3;
-    uint64_t      pairs  = 0;
-    const uint64_t max_pairs = 1ull << 24;
-    // One round pair (12 launches) is captured once into a CUDA graph; per-call settings live in device memory, so
-    // the graph only depends on the scene / shading tables (re-captured when they change).
-    if (!dev->round_graph) {
-        cudaGraph_t g = nullptr;
-        IGB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        cudaError_t e1 = igb::launch_wave_round(dev->view, dev->shade, dev->wave, 0, dev->wave_sort, dev->sm_count, st);
-        cudaError_t e2 = igb::launch_wave_round(dev->view, dev->shade, dev->wave, 1, dev->wave_sort, dev->sm_count, st);
-        cudaError_t e3 = cudaStreamEndCapture(st, &g);
-        if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || !g)
-            return fail(IGB200_E_CUDA, "igb200_render: graph capture failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3)));
-        cudaError_t e4 = cudaGraphInstantiate(&dev->round_graph, g, 0);
-        cudaGraphDestroy(g);
-        if (e4 != cudaSuccess) return fail(IGB200_E_CUDA, "igb200_render: cudaGraphInstantiate failed: %s", cudaGetErrorString(e4));
-    }
-    if (dev->stats) {
-        // --stats (Device::SetupSettings::AcquireStats): rounds are launched one by one with an event between the kernels
-        // and a host sync per pair, so that the time of every kernel kind is known (Statistics.h:9-63 names on the host side).
-        if (!dev->sec_ev[0])
-            for (cudaEvent_t& e : dev->sec_ev) IGB_CUDA(cudaEventCreate(&e));
-        for (; pairs < max_pairs; ++pairs) {
-            for (int parity = 0; parity < 2; ++parity) {
-                IGB_CUDA(igb::launch_wave_round(dev->view, dev->shade, dev->wave, parity, dev->wave_sort, dev->sm_count, st, dev->sec_ev));
-                IGB_CUDA(cudaStreamSynchronize(st));
-                for (int k = 0; k < igb::kWaveLaunchesPerRound; ++k) {
-                    float ms = 0.0f;
-                    if (cudaEventElapsedTime(&ms, dev->sec_ev[k], dev->sec_ev[k + 1]) == cudaSuccess) dev->section.kernel_ms[k] += ms;
-                    dev->section.launches[k] += (k == 3 && !dev->wave_sort) ? 0 : 1;
-                }
-            }
-            if (*reinterpret_cast<volatile uint32_t*>(dev->h_done)) { ++pairs; break; }
-        }
-    } else
-    for (; pairs < max_pairs; ++pairs) {
-        IGB_CUDA(cudaGraphLaunch(dev->round_graph, st));
-        IGB_CUDA(cudaEventRecord(dev->round_ev[pairs % 4], st));
-        if (pairs >= (uint64_t)kAhead) IGB_CUDA(cudaEventSynchronize(dev->round_ev[(pairs - kAhead) % 4]));
-        if (*reinterpret_cast<volatile uint32_t*>(dev->h_done)) { ++pairs; break; }
-    }
+    IGB_CUDA(igb::launch_wave_reset(dev->wave, set, (uint32_t)(per_iter * count), st, dev->wave_pending));
+    IGB_CUDA(cudaStreamSynchronize(st)); // the mapped flags are cleared before the host starts polling them
+    uint64_t pairs = 0;
+    if (int rc = run_wave(dev, pipe, pairs)) return rc;
     IGB_CUDA(cudaEventRecord(dev->ev1, st));
     IGB_CUDA(cudaStreamSynchronize(st));
-    if (!*reinterpret_cast<volatile uint32_t*>(dev->h_done)) return fail(IGB200_E_CUDA, "igb200_render: wavefront did not drain");
-    igb::WaveControl ctl;
-    IGB_CUDA(cudaMemcpy(&ctl, dev->w_ctl.ptr, offsetof(igb::WaveControl, bins), cudaMemcpyDeviceToHost));
-    dev->render_stats.camera_rays     = ctl.camera_rays;
-    dev->render_stats.bounce_rays     = ctl.bounce_rays;
-    dev->render_stats.shadow_rays     = ctl.shadow_rays;
-    dev->render_stats.rounds          = ctl.rounds;
-    dev->render_stats.kernel_launches = 1 + pairs * 2 * (igb::kWaveLaunchesPerRound - (dev->wave_sort ? 0 : 1)) + (list ? 1 : 0);
-    float ms = 0.0f;
-    cudaEventElapsedTime(&ms, dev->ev0, dev->ev1);
-    dev->render_stats.device_ms = ms;
+    dev->wave_pending = pipe && !dev->h_done[0];
+    dev->pending_set  = set;
+    if (!pipe && !dev->h_done[0]) return fail(IGB200_E_CUDA, "igb200_render: wavefront did not drain");
+    if (int rc = read_wave_stats(dev, pairs, list, false)) return rc;
     // Interface::present, Device.cpp:1460-1472: the film counts unless the technique locks it, every used AOV counts
     if (!infobuffer) {
         dev->iterations += count;
@@ -1097,6 +1178,14 @@ int igb200_render(igb200_device* dev, const igb200_render_settings* rs) { return
 int igb200_render_iterations(igb200_device* dev, const igb200_render_settings* rs, uint32_t count)
 {
     return render_batch(dev, rs, count);
+}
+
+int igb200_render_pipelined(igb200_device* dev, const igb200_render_settings* rs) { return render_batch(dev, rs, 1, 0, 1, true); }
+
+int igb200_flush(igb200_device* dev)
+{
+    if (!dev) return fail(IGB200_E_INVALID, "igb200_flush: NULL device");
+    return flush_wave(dev);
 }
 
 int igb200_partition_share(uint32_t total_iterations, uint32_t part, uint32_t parts, uint32_t mode, uint32_t* first, uint32_t* count,
@@ -1175,6 +1264,7 @@ int igb200_framebuffer(igb200_device* dev, const char* name, int device, float**
         return fail(IGB200_E_INVALID, "igb200_framebuffer: unknown AOV '%s'", name); // Device.cpp:1303-1305
     if (!dev->d_film.ptr) return fail(IGB200_E_STATE, "igb200_framebuffer: nothing rendered yet");
     IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (int rc = flush_wave(dev)) return rc;
     if (img >= 0) {
         igb200_device::Aov& a = dev->aov[img];
         if (iterations) *iterations = a.iterations;
@@ -1235,6 +1325,7 @@ int igb200_clear_framebuffer(igb200_device* dev)
 {
     if (!dev) return fail(IGB200_E_INVALID, "igb200_clear_framebuffer: NULL device");
     IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (int rc = flush_wave(dev)) return rc;
     for (int img = -1; img < igb200_device::kAovCount; ++img) // clearAllAOVs, Device.cpp:1406-1411
         if (int rc = clear_image(dev, img)) return rc;
     IGB_CUDA(cudaStreamSynchronize(dev->stream));
@@ -1247,6 +1338,7 @@ int igb200_clear_aov(igb200_device* dev, const char* name)
     const int img = find_image(name);
     if (img == -2 || (img >= 0 && !dev->aov[img].d.ptr)) return fail(IGB200_E_INVALID, "igb200_clear_aov: unknown AOV '%s'", name);
     IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (int rc = flush_wave(dev)) return rc;
     if (int rc = clear_image(dev, img)) return rc;
     IGB_CUDA(cudaStreamSynchronize(dev->stream));
     return IGB200_OK;
@@ -1259,6 +1351,7 @@ int igb200_tonemap(igb200_device* dev, const igb200_tonemap_settings* ts, uint32
     if (img == -2 || (img >= 0 && !dev->aov[img].d.ptr)) return fail(IGB200_E_INVALID, "igb200_tonemap: unknown AOV '%s'", ts->aov);
     if (!dev->d_film.ptr) return fail(IGB200_E_STATE, "igb200_tonemap: nothing rendered yet");
     IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (int rc = flush_wave(dev)) return rc;
     const uint64_t n     = (uint64_t)dev->film_w * dev->film_h;
     const uint64_t iters = img < 0 ? dev->iterations : dev->aov[img].iterations;
     const float*   in    = img < 0 ? dev->d_film.ptr : dev->aov[img].d.ptr;
@@ -1280,6 +1373,7 @@ int igb200_resize(igb200_device* dev, uint32_t width, uint32_t height)
     if (!dev) return fail(IGB200_E_INVALID, "igb200_resize: NULL device");
     if (width == 0 || height == 0) return fail(IGB200_E_INVALID, "igb200_resize: empty film");
     IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (int rc = flush_wave(dev)) return rc;
     dev->film_w = dev->film_h = 0; // force re-allocation + zero (Device.cpp:306-313)
     return ensure_film(dev, width, height);
 }
@@ -1290,6 +1384,7 @@ int igb200_set_framebuffer(igb200_device* dev, const float* d_src, uint64_t coun
     if (!dev->d_film.ptr || count != (uint64_t)dev->film_w * dev->film_h * 3)
         return fail(IGB200_E_INVALID, "igb200_set_framebuffer: size does not match the film");
     IGB_CUDA(cudaSetDevice(dev->ordinal));
+    if (int rc = flush_wave(dev)) return rc;
     IGB_CUDA(igb::launch_film_combine(dev->d_film.ptr, d_src, count, true, dev->stream));
     IGB_CUDA(cudaStreamSynchronize(dev->stream));
     dev->iterations  = iterations;

@@ -181,9 +181,15 @@ __global__ void begin_round_kernel(WaveControl* ctl, uint32_t n_bins, uint32_t* 
         ctl->n_cur    = n_surv + m;
         ctl->n_next   = 0u;
         ctl->n_shadow = 0u;
+        volatile uint32_t* flags = host_done; // [0] nothing left at all, [1] every id of the call has been generated
+        if (ctl->next_id == ctl->total && ctl->gen_done == 0u) {
+            ctl->gen_done = 1u;
+            flags[1]      = 1u;
+            __threadfence_system();
+        }
         if (n_surv + m == 0u) {
             ctl->done = 1u;
-            *reinterpret_cast<volatile uint32_t*>(host_done) = 1u;
+            flags[0]  = 1u;
             __threadfence_system();
         } else {
             ctl->rounds += 1u;
@@ -192,18 +198,23 @@ __global__ void begin_round_kernel(WaveControl* ctl, uint32_t n_bins, uint32_t* 
     for (uint32_t b = threadIdx.x; b < n_bins; b += blockDim.x) ctl->bins[b] = 0u;
 }
 
-__global__ void reset_kernel(WaveControl* ctl, const WaveSettings set, uint32_t total, uint32_t* host_done)
+// keep != 0: the survivors and the shadow-ray count of the previous call's last round stay (pipelined steps, igb200_render_pipelined:
+// calls end on a round PAIR, so the survivors are in stream 0 where the next call's first round expects them)
+__global__ void reset_kernel(WaveControl* ctl, const WaveSettings set, uint32_t total, uint32_t* host_done, int keep)
 {
     ctl->set = set;
-    ctl->n_cur = ctl->n_next = ctl->n_shadow = 0u;
+    ctl->n_cur = 0u;
+    if (!keep) ctl->n_next = ctl->n_shadow = 0u;
     ctl->gen_base = ctl->gen_count = ctl->gen_first = 0u;
     ctl->next_id = 0u;
     ctl->total   = total;
     ctl->done    = 0u;
+    ctl->gen_done = 0u;
     ctl->rounds  = 0u;
     ctl->work_primary[0] = ctl->work_primary[1] = ctl->work_shadow[0] = ctl->work_shadow[1] = 0u;
     ctl->camera_rays = ctl->bounce_rays = ctl->shadow_rays = 0ull;
-    *reinterpret_cast<volatile uint32_t*>(host_done) = 0u;
+    reinterpret_cast<volatile uint32_t*>(host_done)[0] = 0u;
+    reinterpret_cast<volatile uint32_t*>(host_done)[1] = 0u;
     __threadfence_system();
 }
 
@@ -643,9 +654,9 @@ __global__ void __launch_bounds__(128, IGB_SHADE_MIN_BLOCKS) shade_kernel(WaveCo
 // ---------------------------------------------------------------------------------------------------------
 // Launchers
 // ---------------------------------------------------------------------------------------------------------
-cudaError_t launch_wave_reset(const WaveBuffers& buf, const WaveSettings& set, uint32_t total, cudaStream_t stream)
+cudaError_t launch_wave_reset(const WaveBuffers& buf, const WaveSettings& set, uint32_t total, cudaStream_t stream, bool keep_survivors)
 {
-    reset_kernel<<<1, 1, 0, stream>>>(buf.ctl, set, total, buf.host_done);
+    reset_kernel<<<1, 1, 0, stream>>>(buf.ctl, set, total, buf.host_done, keep_survivors ? 1 : 0);
     return cudaGetLastError();
 }
 

@@ -75,6 +75,7 @@ struct WaveControl {
     uint32_t next_id;   // next ray id to generate
     uint32_t total;     // spi * width * height
     uint32_t done;      // set when a round starts with nothing to do
+    uint32_t gen_done;  // set when every ray id of the call has been generated
     uint32_t rounds;
     uint32_t work_primary[2]; // persistent-kernel work counters (self-resetting)
     uint32_t work_shadow[2];
@@ -92,7 +93,7 @@ struct WaveBuffers {
     uint32_t*      sorted; // slot indices in key order
     WaveControl*   ctl;
     const int32_t* ent_mat; // material id per entity
-    uint32_t*      host_done; // device alias of a mapped host flag
+    uint32_t*      host_done; // device alias of two mapped host flags: [0] drained, [1] all ids of the call generated
 };
 
 namespace shade { struct ShadeScene; }
@@ -104,8 +105,10 @@ cudaError_t launch_wave_round(const DeviceScene& scene, const shade::ShadeScene&
                               cudaEvent_t* events = nullptr); // stats mode: kWaveLaunchesPerRound + 1 events, one before each
                                                               // kernel and one after the last (not capturable into a graph)
 
-// Resets the control block for a new call (total = spi * w * h * iterations) and stores its settings.
-cudaError_t launch_wave_reset(const WaveBuffers& buf, const WaveSettings& set, uint32_t total, cudaStream_t stream);
+// Resets the control block for a new call (total = spi * w * h * iterations) and stores its settings.  keep_survivors: the paths
+// the previous call left in flight stay in the stream (pipelined steps).
+cudaError_t launch_wave_reset(const WaveBuffers& buf, const WaveSettings& set, uint32_t total, cudaStream_t stream,
+                              bool keep_survivors = false);
 
 // film[i] += src[i] (overwrite = false) or film[i] = src[i]
 // Device::tonemap (Device.cpp:1662-1687): scale already carries 1 / IterationCount

@@ -106,14 +106,21 @@ class Device:
         sh = shading.c_shading()
         _lib.check(self._lib.igb200_assign_shading(self._h, C.addressof(sh)))
 
-    def render(self, width=0, height=0, spi=1, iteration=0, frame=0, seed=0, rays=None, iterations=1):
+    def render(self, width=0, height=0, spi=1, iteration=0, frame=0, seed=0, rays=None, iterations=1, pipelined=False):
         """`iterations` iterations (spi samples per pixel each) accumulated into the film, in one wavefront.
-        rays != None: igtrace (list) mode."""
+        rays != None: igtrace (list) mode.  pipelined: igb200_render_pipelined (one iteration; its tail continues in the
+        next call, the film is complete after flush() or any call that reads it)."""
         rs, rays = self._settings(width, height, spi, iteration, frame, seed, rays)
-        if iterations == 1:
+        if pipelined:
+            assert iterations == 1
+            _lib.check(self._lib.igb200_render_pipelined(self._h, C.addressof(rs)))
+        elif iterations == 1:
             _lib.check(self._lib.igb200_render(self._h, C.addressof(rs)))
         else:
             _lib.check(self._lib.igb200_render_iterations(self._h, C.addressof(rs), iterations))
+
+    def flush(self):
+        _lib.check(self._lib.igb200_flush(self._h))
 
     def _settings(self, width, height, spi, iteration, frame, seed, rays):
         from .shading import RenderSettings

@@ -103,13 +103,27 @@ void Device::renderIterations(const RenderSettings& settings, size_t count)
         mWidth  = settings.width;
         mHeight = 1;
     }
-    // one member: plain igb200_render_iterations on it; several: partition (AUTO: by iteration when there are enough of them,
-    // else by tile rows), render concurrently, ncclReduce onto member 0
-    if (igb200_group_render(mGroup, &s, (uint32_t)count, IGB200_PARTITION_AUTO) != IGB200_OK) fatal("Device::render");
-    const igb200_render_stats st = renderStats(); // Quantity::{Camera,Bounce,Shadow}RayCount accumulate over the run
+    igb200_render_stats st{};
+    if (count == 1 && !settings.rays && igb200_group_size(mGroup) == 1) {
+        // Runtime::step() on one GPU: pipelined steps -- the call returns when the iteration's rays have been generated, its deep
+        // paths finish in the rounds of the next step (or in flush(); every framebuffer access flushes by itself)
+        if (igb200_render_pipelined(mHandle, &s) != IGB200_OK) fatal("Device::render");
+        igb200_get_render_stats(mHandle, &st);
+    } else {
+        // one member: plain igb200_render_iterations on it; several: partition (AUTO: by iteration when there are enough of them,
+        // else by tile rows), render concurrently, ncclReduce onto member 0
+        if (igb200_group_render(mGroup, &s, (uint32_t)count, IGB200_PARTITION_AUTO) != IGB200_OK) fatal("Device::render");
+        st = renderStats();
+    }
+    // Quantity::{Camera,Bounce,Shadow}RayCount accumulate over the run (devices with AcquireStats render synchronously: exact)
     mRays[0] += st.camera_rays;
     mRays[1] += st.bounce_rays;
     mRays[2] += st.shadow_rays;
+}
+
+void Device::flush()
+{
+    if (igb200_flush(mHandle) != IGB200_OK) error("Device::flush");
 }
 
 void Device::resize(size_t width, size_t height)
@@ -153,7 +167,8 @@ void Device::clearAllFramebuffer()
 igb200_render_stats Device::renderStats() const
 {
     igb200_render_stats st{};
-    igb200_group_get_render_stats(mGroup, &st, nullptr); // summed over the members
+    if (igb200_group_size(mGroup) == 1) igb200_get_render_stats(mHandle, &st); // also covers pipelined steps, which bypass the group
+    else igb200_group_get_render_stats(mGroup, &st, nullptr);                  // summed over the members
     return st;
 }
 

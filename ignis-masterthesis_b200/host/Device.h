@@ -62,6 +62,8 @@ public:
     void render(const TechniqueVariantShaderSet& shader_set, const RenderSettings& settings, const ParameterSet* parameter_set);
     // `count` consecutive iterations in one wavefront (igb200_render_iterations); same film as `count` render() calls
     void renderIterations(const RenderSettings& settings, size_t count);
+    // finishes the paths that pipelined steps (render() on one GPU) left in flight; framebuffer accessors do this by themselves
+    void flush();
     void resize(size_t width, size_t height);
     void releaseAll();
 

@@ -24,11 +24,14 @@ with pkg.Device(0) as dev:
     for it in range(int(os.environ.get('WARM','2'))): dev.render(res, resy, spi=spi, iteration=1_000_000 + it * batch, iterations=batch)  # same shape as the timed calls
     ms, rays = [], 0
     t0 = time.time()
+    pipe = os.environ.get("PIPE", "0") == "1"  # igb200_render_pipelined, one iteration per call; wall includes the final flush
     for it in range(iters):
-        dev.render(res, resy, spi=spi, iteration=2+it*batch, iterations=batch)
+        dev.render(res, resy, spi=spi, iteration=2+it*batch, iterations=batch, pipelined=pipe)
         st = dev.render_stats(); ms.append(st["device_ms"]/batch); rays = (st["camera_rays"]+st["bounce_rays"]+st["shadow_rays"])/batch
+    if pipe: dev.flush()
     wall = time.time()-t0
     ms = np.array(ms)
     print(f"res {res} spi {spi} depth {depth} cap {os.environ.get('IGB200_WAVE_CAPACITY','1M')} sort {os.environ.get('IGB200_WAVE_SORT','1')}: "
           f"{res*resy*spi/np.median(ms)/1e3:.1f} Msamples/s (median {np.median(ms):.2f} ms/iter, wall {wall/iters*1e3:.2f} ms/iter), "
-          f"{rays/np.median(ms)/1e3:.1f} Mrays/s, rounds {st['rounds']} launches {st['kernel_launches']}", flush=True)
+          f"{rays/np.median(ms)/1e3:.1f} Mrays/s, rounds {st['rounds']} launches {st['kernel_launches']}"
+          + (f", pipelined: {res*resy*spi*iters/wall/1e6:.1f} Msamples/s by wall clock incl. flush" if pipe else ""), flush=True)

@@ -16,7 +16,7 @@ def test_library_exports_every_declared_symbol(ig):
     assert declared == set(ig._lib.ABI_SYMBOLS)
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.igb200_abi_version() == 6
+    assert lib.igb200_abi_version() == 7
 
 
 def test_struct_sizes_match_reference_layouts(ig):

@@ -321,6 +321,63 @@ def test_streams_grow_with_the_request(ig, dev):
     assert sa["rounds"] == sb["rounds"]                   # same stream size in the end: same number of rounds
 
 
+def test_pipelined_steps_equal_plain_steps(ig, dev):
+    """igb200_render_pipelined: every call returns when its ids are generated, the deep paths finish in later calls or in the
+    flush; the film, the iteration count and the ray totals are those of plain igb200_render calls -- also with framebuffer reads,
+    a clear, a resize, a technique change and a plain call in between."""
+    tables, sh = room_scene(ig, 160, depth=12)
+    plain, sp = _render(dev, tables, sh, 160, 160, 2, 6, seed=21)
+    with ig.Device(0) as d:
+        d.assign_scene(tables); d.assign_shading(sh)
+        d.resize(160, 160)
+        total = np.zeros(3, np.int64)
+        for it in range(6):
+            d.render(160, 160, spi=2, iteration=it, seed=21, pipelined=True)
+            st = d.render_stats()
+            total += (st["camera_rays"], st["bounce_rays"], st["shadow_rays"])
+            if it == 2:                                   # a read in the middle flushes: the partial film is complete for 3 iterations
+                mid, n = d.framebuffer()
+                assert n == 3
+                st2 = d.render_stats()                    # the flush added its rays to the last call's counters
+                total += (0, st2["bounce_rays"] - st["bounce_rays"], st2["shadow_rays"] - st["shadow_rays"])
+                three, _ = _render(dev, tables, sh, 160, 160, 2, 3, seed=21)
+                np.testing.assert_allclose(mid, three, rtol=2e-5, atol=1e-6)
+        before = d.render_stats()
+        d.flush()
+        after = d.render_stats()
+        total += (0, after["bounce_rays"] - before["bounce_rays"], after["shadow_rays"] - before["shadow_rays"])
+        film, n = d.framebuffer()
+        assert n == 6
+        np.testing.assert_allclose(film, plain, rtol=2e-5, atol=1e-6)
+        assert tuple(total) == tuple(sp)
+        # clear with paths in flight: nothing of them may reach the cleared film
+        d.render(160, 160, spi=2, iteration=6, seed=21, pipelined=True)
+        d.clear_framebuffer()
+        z, n = d.framebuffer()
+        assert n == 0 and not z.any()
+        # another film size, then a plain call, then another technique depth with paths in flight
+        d.render(160, 160, spi=2, iteration=0, seed=21, pipelined=True)
+        d.render(96, 64, spi=1, iteration=1, seed=21, pipelined=True)       # resize: flushes the 160 x 160 paths into the old film first
+        d.render(96, 64, spi=1, iteration=2, seed=21)                       # plain call: flushes, then renders synchronously
+        a, n = d.framebuffer()
+        assert n == 2 and a.shape == (64, 96, 3)
+        d.render(96, 64, spi=1, iteration=3, seed=21, pipelined=True)
+        sh2 = room_scene(ig, 160, depth=3)[1]
+        d.assign_shading(sh2)                                               # flushes under the OLD technique
+        d.render(96, 64, spi=1, iteration=4, seed=21, pipelined=True)
+        b, n = d.framebuffer()
+        assert n == 4
+    with ig.Device(0) as e:                                                 # the same sequence without pipelining
+        e.assign_scene(tables); e.assign_shading(sh)
+        e.resize(96, 64)
+        for it in (1, 2, 3):
+            e.render(96, 64, spi=1, iteration=it, seed=21)
+        e.assign_shading(sh2)
+        e.render(96, 64, spi=1, iteration=4, seed=21)
+        c, n = e.framebuffer()
+    np.testing.assert_allclose(b, c, rtol=2e-5, atol=1e-6)
+
+
 def test_capacity_smaller_than_one_iteration(ig, oracle, monkeypatch):
     # regeneration: 256 x 256 x 8 samples = 512 Ki rays flow through 64 Ki-ray streams
     monkeypatch.setenv("IGB200_WAVE_CAPACITY", "65536")
