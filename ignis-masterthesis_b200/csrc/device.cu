@@ -136,6 +136,8 @@ struct igb200_device {
     igb::WaveSettings             pending_set{};        // settings of the call that left them
     cudaEvent_t                   round_ev[4] = {};
     cudaGraphExec_t               round_graph = nullptr; // one round pair; invalidated by assign_scene / assign_shading
+    cudaGraphExec_t               single_graph[2] = { nullptr, nullptr }; // one round of either parity (pipelined steps)
+    int                           wave_parity = 0;       // stream buffer the next round reads (non-zero only between pipelined steps)
     DeviceBuffer<float4>          d_list_rays;
 
     DeviceBuffer<float>           d_film;
@@ -165,6 +167,15 @@ static const char* const kAovNames[igb200_device::kAovCount] = { "Direct Weights
 extern "C" {
 
 static int flush_wave(igb200_device* dev); // drains the paths left in flight by igb200_render_pipelined
+static void drop_round_graphs(igb200_device* dev)
+{
+    if (dev->round_graph) cudaGraphExecDestroy(dev->round_graph);
+    dev->round_graph = nullptr;
+    for (cudaGraphExec_t& g : dev->single_graph) {
+        if (g) cudaGraphExecDestroy(g);
+        g = nullptr;
+    }
+}
 
 int igb200_abi_version(void) { return IGB200_ABI_VERSION; }
 
@@ -233,7 +244,7 @@ void igb200_destroy(igb200_device* dev)
         if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : dev->sec_ev)
         if (e) cudaEventDestroy(e);
-    if (dev->round_graph) cudaGraphExecDestroy(dev->round_graph);
+    drop_round_graphs(dev);
     if (dev->h_done) cudaFreeHost(dev->h_done);
     if (dev->h_film) cudaFreeHost(dev->h_film);
     for (auto& a : dev->aov)
@@ -477,7 +488,7 @@ int igb200_assign_scene(igb200_device* dev, const igb200_scene* sc)
     IGB_CUDA(dev->spheres.upload(all_spheres.data(), all_spheres.size(), dev->stream));
     // tables the shading kernels read (entities FixTable, shapes DynTable data)
     dev->has_shading = false;
-    if (dev->round_graph) { cudaGraphExecDestroy(dev->round_graph); dev->round_graph = nullptr; }
+    drop_round_graphs(dev);
     {
         std::vector<uint2>   info(sc->shape_count);
         for (uint64_t s = 0; s < sc->shape_count; ++s) {
@@ -854,7 +865,7 @@ int igb200_assign_shading(igb200_device* dev, const igb200_shading* sh)
         const float  x = b[3] - b[0], y = b[4] - b[1], z = b[5] - b[2];
         s.scene_radius = std::sqrt(std::fmaf(x, x, std::fmaf(y, y, z * z))) / 2 * 1.01f;
     }
-    if (dev->round_graph) { cudaGraphExecDestroy(dev->round_graph); dev->round_graph = nullptr; }
+    drop_round_graphs(dev);
     dev->has_shading = true;
     return IGB200_OK;
 }
@@ -912,7 +923,7 @@ static int ensure_wave(igb200_device* dev, uint64_t want)
     if (const char* e = std::getenv("IGB200_WAVE_CAPACITY")) cap = (uint64_t)std::max(1024l, std::atol(e));
     if (const char* e = std::getenv("IGB200_WAVE_SORT")) dev->wave_sort = std::max(0, std::min(2, std::atoi(e)));
     if (cap <= dev->wave_capacity) return IGB200_OK;
-    if (dev->round_graph) { cudaGraphExecDestroy(dev->round_graph); dev->round_graph = nullptr; }
+    drop_round_graphs(dev);
     IGB_CUDA(cudaStreamSynchronize(dev->stream));
     for (int b = 0; b < 2; ++b) {
         IGB_CUDA(dev->w_rec[b].ensure((size_t)cap * igb::kRecVec));
@@ -951,27 +962,30 @@ static uint32_t owned_rows(uint32_t h, uint32_t rank, uint32_t parts)
 // Launches wavefront rounds on dev->stream until the device reports the queue drained (until_generated = false: the host runs
 // ahead by up to kAhead round pairs and polls the mapped flag; rounds enqueued after the drain are no-ops) or until every ray id
 // of the call has been generated (pipelined steps: one host sync per pair, nothing is launched beyond what the ids need).
-static int run_wave(igb200_device* dev, bool until_generated, uint64_t& pairs)
+static int run_wave(igb200_device* dev, bool until_generated, uint64_t& rounds_launched)
 {
+    uint64_t pairs = 0, odd = 0;
     cudaStream_t       st        = dev->stream;
     constexpr int      kAhead    = 3;
     const uint64_t     max_pairs = 1ull << 24;
     volatile uint32_t* flags     = dev->h_done;
-    pairs                        = 0;
     // One round pair (12 launches) is captured once into a CUDA graph; per-call settings live in device memory, so
     // the graph only depends on the scene / shading tables and the stream buffers (re-captured when they change).
-    if (!dev->round_graph) {
-        cudaGraph_t g = nullptr;
-        IGB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        cudaError_t e1 = igb::launch_wave_round(dev->view, dev->shade, dev->wave, 0, dev->wave_sort, dev->sm_count, st);
-        cudaError_t e2 = igb::launch_wave_round(dev->view, dev->shade, dev->wave, 1, dev->wave_sort, dev->sm_count, st);
+    auto capture = [&](cudaGraphExec_t& exec, int first_parity, int rounds) -> int {
+        if (exec) return IGB200_OK;
+        cudaGraph_t g  = nullptr;
+        cudaError_t e1 = cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal);
+        for (int r = 0; r < rounds && e1 == cudaSuccess; ++r)
+            e1 = igb::launch_wave_round(dev->view, dev->shade, dev->wave, (first_parity + r) & 1, dev->wave_sort, dev->sm_count, st);
         cudaError_t e3 = cudaStreamEndCapture(st, &g);
-        if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || !g)
-            return fail(IGB200_E_CUDA, "igb200_render: graph capture failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3)));
-        cudaError_t e4 = cudaGraphInstantiate(&dev->round_graph, g, 0);
+        if (e1 != cudaSuccess || e3 != cudaSuccess || !g)
+            return fail(IGB200_E_CUDA, "igb200_render: graph capture failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e3));
+        cudaError_t e4 = cudaGraphInstantiate(&exec, g, 0);
         cudaGraphDestroy(g);
         if (e4 != cudaSuccess) return fail(IGB200_E_CUDA, "igb200_render: cudaGraphInstantiate failed: %s", cudaGetErrorString(e4));
-    }
+        return IGB200_OK;
+    };
+    if (int rc = capture(dev->round_graph, 0, 2)) return rc;
     if (dev->stats) {
         // --stats (Device::SetupSettings::AcquireStats): rounds are launched one by one with an event between the kernels
         // and a host sync per pair, so that the time of every kernel kind is known (Statistics.h:9-63 names on the host side).
@@ -990,13 +1004,23 @@ static int run_wave(igb200_device* dev, bool until_generated, uint64_t& pairs)
             if (flags[0]) { ++pairs; break; }
         }
     } else if (until_generated) {
+        // ONE round at a time, alternating the stream parity across calls: a step whose ids fit the stream is a single round of
+        // survivors + a whole new iteration (`pairs` counts half pairs here; read_wave_stats is told so)
         for (; pairs < max_pairs; ++pairs) {
-            IGB_CUDA(cudaGraphLaunch(dev->round_graph, st));
+            if (int rc = capture(dev->single_graph[dev->wave_parity], dev->wave_parity, 1)) return rc;
+            IGB_CUDA(cudaGraphLaunch(dev->single_graph[dev->wave_parity], st));
+            dev->wave_parity ^= 1;
             IGB_CUDA(cudaEventRecord(dev->round_ev[0], st));
             IGB_CUDA(cudaEventSynchronize(dev->round_ev[0]));
             if (flags[0] || flags[1]) { ++pairs; break; }
         }
     } else {
+        if (dev->wave_parity) { // a pipelined step ended on an odd round: one round of parity 1 brings the survivors back to stream 0
+            if (int rc = capture(dev->single_graph[1], 1, 1)) return rc;
+            IGB_CUDA(cudaGraphLaunch(dev->single_graph[1], st));
+            dev->wave_parity = 0;
+            odd              = 1;
+        }
         for (; pairs < max_pairs; ++pairs) {
             IGB_CUDA(cudaGraphLaunch(dev->round_graph, st));
             IGB_CUDA(cudaEventRecord(dev->round_ev[pairs % 4], st));
@@ -1004,11 +1028,12 @@ static int run_wave(igb200_device* dev, bool until_generated, uint64_t& pairs)
             if (flags[0]) { ++pairs; break; }
         }
     }
+    rounds_launched = (until_generated && !dev->stats) ? pairs : 2 * pairs + odd;
     return IGB200_OK;
 }
 
 // Copies the device-side ray counters of the call into (add = false) or onto (add = true) dev->render_stats.
-static int read_wave_stats(igb200_device* dev, uint64_t pairs, bool list, bool add)
+static int read_wave_stats(igb200_device* dev, uint64_t rounds_launched, bool list, bool add)
 {
     igb::WaveControl ctl;
     IGB_CUDA(cudaMemcpy(&ctl, dev->w_ctl.ptr, offsetof(igb::WaveControl, bins), cudaMemcpyDeviceToHost));
@@ -1019,7 +1044,7 @@ static int read_wave_stats(igb200_device* dev, uint64_t pairs, bool list, bool a
     s.bounce_rays     = ctl.bounce_rays;
     s.shadow_rays     = ctl.shadow_rays;
     s.rounds          = ctl.rounds;
-    s.kernel_launches = 1 + pairs * 2 * (igb::kWaveLaunchesPerRound - (dev->wave_sort ? 0 : 1)) + (list ? 1 : 0);
+    s.kernel_launches = 1 + rounds_launched * (igb::kWaveLaunchesPerRound - (dev->wave_sort ? 0 : 1)) + (list ? 1 : 0);
     s.device_ms       = ms;
     if (add) {
         s.camera_rays += dev->render_stats.camera_rays;
@@ -1041,9 +1066,10 @@ static int flush_wave(igb200_device* dev)
     if (!dev->wave_pending) return IGB200_OK;
     IGB_CUDA(cudaSetDevice(dev->ordinal));
     cudaStream_t st = dev->stream;
+    reinterpret_cast<volatile uint32_t*>(dev->h_done)[0] = 0u;
+    reinterpret_cast<volatile uint32_t*>(dev->h_done)[1] = 0u;
     IGB_CUDA(cudaEventRecord(dev->ev0, st));
     IGB_CUDA(igb::launch_wave_reset(dev->wave, dev->pending_set, 0u, st, true));
-    IGB_CUDA(cudaStreamSynchronize(st));
     uint64_t pairs = 0;
     if (int rc = run_wave(dev, false, pairs)) return rc;
     IGB_CUDA(cudaEventRecord(dev->ev1, st));
@@ -1149,14 +1175,18 @@ static int render_batch(igb200_device* dev, const igb200_render_settings* rs, ui
     }
     dev->wave.ent_mat = dev->d_ent_mat.ptr;
 
+    // the mapped flags are cleared from the host before anything that could raise them is queued (no wavefront kernel is pending:
+    // every call ends with a stream sync), so the host may start polling without waiting for the reset kernel
+    reinterpret_cast<volatile uint32_t*>(dev->h_done)[0] = 0u;
+    reinterpret_cast<volatile uint32_t*>(dev->h_done)[1] = 0u;
     IGB_CUDA(cudaEventRecord(dev->ev0, st));
     IGB_CUDA(igb::launch_wave_reset(dev->wave, set, (uint32_t)(per_iter * count), st, dev->wave_pending));
-    IGB_CUDA(cudaStreamSynchronize(st)); // the mapped flags are cleared before the host starts polling them
     uint64_t pairs = 0;
     if (int rc = run_wave(dev, pipe, pairs)) return rc;
     IGB_CUDA(cudaEventRecord(dev->ev1, st));
     IGB_CUDA(cudaStreamSynchronize(st));
     dev->wave_pending = pipe && !dev->h_done[0];
+    if (!dev->wave_pending) dev->wave_parity = 0; // drained: the next call starts on stream 0 again
     dev->pending_set  = set;
     if (!pipe && !dev->h_done[0]) return fail(IGB200_E_CUDA, "igb200_render: wavefront did not drain");
     if (int rc = read_wave_stats(dev, pairs, list, false)) return rc;

@@ -396,7 +396,7 @@ int igb200_render_iterations(igb200_device* dev, const igb200_render_settings* s
  * still in flight stay in the wavefront and continue in the rounds of the next igb200_render_pipelined call, so a frontend that
  * steps iteration by iteration (Runtime::step -> Device::render, src/runtime/Runtime.cpp:294-330; src/frontend/cli/main.cpp:120-139)
  * runs at the throughput of one long wavefront instead of paying the low-occupancy tail of deep paths on every step
- * (C4 diamond: 523 -> 1190 Msamples/s per step).  The film is complete again after igb200_flush; every entry that
+ * (C4 diamond: 523 -> 1170 Msamples/s per step).  The film is complete again after igb200_flush; every entry that
  * reads, clears or re-allocates the film or changes what the paths depend on (igb200_framebuffer, igb200_tonemap,
  * igb200_clear_*, igb200_resize, igb200_set_framebuffer, igb200_assign_scene / _shading, a render call with another film size,
  * spi or partition, igb200_render / _iterations / _partition) flushes by itself, so the results are those of igb200_render.
