@@ -251,6 +251,27 @@ def bench_path_tracer(pkg, local_rank, rank, world, total_iterations, warmup, wo
         "gpu_launches": int(launches), "rounds_rank0": int(rounds), "iterations_on_root_film": int(n_total), "film_mean": film_mean,
         "bvh_build_s": build_s,
     }
+    if world == 1:
+        # the reference's frontends step ONE iteration per Device::render call (Runtime.cpp:294-330): the same samples/s metric
+        # stepping through igb200_render_pipelined (wall clock, the final igb200_flush and the film read inside), next to plain
+        # igb200_render calls, each of which drains its deep paths before it returns
+        steps = int(max(1, min(total_iterations, 40)))
+        dev.clear_framebuffer()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for it in range(steps):
+            dev.render(w, h, spi=spi, iteration=it, pipelined=True)
+        dev.flush()
+        dev.framebuffer(copy=False)
+        piped_s = time.perf_counter() - t0
+        plain_steps = int(min(steps, 8))
+        t0 = time.perf_counter()
+        for it in range(plain_steps):
+            dev.render(w, h, spi=spi, iteration=steps + it)
+        plain_s = time.perf_counter() - t0
+        out["per_step"] = {"api": "igb200_render_pipelined + igb200_flush + igb200_framebuffer", "steps": steps,
+                           "value": float(spi) * w * h * steps / piped_s / 1e6,
+                           "plain_igb200_render": float(spi) * w * h * plain_steps / plain_s / 1e6, "unit": "Msamples/s"}
     if comm is not None:
         comm.close()
     dev.close()
