@@ -523,7 +523,9 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
     constexpr uint32_t kNoChunk = 0xFFFFFFFFu;
     uint32_t           ahead    = kNoChunk; // warp-uniform: base of the chunk claimed one step ahead
 #endif
-    bool     exhausted = false;           // warp-uniform
+    // warp-uniform.  A warp beyond the number of chunks never claims: in a nearly empty wavefront round (the deep-path tail) the
+    // 4736 resident warps would otherwise serialise on one atomic just to learn that there is nothing to do
+    bool     exhausted = (uint64_t)((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (uint64_t)kChunk >= (uint64_t)n;
     // a lane is active while it owns a ray: ray_id != kNoRay (one register less than a separate flag, which spilled)
     constexpr uint32_t kNoRay = 0xFFFFFFFFu;
     uint32_t ray_id = kNoRay;

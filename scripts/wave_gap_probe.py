@@ -5,7 +5,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 pkg = importlib.import_module("ignis-masterthesis_b200")
 fx = importlib.import_module("ignis-masterthesis_b200.fixtures")
-for name, res, spi, batch in (("diamond", 1920, 4, 32), ("many-point-lights", 3840, 1, 32), ("office", 256, 64, 64)):
+B = int(os.environ.get("BATCH", "0"))
+for name, res, spi, batch in (("diamond", 1920, 4, B or 32), ("many-point-lights", 3840, 1, B or 32), ("office", 256, 64, B or 64)):
     tables, sh, w0, h0, _ = fx.load_fixture(os.path.join(ROOT, "tests", "golden", name + ".npz"))
     resy = res * h0 // w0
     out = {}
