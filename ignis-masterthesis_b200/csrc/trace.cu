@@ -100,7 +100,7 @@ cudaError_t launch_trace(const DeviceScene& scene, const float4* d_rays, uint64_
     // every warp of the grid overshoots the work counter by up to two chunks: keep it well clear of the 32-bit wrap
     if (n > 0xFF000000ull) return cudaErrorInvalidValue;
     // persistent grid: one wave of resident CTAs (a multiple of the SM count), fewer for tiny batches
-    const uint64_t want = (n + kChunk - 1) / kChunk; // warps that can get at least one chunk
+    const uint64_t want = (n + 31) / 32; // warps that can get at least one ray per lane (the kernel claims 32 rays at a time then)
     const uint32_t grid = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)sm_count * kBlocksPerSM, (want + 3) / 4));
     const bool     all  = out.ent_id && out.prim_id && out.t && out.u && out.v;
     if (normalize) {

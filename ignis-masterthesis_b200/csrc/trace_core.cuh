@@ -525,7 +525,10 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
 #endif
     // warp-uniform.  A warp beyond the number of chunks never claims: in a nearly empty wavefront round (the deep-path tail) the
     // 4736 resident warps would otherwise serialise on one atomic just to learn that there is nothing to do
-    bool     exhausted = (uint64_t)((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (uint64_t)kChunk >= (uint64_t)n;
+    // Rays per claim: 64, or 32 when the launch has no more than one ray per resident lane (nearly empty rounds: a warp then
+    // traces its rays side by side instead of two after another, which halves the latency of the round).
+    const uint32_t chunk = (uint64_t)n <= (uint64_t)gridDim.x * blockDim.x ? 32u : (uint32_t)kChunk;
+    bool     exhausted = (uint64_t)((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (uint64_t)chunk >= (uint64_t)n;
     // a lane is active while it owns a ray: ray_id != kNoRay (one register less than a separate flag, which spilled)
     constexpr uint32_t kNoRay = 0xFFFFFFFFu;
     uint32_t ray_id = kNoRay;
@@ -559,22 +562,22 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
                     // other 31 lanes of the warp for a DRAM round trip.
                     uint32_t base = ahead, next = 0;
                     if (lane == 0) {
-                        if (base == kNoChunk) base = atomicAdd(work, (uint32_t)kChunk);
-                        next = base < n ? atomicAdd(work, (uint32_t)kChunk) : base;
+                        if (base == kNoChunk) base = atomicAdd(work, chunk);
+                        next = base < n ? atomicAdd(work, chunk) : base;
                     }
                     base  = __shfl_sync(0xFFFFFFFFu, base, 0);
                     ahead = __shfl_sync(0xFFFFFFFFu, next, 0);
-                    if (ahead < n) io.prefetch(ahead, min((uint32_t)kChunk, n - ahead), lane);
+                    if (ahead < n) io.prefetch(ahead, min(chunk, n - ahead), lane);
 #else
                     uint32_t base = 0;
-                    if (lane == 0) base = atomicAdd(work, (uint32_t)kChunk);
+                    if (lane == 0) base = atomicAdd(work, chunk);
                     base = __shfl_sync(0xFFFFFFFFu, base, 0);
 #endif
                     if (base >= n) {
                         exhausted = true;
                     } else {
                         pool_next = base;
-                        pool_end  = min(base + (uint32_t)kChunk, n);
+                        pool_end  = min(base + chunk, n);
                     }
                 }
                 const uint32_t avail = pool_end - pool_next;
