@@ -527,7 +527,10 @@ trace_kernel(const DeviceScene sc, const IO io, TraceCounters* __restrict__ coun
     // 4736 resident warps would otherwise serialise on one atomic just to learn that there is nothing to do
     // Rays per claim: 64, or 32 when the launch has no more than one ray per resident lane (nearly empty rounds: a warp then
     // traces its rays side by side instead of two after another, which halves the latency of the round).
-    const uint32_t chunk = (uint64_t)n <= (uint64_t)gridDim.x * blockDim.x ? 32u : (uint32_t)kChunk;
+#ifndef IGB_CHUNK32_LANES
+#define IGB_CHUNK32_LANES 1 // claim 32 rays at a time while the launch has at most this many rays per resident lane
+#endif
+    const uint32_t chunk = (uint64_t)n <= (uint64_t)IGB_CHUNK32_LANES * gridDim.x * blockDim.x ? 32u : (uint32_t)kChunk;
     bool     exhausted = (uint64_t)((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (uint64_t)chunk >= (uint64_t)n;
     // a lane is active while it owns a ray: ray_id != kNoRay (one register less than a separate flag, which spilled)
     constexpr uint32_t kNoRay = 0xFFFFFFFFu;
