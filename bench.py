@@ -544,8 +544,8 @@ def run_ours(args, rank, world, local_rank):
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": "c3-instanced", "triangles": 1032192, "entities": 64, "rays_per_step": n,
-                       "mesh": "procedural UV sphere with the tessellation counts of scenes/meshes/SphereTri.ply (16 128 triangles; "
-                               "same size, not the same mesh: the reference tree is absent on the GPU box)",
+                       "mesh": "procedural unit UV sphere, 64 x 128: the surface of scenes/meshes/SphereTri.ply (16 128 triangles, the same "
+                               "8066 vertex positions to 1e-3, tests/test_primitives.py; generated because the reference tree is absent on the GPU box)",
                        "ray_order": "generation order (incoherent)", "hit_rate": hits / n,
                        "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (n * 52 / 1e6),
                        "bvh": info},

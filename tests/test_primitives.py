@@ -118,3 +118,22 @@ def test_fixture_is_what_the_reader_builds_from_the_reference_scene(ig):
     ft, fsh, fw, fh, _ = load_golden(ig, "primitives")
     assert (w, h) == (fw, fh) and tables.entity_count == ft.entity_count
     assert bytes(tables.shape_data) == bytes(ft.shape_data) and np.array_equal(tables.entities, ft.entities)
+
+
+def test_c3_sphere_is_spheretri():
+    """The benchmark's procedural sphere (workloads.uv_sphere(64, 128)) is the surface of the reference's scenes/meshes/SphereTri.ply:
+    same triangle count, same set of distinct vertex positions (the file repeats the seam for its texture coordinates)."""
+    import importlib
+    import os
+    path = "/root/reference/scenes/meshes/SphereTri.ply"
+    if not os.path.exists(path):
+        pytest.skip("the reference tree is not on this machine")
+    pkg = importlib.import_module("ignis-masterthesis_b200")
+    sio = importlib.import_module("ignis-masterthesis_b200.sceneio")
+    ply = sio.load_ply(path)
+    v, f, _ = pkg.workloads.uv_sphere(64, 128)
+    assert ply.f.shape[0] == f.shape[0] == 16128
+    a = np.unique(np.round(ply.v.astype(np.float64), 3), axis=0)
+    b = np.unique(np.round(v.astype(np.float64), 3), axis=0)
+    assert a.shape == b.shape == (8066, 3)
+    assert np.abs(a - b).max() <= 2e-3
