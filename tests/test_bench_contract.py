@@ -38,3 +38,16 @@ def test_gpu_arm_needs_a_gpu():
     p = _run("--rays", "1000", "--steps", "1", "--warmup", "0", "--pt-iterations", "0", "--c5-spp", "0", "--office-spp", "0")
     assert p.returncode != 0                                 # the product path has no CPU fallback
     assert not [l for l in p.stdout.splitlines() if l.strip().startswith("{")]
+
+
+def test_reference_arm_under_torchrun_prints_once():
+    """Launched like the GPU arm for N > 1 (torchrun, one process per rank): rank 0 alone runs and prints, the others exit 0."""
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29541", os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--rays", "100000",
+                        "--steps", "1", "--warmup", "1", "--pt-iterations", "0", "--c5-spp", "0", "--office-spp", "0"],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [l for l in p.stdout.splitlines() if l.strip().startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["config"]["rays_per_step"] == 100000
