@@ -47,7 +47,9 @@ constexpr int      kVoteEnt     = IGB_VOTE_ENT; // same for the entity-leaf phas
 #endif
 constexpr int      kVoteRefill  = IGB_VOTE_REFILL; // idle lanes that must wait before the warp fetches new rays
 #ifndef IGB_PARK_PRIMS
-#define IGB_PARK_PRIMS 0 // 1: park triangle groups, 2: entity-leaf groups too (measured: see DESIGN.md section 7)
+#define IGB_PARK_PRIMS 0 // 1: park triangle groups, 2: entity-leaf groups too (measured: see DESIGN.md section 7).  Experiment only:
+                         // it pushes up to two entries per level, while the host's depth check (device.cu: stack_budget) counts one --
+                         // run such a build with IGB200_STACK_BUDGET halved (the debug-checks build traps on an overflow)
 #endif
 #ifndef IGB_TRI_LOAD2
 #define IGB_TRI_LOAD2 0
