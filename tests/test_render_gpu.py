@@ -378,6 +378,26 @@ def test_pipelined_steps_equal_plain_steps(ig, dev):
     np.testing.assert_allclose(b, c, rtol=2e-5, atol=1e-6)
 
 
+def test_pipelined_steps_then_partition_render(ig):
+    """A partition render (the multi-GPU entry, synchronous) and a device-pointer read after pipelined steps: the paths in flight
+    are drained first, the film is that of plain calls."""
+    tables, sh = room_scene(ig, 128, depth=10)
+
+    def run(pipe):
+        with ig.Device(0) as d:
+            d.assign_scene(tables); d.assign_shading(sh); d.resize(128, 128)
+            for it in range(3):
+                d.render(128, 128, spi=2, iteration=it, seed=5, pipelined=pipe)
+            d.render_partition(128, 128, 2, 4, 0, 1, iteration=3, seed=5)   # a 4-iteration request, partition 0 of 1
+            _, n_dev = d.framebuffer_device()
+            film, n = d.framebuffer()
+            return film.copy(), n_dev, n
+
+    a, b = run(True), run(False)
+    assert a[1] == a[2] == b[1] == b[2] == 7
+    np.testing.assert_allclose(a[0], b[0], rtol=2e-5, atol=1e-6)
+
+
 def test_capacity_smaller_than_one_iteration(ig, oracle, monkeypatch):
     # regeneration: 256 x 256 x 8 samples = 512 Ki rays flow through 64 Ki-ray streams
     monkeypatch.setenv("IGB200_WAVE_CAPACITY", "65536")
